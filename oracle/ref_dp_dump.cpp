@@ -1,0 +1,228 @@
+// oracle/ref_dp_dump.cpp — TEST INFRASTRUCTURE (our code, links the UNMODIFIED
+// reference objects built by oracle/Makefile).
+//
+// Replays dynamic-programming problems through the reference's own
+// SwAligner (aligner_sw.h:241-374: initRead / initRef / align / nextAlignment)
+// and dumps everything the B200 path must reproduce bit-exactly:
+//   * align(): aligned flag, best score, which width succeeded (u8 / i16),
+//     the sorted candidate list btncand_ (aligner_sw.cpp:722-724)
+//   * every nextAlignment(): score, reference offset, soft trims, ns, gaps,
+//     refns, the edit list (after invertEdits for '-' strand), and a probe of
+//     the RandomSource after the call (re-seed protocol aligner_sw.cpp:794,877,879,932)
+//
+// Inputs
+//   --log FILE --index BASE   problems logged by `bowtie2-align-server-s --log-dp`
+//                             (format bt2_dp.cpp:566-631); the window is re-fetched
+//                             from BASE.{3,4}.bt2 exactly like the server does
+//                             (initRef overload aligner_sw.cpp:155-271, incl. the
+//                             extra right-hand column :174-176)
+//   --problems FILE           self-contained problems (the "P" lines this tool
+//                             prints); window given explicitly incl. extra column,
+//                             run through the raw-buffer overload like bt2_dp.cpp:724
+// Scoring options mirror bt2_dp.cpp:96-130: --local --ma --mp MX,MN --np --rdg C,L
+// --rfg C,L --gbar --no-sse8 --nceil C,L  --maxaln K
+//
+// Output: one "P" line, one "R" line, zero or more "A" lines and one "E" line per problem.
+
+#include <iostream>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+#include <cstring>
+#include <cstdlib>
+#include <limits>
+#define private public
+#define protected public
+#include "aligner_sw.h"
+#undef private
+#undef protected
+#include "reference.h"
+#include "scoring.h"
+#include "simple_func.h"
+#include "aligner_seed_policy.h"
+#include "mask.h"
+#include "alphabet.h"
+#include "tokenize.h"
+
+using namespace std;
+
+int gVerbose = 0;
+int gQuiet = 0;
+
+struct Prob {
+	TRefId refidx; TRefOff reflen; TAlScore minsc; bool fw; DPRect rect;
+	string window; // mask chars, includes the extra column (may be empty => fetch from index)
+};
+
+static void parseRect(istream& is, DPRect& r) {
+	char comma;
+	is >> r.refl >> comma >> r.refr >> comma >> r.refl_pretrim >> comma >> r.refr_pretrim
+	   >> comma >> r.triml >> comma >> r.trimr >> comma >> r.corel >> comma >> r.corer
+	   >> comma >> r.maxgap;
+}
+
+static string rectStr(const DPRect& r) {
+	ostringstream os;
+	os << r.refl << ',' << r.refr << ',' << r.refl_pretrim << ',' << r.refr_pretrim << ','
+	   << r.triml << ',' << r.trimr << ',' << r.corel << ',' << r.corer << ',' << r.maxgap;
+	return os.str();
+}
+
+static pair<int,int> parsePair(const char* s) {
+	pair<int,int> p(0, 0);
+	const char* c = strchr(s, ',');
+	p.first = atoi(s);
+	p.second = c ? atoi(c + 1) : p.first;
+	return p;
+}
+
+int main(int argc, char** argv) {
+	string logfn, idx, probfn;
+	bool local = false, enable8 = true;
+	int ma = -1, mpmax = DEFAULT_MM_PENALTY_MAX, mpmin = DEFAULT_MM_PENALTY_MIN;
+	int np = DEFAULT_N_PENALTY, gbar = 4;
+	int rdgc = DEFAULT_READ_GAP_CONST, rdgl = DEFAULT_READ_GAP_LINEAR;
+	int rfgc = DEFAULT_REF_GAP_CONST, rfgl = DEFAULT_REF_GAP_LINEAR;
+	double nceilC = 0.0, nceilL = 0.15;
+	size_t maxaln = 8, cminlen = 2000, cpow2 = 4, upto = (size_t)-1;
+	for(int i = 1; i < argc; i++) {
+		string a = argv[i];
+		if(a == "--log") logfn = argv[++i];
+		else if(a == "--index") idx = argv[++i];
+		else if(a == "--problems") probfn = argv[++i];
+		else if(a == "--local") local = true;
+		else if(a == "--no-sse8") enable8 = false;
+		else if(a == "--ma") ma = atoi(argv[++i]);
+		else if(a == "--mp") { pair<int,int> p = parsePair(argv[++i]); mpmax = p.first; mpmin = p.second; }
+		else if(a == "--np") np = atoi(argv[++i]);
+		else if(a == "--rdg") { pair<int,int> p = parsePair(argv[++i]); rdgc = p.first; rdgl = p.second; }
+		else if(a == "--rfg") { pair<int,int> p = parsePair(argv[++i]); rfgc = p.first; rfgl = p.second; }
+		else if(a == "--gbar") gbar = atoi(argv[++i]);
+		else if(a == "--nceil") { const char* s = argv[++i]; nceilC = atof(s); const char* c = strchr(s, ','); nceilL = c ? atof(c+1) : 0.0; }
+		else if(a == "--maxaln") maxaln = (size_t)atol(argv[++i]);
+		else if(a == "--cp-min") cminlen = (size_t)atol(argv[++i]);
+		else if(a == "--upto") upto = (size_t)atol(argv[++i]);
+		else { cerr << "unknown arg " << a << endl; return 2; }
+	}
+	if(ma < 0) ma = local ? DEFAULT_MATCH_BONUS_LOCAL : DEFAULT_MATCH_BONUS;
+	SimpleFunc scoreMin, nCeil;
+	scoreMin.init(SIMPLE_FUNC_LINEAR, DEFAULT_MIN_CONST, DEFAULT_MIN_LINEAR);
+	nCeil.init(SIMPLE_FUNC_LINEAR, 0.0f, std::numeric_limits<double>::max(), nceilC, nceilL);
+	Scoring sc(ma, DEFAULT_MM_PENALTY_TYPE, mpmax, mpmin, scoreMin, nCeil,
+	           DEFAULT_N_PENALTY_TYPE, np, DEFAULT_N_CAT_PAIR,
+	           rdgc, rfgc, rdgl, rfgl, gbar);
+	BitPairReference* refs = NULL;
+	if(!idx.empty()) {
+		refs = new BitPairReference(idx, false, false, NULL, NULL, false, false, false, false, false, false);
+	}
+	const string& fn = logfn.empty() ? probfn : logfn;
+	bool isLog = !logfn.empty();
+	ifstream in(fn.c_str());
+	if(!in.good()) { cerr << "cannot open " << fn << endl; return 2; }
+	SwAligner sw(NULL);
+	string ln;
+	size_t pid = 0, nread = 0;
+	BTDnaString seq, seqrc; BTString qual, qualrc;
+	while(getline(in, ln)) {
+		if(ln.empty()) continue;
+		EList<string> buf;
+		tokenize(ln, '\t', buf);
+		if(buf.size() < 3) continue;
+		vector<Prob> probs;
+		size_t first = 2;
+		string sseq, squal;
+		if(isLog) {
+			sseq = buf[0]; squal = buf[1];
+			for(size_t i = 2; i < buf.size(); i++) {
+				Prob p; istringstream is(buf[i]); char comma, tmp;
+				is >> p.refidx >> comma >> p.reflen >> comma >> p.minsc >> comma >> tmp >> comma;
+				p.fw = (tmp == '+');
+				parseRect(is, p.rect);
+				probs.push_back(p);
+			}
+		} else {
+			// P seq qual +/- refidx reflen minsc rect window
+			if(buf[0] != "P") continue;
+			sseq = buf[1]; squal = buf[2];
+			Prob p;
+			p.fw = (buf[3] == "+");
+			p.refidx = (TRefId)atol(buf[4].c_str());
+			p.reflen = (TRefOff)atoll(buf[5].c_str());
+			p.minsc = (TAlScore)atoll(buf[6].c_str());
+			istringstream is(buf[7]);
+			parseRect(is, p.rect);
+			p.window = buf[8];
+			probs.push_back(p);
+			(void)first;
+		}
+		seq.install(sseq.c_str(), true);
+		qual = squal;
+		seqrc = seq; seqrc.reverseComp();
+		qualrc = qual; qualrc.reverse();
+		sw.initRead(seq, seqrc, qual, qualrc, 0, seq.length(), sc);
+		nread++;
+		for(size_t j = 0; j < probs.size(); j++) {
+			Prob& p = probs[j];
+			RandomSource rnd((uint32_t)(pid * 7919u + 17u));
+			vector<char> rfbuf;
+			if(p.window.empty()) {
+				if(refs == NULL) { cerr << "need --index for log input" << endl; return 2; }
+				size_t nsUpto = 0;
+				sw.initRef(p.fw, p.refidx, p.rect, *refs, p.reflen, sc, p.minsc, enable8,
+				           cminlen, cpow2, false, true, 0, nsUpto);
+			} else {
+				size_t n = p.window.length(); // includes the extra column
+				rfbuf.resize(n + 16);
+				for(size_t i = 0; i < n; i++) {
+					int m = asc2dnamask[(int)p.window[i]];
+					if(m == 15) m = 16;
+					rfbuf[i] = (char)m;
+				}
+				sw.initRef(p.fw, p.refidx, p.rect, &rfbuf[0], 0, n - 1, p.reflen, sc, p.minsc,
+				           enable8, cminlen, cpow2, false, true);
+			}
+			// P line (self-contained problem, window incl. extra column)
+			cout << "P\t" << sseq << '\t' << squal << '\t' << (p.fw ? '+' : '-') << '\t'
+			     << p.refidx << '\t' << p.reflen << '\t' << p.minsc << '\t' << rectStr(p.rect) << '\t';
+			for(TRefOff i = sw.rfi_; i <= sw.rff_; i++) cout << mask2dna[(int)sw.rf_[i]];
+			cout << '\n';
+			TAlScore best = std::numeric_limits<TAlScore>::min();
+			bool aligned = sw.align(best);
+			cout << "R\t" << (aligned ? 1 : 0) << '\t' << best << '\t' << (sw.sse8succ_ ? 1 : 0)
+			     << '\t' << (sw.sse16succ_ ? 1 : 0) << '\t' << sw.btncand_.size() << '\t';
+			for(size_t i = 0; i < sw.btncand_.size(); i++) {
+				if(i) cout << ';';
+				cout << sw.btncand_[i].row << ',' << sw.btncand_[i].col << ',' << sw.btncand_[i].score;
+			}
+			cout << '\n';
+			size_t naln = 0;
+			if(aligned) {
+				SwResult res;
+				while(naln < maxaln && !sw.done()) {
+					res.reset();
+					bool ok = sw.nextAlignment(res, p.minsc, rnd);
+					RandomSource probe = rnd;
+					if(!ok) break;
+					const AlnRes& r = res.alres;
+					cout << "A\t" << r.score().score() << '\t' << r.refoff() << '\t'
+					     << r.trimmed5p(true) << '\t' << r.trimmed3p(true) << '\t'
+					     << r.score().ns() << '\t' << r.score().gaps() << '\t' << r.refNs() << '\t'
+					     << r.ned().size() << '\t';
+					for(size_t i = 0; i < r.ned().size(); i++) {
+						const Edit& e = r.ned()[i];
+						if(i) cout << ';';
+						cout << e.pos << ':' << (char)e.chr << ':' << (char)e.qchr << ':' << (int)e.type;
+					}
+					cout << '\t' << sw.cural_ << '\t' << probe.nextU32() << '\n';
+					naln++;
+				}
+			}
+			RandomSource probe = rnd;
+			cout << "E\t" << naln << '\t' << sw.cural_ << '\t' << probe.nextU32() << '\n';
+			pid++;
+			if(pid >= upto) return 0;
+		}
+	}
+	return 0;
+}
