@@ -70,6 +70,7 @@ def parse_dump(path, limit=None):
     """Yield dicts {seq, qual, fw, refidx, reflen, minsc, rect, window, R, A[], E} per problem."""
     cur = None
     n = 0
+    pid = 0
     with open(path) as fh:
         for ln in fh:
             t = ln.rstrip("\n").split("\t")
@@ -84,7 +85,8 @@ def parse_dump(path, limit=None):
                            minsc=int(t[6]),
                            rect=dict(zip(("refl", "refr", "refl_pretrim", "refr_pretrim", "triml", "trimr",
                                           "corel", "corer", "maxgap"), rect)),
-                           window=t[8], R=None, A=[], E=None)
+                           window=t[8], R=None, A=[], E=None, pid=pid)
+                pid += 1
             elif t[0] == "R":
                 cands = []
                 if len(t) > 6 and t[6]:
