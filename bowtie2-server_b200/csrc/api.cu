@@ -1,0 +1,57 @@
+// api.cu — library / context entry points of include/bt2gpu.h.
+#include "common.cuh"
+
+namespace bt2 {
+thread_local std::string g_err;
+void dp_state_free(DpState *d);
+void fm_state_free(FmState *d);
+}
+using namespace bt2;
+
+extern "C" int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
+extern "C" const char *bt2gpu_last_error(void) { return g_err.c_str(); }
+
+extern "C" int bt2gpu_device_count(int *n) {
+	if(!n) BT2_FAIL("null argument");
+	*n = 0;
+	BT2_CUDA(cudaGetDeviceCount(n));
+	return 0;
+}
+
+extern "C" int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
+	if(!out) BT2_FAIL("null argument");
+	*out = nullptr;
+	int n = 0;
+	BT2_CUDA(cudaGetDeviceCount(&n));
+	if(n <= 0) BT2_FAIL("no CUDA device: libbt2gpu has no CPU fallback");
+	if(device < 0 || device >= n) BT2_FAIL("bad device ordinal");
+	BT2_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	BT2_CUDA(cudaGetDeviceProperties(&prop, device));
+	if(prop.major < 10) BT2_FAIL("libbt2gpu is built for sm_100a (Blackwell) only");
+	bt2gpu_ctx *c = new bt2gpu_ctx();
+	c->device = device;
+	c->sm_count = prop.multiProcessorCount;
+	cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+	if(e != cudaSuccess) { delete c; return fail("cudaStreamCreate", __FILE__, __LINE__, e); }
+	*out = c;
+	return 0;
+}
+
+extern "C" void bt2gpu_ctx_destroy(bt2gpu_ctx *ctx) {
+	if(!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	dp_state_free(ctx->dp);
+	fm_state_free(ctx->fm);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+extern "C" int bt2gpu_ctx_sync(bt2gpu_ctx *ctx) {
+	if(!ctx) BT2_FAIL("null ctx");
+	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+extern "C" void *bt2gpu_ctx_stream(bt2gpu_ctx *ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" uint64_t bt2gpu_ctx_launches(bt2gpu_ctx *ctx) { return ctx ? ctx->launches : 0; }

@@ -1,0 +1,77 @@
+// common.cuh — context, error plumbing and device buffers shared by the kernels of
+// libbt2gpu.so (C ABI in include/bt2gpu.h).  sm_100a only; no CPU fallback anywhere.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/bt2gpu.h"
+
+namespace bt2 {
+
+extern thread_local std::string g_err;
+
+inline int fail(const char *what, const char *file, int line, cudaError_t e = cudaSuccess) {
+	char buf[512];
+	if(e != cudaSuccess)
+		snprintf(buf, sizeof(buf), "%s (%s) at %s:%d", what, cudaGetErrorString(e), file, line);
+	else
+		snprintf(buf, sizeof(buf), "%s at %s:%d", what, file, line);
+	g_err = buf;
+	return 1;
+}
+
+#define BT2_CUDA(x) do { cudaError_t e_ = (x); if(e_ != cudaSuccess) return bt2::fail(#x, __FILE__, __LINE__, e_); } while(0)
+#define BT2_FAIL(msg) return bt2::fail(msg, __FILE__, __LINE__)
+
+// Growable device buffer (never shrinks; freed with the context).
+struct DevBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes) {
+		if(bytes <= cap) return 0;
+		if(p) cudaFree(p);
+		p = nullptr; cap = 0;
+		size_t want = bytes + (bytes >> 3) + 256;
+		BT2_CUDA(cudaMalloc(&p, want));
+		cap = want;
+		return 0;
+	}
+	void release() { if(p) cudaFree(p); p = nullptr; cap = 0; }
+	template<typename T> T *as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Pinned host staging buffer.
+struct HostBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes) {
+		if(bytes <= cap) return 0;
+		if(p) cudaFreeHost(p);
+		p = nullptr; cap = 0;
+		size_t want = bytes + (bytes >> 3) + 256;
+		BT2_CUDA(cudaMallocHost(&p, want));
+		cap = want;
+		return 0;
+	}
+	void release() { if(p) cudaFreeHost(p); p = nullptr; cap = 0; }
+	template<typename T> T *as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct DpState;   // dp.cu
+struct FmState;   // fm.cu
+
+} // namespace bt2
+
+struct bt2gpu_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	uint64_t launches = 0;
+	int sm_count = 0;
+	bt2gpu_scoring sc;
+	bool have_sc = false;
+	bt2::DpState *dp = nullptr;
+	bt2::FmState *fm = nullptr;
+};

@@ -1,0 +1,920 @@
+// dp.cu — Smith-Waterman fill / gather / backtrace kernels (sm_100a) and their C ABI.
+//
+// Replaces, behind include/bt2gpu.h, the reference's SwAligner::align + nextAlignment
+// (aligner_sw.cpp:500-1146) and its four striped-SSE back ends
+// (aligner_swsse_{ee,loc}_{u8,i16}.cpp).  The reference vectorises INSIDE one problem
+// (Farrar stripes + lazy-F loop); this design is a B200 one:
+//
+//  * k_dp_fill: a group of 8 lanes owns one read x window problem; each lane owns two
+//    "virtual lanes" packed into the low/high half of s16x2 registers (rows
+//    [2l*S, 2l*S+S) and [(2l+1)*S, (2l+1)*S+S) of a 16*S-row stripe).  The 16 virtual lanes
+//    run a skewed wavefront (virtual lane v is at column t-v at step t), so the vertical
+//    F/H dependency never crosses the two halves of a register in the same step.  All
+//    recurrences are DPX: VIADDMNMX.S16x2 (add + clamp-at-floor) and VIMNMX3.S16x2.  The
+//    gap barrier (--gbar) is folded into per-row gap constants, the query profile lives in
+//    shared memory, E/F/H of every cell are streamed to HBM as 16-byte stores in wavefront
+//    order for the backtrace.
+//  * k_dp_gather_*: candidate cells + best/flag/width with the exact u8/i16 decision rules
+//    of aligner_sw.cpp:516-621 (including the stripe-padding rows that leak into the local
+//    column maxima), two passes + device scan, then a per-job bitonic sort in the order of
+//    DpBtCandidate::operator< (aligner_sw_nuc.h:134).
+//  * k_dp_backtrace: one thread per problem replays the nextAlignment() candidate loop and
+//    the deterministic-priority walk of backtraceNucleotides* (ee_u8.cpp:1283-1877).
+//
+// Values are kept in the SCORE domain (the reference's raw value minus its offset) with the
+// variant's floor: -255 for the u8 end-to-end path (exact saturation emulation), 0 for
+// local, and -16000 for the i16 end-to-end path (the reference's floor of -65535 is
+// unreachable for the supported read lengths; checked in stage()).
+#include "common.cuh"
+#include <algorithm>
+
+namespace bt2 {
+
+static constexpr int   GL      = 8;       // lanes per problem group
+static constexpr int   VL      = 16;      // virtual lanes per group
+static constexpr int   BIG     = 16000;   // veto / padding penalty
+static constexpr int   FL_I16  = -16000;  // floor of the 16-bit end-to-end domain
+static constexpr int   NCH     = 6;       // profile rows: A C G T N pad
+
+__constant__ int32_t c_mmpens[256];
+__constant__ int32_t c_npens[256];
+struct ScConst { int32_t match, rdo, rde, rfo, rfe, gapbar, monotone; };
+__constant__ ScConst c_sc;
+
+// Per-job data prepared on the host by stage().
+struct DpAux {
+	uint64_t mat_off;     // word offset of the E/F/H stream in the matrix arena
+	uint64_t rep_off;     // byte offset of the reportedThrough bitmap
+	uint32_t bound_off;   // word offset of the 2 stripe-boundary rows (2*ncol words)
+	uint32_t escr_off;    // offset (edits) of the per-job edit scratch
+	uint32_t S;           // packed registers per lane (stripe = 16*S rows)
+	uint32_t nstripes;
+	uint32_t T;           // steps per stripe = ncol + 16
+	uint32_t RW;          // words per lane-step record = roundup4(3*S)
+	int32_t  fl;          // floor of the score domain
+	uint32_t pad;
+};
+
+__device__ __forceinline__ uint32_t pack2(int lo, int hi) {
+	return (uint32_t)(lo & 0xffff) | ((uint32_t)(hi & 0xffff) << 16);
+}
+__device__ __forceinline__ int lo16(uint32_t w) { return (int)(int16_t)(w & 0xffff); }
+__device__ __forceinline__ int hi16(uint32_t w) { return (int)(int16_t)(w >> 16); }
+
+// Scoring::score (scoring.h:241) for profile row c (0..4 = A,C,G,T,N).
+__device__ __forceinline__ int dev_score(int rdc, int c, int q) {
+	q = q < 0 ? 0 : (q > 255 ? 255 : q);
+	if(rdc > 3 || c > 3) return -c_npens[q];
+	return rdc == c ? c_sc.match : -c_mmpens[q];
+}
+__device__ __forceinline__ int dev_score_mask(int rdc, int refm, int q) {
+	q = q < 0 ? 0 : (q > 255 ? 255 : q);
+	if(rdc > 3 || refm > 15) return -c_npens[q];
+	return ((refm >> rdc) & 1) ? c_sc.match : -c_mmpens[q];
+}
+__device__ __forceinline__ int dev_mm(int rdc, int refm, int q) {
+	q = q < 0 ? 0 : (q > 255 ? 255 : q);
+	return (rdc > 3 || refm > 15) ? c_npens[q] : c_mmpens[q];
+}
+
+// ---------------------------------------------------------------------------------------
+// Fill.  One 8-lane group per job; jobs of one S class per launch, taken in `order`.
+// ---------------------------------------------------------------------------------------
+template<int S>
+__global__ void __launch_bounds__(128)
+k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
+          const uint8_t *__restrict__ win, const bt2gpu_dp_job *__restrict__ jobs,
+          const DpAux *__restrict__ aux, const uint32_t *__restrict__ order, uint32_t norder,
+          uint32_t *__restrict__ mat, uint32_t *__restrict__ bound)
+{
+	constexpr int SP = (S + 3) & ~3;          // profile row stride (words)
+	constexpr int RW = (3 * S + 3) & ~3;      // record words
+	extern __shared__ uint32_t smem[];
+	const int lane  = threadIdx.x & 31;
+	const int l     = lane & (GL - 1);
+	const int gInW  = lane >> 3;
+	const int gInB  = (threadIdx.x >> 5) * 4 + gInW;
+	const unsigned gmask = 0xffu << (gInW * 8);
+	uint32_t *prof = smem + (size_t)gInB * (NCH * GL * SP);
+	const uint32_t ngroups = gridDim.x * (blockDim.x / GL);
+	for(uint32_t oi = blockIdx.x * (blockDim.x / GL) + gInB; oi < norder; oi += ngroups) {
+		const uint32_t ji = order[oi];
+		const bt2gpu_dp_job jb = jobs[ji];
+		const DpAux ax = aux[ji];
+		const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
+		const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
+		const int fl = ax.fl;
+		const uint32_t FLv = pack2(fl, fl);
+		const uint32_t nrde = pack2(-c_sc.rde, -c_sc.rde);
+		const int T = (int)ax.T;
+		uint32_t *bnd0 = bound + ax.bound_off, *bnd1 = bnd0 + ncol;
+		for(int st = 0; st < (int)ax.nstripes; st++) {
+			const int row0 = st * (VL * S) + (2 * l) * S;     // first row of my low half
+			// --- per-row constants and query profile of this stripe ---
+			uint32_t nrfo[S], nrfe[S], nrdo[S];
+			__syncwarp(gmask);
+#pragma unroll
+			for(int k = 0; k < S; k++) {
+				int rl = row0 + k, rh = row0 + S + k;
+				bool bl = rl < nrow && (rl < c_sc.gapbar || (nrow - rl - 1) < c_sc.gapbar);
+				bool bh = rh < nrow && (rh < c_sc.gapbar || (nrow - rh - 1) < c_sc.gapbar);
+				nrfo[k] = pack2(bl ? -BIG : -c_sc.rfo, bh ? -BIG : -c_sc.rfo);
+				nrfe[k] = pack2(bl ? -BIG : -c_sc.rfe, bh ? -BIG : -c_sc.rfe);
+				nrdo[k] = pack2(bl ? -BIG : -c_sc.rdo, bh ? -BIG : -c_sc.rdo);
+				int cl = rl < nrow ? rd[rl] : 4, ch = rh < nrow ? rd[rh] : 4;
+				int ql = rl < nrow ? (int)qu[rl] - 33 : 0, qh = rh < nrow ? (int)qu[rh] - 33 : 0;
+#pragma unroll
+				for(int c = 0; c < 5; c++) {
+					int sl = rl < nrow ? dev_score(cl, c, ql) : 0;
+					int sh = rh < nrow ? dev_score(ch, c, qh) : 0;
+					prof[(c * GL + l) * SP + k] = pack2(sl, sh);
+				}
+				prof[(5 * GL + l) * SP + k] = pack2(-BIG, -BIG);
+			}
+			__syncwarp(gmask);
+			// --- state ---
+			uint32_t Hprev[S], E[S], Pprev[S];
+#pragma unroll
+			for(int k = 0; k < S; k++) { Hprev[k] = FLv; E[k] = FLv; Pprev[k] = pack2(-BIG, -BIG); }
+			uint32_t Hbot = FLv, Fbot = FLv, HtopPrev = FLv;
+			const uint32_t *bin = (st & 1) ? bnd1 : bnd0;      // written by stripe st-1
+			uint32_t *bout = (st & 1) ? bnd0 : bnd1;
+			const bool lastStripe = (st + 1 == (int)ax.nstripes);
+			// top boundary of the matrix: H(-1,j) = 0 in both modes (0xff / 0x7fff raw end-to-end,
+			// 0 local), F(-1,j) = floor  (ee_u8.cpp:920-927, loc_u8.cpp:1066-1075)
+			const uint32_t top0 = pack2(0, fl);
+			if(l == 0) HtopPrev = (st == 0) ? pack2(0, fl) : FLv;
+			uint32_t *rec_base = mat + ax.mat_off + ((size_t)st * T * GL + l) * RW;
+			for(int t = 0; t < T; t++) {
+				const int col_lo = t - 2 * l;
+				int c = 5;
+				if(col_lo >= 0 && col_lo < ncol) c = __ffs((int)rf[col_lo]) - 1;
+				uint32_t P[S];
+				{
+					const uint4 *pp = reinterpret_cast<const uint4*>(prof + (c * GL + l) * SP);
+#pragma unroll
+					for(int q = 0; q < SP / 4; q++) {
+						uint4 v = pp[q];
+						if(4 * q + 0 < S) P[4 * q + 0] = v.x;
+						if(4 * q + 1 < S) P[4 * q + 1] = v.y;
+						if(4 * q + 2 < S) P[4 * q + 2] = v.z;
+						if(4 * q + 3 < S) P[4 * q + 3] = v.w;
+					}
+				}
+				// bottom row of the previous step: high halves go down to lane l+1 / next stripe
+				const uint32_t X = __byte_perm(Hbot, Fbot, 0x7632);
+				uint32_t recv = __shfl_up_sync(gmask, X, 1, GL);
+				if(l == GL - 1 && !lastStripe) {
+					int cb = t - 2 * (GL - 1) - 2;           // column X belongs to
+					if(cb >= 0 && cb < ncol) bout[cb] = X;
+				}
+				if(l == 0) {
+					if(st == 0) recv = top0;
+					else recv = (col_lo >= 0 && col_lo < ncol) ? __ldcg(bin + col_lo) : FLv;
+				}
+				const uint32_t Htop = __byte_perm(recv, Hbot, 0x5410);
+				const uint32_t Ftop = __byte_perm(recv, Fbot, 0x5432);
+				uint32_t hdiag = HtopPrev; HtopPrev = Htop;
+				uint32_t Hup = Htop, Fup = Ftop;
+				uint32_t rec[RW];
+#pragma unroll
+				for(int k = 0; k < S; k++) {
+					const uint32_t sck = __byte_perm(P[k], Pprev[k], 0x7610);
+					Pprev[k] = P[k];
+					const uint32_t F = __viaddmax_s16x2(Fup, nrfe[k], __viaddmax_s16x2(Hup, nrfo[k], FLv));
+					const uint32_t d = __viaddmax_s16x2(hdiag, sck, FLv);
+					const uint32_t e = E[k];
+					const uint32_t H = __vimax3_s16x2(d, e, F);
+					rec[k] = e; rec[S + k] = F; rec[2 * S + k] = H;
+					E[k] = __viaddmax_s16x2(e, nrde, __viaddmax_s16x2(H, nrdo[k], FLv));
+					hdiag = Hprev[k]; Hprev[k] = H; Hup = H; Fup = F;
+				}
+				Hbot = Hup; Fbot = Fup;
+#pragma unroll
+				for(int k = 3 * S; k < RW; k++) rec[k] = 0;
+				uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW);
+#pragma unroll
+				for(int q = 0; q < RW / 4; q++)
+					dst[q] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
+			}
+			if(!lastStripe) __threadfence();   // boundary row visible to lane 0 of the next stripe
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------
+// Matrix access for gather / backtrace: cell (row, col) of matrix m (0=E, 1=F, 2=H).
+// ---------------------------------------------------------------------------------------
+struct MatView {
+	const uint32_t *base; int S, T, RW;
+	__device__ __forceinline__ int get(int m, int row, int col) const {
+		const int RS = VL * S;
+		const int st = row / RS, r = row - st * RS;
+		const int v = r / S, k = r - v * S;
+		const uint32_t w = __ldcg(base + ((size_t)(st * T + col + v) * GL + (v >> 1)) * RW + m * S + k);
+		return (v & 1) ? hi16(w) : lo16(w);
+	}
+};
+
+__device__ __forceinline__ uint64_t cand_key(int score, int row, int col) {
+	// ascending order of this key == DpBtCandidate::operator< (score desc, row desc, col desc)
+	uint64_t k = ((uint64_t)(uint32_t)(score + 32768) << 32) | ((uint64_t)row << 16) | (uint64_t)col;
+	return ~k;
+}
+
+// ---------------------------------------------------------------------------------------
+// Gather.  One warp per job.  EMIT=false: best/flag/width/ncand (SwAligner::align,
+// aligner_sw.cpp:500-729 + gatherCells*); EMIT=true: write candidate keys.
+// ---------------------------------------------------------------------------------------
+template<bool EMIT>
+__global__ void __launch_bounds__(128)
+k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
+            const uint8_t *__restrict__ win, const bt2gpu_dp_job *__restrict__ jobs,
+            const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
+            const uint32_t *__restrict__ mat, bt2gpu_dp_result *__restrict__ res,
+            uint32_t *__restrict__ counts, const uint32_t *__restrict__ cand_off,
+            uint64_t *__restrict__ keys, uint32_t *__restrict__ fillptr, int maxcol)
+{
+	extern __shared__ int gsm[];
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t ji = job0 + blockIdx.x * (blockDim.x >> 5) + wib;
+	if(ji >= job0 + njobs) return;
+	const bt2gpu_dp_job jb = jobs[ji];
+	const DpAux ax = aux[ji];
+	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
+	const int minsc = jb.minsc;
+	MatView mv; mv.base = mat + ax.mat_off; mv.S = (int)ax.S; mv.T = (int)ax.T; mv.RW = (int)ax.RW;
+	const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
+	const bool local = !c_sc.monotone;
+	if(EMIT && res[ji].ncand == 0) return;
+	const uint32_t coff = EMIT ? cand_off[ji] : 0;
+	if(!local) {
+		// gatherCellsNucleotidesEnd2EndSse* (ee_u8.cpp:1176-1208): last row, score >= minsc
+		int best = INT32_MIN, cnt = 0;
+		for(int j = lane; j < ncol; j += 32) {
+			int h = mv.get(2, nrow - 1, j);
+			best = max(best, h);
+			if(h >= minsc) {
+				if(EMIT) { uint32_t p = atomicAdd(fillptr + ji, 1u); keys[coff + p] = cand_key(h, nrow - 1, j); }
+				cnt++;
+			}
+		}
+		if(EMIT) return;
+		for(int o = 16; o; o >>= 1) {
+			best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+			cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+		}
+		if(lane == 0) {
+			bt2gpu_dp_result r; memset(&r, 0, sizeof(r));
+			const bool w8 = (ax.fl == -255);
+			int64_t b = best; bool ok = true;
+			if(ncol <= 0) { b = INT64_MIN; ok = false; }                 // !found
+			else if(best < minsc) ok = false;                            // flag -1, returns score
+			else if(w8 && best == -255) { b = INT64_MIN; ok = false; }   // flag -2 (ee_u8.cpp:1137)
+			r.best = b; r.width = ok ? (w8 ? 8 : 16) : 0;
+			r.ncand = ok ? (uint32_t)cnt : 0; r.aligned = (ok && cnt > 0) ? 1 : 0;
+			res[ji] = r; counts[ji - job0] = r.ncand;
+		}
+		return;
+	}
+	// ---- local mode ----
+	const int P8 = ((nrow + 7) >> 3) << 3, P16 = ((nrow + 15) >> 4) << 4;
+	int *cmA = gsm + (size_t)wib * 2 * maxcol, *cmB = cmA + maxcol;
+	if(!EMIT) { for(int j = lane; j < ncol; j += 32) { cmA[j] = 0; cmB[j] = 0; } __syncwarp(); }
+	const uint64_t bonus = (uint64_t)c_sc.match;
+	const uint64_t minrow64 = (((uint64_t)(int64_t)minsc + bonus - 1) / bonus) - 1;   // loc_u8.cpp:1408
+	const int S = mv.S, T = mv.T, RS = VL * S;
+	const int nrec = (int)ax.nstripes * T * GL;
+	int cnt = 0;
+	for(int rix = lane; rix < nrec; rix += 32) {
+		const int l = rix & (GL - 1), t = (rix >> 3) % T, st = (rix >> 3) / T;
+		const uint32_t *rp = mv.base + (size_t)rix * mv.RW + 2 * S;
+		for(int k = 0; k < S; k++) {
+			const uint32_t w = __ldcg(rp + k);
+#pragma unroll
+			for(int half = 0; half < 2; half++) {
+				const int v = 2 * l + half;
+				const int row = st * RS + v * S + k, col = t - v;
+				if(col < 0 || col >= ncol || row >= P16) continue;
+				const int h = half ? hi16(w) : lo16(w);
+				if(!EMIT) { if(h > 0) atomicMax(row < P8 ? &cmA[col] : &cmB[col], h); }
+				if(row < nrow && h >= minsc && (uint64_t)row >= minrow64) {
+					const int readc = rd[row], refc = rf[col];
+					const bool match = (refc & (1 << readc)) != 0;
+					bool matchSucc = false;
+					if(row < nrow - 1) matchSucc = ((int)rf[col + 1] & (1 << (int)rd[row + 1])) != 0;
+					if(match && !matchSucc) {
+						if(EMIT) { uint32_t p = atomicAdd(fillptr + ji, 1u); keys[coff + p] = cand_key(h, row, col); }
+						cnt++;
+					}
+				}
+			}
+		}
+	}
+	if(EMIT) return;
+	// bias of the u8 profile (loc_u8.cpp:98-110): largest penalty over the read
+	int bias = 0;
+	for(int i = lane; i < nrow; i += 32) {
+		int q = (int)qu[i] - 33; q = q < 0 ? 0 : (q > 255 ? 255 : q);
+		int pen = c_npens[q];
+		if(rd[i] < 4) pen = max(pen, c_mmpens[q]);
+		bias = max(bias, pen);
+	}
+	for(int o = 16; o; o >>= 1) {
+		cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+		bias = max(bias, __shfl_xor_sync(0xffffffffu, bias, o));
+	}
+	__syncwarp();
+	if(lane == 0) {
+		bt2gpu_dp_result r; memset(&r, 0, sizeof(r));
+		int flag = -2; int64_t best = INT64_MIN; int width = 0;
+		if(jb.enable8) {                                   // alignNucleotidesLocalSseU8
+			int vmax = 0; bool sat = false;
+			for(int j = 0; j < ncol; j++) {
+				const int cm = max(cmA[j], cmB[j]);
+				vmax = max(vmax, cm);
+				if(cm + bias >= 255) { sat = true; break; }
+				if(cm < minsc && (int64_t)cm + (int64_t)(ncol - j - 1) * c_sc.match < minsc) break;
+			}
+			if(sat || vmax + bias >= 255) flag = -2;
+			else if(vmax == 0 || vmax < minsc) { flag = -1; best = vmax; }
+			else { flag = 0; best = vmax; width = 8; }
+		}
+		if(flag == -2) {                                   // alignNucleotidesLocalSseI16
+			int vmax = 0;
+			for(int j = 0; j < ncol; j++) {
+				const int cm = cmA[j];
+				vmax = max(vmax, cm);
+				if(cm < minsc && (int64_t)cm + (int64_t)(ncol - j - 1) * c_sc.match < minsc) break;
+			}
+			if(vmax == 0) { flag = -1; best = INT64_MIN; }
+			else if(vmax < minsc) { flag = -1; best = vmax; }
+			else { flag = 0; best = vmax; width = 16; }
+		}
+		const bool ok = (flag == 0) && best != INT64_MIN && best >= minsc;
+		r.best = best; r.width = width;
+		r.ncand = ok ? (uint32_t)cnt : 0; r.aligned = (ok && cnt > 0) ? 1 : 0;
+		res[ji] = r; counts[ji - job0] = r.ncand;
+	}
+}
+
+// Exclusive scan of per-job candidate counts (one block); also resets the fill pointers.
+__global__ void k_dp_scan(const uint32_t *__restrict__ counts, uint32_t n, uint32_t job0,
+                          uint32_t *__restrict__ cand_off, uint32_t *__restrict__ fillptr,
+                          bt2gpu_dp_result *__restrict__ res, unsigned long long *__restrict__ total,
+                          unsigned long long cap, int *__restrict__ errflag)
+{
+	__shared__ unsigned long long warpsum[32];
+	__shared__ unsigned long long carry;
+	if(threadIdx.x == 0) carry = *total;
+	__syncthreads();
+	for(uint32_t base = 0; base < n; base += blockDim.x) {
+		uint32_t i = base + threadIdx.x;
+		unsigned long long v = i < n ? counts[i] : 0, x = v;
+		for(int o = 1; o < 32; o <<= 1) { unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if((threadIdx.x & 31) >= o) x += y; }
+		if((threadIdx.x & 31) == 31) warpsum[threadIdx.x >> 5] = x;
+		__syncthreads();
+		if(threadIdx.x < 32) {
+			unsigned long long w = threadIdx.x < (blockDim.x >> 5) ? warpsum[threadIdx.x] : 0, z = w;
+			for(int o = 1; o < 32; o <<= 1) { unsigned long long y = __shfl_up_sync(0xffffffffu, z, o); if(threadIdx.x >= o) z += y; }
+			warpsum[threadIdx.x] = z - w;
+		}
+		__syncthreads();
+		unsigned long long off = carry + warpsum[threadIdx.x >> 5] + x - v;
+		if(i < n) {
+			if(off + v > cap) { *errflag = 1; off = 0; }
+			cand_off[job0 + i] = (uint32_t)off; fillptr[job0 + i] = 0; res[job0 + i].cand_off = (uint32_t)off;
+		}
+		__syncthreads();
+		if(threadIdx.x == blockDim.x - 1) carry = off + v;
+		__syncthreads();
+	}
+	if(threadIdx.x == 0) *total = carry;
+}
+
+// Per-job bitonic sort of the candidate keys (one CTA per job) + conversion to bt2gpu_dp_cand.
+__global__ void __launch_bounds__(256)
+k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__restrict__ keys,
+          bt2gpu_dp_cand *__restrict__ cands)
+{
+	extern __shared__ uint64_t skeys[];
+	const uint32_t ji = job0 + blockIdx.x;
+	const uint32_t n = res[ji].ncand;
+	if(n == 0) return;
+	uint64_t *g = keys + res[ji].cand_off;
+	const bool insm = n <= 4096;
+	uint64_t *a = insm ? skeys : g;
+	if(insm) { for(uint32_t i = threadIdx.x; i < n; i += blockDim.x) skeys[i] = g[i]; }
+	__syncthreads();
+	uint32_t np2 = 1; while(np2 < n) np2 <<= 1;
+	for(uint32_t size = 2; size <= np2; size <<= 1) {
+		for(uint32_t i = threadIdx.x; i < np2 / 2; i += blockDim.x) {     // flip step
+			uint32_t blk = i / (size / 2), off = i % (size / 2);
+			uint32_t x = blk * size + off, y = blk * size + size - 1 - off;
+			if(y < n) { uint64_t kx = a[x], ky = a[y]; if(kx > ky) { a[x] = ky; a[y] = kx; } }
+		}
+		__syncthreads();
+		for(uint32_t stride = size / 4; stride > 0; stride >>= 1) {
+			for(uint32_t i = threadIdx.x; i < np2 / 2; i += blockDim.x) {
+				uint32_t x = (i / stride) * stride * 2 + (i % stride), y = x + stride;
+				if(y < n) { uint64_t kx = a[x], ky = a[y]; if(kx > ky) { a[x] = ky; a[y] = kx; } }
+			}
+			__syncthreads();
+		}
+	}
+	bt2gpu_dp_cand *out = cands + res[ji].cand_off;
+	for(uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+		uint64_t k = ~a[i];
+		if(insm) g[i] = a[i];
+		bt2gpu_dp_cand c; c.score = (int32_t)(uint32_t)(k >> 32) - 32768; c.row = (uint32_t)((k >> 16) & 0xffff); c.col = (uint32_t)(k & 0xffff);
+		out[i] = c;
+	}
+}
+
+// ---------------------------------------------------------------------------------------
+// Backtrace.  One thread per job replays SwAligner::nextAlignment (aligner_sw.cpp:737-1146)
+// over the sorted candidates.  The walk is backtraceNucleotides* (ee_u8.cpp:1283-1877).
+// In the reference a cell is marked reportedThrough the moment it is visited, and a popped
+// branch frame re-enters its (already marked) cell, so every dead end unwinds the whole
+// branch stack and fails: the masks_/btnstack_ state never changes an outcome.  The kernel
+// therefore keeps only the reportedThrough bit and fails at the first blocked cell
+// (equivalence is exercised by the goldens; the CPU oracle keeps the full state).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint8_t dev_mask2dna(int m) { return (uint8_t)"?ACMGRSVTWYHKDBNN"[m & 31 ? (m > 16 ? 16 : m) : 0]; }
+
+__global__ void __launch_bounds__(64)
+k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
+               const uint8_t *__restrict__ win, const bt2gpu_dp_job *__restrict__ jobs,
+               const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
+               const uint32_t *__restrict__ mat, bt2gpu_dp_result *__restrict__ res,
+               const bt2gpu_dp_cand *__restrict__ cands, uint8_t *__restrict__ rep,
+               uint32_t *__restrict__ donelist, bt2gpu_dp_aln *__restrict__ alns,
+               bt2gpu_edit *__restrict__ escr, bt2gpu_edit *__restrict__ edits,
+               unsigned long long *__restrict__ nedits, unsigned long long edit_cap,
+               uint32_t max_aln, int *__restrict__ errflag)
+{
+	const uint32_t ji = job0 + blockIdx.x * blockDim.x + threadIdx.x;
+	if(ji >= job0 + njobs) return;
+	bt2gpu_dp_result r = res[ji];
+	r.naln = 0; r.aln_off = ji * max_aln; r.tail_tries = 0; r.cural = 0;
+	if(!r.aligned) { res[ji] = r; return; }
+	const bt2gpu_dp_job jb = jobs[ji];
+	const DpAux ax = aux[ji];
+	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
+	MatView mv; mv.base = mat + ax.mat_off; mv.S = (int)ax.S; mv.T = (int)ax.T; mv.RW = (int)ax.RW;
+	const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
+	uint8_t *rp = rep + ax.rep_off;
+	const bool local = !c_sc.monotone;
+	const int gapbar = c_sc.gapbar;
+	const bt2gpu_dp_cand *cd = cands + r.cand_off;
+	uint32_t *done = donelist + r.cand_off;
+	bt2gpu_edit *ed = escr + ax.escr_off;
+	const uint32_t ncand = r.ncand;
+	uint32_t SQ = (uint32_t)nrow >> 4; if(SQ == 0) SQ = 1;
+	uint32_t cural = 0, ndone = 0, tries = 0;
+	while(r.naln < max_aln && cural < ncand) {
+		bool got = false;
+		bt2gpu_dp_aln out;
+		while(cural < ncand) {
+			const bt2gpu_dp_cand c0 = cd[cural];
+			if(c0.score < jb.minsc) { cural++; continue; }
+			int row = (int)c0.row, col = (int)c0.col;
+			{ const size_t b = (size_t)row * ncol + col; if((rp[b >> 3] >> (b & 7)) & 1) { cural++; continue; } }
+			if(local) {
+				bool dom = false;
+				for(uint32_t i = 0; i < ndone; i++) {
+					uint32_t dr = done[i] >> 16, dc = done[i] & 0xffff;
+					uint32_t rh = max((uint32_t)row, dr), rl = min((uint32_t)row, dr);
+					uint32_t ch = max((uint32_t)col, dc), cl = min((uint32_t)col, dc);
+					if(ch - cl <= SQ && rh - rl <= SQ) { dom = true; break; }
+				}
+				if(dom) { cural++; continue; }
+			}
+			tries++;
+			// ---- walk ----
+			int score = 0, ns = 0, gaps = 0, ned = 0, ct = 2;
+			const int origCol = col;
+			const int trimEnd = nrow - row - 1;
+			int trimBeg = 0;
+			bool ok = false, overlapped = false, blocked = false;
+			while(row >= 0) {
+				const size_t b = (size_t)row * ncol + col;
+				const bool reported = (rp[b >> 3] >> (b & 7)) & 1;
+				bool empty = false, canMove = !reported;
+				int cur = 0;
+				if(!reported && row > 0) {
+					const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
+					if(ct == 0) {
+						const int sc_cur = mv.get(0, row, col);
+						const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
+						int mask = 0;
+						if((!local || hl > 0) && hl - c_sc.rdo == sc_cur) mask |= 1;
+						if((!local || el > 0) && el - c_sc.rde == sc_cur) mask |= 2;
+						if(mask & 1) cur = 3; else if(mask == 2) cur = 4; else { empty = true; }
+					} else if(ct == 1) {
+						const int sc_cur = mv.get(1, row, col);
+						const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
+						int mask = 0;
+						if((!local || hu > 0) && hu - c_sc.rfo == sc_cur) mask |= 1;
+						if((!local || fu > 0) && fu - c_sc.rfe == sc_cur) mask |= 2;
+						if(mask & 1) cur = 2; else if(mask == 2) cur = 5; else { empty = true; }
+					} else {
+						const int sc_cur = mv.get(2, row, col);
+						int mask = 0;
+						if(gapsAllowed) {
+							const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
+							if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) mask |= 1;
+							if((!local || fu > 0) && sc_cur == fu - c_sc.rfe) mask |= 4;
+							if(col > 0) {
+								const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
+								if((!local || hl > 0) && sc_cur == hl - c_sc.rdo) mask |= 2;
+								if((!local || el > 0) && sc_cur == el - c_sc.rde) mask |= 8;
+							}
+						}
+						if(col > 0) {
+							const int hd = mv.get(2, row - 1, col - 1);
+							const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
+							if((!local || hd > 0) && sc_cur == hd + sd) mask |= 16;
+						}
+						if(mask & 16) cur = 1;            // diag > ref open > ref ext > read open > read ext
+						else if(mask & 1) cur = 2;
+						else if(mask & 4) cur = 5;
+						else if(mask & 2) cur = 3;
+						else if(mask & 8) cur = 4;
+						else empty = true;
+					}
+					// empty => origMask == 0 here (no stored mask state), so canMoveThru stays true
+				}
+				rp[b >> 3] |= (uint8_t)(1u << (b & 7));
+				if(!canMove) { blocked = true; break; }
+				{
+					const long long diagi = (long long)col - row + (long long)jb.triml;
+					if(diagi >= 0 && (unsigned long long)diagi >= jb.corel && (unsigned long long)diagi <= jb.corer) overlapped = true;
+				}
+				if(empty || row == 0) { trimBeg = row; ok = true; break; }
+				bt2gpu_edit e; e.pad = 0;
+				if(cur == 1) {
+					const int rc = rd[row], rm = rf[col];
+					const int mm = (rm >= 16 || rc > 3) ? -1 : (((1 << rc) & rm) ? 1 : 0);
+					ct = 2;
+					if(mm != 1) {
+						e.pos = (uint32_t)row; e.chr = dev_mask2dna(rm); e.qchr = (uint8_t)"ACGTN"[rc]; e.type = BT2GPU_EDIT_MM;
+						ed[ned++] = e;
+						score -= dev_mm(rc, rm, (int)qu[row] - 33);
+					} else score += c_sc.match;
+					if(mm == -1) ns++;
+					row--; col--;
+				} else if(cur == 2 || cur == 5) {
+					e.pos = (uint32_t)row; e.chr = '-'; e.qchr = (uint8_t)"ACGTN"[rd[row]]; e.type = BT2GPU_EDIT_REF_GAP;
+					ed[ned++] = e;
+					row--;
+					if(cur == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; }
+					gaps++;
+				} else {
+					e.pos = (uint32_t)row + 1; e.chr = dev_mask2dna(rf[col]); e.qchr = '-'; e.type = BT2GPU_EDIT_READ_GAP;
+					ed[ned++] = e;
+					col--;
+					if(cur == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; }
+					gaps++;
+				}
+			}
+			if(ok && !blocked) {
+				ok = overlapped;                                           // core-diagonal test
+				if(ok) {
+					const int rc = rd[row], rm = rf[col];
+					const int mm = (rm >= 16 || rc > 3) ? -1 : (((1 << rc) & rm) ? 1 : 0);
+					if(mm != 1) {
+						bt2gpu_edit e; e.pad = 0;
+						e.pos = (uint32_t)row; e.chr = dev_mask2dna(rm); e.qchr = (uint8_t)"ACGTN"[rc]; e.type = BT2GPU_EDIT_MM;
+						ed[ned++] = e;
+						score -= dev_mm(rc, rm, (int)qu[row] - 33);
+					} else score += c_sc.match;
+					if(mm == -1) ns++;
+					if(ns > jb.nceil) ok = false;
+				}
+			} else ok = false;
+			if(local) { done[ndone++] = ((uint32_t)c0.row << 16) | (uint32_t)c0.col; }
+			if(ok) {
+				out.score = score; out.ns = ns; out.gaps = gaps;
+				out.refoff = (int64_t)col + jb.refl;
+				out.trim5 = (uint32_t)(jb.fw ? trimBeg : trimEnd);
+				out.trim3 = (uint32_t)(jb.fw ? trimEnd : trimBeg);
+				int refns = 0;
+				for(int i = col; i <= origCol; i++) if(rf[i] > 15) refns++;
+				out.refns = refns;
+				const unsigned long long eo = atomicAdd(nedits, (unsigned long long)ned);
+				if(eo + ned > edit_cap) { *errflag = 2; res[ji] = r; return; }
+				out.edit_off = (uint32_t)eo; out.nedits = (uint32_t)ned;
+				// scratch holds edits in walk order (descending row); reference order after
+				// res.reverse() is ascending; '-' strand then inverts again (edit.cpp:50-78)
+				const int rdex = nrow - trimBeg - trimEnd;
+				for(int i = 0; i < ned; i++) {
+					bt2gpu_edit e = ed[jb.fw ? (ned - 1 - i) : i];
+					e.pos -= (uint32_t)trimBeg;
+					if(!jb.fw) e.pos = (uint32_t)(rdex - (int)e.pos - (e.type == BT2GPU_EDIT_READ_GAP ? 0 : 1));
+					edits[eo + i] = e;
+				}
+				got = true;
+				break;
+			}
+			cural++;
+		}
+		if(!got) break;
+		cural++;
+		out.cural = cural; out.tries = tries; tries = 0;
+		alns[(size_t)ji * max_aln + r.naln] = out;
+		r.naln++;
+	}
+	r.tail_tries = tries; r.cural = cural;
+	res[ji] = r;
+}
+
+// ---------------------------------------------------------------------------------------
+// Host side: staging, chunking, launches.
+// ---------------------------------------------------------------------------------------
+static const int kSClasses[] = {3, 4, 5, 6, 8, 10, 12, 16};
+static constexpr int kNClasses = sizeof(kSClasses) / sizeof(int);
+
+struct DpChunk {
+	uint32_t job0, njobs;
+	uint64_t mat_words, rep_bytes;
+	uint32_t bound_words, escr_edits;
+	uint32_t cls_off[kNClasses + 1];   // ranges into `order` (absolute)
+	int maxcol;
+};
+
+struct DpState {
+	size_t njobs = 0; uint32_t max_aln = 1;
+	size_t cand_cap = 0, edit_cap = 0;
+	uint64_t cells = 0;
+	std::vector<DpChunk> chunks;
+	DevBuf seq, qual, win, jobs, aux, order, res, counts, cand_off, fillptr, keys, cands, done,
+	       alns, edits, escr, mat, bound, rep, scal;   // scal: [0]=total cands, [1]=total edits, [2]=errflag
+	HostBuf h_scal;
+	int maxcol_all = 0;
+};
+
+template<int S> static int launch_fill(bt2gpu_ctx *ctx, DpState *d, const uint32_t *order, uint32_t n) {
+	if(n == 0) return 0;
+	constexpr int SP = (S + 3) & ~3;
+	const size_t smem = (size_t)16 * NCH * GL * SP * 4;
+	static bool attr = false;
+	if(!attr) {
+		BT2_CUDA(cudaFuncSetAttribute(k_dp_fill<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		attr = true;
+	}
+	uint32_t blocks = (n + 15) / 16;
+	uint32_t maxb = (uint32_t)ctx->sm_count * 8;
+	if(blocks > maxb) blocks = maxb;
+	k_dp_fill<S><<<blocks, 128, smem, ctx->stream>>>(
+		d->seq.as<uint8_t>(), d->qual.as<uint8_t>(), d->win.as<uint8_t>(), d->jobs.as<bt2gpu_dp_job>(),
+		d->aux.as<DpAux>(), order, n, d->mat.as<uint32_t>(), d->bound.as<uint32_t>());
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	return 0;
+}
+
+static int dispatch_fill(bt2gpu_ctx *ctx, DpState *d, int cls, const uint32_t *order, uint32_t n) {
+	switch(kSClasses[cls]) {
+	case 3:  return launch_fill<3>(ctx, d, order, n);
+	case 4:  return launch_fill<4>(ctx, d, order, n);
+	case 5:  return launch_fill<5>(ctx, d, order, n);
+	case 6:  return launch_fill<6>(ctx, d, order, n);
+	case 8:  return launch_fill<8>(ctx, d, order, n);
+	case 10: return launch_fill<10>(ctx, d, order, n);
+	case 12: return launch_fill<12>(ctx, d, order, n);
+	case 16: return launch_fill<16>(ctx, d, order, n);
+	}
+	BT2_FAIL("bad S class");
+}
+
+static int choose_class(int nrow) {
+	int best = -1; long bestRows = 0, bestStripes = 0;
+	for(int c = 0; c < kNClasses; c++) {
+		long rs = 16L * kSClasses[c];
+		long ns = (nrow + rs - 1) / rs;
+		long rows = ns * rs;
+		if(best < 0 || rows < bestRows || (rows == bestRows && ns < bestStripes)) { best = c; bestRows = rows; bestStripes = ns; }
+	}
+	return best;
+}
+
+} // namespace bt2
+
+using namespace bt2;
+
+extern "C" int bt2gpu_scoring_set(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc) {
+	if(!ctx || !sc) BT2_FAIL("null argument");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	if(sc->gapbar < 1) BT2_FAIL("gapbar must be >= 1 (ee_u8.cpp:781)");
+	if(sc->rd_gap_ext > sc->rd_gap_open || sc->rf_gap_ext > sc->rf_gap_open) BT2_FAIL("gap extend > gap open");
+	ctx->sc = *sc; ctx->have_sc = true;
+	ScConst c = { sc->match_bonus, sc->rd_gap_open, sc->rd_gap_ext, sc->rf_gap_open, sc->rf_gap_ext, sc->gapbar, sc->monotone };
+	BT2_CUDA(cudaMemcpyToSymbolAsync(c_mmpens, sc->mmpens, sizeof(c_mmpens), 0, cudaMemcpyHostToDevice, ctx->stream));
+	BT2_CUDA(cudaMemcpyToSymbolAsync(c_npens, sc->npens, sizeof(c_npens), 0, cudaMemcpyHostToDevice, ctx->stream));
+	BT2_CUDA(cudaMemcpyToSymbolAsync(c_sc, &c, sizeof(c), 0, cudaMemcpyHostToDevice, ctx->stream));
+	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	return 0;
+}
+
+extern "C" int bt2gpu_dp_stage(
+	bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len, const bt2gpu_dp_job *jobs, size_t njobs,
+	uint32_t max_aln, size_t cand_cap, size_t edit_cap)
+{
+	if(!ctx) BT2_FAIL("null ctx");
+	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set must be called first");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	if(!ctx->dp) ctx->dp = new DpState();
+	DpState *d = ctx->dp;
+	d->njobs = njobs; d->max_aln = max_aln ? max_aln : 1; d->cand_cap = cand_cap; d->edit_cap = edit_cap;
+	d->chunks.clear(); d->cells = 0; d->maxcol_all = 0;
+	if(njobs == 0) return 0;
+	if(njobs > 0x7fffffffu / d->max_aln) BT2_FAIL("too many jobs");
+	const bool local = !ctx->sc.monotone;
+	size_t freeB = 0, totalB = 0;
+	BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
+	const uint64_t mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
+	std::vector<DpAux> aux(njobs);
+	std::vector<uint32_t> order(njobs);
+	std::vector<uint8_t> cls(njobs);
+	DpChunk ch; memset(&ch, 0, sizeof(ch)); ch.job0 = 0;
+	std::vector<std::pair<uint64_t, uint32_t>> tmp;
+	auto close_chunk = [&](uint32_t end) {
+		ch.njobs = end - ch.job0;
+		// order: by class, then by work descending (keeps the 4 groups of a warp in step)
+		uint32_t pos = ch.job0;
+		for(int c = 0; c < kNClasses; c++) {
+			ch.cls_off[c] = pos;
+			tmp.clear();
+			for(uint32_t i = ch.job0; i < end; i++) if(cls[i] == c) tmp.emplace_back((uint64_t)aux[i].nstripes * aux[i].T, i);
+			std::sort(tmp.begin(), tmp.end(), [](const std::pair<uint64_t, uint32_t> &a, const std::pair<uint64_t, uint32_t> &b) {
+				return a.first != b.first ? a.first > b.first : a.second < b.second; });
+			for(auto &p : tmp) order[pos++] = p.second;
+		}
+		ch.cls_off[kNClasses] = pos;
+		d->chunks.push_back(ch);
+	};
+	for(size_t i = 0; i < njobs; i++) {
+		const bt2gpu_dp_job &j = jobs[i];
+		if(j.rd_len == 0 || j.ncol == 0) BT2_FAIL("empty DP problem");
+		if((size_t)j.rd_off + j.rd_len > pool_len || (size_t)j.rf_off + j.ncol + 1 > win_len) BT2_FAIL("job outside pool");
+		if(j.ncol > 60000 || j.rd_len > 60000) BT2_FAIL("DP problem too large");
+		if(!local && j.rd_len > 2270) BT2_FAIL("end-to-end read longer than 2270 rows: checkpointed path (rdlen >= cminlen, aligner_sw.cpp:514) not implemented");
+		if(local && j.rd_len > 16000) BT2_FAIL("local read longer than 16000 rows not supported by the s16 domain");
+		DpAux a; memset(&a, 0, sizeof(a));
+		const int c = choose_class((int)j.rd_len);
+		cls[i] = (uint8_t)c;
+		a.S = (uint32_t)kSClasses[c];
+		a.nstripes = (j.rd_len + 16 * a.S - 1) / (16 * a.S);
+		a.T = j.ncol + 16;
+		a.RW = (3 * a.S + 3) & ~3u;
+		if(local) a.fl = 0;
+		else if(j.enable8 && j.minsc >= -254) a.fl = -255;            // aligner_sw.cpp:518
+		else { a.fl = FL_I16; if(j.minsc < -15000) BT2_FAIL("minsc below the 16-bit end-to-end domain"); }
+		const uint64_t mw = (uint64_t)a.nstripes * a.T * GL * a.RW;
+		if(mw > mat_budget_words) BT2_FAIL("single DP problem exceeds the matrix arena");
+		if(ch.mat_words + mw > mat_budget_words || ch.bound_words > 0x70000000u || ch.escr_edits > 0x70000000u) {
+			close_chunk((uint32_t)i);
+			memset(&ch, 0, sizeof(ch)); ch.job0 = (uint32_t)i;
+		}
+		a.mat_off = ch.mat_words; ch.mat_words += mw;
+		a.rep_off = ch.rep_bytes; ch.rep_bytes += ((uint64_t)j.rd_len * j.ncol + 7) / 8;
+		a.bound_off = ch.bound_words; ch.bound_words += 2 * j.ncol;
+		a.escr_off = ch.escr_edits; ch.escr_edits += j.rd_len + j.ncol + 4;
+		if((int)j.ncol > ch.maxcol) ch.maxcol = (int)j.ncol;
+		aux[i] = a;
+		d->cells += (uint64_t)j.rd_len * j.ncol;
+	}
+	close_chunk((uint32_t)njobs);
+	uint64_t maxMat = 0, maxRep = 0; uint32_t maxBound = 0, maxEscr = 0;
+	for(auto &c : d->chunks) {
+		maxMat = std::max(maxMat, c.mat_words); maxRep = std::max(maxRep, c.rep_bytes);
+		maxBound = std::max(maxBound, c.bound_words); maxEscr = std::max(maxEscr, c.escr_edits);
+		d->maxcol_all = std::max(d->maxcol_all, c.maxcol);
+	}
+	if(d->seq.reserve(pool_len) || d->qual.reserve(pool_len) || d->win.reserve(win_len) ||
+	   d->jobs.reserve(njobs * sizeof(bt2gpu_dp_job)) || d->aux.reserve(njobs * sizeof(DpAux)) ||
+	   d->order.reserve(njobs * 4) || d->res.reserve(njobs * sizeof(bt2gpu_dp_result)) ||
+	   d->counts.reserve(njobs * 4) || d->cand_off.reserve(njobs * 4) || d->fillptr.reserve(njobs * 4) ||
+	   d->keys.reserve(cand_cap * 8) || d->cands.reserve(cand_cap * sizeof(bt2gpu_dp_cand)) ||
+	   d->done.reserve(cand_cap * 4) || d->alns.reserve(njobs * d->max_aln * sizeof(bt2gpu_dp_aln)) ||
+	   d->edits.reserve(edit_cap * sizeof(bt2gpu_edit)) || d->escr.reserve((size_t)maxEscr * sizeof(bt2gpu_edit)) ||
+	   d->mat.reserve(maxMat * 4) || d->bound.reserve((size_t)maxBound * 4) || d->rep.reserve(maxRep) ||
+	   d->scal.reserve(64) || d->h_scal.reserve(64)) return 1;
+	cudaStream_t s = ctx->stream;
+	BT2_CUDA(cudaMemcpyAsync(d->seq.p, seq_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(d->qual.p, qual_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(d->win.p, win_pool, win_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(d->jobs.p, jobs, njobs * sizeof(bt2gpu_dp_job), cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(d->aux.p, aux.data(), njobs * sizeof(DpAux), cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(d->order.p, order.data(), njobs * 4, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaStreamSynchronize(s));   // aux/order are stack-owned host vectors
+	return 0;
+}
+
+extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
+	if(!ctx || !ctx->dp) BT2_FAIL("nothing staged");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	DpState *d = ctx->dp;
+	if(d->njobs == 0) return 0;
+	cudaStream_t s = ctx->stream;
+	if(d->chunks.size() > 1 && phases != 7) BT2_FAIL("partial phases need a single-chunk batch");
+	BT2_CUDA(cudaMemsetAsync(d->scal.p, 0, 64, s));
+	unsigned long long *scal = d->scal.as<unsigned long long>();
+	int *errflag = reinterpret_cast<int*>(scal + 2);
+	const bool local = !ctx->sc.monotone;
+	for(const DpChunk &c : d->chunks) {
+		if(phases & 1) {
+			for(int k = 0; k < kNClasses; k++) {
+				uint32_t n = c.cls_off[k + 1] - c.cls_off[k];
+				if(dispatch_fill(ctx, d, k, d->order.as<uint32_t>() + c.cls_off[k], n)) return 1;
+			}
+		}
+		if(phases & 2) {
+			const uint32_t gb = (c.njobs + 3) / 4;
+			const size_t gsm = local ? (size_t)4 * 2 * c.maxcol * sizeof(int) : 0;
+			if(gsm > 48 * 1024) {
+				BT2_CUDA(cudaFuncSetAttribute(k_dp_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+				BT2_CUDA(cudaFuncSetAttribute(k_dp_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+			}
+			k_dp_gather<false><<<gb, 128, gsm, s>>>(
+				d->seq.as<uint8_t>(), d->qual.as<uint8_t>(), d->win.as<uint8_t>(), d->jobs.as<bt2gpu_dp_job>(),
+				d->aux.as<DpAux>(), c.job0, c.njobs, d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(),
+				d->counts.as<uint32_t>(), d->cand_off.as<uint32_t>(), d->keys.as<uint64_t>(), d->fillptr.as<uint32_t>(), c.maxcol);
+			k_dp_scan<<<1, 1024, 0, s>>>(d->counts.as<uint32_t>(), c.njobs, c.job0, d->cand_off.as<uint32_t>(),
+				d->fillptr.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), scal, (unsigned long long)d->cand_cap, errflag);
+			k_dp_gather<true><<<gb, 128, gsm, s>>>(
+				d->seq.as<uint8_t>(), d->qual.as<uint8_t>(), d->win.as<uint8_t>(), d->jobs.as<bt2gpu_dp_job>(),
+				d->aux.as<DpAux>(), c.job0, c.njobs, d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(),
+				d->counts.as<uint32_t>(), d->cand_off.as<uint32_t>(), d->keys.as<uint64_t>(), d->fillptr.as<uint32_t>(), c.maxcol);
+			k_dp_sort<<<c.njobs, 256, 4096 * 8, s>>>(c.job0, d->res.as<bt2gpu_dp_result>(), d->keys.as<uint64_t>(), d->cands.as<bt2gpu_dp_cand>());
+			ctx->launches += 4;
+			BT2_CUDA(cudaGetLastError());
+		}
+		if(phases & 4) {
+			BT2_CUDA(cudaMemsetAsync(d->rep.p, 0, c.rep_bytes, s));
+			k_dp_backtrace<<<(c.njobs + 63) / 64, 64, 0, s>>>(
+				d->seq.as<uint8_t>(), d->qual.as<uint8_t>(), d->win.as<uint8_t>(), d->jobs.as<bt2gpu_dp_job>(),
+				d->aux.as<DpAux>(), c.job0, c.njobs, d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(),
+				d->cands.as<bt2gpu_dp_cand>(), d->rep.as<uint8_t>(), d->done.as<uint32_t>(), d->alns.as<bt2gpu_dp_aln>(),
+				d->escr.as<bt2gpu_edit>(), d->edits.as<bt2gpu_edit>(), scal + 1, (unsigned long long)d->edit_cap,
+				d->max_aln, errflag);
+			ctx->launches++;
+			BT2_CUDA(cudaGetLastError());
+		}
+	}
+	return 0;
+}
+
+extern "C" int bt2gpu_dp_fetch(
+	bt2gpu_ctx *ctx, bt2gpu_dp_result *results, bt2gpu_dp_cand *cands, bt2gpu_dp_aln *alns,
+	bt2gpu_edit *edits, size_t *ncands, size_t *nedits)
+{
+	if(!ctx || !ctx->dp) BT2_FAIL("nothing staged");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	DpState *d = ctx->dp;
+	cudaStream_t s = ctx->stream;
+	if(ncands) *ncands = 0;
+	if(nedits) *nedits = 0;
+	if(d->njobs == 0) return 0;
+	BT2_CUDA(cudaMemcpyAsync(d->h_scal.p, d->scal.p, 64, cudaMemcpyDeviceToHost, s));
+	if(results) BT2_CUDA(cudaMemcpyAsync(results, d->res.p, d->njobs * sizeof(bt2gpu_dp_result), cudaMemcpyDeviceToHost, s));
+	if(alns) BT2_CUDA(cudaMemcpyAsync(alns, d->alns.p, d->njobs * d->max_aln * sizeof(bt2gpu_dp_aln), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamSynchronize(s));
+	const unsigned long long *hs = d->h_scal.as<unsigned long long>();
+	const int err = *reinterpret_cast<const int*>(hs + 2);
+	if(err == 1) BT2_FAIL("candidate pool overflow (raise cand_cap)");
+	if(err == 2) BT2_FAIL("edit pool overflow (raise edit_cap)");
+	if(cands && hs[0]) BT2_CUDA(cudaMemcpyAsync(cands, d->cands.p, hs[0] * sizeof(bt2gpu_dp_cand), cudaMemcpyDeviceToHost, s));
+	if(edits && hs[1]) BT2_CUDA(cudaMemcpyAsync(edits, d->edits.p, hs[1] * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamSynchronize(s));
+	if(ncands) *ncands = (size_t)hs[0];
+	if(nedits) *nedits = (size_t)hs[1];
+	return 0;
+}
+
+extern "C" uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx) { return (ctx && ctx->dp) ? ctx->dp->cells : 0; }
+
+extern "C" int bt2gpu_dp_align_batch(
+	bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len, const bt2gpu_dp_job *jobs, size_t njobs, uint32_t max_aln,
+	bt2gpu_dp_result *results, bt2gpu_dp_cand *cands, size_t cand_cap, bt2gpu_dp_aln *alns,
+	bt2gpu_edit *edits, size_t edit_cap)
+{
+	if(bt2gpu_dp_stage(ctx, seq_pool, qual_pool, pool_len, win_pool, win_len, jobs, njobs, max_aln, cand_cap, edit_cap)) return 1;
+	if(bt2gpu_dp_run(ctx, 7)) return 1;
+	return bt2gpu_dp_fetch(ctx, results, cands, alns, edits, nullptr, nullptr);
+}
+
+namespace bt2 {
+void dp_state_free(DpState *d) {
+	if(!d) return;
+	DevBuf *bufs[] = { &d->seq, &d->qual, &d->win, &d->jobs, &d->aux, &d->order, &d->res, &d->counts, &d->cand_off,
+	                   &d->fillptr, &d->keys, &d->cands, &d->done, &d->alns, &d->edits, &d->escr, &d->mat, &d->bound,
+	                   &d->rep, &d->scal };
+	for(DevBuf *b : bufs) b->release();
+	d->h_scal.release();
+	delete d;
+}
+}
