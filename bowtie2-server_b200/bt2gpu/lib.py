@@ -15,7 +15,7 @@ SYMBOLS = [
     "bt2gpu_abi_version", "bt2gpu_last_error", "bt2gpu_device_count", "bt2gpu_ctx_create",
     "bt2gpu_ctx_destroy", "bt2gpu_ctx_sync", "bt2gpu_ctx_stream", "bt2gpu_ctx_launches",
     "bt2gpu_scoring_set", "bt2gpu_dp_align_batch", "bt2gpu_dp_stage", "bt2gpu_dp_run",
-    "bt2gpu_dp_fetch", "bt2gpu_dp_staged_cells",
+    "bt2gpu_dp_fetch", "bt2gpu_dp_staged_cells", "bt2gpu_dp_phase_ms",
 ]
 
 _lib = None
@@ -124,6 +124,11 @@ class Context:
                 cands = cands[: nc.value]
             edits = edits[: ne.value]
         return results, cands, alns, edits, nc.value, ne.value
+
+    def dp_phase_ms(self):
+        ms = (C.c_float * 3)()
+        _check(self.lib.bt2gpu_dp_phase_ms(self._h, ms))
+        return [float(x) for x in ms]
 
     def dp_cells(self):
         return int(self.lib.bt2gpu_dp_staged_cells(self._h))

@@ -652,6 +652,8 @@ struct DpState {
 	       alns, edits, escr, mat, bound, rep, scal;   // scal: [0]=total cands, [1]=total edits, [2]=errflag
 	HostBuf h_scal;
 	int maxcol_all = 0;
+	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // fill | gather | backtrace boundaries (single-chunk runs)
+	uint32_t ev_phases = 0;
 };
 
 template<int S> static int launch_fill(bt2gpu_ctx *ctx, DpState *d, const uint32_t *order, uint32_t n) {
@@ -824,6 +826,12 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 	unsigned long long *scal = d->scal.as<unsigned long long>();
 	int *errflag = reinterpret_cast<int*>(scal + 2);
 	const bool local = !ctx->sc.monotone;
+	const bool timed = d->chunks.size() == 1;
+	if(timed) {
+		for(int i = 0; i < 4; i++) if(!d->ev[i]) BT2_CUDA(cudaEventCreate(&d->ev[i]));
+		d->ev_phases = phases;
+		BT2_CUDA(cudaEventRecord(d->ev[0], s));
+	} else d->ev_phases = 0;
 	for(const DpChunk &c : d->chunks) {
 		if(phases & 1) {
 			for(int k = 0; k < kNClasses; k++) {
@@ -831,6 +839,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 				if(dispatch_fill(ctx, d, k, d->order.as<uint32_t>() + c.cls_off[k], n)) return 1;
 			}
 		}
+		if(timed) BT2_CUDA(cudaEventRecord(d->ev[1], s));
 		if(phases & 2) {
 			const uint32_t gb = (c.njobs + 3) / 4;
 			const size_t gsm = local ? (size_t)4 * 2 * c.maxcol * sizeof(int) : 0;
@@ -852,6 +861,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 			ctx->launches += 4;
 			BT2_CUDA(cudaGetLastError());
 		}
+		if(timed) BT2_CUDA(cudaEventRecord(d->ev[2], s));
 		if(phases & 4) {
 			BT2_CUDA(cudaMemsetAsync(d->rep.p, 0, c.rep_bytes, s));
 			k_dp_backtrace<<<(c.njobs + 63) / 64, 64, 0, s>>>(
@@ -863,7 +873,18 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 			ctx->launches++;
 			BT2_CUDA(cudaGetLastError());
 		}
+		if(timed) BT2_CUDA(cudaEventRecord(d->ev[3], s));
 	}
+	return 0;
+}
+
+extern "C" int bt2gpu_dp_phase_ms(bt2gpu_ctx *ctx, float *ms3) {
+	if(!ctx || !ctx->dp || !ms3) BT2_FAIL("nothing staged");
+	DpState *d = ctx->dp;
+	ms3[0] = ms3[1] = ms3[2] = 0.f;
+	if(!d->ev_phases) BT2_FAIL("phase times are recorded for single-chunk runs only");
+	BT2_CUDA(cudaEventSynchronize(d->ev[3]));
+	for(int i = 0; i < 3; i++) BT2_CUDA(cudaEventElapsedTime(&ms3[i], d->ev[i], d->ev[i + 1]));
 	return 0;
 }
 
@@ -915,6 +936,7 @@ void dp_state_free(DpState *d) {
 	                   &d->rep, &d->scal };
 	for(DevBuf *b : bufs) b->release();
 	d->h_scal.release();
+	for(int i = 0; i < 4; i++) if(d->ev[i]) cudaEventDestroy(d->ev[i]);
 	delete d;
 }
 }

@@ -149,6 +149,9 @@ int bt2gpu_dp_fetch(
 	bt2gpu_dp_result *results,
 	bt2gpu_dp_cand *cands, bt2gpu_dp_aln *alns, bt2gpu_edit *edits,
 	size_t *ncands, size_t *nedits);
+/* Device time (ms, CUDA events on the context's stream) of the last bt2gpu_dp_run():
+ * ms3[0] fill, ms3[1] gather+scan+sort, ms3[2] backtrace. Single-chunk batches only. */
+int bt2gpu_dp_phase_ms(bt2gpu_ctx *ctx, float *ms3);
 /* DP cells (rows x cols, the bowtie2-dp CUPS numerator bt2_dp.cpp:744) of the staged batch. */
 uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx);
 

@@ -32,6 +32,8 @@
 #include <cstring>
 #include <cstdlib>
 #include <limits>
+#include <thread>
+#include <chrono>
 #define private public
 #define protected public
 #include "aligner_sw.h"
@@ -86,6 +88,7 @@ int main(int argc, char** argv) {
 	int rfgc = DEFAULT_REF_GAP_CONST, rfgl = DEFAULT_REF_GAP_LINEAR;
 	double nceilC = 0.0, nceilL = 0.15;
 	size_t maxaln = 8, cminlen = 2000, cpow2 = 4, upto = (size_t)-1;
+	bool bench = false; int nthreads = 1;
 	for(int i = 1; i < argc; i++) {
 		string a = argv[i];
 		if(a == "--log") logfn = argv[++i];
@@ -103,6 +106,8 @@ int main(int argc, char** argv) {
 		else if(a == "--maxaln") maxaln = (size_t)atol(argv[++i]);
 		else if(a == "--cp-min") cminlen = (size_t)atol(argv[++i]);
 		else if(a == "--upto") upto = (size_t)atol(argv[++i]);
+		else if(a == "--bench") bench = true;
+		else if(a == "--threads") nthreads = atoi(argv[++i]);
 		else { cerr << "unknown arg " << a << endl; return 2; }
 	}
 	if(ma < 0) ma = local ? DEFAULT_MATCH_BONUS_LOCAL : DEFAULT_MATCH_BONUS;
@@ -115,6 +120,61 @@ int main(int argc, char** argv) {
 	BitPairReference* refs = NULL;
 	if(!idx.empty()) {
 		refs = new BitPairReference(idx, false, false, NULL, NULL, false, false, false, false, false, false);
+	}
+
+	if(bench) {
+		// --bench: time the reference's own SwAligner (initRead/initRef/align/nextAlignment*)
+		// over all problems of a --problems file with `nthreads` worker threads (one
+		// SwAligner each, as bt2_search.cpp:3128-3130 does); prints one JSON line.
+		struct BP { string seq, qual; Prob p; };
+		vector<BP> all;
+		{
+			ifstream bin(probfn.c_str());
+			string bl;
+			while(getline(bin, bl)) {
+				EList<string> b; tokenize(bl, '\t', b);
+				if(b.size() < 9 || b[0] != "P") continue;
+				BP x; x.seq = b[1]; x.qual = b[2];
+				x.p.fw = (b[3] == "+"); x.p.refidx = (TRefId)atol(b[4].c_str());
+				x.p.reflen = (TRefOff)atoll(b[5].c_str()); x.p.minsc = (TAlScore)atoll(b[6].c_str());
+				istringstream is(b[7]); parseRect(is, x.p.rect); x.p.window = b[8];
+				all.push_back(x);
+			}
+		}
+		vector<uint64_t> cells(nthreads, 0), alns(nthreads, 0);
+		auto t0 = chrono::steady_clock::now();
+		vector<thread> th;
+		for(int t = 0; t < nthreads; t++) th.emplace_back([&, t]() {
+			SwAligner swl(NULL);
+			BTDnaString sq, sqrc; BTString ql, qlrc;
+			vector<char> rfb;
+			for(size_t i = t; i < all.size(); i += nthreads) {
+				BP& x = all[i];
+				sq.install(x.seq.c_str(), true); ql = x.qual;
+				sqrc = sq; sqrc.reverseComp(); qlrc = ql; qlrc.reverse();
+				swl.initRead(sq, sqrc, ql, qlrc, 0, sq.length(), sc);
+				size_t n = x.p.window.length();
+				rfb.resize(n + 16);
+				for(size_t k = 0; k < n; k++) { int m = asc2dnamask[(int)x.p.window[k]]; if(m == 15) m = 16; rfb[k] = (char)m; }
+				swl.initRef(x.p.fw, x.p.refidx, x.p.rect, &rfb[0], 0, n - 1, x.p.reflen, sc, x.p.minsc,
+				            enable8, cminlen, cpow2, false, true);
+				TAlScore best = std::numeric_limits<TAlScore>::min();
+				bool aligned = swl.align(best);
+				cells[t] += (uint64_t)sq.length() * (n - 1);
+				if(aligned) {
+					RandomSource rnd((uint32_t)(i * 7919u + 17u));
+					SwResult res; size_t na = 0;
+					while(na < maxaln && !swl.done()) { res.reset(); if(!swl.nextAlignment(res, x.p.minsc, rnd)) break; na++; }
+					alns[t] += na;
+				}
+			}
+		});
+		for(auto& x : th) x.join();
+		double sec = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
+		uint64_t c = 0, a = 0; for(int t = 0; t < nthreads; t++) { c += cells[t]; a += alns[t]; }
+		cout << "{\"problems\": " << all.size() << ", \"cells\": " << c << ", \"alignments\": " << a
+		     << ", \"seconds\": " << sec << ", \"threads\": " << nthreads << "}" << endl;
+		return 0;
 	}
 	const string& fn = logfn.empty() ? probfn : logfn;
 	bool isLog = !logfn.empty();
