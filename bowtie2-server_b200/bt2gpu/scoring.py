@@ -10,7 +10,7 @@ COST_MODEL_ROUNDED_QUAL, COST_MODEL_QUAL, COST_MODEL_CONSTANT = 1, 2, 3
 class SimpleFunc:
     """simple_func.h: f(x) = max(mn, min(mx, I + S * g(x))), g in {const, linear, sqrt, log}."""
 
-    def __init__(self, kind="L", const=0.0, coeff=0.0, mn=0.0, mx=float("inf")):
+    def __init__(self, kind="L", const=0.0, coeff=0.0, mn=-float("inf"), mx=float("inf")):
         self.kind, self.const, self.coeff, self.mn, self.mx = kind, const, coeff, mn, mx
 
     @staticmethod
