@@ -144,7 +144,7 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 			// 0 local), F(-1,j) = floor  (ee_u8.cpp:920-927, loc_u8.cpp:1066-1075)
 			const uint32_t top0 = pack2(0, fl);
 			if(l == 0) HtopPrev = (st == 0) ? pack2(0, fl) : FLv;
-			uint32_t *rec_base = mat + ax.mat_off + ((size_t)st * T * GL + l) * RW;
+			uint32_t *rec_base = mat + ax.mat_off + (size_t)st * T * GL * RW + l * 4;
 			for(int t = 0; t < T; t++) {
 				const int col_lo = t - 2 * l;
 				int c = 5;
@@ -194,8 +194,8 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 				for(int k = 3 * S; k < RW; k++) rec[k] = 0;
 				uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW);
 #pragma unroll
-				for(int q = 0; q < RW / 4; q++)
-					dst[q] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
+				for(int q = 0; q < RW / 4; q++)      // chunk q of the 8 lanes is one contiguous 128-byte line
+					dst[q * GL] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
 			}
 			if(!lastStripe) __threadfence();   // boundary row visible to lane 0 of the next stripe
 		}
@@ -211,7 +211,8 @@ struct MatView {
 		const int RS = VL * S;
 		const int st = row / RS, r = row - st * RS;
 		const int v = r / S, k = r - v * S;
-		const uint32_t w = __ldcg(base + ((size_t)(st * T + col + v) * GL + (v >> 1)) * RW + m * S + k);
+		const int idx = m * S + k;
+		const uint32_t w = __ldcg(base + (size_t)(st * T + col + v) * GL * RW + ((idx >> 2) * GL + (v >> 1)) * 4 + (idx & 3));
 		return (v & 1) ? hi16(w) : lo16(w);
 	}
 };
@@ -288,9 +289,10 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	int cnt = 0;
 	for(int rix = lane; rix < nrec; rix += 32) {
 		const int l = rix & (GL - 1), t = (rix >> 3) % T, st = (rix >> 3) / T;
-		const uint32_t *rp = mv.base + (size_t)rix * mv.RW + 2 * S;
+		const uint32_t *rp = mv.base + (size_t)(rix >> 3) * GL * mv.RW;
 		for(int k = 0; k < S; k++) {
-			const uint32_t w = __ldcg(rp + k);
+			const int idx = 2 * S + k;
+			const uint32_t w = __ldcg(rp + ((idx >> 2) * GL + l) * 4 + (idx & 3));
 #pragma unroll
 			for(int half = 0; half < 2; half++) {
 				const int v = 2 * l + half;
