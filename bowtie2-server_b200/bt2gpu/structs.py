@@ -30,3 +30,51 @@ assert dp_aln.itemsize == 48 and edit.itemsize == 8 and scoring.itemsize == 2048
 
 EDIT_READ_GAP, EDIT_REF_GAP, EDIT_MM = 1, 2, 3
 INT64_MIN = -(1 << 63)
+
+# ---- FM-index side (include/bt2gpu.h) ----
+read = np.dtype([("rd_off", "<u4"), ("rd_len", "<u4")], align=True)
+seed_job = np.dtype([("read", "<u4"), ("off", "<u2"), ("len", "u1"), ("fw", "u1")], align=True)
+seed_hit = np.dtype([("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"), ("bwops", "<u4")], align=True)
+sweep_result = np.dtype([("top", "<u4", (2,)), ("bot", "<u4", (2,)), ("nedit", "<u2", (2,)),
+                         ("done", "u1", (2,)), ("bwops", "<u4")], align=True)
+onemm_job = np.dtype([("minsc", "<i4"), ("nceil", "<i4"), ("nofw", "u1"), ("norc", "u1"), ("pad", "u1", (2,))], align=True)
+ee_hit = np.dtype([("top", "<u4"), ("bot", "<u4"), ("score", "<i4"), ("pos", "<u2"), ("chr", "u1"),
+                   ("qchr", "u1"), ("fw", "u1"), ("pad", "u1", (3,))], align=True)
+onemm_result = np.dtype([("hit_off", "<u4"), ("nhits", "<u4"), ("bwops", "<u4")], align=True)
+extend_job = np.dtype([("read", "<u4"), ("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"),
+                       ("off", "<u2"), ("len", "u1"), ("fw", "u1")], align=True)
+extend_result = np.dtype([("nlex", "<u2"), ("nrex", "<u2"), ("fmops", "<u4")], align=True)
+
+assert read.itemsize == 8 and seed_job.itemsize == 8 and seed_hit.itemsize == 20
+assert sweep_result.itemsize == 28 and onemm_job.itemsize == 12 and ee_hit.itemsize == 20
+assert onemm_result.itemsize == 12 and extend_job.itemsize == 24 and extend_result.itemsize == 8
+
+
+class IndexDesc(__import__("ctypes").Structure):
+    """bt2gpu_index_desc"""
+    import ctypes as _C
+    _fields_ = [
+        ("ebwt", _C.c_void_p), ("ebwt_bytes", _C.c_uint64), ("offs", _C.c_void_p), ("n_offs", _C.c_uint64),
+        ("ftab", _C.c_void_p), ("eftab", _C.c_void_p), ("fchr", _C.c_uint32 * 5), ("zoff", _C.c_uint32),
+        ("len", _C.c_uint32), ("off_rate", _C.c_int32), ("ftab_chars", _C.c_int32), ("is_fw", _C.c_int32),
+    ]
+
+
+def index_desc(e):
+    """bt2gpu_index_desc over the numpy arrays of an index.EbwtData (keeps them alive via ._keep)."""
+    d = IndexDesc()
+    d.ebwt = e.ebwt.ctypes.data
+    d.ebwt_bytes = e.ebwt.nbytes
+    if e.offs is not None:
+        d.offs = e.offs.ctypes.data
+        d.n_offs = len(e.offs)
+    else:
+        d.offs = None
+        d.n_offs = 0
+    d.ftab = e.ftab.ctypes.data
+    d.eftab = e.eftab.ctypes.data
+    for i in range(5):
+        d.fchr[i] = int(e.fchr[i])
+    d.zoff, d.len, d.off_rate, d.ftab_chars, d.is_fw = e.zoff, e.len, e.off_rate, e.ftab_chars, int(e.fw)
+    d._keep = e
+    return d

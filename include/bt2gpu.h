@@ -155,6 +155,102 @@ int bt2gpu_dp_phase_ms(bt2gpu_ctx *ctx, float *ms3);
 /* DP cells (rows x cols, the bowtie2-dp CUPS numerator bt2_dp.cpp:744) of the staged batch. */
 uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx);
 
+/* ======================================================================== */
+/* ---- FM index (replaces Ebwt's search-side state, bt2_idx.h:2530-2570) --- */
+
+/* One Ebwt as the reference holds it in memory after Ebwt::readIntoMemory
+ * (bt2_io.cpp:131-614), small index (TIndexOffU = uint32_t, 64-byte sides).
+ * The side layout is uploaded verbatim: bytes 0..47 = 192 bases (2 bit each,
+ * base k of a byte at bits 2k..2k+1), bytes 48..63 = u32 occ[A,C,G,T]. */
+typedef struct {
+	const uint8_t  *ebwt;        /* Ebwt::ebwt()      numSides*64 bytes             */
+	uint64_t        ebwt_bytes;
+	const uint32_t *offs;        /* Ebwt::offs()      SA sample, may be NULL (mirror) */
+	uint64_t        n_offs;
+	const uint32_t *ftab;        /* Ebwt::ftab()      4^ftab_chars + 1 entries       */
+	const uint32_t *eftab;       /* Ebwt::eftab()     2*ftab_chars entries           */
+	uint32_t        fchr[5];     /* Ebwt::fchr()                                     */
+	uint32_t        zoff;        /* Ebwt::_zOff                                      */
+	uint32_t        len;         /* EbwtParams::_len                                 */
+	int32_t         off_rate;    /* EbwtParams::_offRate                             */
+	int32_t         ftab_chars;  /* EbwtParams::_ftabChars                           */
+	int32_t         is_fw;       /* Ebwt::fw(): 1 forward index, 0 mirror (.rev)     */
+} bt2gpu_index_desc;
+int  bt2gpu_index_create(int device, const bt2gpu_index_desc *desc, bt2gpu_index **out);
+void bt2gpu_index_destroy(bt2gpu_index *idx);
+/* Bytes of HBM the index occupies. */
+uint64_t bt2gpu_index_bytes(const bt2gpu_index *idx);
+
+/* A read in the pools: bytes 0..4 (A,C,G,T,N), forward strand (Read::patFw);
+ * quality bytes Phred+33 (Read::qual).  The kernels derive patRc/patFwRev/... */
+typedef struct { uint32_t rd_off; uint32_t rd_len; } bt2gpu_read;
+
+/* Stage a batch of reads on the device for the seed-side calls below (replaces the
+ * per-read `const Read&` argument of the SeedAligner entry points). */
+int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool,
+                       size_t pool_len, const bt2gpu_read *reads, size_t nreads);
+
+/* BwtTopBot (aligner_cache.h:68) + the bwops_ this seed cost (aligner_seed.cpp:1906,1999).
+ * topf == botf means "no hit" (then topb/botb are 0). */
+typedef struct { uint32_t topf, botf, topb, botb, bwops; } bt2gpu_seed_hit;
+
+/* One exact seed = one InstantiatedSeed of type SEED_TYPE_EXACT
+ * (aligner_seed.cpp:213-358): window [off, off+len) of the read, strand fw. */
+typedef struct { uint32_t read; uint16_t off; uint8_t len; uint8_t fw; } bt2gpu_seed_job;
+
+/* SeedAligner::searchAllSeeds for exact seeds (aligner_seed.cpp:597-718 ->
+ * startSearchSeedBi :1633 -> searchSeedBi :1854): ftab jump + mapBiLFEx/mapLF1 steps. */
+int bt2gpu_seed_exact_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+                            const bt2gpu_seed_job *jobs, size_t njobs, bt2gpu_seed_hit *out);
+
+/* SeedAligner::exactSweep (aligner_seed.cpp:854-968), both strands of every staged read.
+ * nedit = the reference's nedit[fwi] when the strand stopped; done = stopped because
+ * nedit reached mine_max (then mineFw/mineRc = nedit); otherwise the sweep ran to the end
+ * of the read: mineFw/mineRc = nedit and, if nedit == 0 and bot > top, [top,bot) is the
+ * exact end-to-end hit.  Index 0 = forward read, 1 = reverse complement. */
+typedef struct { uint32_t top[2], bot[2]; uint16_t nedit[2]; uint8_t done[2]; uint32_t bwops; } bt2gpu_sweep_result;
+int bt2gpu_exact_sweep_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, int nofw, int norc,
+                             uint32_t mine_max, bt2gpu_sweep_result *out);
+
+/* SeedAligner::oneMmSearch (aligner_seed.cpp:973-1323).  Per read: minsc,
+ * nceil = sc.nCeil.f(len) and the nofw/norc arguments (the driver derives them per read
+ * from exactSweep's bounds, bt2_search.cpp:3649-3661).  Hits are returned in the
+ * reference's order of hits.add1mmEe / addExactEe* calls, grouped per read
+ * (hit_off/nhits). */
+typedef struct { int32_t minsc; int32_t nceil; uint8_t nofw, norc, pad[2]; } bt2gpu_onemm_job;
+typedef struct {
+	uint32_t top, bot;     /* BW range in the forward index (toprep/botrep)              */
+	int32_t  score;        /* EEHit::score                                               */
+	uint16_t pos;          /* Edit::pos (off5p); 0xffff for an exact hit                 */
+	uint8_t  chr, qchr;    /* Edit::chr = "ACGT"[j], Edit::qchr = "ACGTN"[rdc]           */
+	uint8_t  fw;           /* strand                                                     */
+	uint8_t  pad[3];
+} bt2gpu_ee_hit;
+typedef struct { uint32_t hit_off, nhits, bwops; } bt2gpu_onemm_result;
+int bt2gpu_onemm_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+                       const bt2gpu_onemm_job *jobs, int local, int repex, int rep1mm,
+                       bt2gpu_onemm_result *out, bt2gpu_ee_hit *hits, size_t hit_cap, size_t *nhits);
+
+/* SwDriver::extend (aligner_sw_driver.cpp:299-484): exact extension of a seed hit. */
+typedef struct { uint32_t read; uint32_t topf, botf, topb, botb; uint16_t off; uint8_t len; uint8_t fw; } bt2gpu_extend_job;
+typedef struct { uint16_t nlex, nrex; uint32_t fmops; } bt2gpu_extend_result;
+int bt2gpu_extend_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+                        const bt2gpu_extend_job *jobs, size_t njobs, bt2gpu_extend_result *out);
+
+/* Ebwt::getOffset(row) (bt2_idx.cpp:145-171) == what GroupWalk2S resolves per element
+ * (group_walk.h:1105-1216): LF-walk to the next sampled row, then offs[] gather.
+ * steps[i] (optional) = LF steps walked. */
+int bt2gpu_locate_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const uint32_t *rows, size_t n,
+                        uint32_t *offs_out, uint32_t *steps_out);
+
+/* Device-resident variants for timing: stage jobs once, run the kernel repeatedly. */
+int bt2gpu_seed_exact_stage(bt2gpu_ctx *ctx, const bt2gpu_seed_job *jobs, size_t njobs);
+int bt2gpu_seed_exact_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw);
+int bt2gpu_seed_exact_fetch(bt2gpu_ctx *ctx, bt2gpu_seed_hit *out);
+int bt2gpu_locate_stage(bt2gpu_ctx *ctx, const uint32_t *rows, size_t n);
+int bt2gpu_locate_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw);
+int bt2gpu_locate_fetch(bt2gpu_ctx *ctx, uint32_t *offs_out, uint32_t *steps_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -108,3 +108,155 @@ def compare_with_dump(problems, results, cands, alns, edits, max_aln=8, check_ca
             assert E["cural"] == p["E"]["cural"], (ctx, E, p["E"])
             assert rnd.copy().next_u32() == p["E"]["rnd"], (ctx, "rng at end")
     return len(problems)
+
+
+# ---------------------------------------------------------------------------------------
+# FM-index side: CPU oracle bindings (oracle/fm_oracle.c) and golden comparison
+# ---------------------------------------------------------------------------------------
+from bt2gpu import fmio, index as bt2index  # noqa: E402
+
+
+def load_index_fixture(name):
+    return bt2index.Index.load_npz(os.path.join(GOLDEN, name))
+
+
+class FmOracle:
+    """Same call surface as bt2gpu.lib.FmContext, answered by the C restatement on the CPU."""
+
+    def __init__(self, ix, sc_struct):
+        self.lib = oracle_lib()
+        self.ix = ix
+        self.dfw, self.dbw = structs.index_desc(ix.fw), structs.index_desc(ix.bw)
+        self.sc = sc_struct
+
+    def stage_reads(self, pool):
+        self.pool = pool
+
+    def seed_exact(self, jobs):
+        out = np.zeros(len(jobs), dtype=structs.seed_hit)
+        rc = self.lib.bt2oracle_seed_exact_batch(C.byref(self.dfw), C.byref(self.dbw), _ptr(self.pool.seq),
+                                                 _ptr(self.pool.reads), _ptr(jobs), C.c_size_t(len(jobs)), _ptr(out))
+        assert rc == 0
+        return out
+
+    def exact_sweep(self, nofw=False, norc=False, mine_max=2):
+        out = np.zeros(len(self.pool), dtype=structs.sweep_result)
+        rc = self.lib.bt2oracle_exact_sweep_batch(C.byref(self.dfw), _ptr(self.pool.seq), _ptr(self.pool.reads),
+                                                  C.c_size_t(len(self.pool)), C.c_int(nofw), C.c_int(norc),
+                                                  C.c_uint32(mine_max), _ptr(out))
+        assert rc == 0
+        return out
+
+    def one_mm(self, jobs, local=False, repex=True, rep1mm=True, hit_cap=None):
+        n = len(self.pool)
+        hit_cap = hit_cap or 64 * n + 1024
+        out = np.zeros(n, dtype=structs.onemm_result)
+        hits = np.zeros(hit_cap, dtype=structs.ee_hit)
+        nh = C.c_size_t(0)
+        rc = self.lib.bt2oracle_onemm_batch(
+            C.byref(self.dfw), C.byref(self.dbw), _ptr(self.sc), _ptr(self.pool.seq), _ptr(self.pool.qual),
+            _ptr(self.pool.reads), C.c_size_t(n), _ptr(jobs), C.c_int(local),
+            C.c_int(repex), C.c_int(rep1mm), _ptr(out), _ptr(hits), C.c_size_t(hit_cap), C.byref(nh))
+        assert rc == 0, "oracle hit pool overflow"
+        return out, hits[: nh.value]
+
+    def extend(self, jobs):
+        out = np.zeros(len(jobs), dtype=structs.extend_result)
+        rc = self.lib.bt2oracle_extend_batch(C.byref(self.dfw), C.byref(self.dbw), _ptr(self.pool.seq),
+                                             _ptr(self.pool.reads), _ptr(jobs), C.c_size_t(len(jobs)), _ptr(out))
+        assert rc == 0
+        return out
+
+    def locate(self, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        offs = np.zeros(len(rows), dtype=np.uint32)
+        steps = np.zeros(len(rows), dtype=np.uint32)
+        rc = self.lib.bt2oracle_locate_batch(C.byref(self.dfw), _ptr(rows), C.c_size_t(len(rows)), _ptr(offs), _ptr(steps))
+        assert rc == 0
+        return offs, steps
+
+
+def compare_fm_with_dump(eng, recs, sc, local, seed_len, interval_fn):
+    """Drive `eng` (FmOracle or the CUDA FmContext) with the reads of a ref_seed_dump golden and
+    assert bit-exact equality with everything the reference printed.  Returns #checks."""
+    pool = fmio.ReadPool([r["seq"] for r in recs], [r["qual"] for r in recs])
+    eng.stage_reads(pool)
+    n = len(recs)
+    checks = 0
+    # ---- exactSweep ----
+    sw = eng.exact_sweep(False, False, 2)
+    for i, r in enumerate(recs):
+        nelt, mine_fw, mine_rc, ft, fb, rt, rb, bwops = r["SW"]
+        s = sw[i]
+        ctx = ("sweep", i)
+        assert int(s["nedit"][0]) == mine_fw and int(s["nedit"][1]) == mine_rc, (ctx, s, r["SW"])
+        got_nelt = 0
+        for k, (t, b) in enumerate(((ft, fb), (rt, rb))):
+            hit = (not s["done"][k]) and s["nedit"][k] == 0 and s["bot"][k] > s["top"][k]
+            if hit:
+                assert (int(s["top"][k]), int(s["bot"][k])) == (t, b), (ctx, k, s, r["SW"])
+                got_nelt += int(s["bot"][k]) - int(s["top"][k])
+            else:
+                assert (t, b) == (0, 0), (ctx, k, s, r["SW"])
+        assert got_nelt == nelt and int(s["bwops"]) == bwops, (ctx, s, r["SW"])
+        checks += 1
+    # ---- oneMmSearch ----
+    jobs = np.zeros(n, dtype=structs.onemm_job)
+    for i, r in enumerate(recs):
+        jobs["minsc"][i] = r["M1"][7]
+        jobs["nceil"][i] = sc.nceil(len(r["seq"]))
+    res, hits = eng.one_mm(jobs, local, True, True)
+    for i, r in enumerate(recs):
+        ret, nmm, ft, fb, rt, rb, bwops, _ = r["M1"]
+        h = hits[int(res["hit_off"][i]): int(res["hit_off"][i]) + int(res["nhits"][i])]
+        mm = [(int(x["fw"]), int(x["top"]), int(x["bot"]), int(x["score"]), int(x["pos"]), chr(x["chr"]), chr(x["qchr"]))
+              for x in h if x["pos"] != 0xFFFF]
+        ex = {int(x["fw"]): (int(x["top"]), int(x["bot"])) for x in h if x["pos"] == 0xFFFF}
+        ctx = ("onemm", i)
+        assert mm == r["H"], (ctx, mm, r["H"])
+        assert ex.get(1, (0, 0)) == (ft, fb) and ex.get(0, (0, 0)) == (rt, rb), (ctx, ex, r["M1"])
+        assert int(res["bwops"][i]) == bwops, (ctx, int(res["bwops"][i]), bwops)
+        checks += 1
+    # ---- exact seeds ----
+    sjobs, per_read = fmio.instantiate_exact_seeds(pool, seed_len, interval_fn)
+    sh = eng.seed_exact(sjobs)
+    by_key = {(int(j["read"]), int(j["fw"]), int(j["off"])): k for k, j in enumerate(sjobs)}
+    bw_tot = np.zeros(n, dtype=np.int64)
+    np.add.at(bw_tot, sjobs["read"].astype(np.int64), sh["bwops"].astype(np.int64))
+    xjobs, xexp, lrows, lexp = [], [], [], []
+    for i, r in enumerate(recs):
+        sd = r["SD"]
+        assert sd[0] == seed_len and sd[1] == per_read[i][0], (i, sd, per_read[i])
+        if sd[2] == 0:
+            assert not any(int(j["read"]) == i for j in sjobs[:0]), i
+            continue
+        assert sd[2] == per_read[i][1] and sd[3] == int(bw_tot[i]), ("seeds", i, sd, per_read[i], int(bw_tot[i]))
+        for fw, offidx, off, ranges in r["S"]:
+            k = by_key.get((i, fw, off))
+            if k is None:
+                assert ranges == [], ("seed with N", i, fw, off)
+                continue
+            g = sh[k]
+            got = [] if g["topf"] == g["botf"] else [(int(g["topf"]), int(g["botf"]), int(g["topb"]), int(g["botb"]))]
+            assert got == ranges, ("seed", i, fw, off, got, ranges)
+            checks += 1
+        for x in r["X"]:
+            xjobs.append((i,) + x[3:7] + (x[1], x[2], x[0]))
+            xexp.append(x[7:10])
+        for row, off in r["L"]:
+            lrows.append(row)
+            lexp.append(off)
+    xj = np.zeros(len(xjobs), dtype=structs.extend_job)
+    if xjobs:
+        a = np.array(xjobs, dtype=np.int64)
+        for c, name in enumerate(("read", "topf", "botf", "topb", "botb", "off", "len", "fw")):
+            xj[name] = a[:, c]
+    xr = eng.extend(xj)
+    for k in range(len(xjobs)):
+        got = (int(xr["nlex"][k]), int(xr["nrex"][k]), int(xr["fmops"][k]))
+        assert got == tuple(xexp[k]), ("extend", xjobs[k], got, xexp[k])
+        checks += 1
+    offs, _ = eng.locate(np.array(lrows, dtype=np.uint32))
+    assert [int(x) for x in offs] == lexp, "locate"
+    checks += len(lrows)
+    return checks
