@@ -16,6 +16,10 @@ SYMBOLS = [
     "bt2gpu_ctx_destroy", "bt2gpu_ctx_sync", "bt2gpu_ctx_stream", "bt2gpu_ctx_launches",
     "bt2gpu_scoring_set", "bt2gpu_dp_align_batch", "bt2gpu_dp_stage", "bt2gpu_dp_run",
     "bt2gpu_dp_fetch", "bt2gpu_dp_staged_cells", "bt2gpu_dp_phase_ms",
+    "bt2gpu_index_create", "bt2gpu_index_destroy", "bt2gpu_index_bytes", "bt2gpu_reads_stage",
+    "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
+    "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
+    "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch",
 ]
 
 _lib = None
@@ -35,6 +39,10 @@ def load():
         lib.bt2gpu_ctx_stream.restype = C.c_void_p
         lib.bt2gpu_ctx_launches.restype = C.c_uint64
         lib.bt2gpu_dp_staged_cells.restype = C.c_uint64
+        lib.bt2gpu_index_bytes.restype = C.c_uint64
+        lib.bt2gpu_index_bytes.argtypes = [C.c_void_p]
+        lib.bt2gpu_index_destroy.argtypes = [C.c_void_p]
+        lib.bt2gpu_index_destroy.restype = None
         for name in SYMBOLS:
             getattr(lib, name)
         _lib = lib
@@ -139,3 +147,107 @@ class Context:
         self.dp_run(7)
         r = self.dp_fetch()
         return r[0], r[1], r[2], r[3]
+
+    # ---- FM index (seed side) ---------------------------------------------------------------
+    def stage_reads(self, pool):
+        """bt2gpu_reads_stage: pool = fmio.ReadPool (replaces the per-call `const Read&`)."""
+        self._pool_n = len(pool)
+        _check(self.lib.bt2gpu_reads_stage(self._h, _ptr(pool.seq), _ptr(pool.qual), C.c_size_t(len(pool.seq)),
+                                           _ptr(pool.reads), C.c_size_t(len(pool))))
+
+    def bind_index(self, dev_index):
+        """Forward + mirror DeviceIndex pair used by the seed-side calls."""
+        self._ix = dev_index
+
+    def seed_exact(self, jobs):
+        out = np.zeros(len(jobs), dtype=structs.seed_hit)
+        _check(self.lib.bt2gpu_seed_exact_batch(self._h, self._ix.fw, self._ix.bw, _ptr(jobs),
+                                                C.c_size_t(len(jobs)), _ptr(out)))
+        return out
+
+    def seed_exact_stage(self, jobs):
+        self._n_seed = len(jobs)
+        _check(self.lib.bt2gpu_seed_exact_stage(self._h, _ptr(jobs), C.c_size_t(len(jobs))))
+
+    def seed_exact_run(self):
+        _check(self.lib.bt2gpu_seed_exact_run(self._h, self._ix.fw, self._ix.bw))
+
+    def seed_exact_fetch(self, out=None):
+        out = np.zeros(self._n_seed, dtype=structs.seed_hit) if out is None else out
+        _check(self.lib.bt2gpu_seed_exact_fetch(self._h, _ptr(out)))
+        return out
+
+    def exact_sweep(self, nofw=False, norc=False, mine_max=2):
+        out = np.zeros(self._pool_n, dtype=structs.sweep_result)
+        _check(self.lib.bt2gpu_exact_sweep_batch(self._h, self._ix.fw, C.c_int(nofw), C.c_int(norc),
+                                                 C.c_uint32(mine_max), _ptr(out)))
+        return out
+
+    def one_mm(self, jobs, local=False, repex=True, rep1mm=True, hit_cap=None):
+        n = self._pool_n
+        hit_cap = hit_cap or 64 * n + 1024
+        out = np.zeros(n, dtype=structs.onemm_result)
+        hits = np.zeros(hit_cap, dtype=structs.ee_hit)
+        nh = C.c_size_t(0)
+        _check(self.lib.bt2gpu_onemm_batch(self._h, self._ix.fw, self._ix.bw, _ptr(jobs), C.c_int(local),
+                                           C.c_int(repex), C.c_int(rep1mm), _ptr(out), _ptr(hits),
+                                           C.c_size_t(hit_cap), C.byref(nh)))
+        return out, hits[: nh.value]
+
+    def extend(self, jobs):
+        out = np.zeros(len(jobs), dtype=structs.extend_result)
+        _check(self.lib.bt2gpu_extend_batch(self._h, self._ix.fw, self._ix.bw, _ptr(jobs),
+                                            C.c_size_t(len(jobs)), _ptr(out)))
+        return out
+
+    def locate(self, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        offs = np.zeros(len(rows), dtype=np.uint32)
+        steps = np.zeros(len(rows), dtype=np.uint32)
+        _check(self.lib.bt2gpu_locate_batch(self._h, self._ix.fw, _ptr(rows), C.c_size_t(len(rows)),
+                                            _ptr(offs), _ptr(steps)))
+        return offs, steps
+
+    def locate_stage(self, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        self._n_rows = len(rows)
+        _check(self.lib.bt2gpu_locate_stage(self._h, _ptr(rows), C.c_size_t(len(rows))))
+
+    def locate_run(self):
+        _check(self.lib.bt2gpu_locate_run(self._h, self._ix.fw))
+
+    def locate_fetch(self):
+        offs = np.zeros(self._n_rows, dtype=np.uint32)
+        steps = np.zeros(self._n_rows, dtype=np.uint32)
+        _check(self.lib.bt2gpu_locate_fetch(self._h, _ptr(offs), _ptr(steps)))
+        return offs, steps
+
+
+class DeviceIndex:
+    """Forward + mirror Ebwt resident in HBM (bt2gpu_index_create x2); immutable, shareable by
+    every Context of the same device (mirrors the shared read-only Ebwt objects of
+    bt2_search.cpp:4870-4892)."""
+
+    def __init__(self, ix, device=0):
+        self.lib = load()
+        self.fw, self.bw = C.c_void_p(0), C.c_void_p(0)
+        for e, h in ((ix.fw, self.fw), (ix.bw, self.bw)):
+            d = structs.index_desc(e)
+            _check(self.lib.bt2gpu_index_create(C.c_int(device), C.byref(d), C.byref(h)))
+        self.device = device
+
+    @property
+    def nbytes(self):
+        return int(self.lib.bt2gpu_index_bytes(self.fw)) + int(self.lib.bt2gpu_index_bytes(self.bw))
+
+    def close(self):
+        for h in (self.fw, self.bw):
+            if h:
+                self.lib.bt2gpu_index_destroy(h)
+        self.fw, self.bw = C.c_void_p(0), C.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

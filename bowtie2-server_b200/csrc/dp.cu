@@ -703,6 +703,8 @@ static int choose_class(int nrow) {
 	return best;
 }
 
+int fm_set_scoring(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc);   // fm.cu
+
 } // namespace bt2
 
 using namespace bt2;
@@ -717,6 +719,7 @@ extern "C" int bt2gpu_scoring_set(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc) {
 	BT2_CUDA(cudaMemcpyToSymbolAsync(c_mmpens, sc->mmpens, sizeof(c_mmpens), 0, cudaMemcpyHostToDevice, ctx->stream));
 	BT2_CUDA(cudaMemcpyToSymbolAsync(c_npens, sc->npens, sizeof(c_npens), 0, cudaMemcpyHostToDevice, ctx->stream));
 	BT2_CUDA(cudaMemcpyToSymbolAsync(c_sc, &c, sizeof(c), 0, cudaMemcpyHostToDevice, ctx->stream));
+	if(fm_set_scoring(ctx, sc)) return 1;
 	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
 	return 0;
 }
