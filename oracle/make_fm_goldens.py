@@ -89,6 +89,8 @@ def main():
     if not index.exists(lam):
         build_index(os.path.join(REF, "example/reference/lambda_virus.fa"), lam)
     index.Index.load(lam).save_npz(os.path.join(GOLD, "lambda_index.npz"))
+    import shutil
+    shutil.copyfile(os.path.join(REF, "example/reference/lambda_virus.fa"), os.path.join(GOLD, "lambda.fa"))
     ex = os.path.join(REF, "example/reads")
     dump(lam, os.path.join(ex, "reads_1.fq"), os.path.join(GOLD, "fm_lambda_r1.txt"), ["--limit", "200"])
     dump(lam, os.path.join(ex, "longreads.fq"), os.path.join(GOLD, "fm_lambda_long.txt"), ["--limit", "40"])
@@ -106,6 +108,7 @@ def main():
     rep = os.path.join(IDX, "rep")
     build_index(fa, rep)
     index.Index.load(rep).save_npz(os.path.join(GOLD, "rep_index.npz"))
+    shutil.copyfile(fa, os.path.join(GOLD, "rep.fa"))     # inputs of tests/test_index_build.py
     fq = os.path.join(IDX, "rep_reads.fq")
     with open(fq, "w") as fh:
         fh.write(simulate_reads(rng, seqs, 240, (30, 160)))
