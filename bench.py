@@ -1,13 +1,22 @@
 #!/usr/bin/env python3
 """bench.py -- hot-path throughput of the B200 build vs the reference's CPU path.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                  [--batch B] [--genome-mbp G]
 
 A "step" is one pass of the alignment hot path over one batch of synthetic 150 bp reads
-(config.workload).  Prints ONE JSON line (contract in the task statement): `value` = reads/s
-with inputs resident in HBM, `e2e` = the same through the C ABI with pinned HOST buffers
-(H2D + D2H inside the timed region), `roofline` for the dominant kernel, `cpu_baseline` =
-the reference's own SwAligner (oracle/_ref/ref_dp_dump --bench) on a bounded sample.
+(simulate.pl model) against an FM index of a random genome (C3-scale, 256 Mbp by default):
+exactSweep -> exact seeds (-L 22, interval S,1,1.15) -> extend -> locate -> one
+seed-extension DP window per read (fill + gather + nextAlignment loop).  The index is built
+at set-up by bt2gpu.build (byte-identical to bowtie2-build-s output, tests/test_index_build.py)
+and written to /tmp so the reference arm loads the same files.
+
+Prints ONE JSON line (contract in the task statement): `value` = reads/s over the device time
+of the step's kernels (CUDA events on the launching stream, inputs resident in HBM when each
+timed region starts), `e2e` = the same step through the C ABI with HOST buffers (H2D, D2H and
+the batch-level host glue inside the timed region), `roofline` for the dominant kernel
+(`rooflines` lists every kernel), `cpu_baseline` = the unmodified reference (SeedAligner,
+SwDriver::extend, Ebwt::getOffset, SwAligner via oracle/_ref harnesses) on a bounded sample.
 """
 import argparse
 import json
@@ -25,38 +34,47 @@ import numpy as np  # noqa: E402
 
 RDLEN = 150
 MAXGAP = 15
-GENOME = 1 << 24
+SEED_LEN = 22
 METRIC = "aligned reads/sec (2x150 end-to-end)"
 UNIT = "reads/s"
 
 
-def make_batch(seed, nreads):
-    from bt2gpu import synth, scoring
+def workload_name(batch, gmbp):
+    return ("synthetic 150 bp reads (simulate.pl model) vs FM index of a random %d Mbp genome: exactSweep + "
+            "exact seeds (-L 22, S,1,1.15) + extend + locate + one seed-extension DP window (150 x %d, "
+            "end-to-end u8: fill + gather + nextAlignment loop) per read, %d reads per step per GPU"
+            % (gmbp, RDLEN + 4 * MAXGAP, batch))
+
+
+def make_genome(seed, gmbp):
     rng = np.random.default_rng(seed)
-    sc = scoring.Scoring(local=False)
-    genome = synth.random_genome(rng, GENOME)
-    return sc, synth.dp_extend_batch(rng, genome, nreads, RDLEN, sc, MAXGAP)
+    return rng.integers(0, 4, size=gmbp << 20, dtype=np.uint8)
 
 
-def workload_name(batch):
-    return ("synthetic 2x150-style reads (simulate.pl model, random %d Mbp genome), one seed-extension "
-            "DP window (150 x %d, end-to-end u8 path: fill + gather + nextAlignment loop) per read, "
-            "%d reads per step per GPU" % (GENOME >> 20, RDLEN + 4 * MAXGAP, batch))
+def get_index(genome, seed, gmbp, need_files):
+    """Build (or reload from /tmp) the index of `genome`; returns (Index, base path or None)."""
+    from bt2gpu import build, index
+    base = os.path.join(tempfile.gettempdir(), "bt2gpu_bench_idx_%d_%d" % (gmbp, seed))
+    if index.exists(base) and os.path.exists(base + ".ok"):
+        return index.Index.load(base), base
+    ix, extras = build.build_index([genome], ["chr1"])
+    if need_files:
+        build.write_index(ix, extras, base)
+        open(base + ".ok", "w").write("ok")
+        return ix, base
+    return ix, None
 
 
-def ref_bench(problem_file, threads, repeat=1):
-    exe = os.path.join(ROOT, "oracle", "_ref", "ref_dp_dump")
-    if not os.path.exists(exe):
-        return None
-    tot_s, out = 0.0, None
-    for _ in range(repeat):
-        out = json.loads(subprocess.check_output([exe, "--problems", problem_file, "--bench",
-                                                  "--threads", str(threads)]).decode())
-        tot_s += out["seconds"]
-    out["seconds"] = tot_s
-    out["problems"] *= repeat
-    out["cells"] *= repeat
-    return out
+def make_reads(seed, genome, n):
+    from bt2gpu import synth
+    rng = np.random.default_rng(seed)
+    reads, quals, pos, _ = synth.simulate_reads(rng, genome, n, RDLEN)
+    # strand coin-flip as simulate.pl does: half of the reads are given reverse-complemented
+    rc = rng.random(n) < 0.5
+    comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
+    reads[rc] = comp[reads[rc][:, ::-1]]
+    quals[rc] = quals[rc][:, ::-1]
+    return np.ascontiguousarray(reads), np.ascontiguousarray(quals), pos, ~rc
 
 
 class ClockSampler(threading.Thread):
@@ -90,61 +108,109 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons)}
 
 
+# ---------------------------------------------------------------------------------------------
+# reference arm: the unmodified reference on the host cores
+# ---------------------------------------------------------------------------------------------
+def write_fastq(path, reads, quals):
+    c2a = np.frombuffer(b"ACGTN", dtype=np.uint8)
+    with open(path, "wb") as fh:
+        for i in range(len(reads)):
+            fh.write(b"@r%d\n" % i + c2a[reads[i]].tobytes() + b"\n+\n" + quals[i].tobytes() + b"\n")
+
+
+def reference_step(base, genome, reads, quals, pos, fw, threads, td):
+    """One bounded step through the reference's own code: ref_seed_dump --bench (exactSweep,
+    searchAllSeeds, extend, getOffset) + ref_dp_dump --bench (SwAligner) with `threads` threads.
+    Returns (seconds, detail)."""
+    from bt2gpu import synth, scoring, structs
+    bin_ = os.path.join(ROOT, "oracle", "_ref")
+    fq = os.path.join(td, "reads.fq")
+    if not os.path.exists(fq):
+        write_fastq(fq, reads, quals)
+    o1 = json.loads(subprocess.check_output([os.path.join(bin_, "ref_seed_dump"), "--index", base, "--reads", fq,
+                                             "--bench", "--threads", str(threads)]).decode())
+    pf = os.path.join(td, "p.txt")
+    if not os.path.exists(pf):
+        sc = scoring.Scoring(local=False)
+        n = len(reads)
+        comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
+        orient = np.where(fw[:, None], reads, comp[reads[:, ::-1]])
+        oq = np.where(fw[:, None], quals, quals[:, ::-1])
+        ncol = RDLEN + 4 * MAXGAP
+        refl = pos - 2 * MAXGAP
+        cols = refl[:, None] + np.arange(ncol + 1)[None, :]
+        G = len(genome)
+        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
+        jobs = np.zeros(n, dtype=structs.dp_job)
+        jobs["rd_off"] = np.arange(n, dtype=np.int64) * RDLEN
+        jobs["rd_len"] = RDLEN
+        jobs["rf_off"] = np.arange(n, dtype=np.int64) * (ncol + 1)
+        jobs["ncol"] = ncol
+        jobs["minsc"] = sc.score_min.f_int(RDLEN)
+        jobs["nceil"] = sc.nceil(RDLEN)
+        jobs["refl"] = refl
+        jobs["corel"], jobs["corer"] = MAXGAP, 3 * MAXGAP
+        jobs["fw"] = 1          # the window is framed for the oriented read; '+' keeps it as given
+        jobs["enable8"] = 1
+        synth.problems_to_plines(orient.reshape(-1), oq.reshape(-1), (1 << codes).astype(np.uint8).reshape(-1), jobs, pf)
+    o2 = json.loads(subprocess.check_output([os.path.join(bin_, "ref_dp_dump"), "--problems", pf, "--bench",
+                                             "--threads", str(threads)]).decode())
+    return o1["seconds"] + o2["seconds"], {"seed_s": o1["seconds"], "dp_s": o2["seconds"],
+                                           "lf_steps_per_s": o1["lf_steps_per_s"],
+                                           "gcups": o2["cells"] / o2["seconds"] / 1e9}
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation (SwAligner) on the host cores."""
     if rank != 0:
         return
     ncores = os.cpu_count() or 1
-    sample = min(args.batch, 40000)
-    sc, (seq, qual, win, jobs) = make_batch(args.seed, sample)
-    from bt2gpu import synth
+    sample = min(args.batch, args.cpu_sample)
+    genome = make_genome(args.seed, args.genome_mbp)
+    ix, base = get_index(genome, args.seed, args.genome_mbp, True)
+    reads, quals, pos, fw = make_reads(args.seed + 7, genome, sample)
     with tempfile.TemporaryDirectory() as td:
-        pf = os.path.join(td, "p.txt")
-        synth.problems_to_plines(seq, qual, win, jobs, pf)
         for _ in range(args.warmup):
-            ref_bench(pf, ncores)
-        t = 0.0
+            reference_step(base, genome, reads, quals, pos, fw, ncores, td)
+        t, det = 0.0, None
         for _ in range(args.steps):
-            t += ref_bench(pf, ncores)["seconds"]
+            s, det = reference_step(base, genome, reads, quals, pos, fw, ncores, td)
+            t += s
     val = sample * args.steps / t
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16",
-            "data": "synthetic", "config": {"workload": workload_name(args.batch),
-                                            "sample_per_step": sample},
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/i16/u32",
+            "data": "synthetic", "config": {"workload": workload_name(args.batch, args.genome_mbp),
+                                            "sample_per_step": sample, "detail": det},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": ncores, "kind": "reference",
-                             "sample": "%d reads per step through the unmodified reference SwAligner "
-                                       "(oracle/_ref/ref_dp_dump --bench)" % sample},
+                             "sample": "%d reads per step through the unmodified reference (oracle/_ref/ref_seed_dump "
+                                       "--bench + ref_dp_dump --bench, %d threads)" % (sample, ncores)},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from bt2gpu import lib, structs
+    from bt2gpu import lib, scoring, pipeline
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device and the product has no CPU path")
     torch.cuda.set_device(local_rank)
+    genome = make_genome(args.seed, args.genome_mbp)          # same genome / index on every rank (replicated)
+    if world > 1 and rank != 0:
+        dist.barrier()                                        # rank 0 builds and writes the files first
+    ix, base = get_index(genome, args.seed, args.genome_mbp, world > 1)
+    if world > 1 and rank == 0:
+        dist.barrier()
+    torch.cuda.empty_cache()
     ctx = lib.Context(local_rank)
-    sc, (seq, qual, win, jobs) = make_batch(args.seed + 1000 * rank, args.batch)
-    ctx.set_scoring(sc)
-    n = len(jobs)
-    max_aln = 2
-    cand_cap, edit_cap = 256 * n, 64 * n
-
-    def pinned(a):
-        t = torch.empty(a.nbytes, dtype=torch.uint8, pin_memory=True)
-        v = t.numpy().view(a.dtype)
-        v[...] = a
-        return t, v
-    keep = [pinned(x) for x in (seq, qual, win, jobs)]
-    hseq, hqual, hwin, hjobs = [k[1] for k in keep]
-    out = (np.zeros(n, dtype=structs.dp_result), None, np.zeros(n * max_aln, dtype=structs.dp_aln),
-           np.zeros(edit_cap, dtype=structs.edit))
-    okeep = [pinned(out[0]), pinned(out[2]), pinned(out[3])]
-    out = (okeep[0][1], None, okeep[1][1], okeep[2][1])
-    h2d = int(hseq.nbytes + hqual.nbytes + hwin.nbytes + hjobs.nbytes)
+    dix = lib.DeviceIndex(ix, local_rank)
+    sc = scoring.Scoring(local=False)
+    hp = pipeline.HotPath(ctx, dix, genome, sc, seed_len=SEED_LEN, maxgap=MAXGAP, max_aln=2)
+    reads, quals, pos, fw = make_reads(args.seed + 7 + 1000 * rank, genome, args.batch)   # each rank its own shard
+    n = len(reads)
 
     def barrier():
         if world > 1:
@@ -152,96 +218,103 @@ def run_ours(args, rank, world, local_rank):
         ctx.sync()
         torch.cuda.synchronize()
 
-    # ---------------- device-resident: kernels only ----------------
-    ctx.dp_stage(hseq, hqual, hwin, hjobs, max_aln=max_aln, cand_cap=cand_cap, edit_cap=edit_cap)
-    cells = ctx.dp_cells()
     for _ in range(args.warmup):
-        ctx.dp_run(7)
+        hp.step(reads, quals)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = ctx.launches
-    phase = np.zeros(3)
+    kms = {}
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ctx.dp_run(7)
-        phase += np.array(ctx.dp_phase_ms())      # CUDA events on the launching stream
-    barrier()
-    wall_dev = time.perf_counter() - t0
-    launches = ctx.launches - l0
-    dev_ms = float(phase.sum())                   # device time of the K steps
-    res = ctx.dp_fetch(want_cands=False, out=out)
-    d2h = int(out[0].nbytes + out[2].nbytes + res[5] * structs.edit.itemsize)
-    naln = int(out[0]["naln"].sum())
-
-    # ---------------- end to end through the C ABI (host buffers) ----------------
-    for _ in range(max(1, args.warmup // 2)):
-        ctx.dp_stage(hseq, hqual, hwin, hjobs, max_aln=max_aln, cand_cap=cand_cap, edit_cap=edit_cap)
-        ctx.dp_run(7)
-        ctx.dp_fetch(want_cands=False, out=out)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        ctx.dp_stage(hseq, hqual, hwin, hjobs, max_aln=max_aln, cand_cap=cand_cap, edit_cap=edit_cap)
-        ctx.dp_run(7)
-        ctx.dp_fetch(want_cands=False, out=out)
+        hp.step(reads, quals)
+        for k, v in hp.kernel_ms.items():
+            kms[k] = kms.get(k, 0.0) + v
     barrier()
     wall_e2e = time.perf_counter() - t0
+    launches = ctx.launches - l0
     sampler.stop_flag = True
     sampler.join()
+    cnt = hp.counters
+    phases = ("sweep", "seed", "extend", "locate", "dp")
+    dev_ms = sum(kms[k] for k in phases)
+    # sanity: the located diagonal of an aligned read is its simulated origin (SNP/indel shifts aside)
+    L = hp.last
+    ok = np.abs(L["start"] - pos[L["rid"]]) <= 64
+    frac_true = float(ok.mean()) if len(ok) else 0.0
+    probe = ctx.gather_probe("fw", 1 << 27)
 
-    # max over ranks
-    t = torch.tensor([dev_ms, wall_e2e, wall_dev], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, wall_e2e], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, wall_e2e, wall_dev = [float(x) for x in t.tolist()]
+    dev_ms, wall_e2e = [float(x) for x in t.tolist()]
     if rank != 0:
         return
     total_reads = n * world * args.steps
     value = total_reads / (dev_ms / 1e3)
     e2e = total_reads / wall_e2e
-    # roofline of the dominant kernel (k_dp_fill): algorithmic bytes = the E, F and H value of every
-    # cell the reference's fill also stores (SSEMatrix, 3 x 1 byte in the u8 path) per launch
-    fill_ms = float(phase[0]) / args.steps
     peaks = {}
     pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(pk):
         peaks = json.load(open(pk))
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    alg_bytes = 3.0 * cells
-    achieved = alg_bytes / (fill_ms / 1e3) / 1e9
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    K = args.steps
+
+    def rl(kernel, alg_bytes, ms, extra=None):
+        a = alg_bytes / (ms / 1e3) / 1e9 if ms > 0 else 0.0
+        d = {"bound": "hbm", "kernel": kernel, "achieved": a, "peak": hbm, "unit": "GB/s", "frac": a / hbm,
+             "traffic": None, "ms": ms}
+        d.update(extra or {})
+        return d
+    # algorithmic bytes per launch: 64 B per distinct BWT side + 16 B of ftab per seed;
+    # 64 B per LF step (+4 B offs) in locate; 64 B per side in sweep/extend (bwops counts sides);
+    # E, F, H of every DP cell (3 B/cell in the u8 path) for the fill
+    rls = [
+        rl("k_seed_exact", 64.0 * cnt["seed_sides"] + 16.0 * cnt["seeds"], kms["seed"] / K,
+           {"lf_steps_per_s": cnt["seed_bwops"] / (kms["seed"] / K / 1e3), "random_gather_peak_gbs": probe,
+            "frac_of_random_gather": (64.0 * cnt["seed_sides"] / (kms["seed"] / K / 1e3) / 1e9) / probe}),
+        rl("k_exact_sweep", 64.0 * cnt["sweep_bwops"], kms["sweep"] / K,
+           {"lf_steps_per_s": cnt["sweep_bwops"] / (kms["sweep"] / K / 1e3), "random_gather_peak_gbs": probe}),
+        rl("k_extend", 64.0 * cnt["extend_fmops"], kms["extend"] / K),
+        rl("k_locate", 68.0 * cnt["locate_steps"] + 4.0 * cnt["locate_rows"], kms["locate"] / K),
+        rl("k_dp_fill", 3.0 * cnt["dp_cells"], kms["dp_fill"] / K,
+           {"gcups": cnt["dp_cells"] / (kms["dp_fill"] / K / 1e3) / 1e9}),
+        rl("k_dp_backtrace", 0.0, kms["dp_backtrace"] / K),
+        rl("k_dp_gather+sort", 0.0, kms["dp_gather"] / K),
+    ]
+    dominant = max(rls, key=lambda r: r["ms"])
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "int16", "data": "synthetic",
-        "config": {"workload": workload_name(args.batch), "l2": "per-step working set (inputs + E/F/H "
-                   "stream, >10 GB) far exceeds the 126 MB L2", "max_aln": max_aln,
-                   "aligned_per_step": naln, "peak_source": "measured" if peaks else "fallback"},
-        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": dev_ms / K, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8/i16/u32", "data": "synthetic",
+        "config": {"workload": workload_name(args.batch, args.genome_mbp),
+                   "l2": "index %.0f MB + per-step E/F/H stream (>10 GB) exceed the 126 MB L2" % (dix.nbytes / 1e6),
+                   "index_bytes": dix.nbytes, "counters": cnt, "located_at_origin_frac": frac_true,
+                   "peak_source": "measured" if peaks else "fallback"},
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": cnt["h2d_bytes"], "d2h_bytes_per_step": cnt["d2h_bytes"]},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_dp_fill", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
-                     "gcups": cells / (fill_ms / 1e3) / 1e9, "fill_ms": fill_ms,
-                     "phase_ms": [float(x) / args.steps for x in phase]},
+        "roofline": dominant, "rooflines": rls,
+        "phase_ms": {k: v / K for k, v in kms.items()},
         "clocks": sampler.summary(),
-        "wall_s_device_loop": wall_dev,
     }
-    # CPU baseline: the unmodified reference SwAligner on the box's host cores, bounded sample
-    sample = min(n, 40000)
-    ncores = os.cpu_count() or 1
-    from bt2gpu import synth
-    with tempfile.TemporaryDirectory() as td:
-        pf = os.path.join(td, "p.txt")
-        synth.problems_to_plines(seq, qual, win, jobs[:sample], pf)
-        rb = ref_bench(pf, ncores, repeat=3)
-    if rb is not None:
-        line["cpu_baseline"] = {"value": rb["problems"] / rb["seconds"], "unit": UNIT, "cores": ncores,
-                                "kind": "reference", "gcups": rb["cells"] / rb["seconds"] / 1e9,
-                                "sample": "%d reads x3 through the unmodified reference SwAligner "
-                                          "(oracle/_ref/ref_dp_dump --bench, %d threads)" % (sample, ncores)}
-    else:
-        line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
-                                "sample": "oracle/_ref not built"}
+    # CPU baseline on rank 0 at N=1: the unmodified reference on the host cores, bounded sample
+    if world == 1 and not args.no_cpu_baseline:
+        ncores = os.cpu_count() or 1
+        sample = min(n, args.cpu_sample)
+        if base is None:
+            from bt2gpu import build
+            base = os.path.join(tempfile.gettempdir(), "bt2gpu_bench_idx_%d_%d" % (args.genome_mbp, args.seed))
+            ix2, extras = ix, {"recs": [(0, len(genome), 1)], "joined": genome}
+            build.write_index(ix2, extras, base)
+            open(base + ".ok", "w").write("ok")
+        try:
+            with tempfile.TemporaryDirectory() as td:
+                s, det = reference_step(base, genome, reads[:sample], quals[:sample], pos[:sample], fw[:sample], ncores, td)
+            line["cpu_baseline"] = {"value": sample / s, "unit": UNIT, "cores": ncores, "kind": "reference", "detail": det,
+                                    "sample": "%d reads through the unmodified reference (oracle/_ref/ref_seed_dump --bench + "
+                                              "ref_dp_dump --bench, %d threads)" % (sample, ncores)}
+        except Exception as e:   # oracle/_ref missing on this box
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %r" % (e,)}
     print(json.dumps(line))
 
 
@@ -252,6 +325,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--batch", type=int, default=65536)
+    ap.add_argument("--genome-mbp", type=int, default=256)
+    ap.add_argument("--cpu-sample", type=int, default=40000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -13,10 +13,11 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "libbt2gpu.so")
 # every symbol include/bt2gpu.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "bt2gpu_abi_version", "bt2gpu_last_error", "bt2gpu_device_count", "bt2gpu_ctx_create",
-    "bt2gpu_ctx_destroy", "bt2gpu_ctx_sync", "bt2gpu_ctx_stream", "bt2gpu_ctx_launches",
+    "bt2gpu_ctx_destroy", "bt2gpu_ctx_sync", "bt2gpu_ctx_stream", "bt2gpu_ctx_launches", "bt2gpu_ctx_kernel_ms",
     "bt2gpu_scoring_set", "bt2gpu_dp_align_batch", "bt2gpu_dp_stage", "bt2gpu_dp_run",
     "bt2gpu_dp_fetch", "bt2gpu_dp_staged_cells", "bt2gpu_dp_phase_ms",
-    "bt2gpu_index_create", "bt2gpu_index_destroy", "bt2gpu_index_bytes", "bt2gpu_reads_stage",
+    "bt2gpu_index_create", "bt2gpu_index_destroy", "bt2gpu_index_bytes", "bt2gpu_index_gather_probe",
+    "bt2gpu_reads_stage",
     "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch",
@@ -93,6 +94,12 @@ class Context:
 
     def sync(self):
         _check(self.lib.bt2gpu_ctx_sync(self._h))
+
+    def kernel_ms(self):
+        """Device time of the kernels of the last compute call (CUDA events on the ctx stream)."""
+        ms = C.c_float(0)
+        _check(self.lib.bt2gpu_ctx_kernel_ms(self._h, C.byref(ms)))
+        return float(ms.value)
 
     def set_scoring(self, sc):
         s = sc.to_struct() if hasattr(sc, "to_struct") else sc
@@ -207,6 +214,13 @@ class Context:
         _check(self.lib.bt2gpu_locate_batch(self._h, self._ix.fw, _ptr(rows), C.c_size_t(len(rows)),
                                             _ptr(offs), _ptr(steps)))
         return offs, steps
+
+    def gather_probe(self, which="fw", nloads=1 << 28):
+        """Random 64-byte gather bandwidth (GB/s) over the bound index (roofline denominator)."""
+        g = C.c_double(0)
+        h = self._ix.fw if which == "fw" else self._ix.bw
+        _check(self.lib.bt2gpu_index_gather_probe(self._h, h, C.c_uint64(nloads), C.byref(g)))
+        return float(g.value)
 
     def locate_stage(self, rows):
         rows = np.ascontiguousarray(rows, dtype=np.uint32)

@@ -34,7 +34,7 @@ INT64_MIN = -(1 << 63)
 # ---- FM-index side (include/bt2gpu.h) ----
 read = np.dtype([("rd_off", "<u4"), ("rd_len", "<u4")], align=True)
 seed_job = np.dtype([("read", "<u4"), ("off", "<u2"), ("len", "u1"), ("fw", "u1")], align=True)
-seed_hit = np.dtype([("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"), ("bwops", "<u4")], align=True)
+seed_hit = np.dtype([("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"), ("bwops", "<u4"), ("sides", "<u4")], align=True)
 sweep_result = np.dtype([("top", "<u4", (2,)), ("bot", "<u4", (2,)), ("nedit", "<u2", (2,)),
                          ("done", "u1", (2,)), ("bwops", "<u4")], align=True)
 onemm_job = np.dtype([("minsc", "<i4"), ("nceil", "<i4"), ("nofw", "u1"), ("norc", "u1"), ("pad", "u1", (2,))], align=True)
@@ -45,7 +45,7 @@ extend_job = np.dtype([("read", "<u4"), ("topf", "<u4"), ("botf", "<u4"), ("topb
                        ("off", "<u2"), ("len", "u1"), ("fw", "u1")], align=True)
 extend_result = np.dtype([("nlex", "<u2"), ("nrex", "<u2"), ("fmops", "<u4")], align=True)
 
-assert read.itemsize == 8 and seed_job.itemsize == 8 and seed_hit.itemsize == 20
+assert read.itemsize == 8 and seed_job.itemsize == 8 and seed_hit.itemsize == 24
 assert sweep_result.itemsize == 28 and onemm_job.itemsize == 12 and ee_hit.itemsize == 20
 assert onemm_result.itemsize == 12 and extend_job.itemsize == 24 and extend_result.itemsize == 8
 

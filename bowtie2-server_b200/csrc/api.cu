@@ -44,6 +44,7 @@ extern "C" void bt2gpu_ctx_destroy(bt2gpu_ctx *ctx) {
 	cudaStreamSynchronize(ctx->stream);
 	dp_state_free(ctx->dp);
 	fm_state_free(ctx->fm);
+	for(int i = 0; i < 2; i++) if(ctx->kev[i]) cudaEventDestroy(ctx->kev[i]);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -55,3 +56,12 @@ extern "C" int bt2gpu_ctx_sync(bt2gpu_ctx *ctx) {
 }
 extern "C" void *bt2gpu_ctx_stream(bt2gpu_ctx *ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 extern "C" uint64_t bt2gpu_ctx_launches(bt2gpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int bt2gpu_ctx_kernel_ms(bt2gpu_ctx *ctx, float *ms) {
+	if(!ctx || !ms) BT2_FAIL("null argument");
+	*ms = 0.f;
+	if(!ctx->kev_valid) BT2_FAIL("no kernel has been launched through this context yet");
+	BT2_CUDA(cudaEventSynchronize(ctx->kev[1]));
+	BT2_CUDA(cudaEventElapsedTime(ms, ctx->kev[0], ctx->kev[1]));
+	return 0;
+}

@@ -74,4 +74,18 @@ struct bt2gpu_ctx {
 	bool have_sc = false;
 	bt2::DpState *dp = nullptr;
 	bt2::FmState *fm = nullptr;
+	// device time of the kernels of the last entry point (events on `stream`)
+	cudaEvent_t kev[2] = {nullptr, nullptr};
+	bool kev_valid = false;
+	int kstart() {
+		for(int i = 0; i < 2; i++) if(!kev[i]) BT2_CUDA(cudaEventCreate(&kev[i]));
+		kev_valid = false;
+		BT2_CUDA(cudaEventRecord(kev[0], stream));
+		return 0;
+	}
+	int kend() {
+		BT2_CUDA(cudaEventRecord(kev[1], stream));
+		kev_valid = true;
+		return 0;
+	}
 };

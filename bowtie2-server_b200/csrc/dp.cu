@@ -827,6 +827,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 	if(d->njobs == 0) return 0;
 	cudaStream_t s = ctx->stream;
 	if(d->chunks.size() > 1 && phases != 7) BT2_FAIL("partial phases need a single-chunk batch");
+	if(ctx->kstart()) return 1;
 	BT2_CUDA(cudaMemsetAsync(d->scal.p, 0, 64, s));
 	unsigned long long *scal = d->scal.as<unsigned long long>();
 	int *errflag = reinterpret_cast<int*>(scal + 2);
@@ -880,6 +881,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 		}
 		if(timed) BT2_CUDA(cudaEventRecord(d->ev[3], s));
 	}
+	if(ctx->kend()) return 1;
 	return 0;
 }
 

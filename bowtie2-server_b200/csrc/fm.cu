@@ -40,6 +40,7 @@ struct bt2gpu_index {
 	bt2::DevBuf ebwt, offs, ftab, eftab;
 	bt2::IndexDev dev;
 	uint64_t bytes = 0;
+	uint64_t nsides = 0;
 };
 
 namespace bt2 {
@@ -200,7 +201,7 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 			if(ji >= njobs) break;
 			const unsigned long long p = s_seq[k];
 			const int len = s_len[k];
-			uint32_t topf, botf, topb, botb, bwops = 0;
+			uint32_t topf, botf, topb, botb, bwops = 0, nsides = 0;
 			int step;
 			const int fl = fw.ftab_chars;
 			bool alive = true;
@@ -227,6 +228,7 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 				const bool single = (botf - topf == 1);
 				octet_lf(fw, topf, single ? topf : botf, gmask, l8, t, b, topc);
 				bwops++;
+				nsides += (single || topf / 192u == botf / 192u) ? 1 : 2;
 				if(single) {                                    // mapLF1(row, l, c), bt2_idx.h:2420
 					if(topc != c || topf == fw.zoff) { alive = false; break; }
 					topf = t[c]; botf = topf + 1;               // mirror range unchanged
@@ -243,7 +245,7 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 				bt2gpu_seed_hit h;
 				if(alive) { h.topf = topf; h.botf = botf; h.topb = topb; h.botb = botb; }
 				else { h.topf = h.botf = h.topb = h.botb = 0; }
-				h.bwops = bwops;
+				h.bwops = bwops; h.sides = nsides;
 				out[ji] = h;
 			}
 		}
@@ -652,6 +654,7 @@ extern "C" int bt2gpu_index_create(int device, const bt2gpu_index_desc *d, bt2gp
 	BT2_CUDA(cudaSetDevice(device));
 	bt2gpu_index *ix = new bt2gpu_index();
 	ix->device = device;
+	ix->nsides = d->ebwt_bytes / 64;
 	const size_t ftab_n = ((size_t)1 << (2 * d->ftab_chars)) + 1, eftab_n = (size_t)2 * d->ftab_chars;
 	auto up = [&](DevBuf &b, const void *src, size_t bytes) -> int {
 		if(b.reserve(bytes)) return 1;
@@ -740,10 +743,12 @@ extern "C" int bt2gpu_seed_exact_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw, co
 	uint32_t blocks = (uint32_t)((f->n_seed_jobs + SEED_TILE - 1) / SEED_TILE);
 	const uint32_t maxb = (uint32_t)ctx->sm_count * 8;          // 8 resident CTAs of 256 threads per SM
 	if(blocks > maxb) blocks = maxb;
+	if(ctx->kstart()) return 1;
 	k_seed_exact<<<blocks, SEED_BLOCK, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
 		f->sjobs.as<bt2gpu_seed_job>(), (uint32_t)f->n_seed_jobs, f->sout.as<bt2gpu_seed_hit>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
 	return 0;
 }
 
@@ -777,10 +782,12 @@ extern "C" int bt2gpu_exact_sweep_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw,
 	if(f->out.reserve(n * sizeof(bt2gpu_sweep_result))) return 1;
 	cudaStream_t s = ctx->stream;
 	BT2_CUDA(cudaMemsetAsync(f->out.p, 0, n * sizeof(bt2gpu_sweep_result), s));
+	if(ctx->kstart()) return 1;
 	k_exact_sweep<<<blocks_for(2 * n, 8, 256), 256, 0, s>>>(fw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
 		(uint32_t)n, nofw, norc, mine_max, f->out.as<bt2gpu_sweep_result>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
 	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, n * sizeof(bt2gpu_sweep_result), cudaMemcpyDeviceToHost, s));
 	BT2_CUDA(cudaStreamSynchronize(s));
 	return 0;
@@ -808,12 +815,14 @@ extern "C" int bt2gpu_onemm_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const
 	BT2_CUDA(cudaMemcpyAsync(f->jobs.p, jobs, n * sizeof(bt2gpu_onemm_job), cudaMemcpyHostToDevice, s));
 	BT2_CUDA(cudaMemsetAsync(f->out.p, 0, n * sizeof(bt2gpu_onemm_result), s));
 	BT2_CUDA(cudaMemsetAsync(f->scal.p, 0, 64, s));
+	if(ctx->kstart()) return 1;
 	k_onemm<<<blocks_for(4 * n, 8, 256), 256, 0, s>>>(fw->dev, rep1mm ? bw->dev : fw->dev, f->seq.as<uint8_t>(),
 		f->qual.as<uint8_t>(), f->reads.as<bt2gpu_read>(), (uint32_t)n, f->jobs.as<bt2gpu_onemm_job>(), local, repex, rep1mm,
 		f->out.as<bt2gpu_onemm_result>(), f->aux.as<bt2gpu_ee_hit>(), f->keys.as<unsigned long long>(),
 		(unsigned long long)hit_cap, f->scal.as<unsigned long long>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
 	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, n * sizeof(bt2gpu_onemm_result), cudaMemcpyDeviceToHost, s));
 	BT2_CUDA(cudaMemcpyAsync(f->h_scal.p, f->scal.p, 8, cudaMemcpyDeviceToHost, s));
 	BT2_CUDA(cudaStreamSynchronize(s));
@@ -857,10 +866,12 @@ extern "C" int bt2gpu_extend_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, cons
 	if(f->jobs.reserve(njobs * sizeof(bt2gpu_extend_job)) || f->out.reserve(njobs * sizeof(bt2gpu_extend_result))) return 1;
 	cudaStream_t s = ctx->stream;
 	BT2_CUDA(cudaMemcpyAsync(f->jobs.p, jobs, njobs * sizeof(bt2gpu_extend_job), cudaMemcpyHostToDevice, s));
+	if(ctx->kstart()) return 1;
 	k_extend<<<blocks_for(njobs, 8, 256), 256, 0, s>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
 		f->jobs.as<bt2gpu_extend_job>(), (uint32_t)njobs, f->out.as<bt2gpu_extend_result>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
 	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, njobs * sizeof(bt2gpu_extend_result), cudaMemcpyDeviceToHost, s));
 	BT2_CUDA(cudaStreamSynchronize(s));
 	return 0;
@@ -886,10 +897,12 @@ extern "C" int bt2gpu_locate_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw) {
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	FmState *f = ctx->fm;
 	if(f->n_rows == 0) return 0;
+	if(ctx->kstart()) return 1;
 	k_locate<<<blocks_for(f->n_rows, 4, 256), 256, 0, ctx->stream>>>(fw->dev, f->lrows.as<uint32_t>(), (uint32_t)f->n_rows,
 		f->loffs.as<uint32_t>(), f->lsteps.as<uint32_t>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
 	return 0;
 }
 
@@ -910,4 +923,50 @@ extern "C" int bt2gpu_locate_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, cons
 	if(bt2gpu_locate_stage(ctx, rows, n)) return 1;
 	if(bt2gpu_locate_run(ctx, fw)) return 1;
 	return bt2gpu_locate_fetch(ctx, offs_out, steps_out);
+}
+
+
+// ---- roofline probe ---------------------------------------------------------------------
+// Independent (not dependent-chain) random 64-byte side gathers over the index itself at full
+// occupancy: the HBM random-access ceiling the seed kernels are measured against
+// ("measured 64-B-sector random-gather GB/s on the same B200").
+namespace bt2 {
+__global__ void __launch_bounds__(256)
+k_gather_probe(const uint4 *__restrict__ sides, uint32_t nsides, uint32_t per_quad, uint32_t *__restrict__ sink)
+{
+	const uint32_t gq = (blockIdx.x * blockDim.x + threadIdx.x) >> 2;
+	const int q = threadIdx.x & 3;
+	uint32_t x = gq * 2654435761u + 12345u, acc = 0;
+#pragma unroll 4
+	for(uint32_t i = 0; i < per_quad; i++) {
+		x = x * 1664525u + 1013904223u;
+		const uint32_t side = (uint32_t)(((unsigned long long)(x ^ (x >> 15)) * nsides) >> 32);
+		const uint4 v = __ldg(sides + (size_t)side * 4 + q);
+		acc ^= v.x ^ v.y ^ v.z ^ v.w;
+	}
+	if(acc == 0x9e3779b9u) sink[0] = acc;
+}
+}
+
+extern "C" int bt2gpu_index_gather_probe(bt2gpu_ctx *ctx, const bt2gpu_index *ix, uint64_t nloads, double *gbs) {
+	if(!ctx || !gbs) BT2_FAIL("null argument");
+	if(check_idx(ctx, ix, false)) return 1;
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	FmState *f = fm_state(ctx);
+	if(f->scal.reserve(64)) return 1;
+	const uint32_t nsides = (uint32_t)ix->nsides;
+	if(nsides == 0) BT2_FAIL("empty index");
+	const uint32_t blocks = (uint32_t)ctx->sm_count * 8, quads = blocks * 64;
+	uint32_t per = (uint32_t)std::max<uint64_t>(1, nloads / quads);
+	for(int rep = 0; rep < 2; rep++) {                          // first pass warms up
+		if(ctx->kstart()) return 1;
+		k_gather_probe<<<blocks, 256, 0, ctx->stream>>>(ix->dev.sides, nsides, per, f->scal.as<uint32_t>());
+		ctx->launches++;
+		BT2_CUDA(cudaGetLastError());
+		if(ctx->kend()) return 1;
+	}
+	float ms = 0.f;
+	if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1;
+	*gbs = (double)quads * per * 64.0 / (ms * 1e-3) / 1e9;
+	return 0;
 }

@@ -44,6 +44,9 @@ int         bt2gpu_ctx_sync(bt2gpu_ctx *ctx);
 void       *bt2gpu_ctx_stream(bt2gpu_ctx *ctx);
 /* Number of kernel launches issued through this context so far. */
 uint64_t    bt2gpu_ctx_launches(bt2gpu_ctx *ctx);
+/* Device time (ms) of the kernels the last compute entry point launched: CUDA events on the
+ * context's stream around the kernels only (host<->device copies excluded). */
+int         bt2gpu_ctx_kernel_ms(bt2gpu_ctx *ctx, float *ms);
 
 /* ---- scoring (replaces class Scoring, scoring.h:96-486) ----------------- */
 typedef struct {
@@ -180,6 +183,9 @@ int  bt2gpu_index_create(int device, const bt2gpu_index_desc *desc, bt2gpu_index
 void bt2gpu_index_destroy(bt2gpu_index *idx);
 /* Bytes of HBM the index occupies. */
 uint64_t bt2gpu_index_bytes(const bt2gpu_index *idx);
+/* Roofline probe: bandwidth (GB/s) of `nloads` independent random 64-byte side gathers over this
+ * index at full occupancy -- the HBM random-access ceiling of the seed kernels. */
+int bt2gpu_index_gather_probe(bt2gpu_ctx *ctx, const bt2gpu_index *idx, uint64_t nloads, double *gbs);
 
 /* A read in the pools: bytes 0..4 (A,C,G,T,N), forward strand (Read::patFw);
  * quality bytes Phred+33 (Read::qual).  The kernels derive patRc/patFwRev/... */
@@ -191,8 +197,10 @@ int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *
                        size_t pool_len, const bt2gpu_read *reads, size_t nreads);
 
 /* BwtTopBot (aligner_cache.h:68) + the bwops_ this seed cost (aligner_seed.cpp:1906,1999).
- * topf == botf means "no hit" (then topb/botb are 0). */
-typedef struct { uint32_t topf, botf, topb, botb, bwops; } bt2gpu_seed_hit;
+ * topf == botf means "no hit" (then topb/botb are 0).  sides = distinct 64-byte BWT sides the
+ * search had to read (1 per mapLF1 step, 1 or 2 per mapBiLFEx step, bt2_idx.h:339-351): the
+ * algorithmic HBM traffic of the seed in 64-byte units. */
+typedef struct { uint32_t topf, botf, topb, botb, bwops, sides; } bt2gpu_seed_hit;
 
 /* One exact seed = one InstantiatedSeed of type SEED_TYPE_EXACT
  * (aligner_seed.cpp:213-358): window [off, off+len) of the read, strand fw. */

@@ -187,9 +187,11 @@ static void seed_exact_one(const Idx *fw, const Idx *bw, const uint8_t *seq, int
 		bp[0] = bp[1] = bp[2] = bp[3] = botb;
 		if(bl.valid) {
 			bwops++;
+			out->sides += (tl.side_off == bl.side_off) ? 1 : 2;
 			map_bi_lf_ex(fw, &tl, &bl, t, b, tp, bp);
 		} else {
 			bwops++;
+			out->sides++;
 			t[c] = map_lf1_c(fw, topf, &tl, c);
 			if(t[c] == OFF_MASK) { out->bwops = bwops; return; }
 			b[c] = t[c] + 1;

@@ -98,7 +98,7 @@ int main(int argc, char** argv) {
 		// Threaded timing of the same calls (no output): one SeedAligner per thread as
 		// bt2_search.cpp:3128 does.  Prints one JSON line with reads/s and LF steps/s.
 		atomic<size_t> next(0);
-		atomic<uint64_t> totOps(0), totSeeds(0);
+		atomic<uint64_t> totOps(0), totSeeds(0), totLoc(0);
 		const size_t total = fq.size() * (size_t)reps;
 		auto t0 = chrono::steady_clock::now();
 		vector<thread> th;
@@ -107,7 +107,8 @@ int main(int argc, char** argv) {
 			AlignmentCache scCurrent(20 * 1024 * 1024, false);
 			AlignmentCacheIface ca(&scCurrent, NULL, NULL);
 			EList<Seed> seeds; Constraint gc = Constraint::penaltyFuncBased(scoreMin);
-			Read rd; uint64_t ops = 0, nsd = 0;
+			Read rd; uint64_t ops = 0, nsd = 0, sink = 0, nloc = 0;
+			SwDriver sd(4 * 1024 * 1024); EList<SATuple, 16> satups;
 			for(;;) {
 				size_t k = next.fetch_add(64);
 				if(k >= total) break;
@@ -128,16 +129,34 @@ int main(int argc, char** argv) {
 					if(inst.first + inst.second > 0) {
 						al.searchAllSeeds(seeds, ebwtFw, ebwtBw, rd, sc, ca, shs, sdm, prm);
 						ops += al.bwops_; nsd += inst.first;
+						// extend every hit, then resolve the first row of the narrowest range
+						size_t sl = min<size_t>((size_t)seedLen, len);
+						TIndexOffU bestTop = 0, bestSz = 0;
+						for(int fwi = 0; fwi < 2; fwi++) for(size_t i = 0; i < shs.numOffs(); i++) {
+							const QVal& qv = shs.hitsAtOffIdx(fwi == 0, i);
+							if(!qv.valid()) continue;
+							satups.clear(); size_t nr = 0, ne = 0;
+							ca.queryQval(qv, satups, nr, ne);
+							for(size_t k = 0; k < satups.size(); k++) {
+								TIndexOffU sz = (TIndexOffU)satups[k].offs.size();
+								size_t nlex = 0, nrex = 0; PerReadMetrics prm2;
+								sd.extend(rd, *ebwtFw, ebwtBw, satups[k].topf, satups[k].topf + sz, satups[k].topb,
+								          satups[k].topb + sz, fwi == 0, (size_t)interval * i, sl, prm2, nlex, nrex);
+								ops += prm2.nSdFmops;
+								if(bestSz == 0 || sz < bestSz) { bestSz = sz; bestTop = satups[k].topf; }
+							}
+						}
+						if(bestSz > 0) { sink += ebwtFw->getOffset(bestTop); nloc++; }
 					}
 				}
 			}
-			totOps += ops; totSeeds += nsd;
+			totOps += ops; totSeeds += nsd; totLoc += nloc + (sink == 0xdeadbeefdeadull);
 		});
 		for(auto& t : th) t.join();
 		double sec = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
-		printf("{\"reads\": %zu, \"seconds\": %.6f, \"reads_per_s\": %.1f, \"lf_steps\": %llu, \"lf_steps_per_s\": %.1f, \"seeds\": %llu, \"threads\": %d}\n",
+		printf("{\"reads\": %zu, \"seconds\": %.6f, \"reads_per_s\": %.1f, \"lf_steps\": %llu, \"lf_steps_per_s\": %.1f, \"seeds\": %llu, \"located\": %llu, \"threads\": %d}\n",
 		       total, sec, total / sec, (unsigned long long)totOps.load(), totOps.load() / sec,
-		       (unsigned long long)totSeeds.load(), nthreads);
+		       (unsigned long long)totSeeds.load(), (unsigned long long)totLoc.load(), nthreads);
 		return 0;
 	}
 
