@@ -62,8 +62,9 @@ def suffix_array(s, device):
     new = torch.ones(n1, dtype=torch.bool, device=device)
     new[1:] = skey[1:] != skey[:-1]
     del skey
-    posidx = torch.arange(n1, device=device)
-    grp = torch.cummax(torch.where(new, posidx, torch.zeros_like(posidx)), 0).values
+    starts = torch.nonzero(new).squeeze(1)
+    grp = starts[torch.cumsum(new, 0) - 1]            # first SA position of each run
+    del starts, new
     depth = _KCH
     while True:
         tied = torch.zeros(n1, dtype=torch.bool, device=device)
@@ -82,7 +83,7 @@ def suffix_array(s, device):
         g2, k2 = g[o], k2[o]
         nb = torch.ones(tpos.numel(), dtype=torch.bool, device=device)
         nb[1:] = (g2[1:] != g2[:-1]) | (k2[1:] != k2[:-1])
-        grp[tpos] = torch.cummax(torch.where(nb, tpos, torch.zeros_like(tpos)), 0).values
+        grp[tpos] = tpos[torch.nonzero(nb).squeeze(1)][torch.cumsum(nb, 0) - 1]
         depth += _KCH
         if depth > n + _KCH:
             break

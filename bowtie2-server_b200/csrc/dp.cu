@@ -18,8 +18,9 @@
 //    of aligner_sw.cpp:516-621 (including the stripe-padding rows that leak into the local
 //    column maxima), two passes + device scan, then a per-job bitonic sort in the order of
 //    DpBtCandidate::operator< (aligner_sw_nuc.h:134).
-//  * k_dp_backtrace: one thread per problem replays the nextAlignment() candidate loop and
-//    the deterministic-priority walk of backtraceNucleotides* (ee_u8.cpp:1283-1877).
+//  * k_dp_backtrace: one warp per problem replays the nextAlignment() candidate loop and
+//    the deterministic-priority walk of backtraceNucleotides* (ee_u8.cpp:1283-1877), 32
+//    speculated diagonal cells per round trip to the matrices.
 //
 // Values are kept in the SCORE domain (the reference's raw value minus its offset) with the
 // variant's floor: -255 for the u8 end-to-end path (exact saturation emulation), 0 for
@@ -205,16 +206,27 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 // ---------------------------------------------------------------------------------------
 // Matrix access for gather / backtrace: cell (row, col) of matrix m (0=E, 1=F, 2=H).
 // ---------------------------------------------------------------------------------------
+struct RowRef { int stT, v, k; };    // stripe * T, virtual lane and register of a DP row
 struct MatView {
 	const uint32_t *base; int S, T, RW;
-	__device__ __forceinline__ int get(int m, int row, int col) const {
-		const int RS = VL * S;
-		const int st = row / RS, r = row - st * RS;
-		const int v = r / S, k = r - v * S;
-		const int idx = m * S + k;
-		const uint32_t w = __ldcg(base + (size_t)(st * T + col + v) * GL * RW + ((idx >> 2) * GL + (v >> 1)) * 4 + (idx & 3));
-		return (v & 1) ? hi16(w) : lo16(w);
+	uint32_t invS, invRS; int stride;     // ceil(2^32 / S), ceil(2^32 / (16 S)), GL * RW
+	__device__ __forceinline__ void init(const uint32_t *b, int S_, int T_, int RW_) {
+		base = b; S = S_; T = T_; RW = RW_;
+		invS = 0xffffffffu / (uint32_t)S + 1u; invRS = 0xffffffffu / (uint32_t)(VL * S) + 1u;
+		stride = GL * RW;
 	}
+	// row -> (stripe, virtual lane, register) by multiply-high: exact for rows < 2^16
+	__device__ __forceinline__ RowRef rowref(int row) const {
+		const int st = (int)__umulhi((uint32_t)row, invRS), r = row - st * (VL * S);
+		RowRef rr; rr.v = (int)__umulhi((uint32_t)r, invS); rr.k = r - rr.v * S; rr.stT = st * T;
+		return rr;
+	}
+	__device__ __forceinline__ int at(int m, const RowRef &rr, int col) const {
+		const int idx = m * S + rr.k;
+		const uint32_t w = __ldcg(base + (size_t)(rr.stT + col + rr.v) * stride + ((idx >> 2) * GL + (rr.v >> 1)) * 4 + (idx & 3));
+		return (rr.v & 1) ? hi16(w) : lo16(w);
+	}
+	__device__ __forceinline__ int get(int m, int row, int col) const { return at(m, rowref(row), col); }
 };
 
 __device__ __forceinline__ uint64_t cand_key(int score, int row, int col) {
@@ -244,7 +256,7 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	const DpAux ax = aux[ji];
 	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
 	const int minsc = jb.minsc;
-	MatView mv; mv.base = mat + ax.mat_off; mv.S = (int)ax.S; mv.T = (int)ax.T; mv.RW = (int)ax.RW;
+	MatView mv; mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW);
 	const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
 	const bool local = !c_sc.monotone;
 	if(EMIT && res[ji].ncand == 0) return;
@@ -434,17 +446,73 @@ k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__r
 }
 
 // ---------------------------------------------------------------------------------------
-// Backtrace.  One thread per job replays SwAligner::nextAlignment (aligner_sw.cpp:737-1146)
+// Backtrace.  One WARP per job replays SwAligner::nextAlignment (aligner_sw.cpp:737-1146)
 // over the sorted candidates.  The walk is backtraceNucleotides* (ee_u8.cpp:1283-1877).
 // In the reference a cell is marked reportedThrough the moment it is visited, and a popped
 // branch frame re-enters its (already marked) cell, so every dead end unwinds the whole
 // branch stack and fails: the masks_/btnstack_ state never changes an outcome.  The kernel
 // therefore keeps only the reportedThrough bit and fails at the first blocked cell
 // (equivalence is exercised by the goldens; the CPU oracle keeps the full state).
+//
+// The reference walks one cell per step, each step a dependent gather from the E/F/H
+// matrices.  What a cell decides in the H state depends only on the stored values around it,
+// and >95% of the steps are diagonal, so the warp SPECULATES the diagonal: lane i evaluates
+// cell (row-i, col-i) as if the path arrived there in the H state; a ballot finds the first
+// lane whose cell is not a plain diagonal move; lanes before it are committed together
+// (reportedThrough bits, core-diagonal test, mismatch edits, score), that lane's event is
+// handled, and the E/F (gap extension) states run as uniform scalar code.  One round trip to
+// the matrices then covers up to 32 cells of the path.
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint8_t dev_mask2dna(int m) { return (uint8_t)"?ACMGRSVTWYHKDBNN"[m & 31 ? (m > 16 ? 16 : m) : 0]; }
 
-__global__ void __launch_bounds__(64)
+struct BtJob {
+	MatView mv; const uint8_t *rd, *qu, *rf; uint32_t *rp32;
+	int nrow, ncol, gapbar; bool local;
+	long long triml; unsigned long long corel, corer;
+	__device__ __forceinline__ bool reported(int row, int col) const {
+		const size_t b = (size_t)row * ncol + col;
+		return (__ldcg(rp32 + (b >> 5)) >> (b & 31)) & 1u;
+	}
+	__device__ __forceinline__ void mark(int row, int col) const {
+		const size_t b = (size_t)row * ncol + col;
+		atomicOr(rp32 + (b >> 5), 1u << (b & 31));
+	}
+	__device__ __forceinline__ bool on_core(int row, int col) const {
+		const long long d = (long long)col - row + triml;
+		return d >= 0 && (unsigned long long)d >= corel && (unsigned long long)d <= corer;
+	}
+	// move out of an H cell: 0 = none (empty mask), 1 diag, 2 ref-open, 5 ref-ext, 3 read-open, 4 read-ext
+	__device__ __forceinline__ int h_move(int row, int col) const {
+		const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
+		const RowRef rc = mv.rowref(row), ru = mv.rowref(row - 1);
+		// all neighbours are fetched up front (independent loads, one round trip)
+		const int sc_cur = mv.at(2, rc, col);
+		const int hu = mv.at(2, ru, col), fu = mv.at(1, ru, col);
+		const int cl = col > 0 ? col - 1 : 0;
+		const int hl = mv.at(2, rc, cl), el = mv.at(0, rc, cl), hd = mv.at(2, ru, cl);
+		int mask = 0;
+		if(gapsAllowed) {
+			if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) mask |= 1;
+			if((!local || fu > 0) && sc_cur == fu - c_sc.rfe) mask |= 4;
+			if(col > 0) {
+				if((!local || hl > 0) && sc_cur == hl - c_sc.rdo) mask |= 2;
+				if((!local || el > 0) && sc_cur == el - c_sc.rde) mask |= 8;
+			}
+		}
+		if(col > 0) {
+			const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
+			if((!local || hd > 0) && sc_cur == hd + sd) mask |= 16;
+		}
+		if(mask & 16) return 1;            // diag > ref open > ref ext > read open > read ext
+		if(mask & 1) return 2;
+		if(mask & 4) return 5;
+		if(mask & 2) return 3;
+		if(mask & 8) return 4;
+		return 0;
+	}
+};
+
+__global__ void __launch_bounds__(128)
 k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
                const uint8_t *__restrict__ win, const bt2gpu_dp_job *__restrict__ jobs,
                const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
@@ -455,44 +523,50 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
                unsigned long long *__restrict__ nedits, unsigned long long edit_cap,
                uint32_t max_aln, int *__restrict__ errflag)
 {
-	const uint32_t ji = job0 + blockIdx.x * blockDim.x + threadIdx.x;
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	const uint32_t ji = job0 + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if(ji >= job0 + njobs) return;
 	bt2gpu_dp_result r = res[ji];
 	r.naln = 0; r.aln_off = ji * max_aln; r.tail_tries = 0; r.cural = 0;
-	if(!r.aligned) { res[ji] = r; return; }
+	if(!r.aligned) { if(lane == 0) res[ji] = r; return; }
 	const bt2gpu_dp_job jb = jobs[ji];
 	const DpAux ax = aux[ji];
-	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
-	MatView mv; mv.base = mat + ax.mat_off; mv.S = (int)ax.S; mv.T = (int)ax.T; mv.RW = (int)ax.RW;
-	const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
-	uint8_t *rp = rep + ax.rep_off;
-	const bool local = !c_sc.monotone;
-	const int gapbar = c_sc.gapbar;
+	BtJob J;
+	J.nrow = (int)jb.rd_len; J.ncol = (int)jb.ncol;
+	J.mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW);
+	J.rd = seq + jb.rd_off; J.qu = qual + jb.rd_off; J.rf = win + jb.rf_off;
+	J.rp32 = reinterpret_cast<uint32_t*>(rep + ax.rep_off);
+	J.local = !c_sc.monotone; J.gapbar = c_sc.gapbar;
+	J.triml = (long long)jb.triml; J.corel = jb.corel; J.corer = jb.corer;
+	const int nrow = J.nrow;
+	const uint8_t *rd = J.rd, *qu = J.qu, *rf = J.rf;
+	const bool local = J.local;
 	const bt2gpu_dp_cand *cd = cands + r.cand_off;
 	uint32_t *done = donelist + r.cand_off;
 	bt2gpu_edit *ed = escr + ax.escr_off;
 	const uint32_t ncand = r.ncand;
 	uint32_t SQ = (uint32_t)nrow >> 4; if(SQ == 0) SQ = 1;
-	uint32_t cural = 0, ndone = 0, tries = 0;
+	uint32_t cural = 0, ndone = 0, tries = 0, cbase = 0xffffffffu;
+	bt2gpu_dp_cand cc; cc.row = cc.col = 0; cc.score = 0;
 	while(r.naln < max_aln && cural < ncand) {
 		bool got = false;
 		bt2gpu_dp_aln out;
 		while(cural < ncand) {
-			const bt2gpu_dp_cand c0 = cd[cural];
+			// candidates are read 32 at a time (one round trip per 32 of them)
+			if(cural < cbase || cural >= cbase + 32) {
+				cbase = cural;
+				if(cbase + lane < ncand) cc = cd[cbase + lane];
+			}
+			bt2gpu_dp_cand c0;
+			c0.row = __shfl_sync(FULL, cc.row, cural - cbase);
+			c0.col = __shfl_sync(FULL, cc.col, cural - cbase);
+			c0.score = __shfl_sync(FULL, cc.score, cural - cbase);
 			if(c0.score < jb.minsc) { cural++; continue; }
 			int row = (int)c0.row, col = (int)c0.col;
-			{ const size_t b = (size_t)row * ncol + col; if((rp[b >> 3] >> (b & 7)) & 1) { cural++; continue; } }
-			if(local) {
-				bool dom = false;
-				for(uint32_t i = 0; i < ndone; i++) {
-					uint32_t dr = done[i] >> 16, dc = done[i] & 0xffff;
-					uint32_t rh = max((uint32_t)row, dr), rl = min((uint32_t)row, dr);
-					uint32_t ch = max((uint32_t)col, dc), cl = min((uint32_t)col, dc);
-					if(ch - cl <= SQ && rh - rl <= SQ) { dom = true; break; }
-				}
-				if(dom) { cural++; continue; }
-			}
-			tries++;
+			// the "start cell already reported" test (aligner_sw.cpp:774-789) rides on the first
+			// speculative batch below (lane 0 is the start cell) instead of its own round trip
+			bool fresh = true, skipped = false;
 			// ---- walk ----
 			int score = 0, ns = 0, gaps = 0, ned = 0, ct = 2;
 			const int origCol = col;
@@ -500,86 +574,130 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 			int trimBeg = 0;
 			bool ok = false, overlapped = false, blocked = false;
 			while(row >= 0) {
-				const size_t b = (size_t)row * ncol + col;
-				const bool reported = (rp[b >> 3] >> (b & 7)) & 1;
-				bool empty = false, canMove = !reported;
+				if(ct == 2) {
+					// ---- speculative diagonal batch: lane i looks at (row-i, col-i) in the H state ----
+					const int ri = row - lane, ci = col - lane;
+					const bool valid = ri >= 0 && ci >= 0;
+					bool rep_i = false; int mv_i = 0;
+					if(valid) {
+						rep_i = J.reported(ri, ci);
+						if(!rep_i && ri > 0) mv_i = J.h_move(ri, ci);
+					}
+					const bool plain = valid && !rep_i && ri > 0 && mv_i == 1;
+					const unsigned pb = __ballot_sync(FULL, plain);
+					const int k = __ffs(~pb) - 1;             // first lane that is not a plain diagonal step (32 if none)
+					const int nk = k < 0 ? 32 : k;
+					if(fresh) {
+						fresh = false;
+						if(__shfl_sync(FULL, (int)rep_i, 0)) { skipped = true; break; }
+						if(local) {
+							bool dom = false;
+							for(uint32_t i = lane; i < ndone; i += 32) {
+								const uint32_t dv = done[i];
+								uint32_t dr = dv >> 16, dc = dv & 0xffff;
+								uint32_t rh = max((uint32_t)row, dr), rl = min((uint32_t)row, dr);
+								uint32_t ch = max((uint32_t)col, dc), cl = min((uint32_t)col, dc);
+								if(ch - cl <= SQ && rh - rl <= SQ) dom = true;
+							}
+							if(__any_sync(FULL, dom)) { skipped = true; break; }
+						}
+						tries++;
+					}
+					// commit lanes [0, nk): diagonal moves
+					{
+						const bool mine = lane < nk;
+						int mm = 1, pen = 0;
+						if(mine) {
+							J.mark(ri, ci);
+							const int rc = rd[ri], rm = rf[ci];
+							mm = (rm >= 16 || rc > 3) ? -1 : (((1 << rc) & rm) ? 1 : 0);
+							pen = (mm != 1) ? -dev_mm(rc, rm, (int)qu[ri] - 33) : c_sc.match;
+						}
+						const bool isEd = mine && mm != 1;
+						const unsigned eb = __ballot_sync(FULL, isEd);
+						if(isEd) {
+							bt2gpu_edit e; e.pad = 0;
+							e.pos = (uint32_t)ri; e.chr = dev_mask2dna(rf[ci]); e.qchr = (uint8_t)"ACGTN"[rd[ri]]; e.type = BT2GPU_EDIT_MM;
+							ed[ned + __popc(eb & ((1u << lane) - 1u))] = e;
+						}
+						ned += __popc(eb);
+						score += __reduce_add_sync(FULL, mine ? pen : 0);
+						ns += __popc(__ballot_sync(FULL, mine && mm == -1));
+						if(__any_sync(FULL, mine && J.on_core(ri, ci))) overlapped = true;
+					}
+					row -= nk; col -= nk;
+					if(nk == 32) continue;
+					// ---- event at lane nk: cell (row, col), still in the H state ----
+					if(col < 0) {
+						// ran off the left edge on a diagonal: the scalar walk would be at (row, -1); cannot
+						// happen (a diagonal move needs col > 0), kept as a guard
+						blocked = true; break;
+					}
+					const bool e_rep = __shfl_sync(FULL, (int)rep_i, nk) != 0;
+					const int e_mv = __shfl_sync(FULL, mv_i, nk);
+					J.mark(row, col);
+					if(e_rep) { blocked = true; break; }
+					if(J.on_core(row, col)) overlapped = true;
+					if(row == 0 || e_mv == 0) { trimBeg = row; ok = true; break; }
+					bt2gpu_edit e; e.pad = 0;
+					if(e_mv == 2 || e_mv == 5) {
+						e.pos = (uint32_t)row; e.chr = '-'; e.qchr = (uint8_t)"ACGTN"[rd[row]]; e.type = BT2GPU_EDIT_REF_GAP;
+						if(lane == 0) ed[ned] = e;
+						ned++; row--;
+						if(e_mv == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; }
+						gaps++;
+					} else {
+						e.pos = (uint32_t)row + 1; e.chr = dev_mask2dna(rf[col]); e.qchr = '-'; e.type = BT2GPU_EDIT_READ_GAP;
+						if(lane == 0) ed[ned] = e;
+						ned++; col--;
+						if(e_mv == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; }
+						gaps++;
+					}
+					continue;
+				}
+				// ---- E / F states: uniform scalar steps (every lane computes the same thing) ----
+				const bool reported = J.reported(row, col);
+				bool empty = false;
 				int cur = 0;
 				if(!reported && row > 0) {
-					const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
 					if(ct == 0) {
-						const int sc_cur = mv.get(0, row, col);
-						const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
+						const int sc_cur = J.mv.get(0, row, col);
+						const int hl = J.mv.get(2, row, col - 1), el = J.mv.get(0, row, col - 1);
 						int mask = 0;
 						if((!local || hl > 0) && hl - c_sc.rdo == sc_cur) mask |= 1;
 						if((!local || el > 0) && el - c_sc.rde == sc_cur) mask |= 2;
-						if(mask & 1) cur = 3; else if(mask == 2) cur = 4; else { empty = true; }
-					} else if(ct == 1) {
-						const int sc_cur = mv.get(1, row, col);
-						const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
+						if(mask & 1) cur = 3; else if(mask == 2) cur = 4; else empty = true;
+					} else {
+						const int sc_cur = J.mv.get(1, row, col);
+						const int hu = J.mv.get(2, row - 1, col), fu = J.mv.get(1, row - 1, col);
 						int mask = 0;
 						if((!local || hu > 0) && hu - c_sc.rfo == sc_cur) mask |= 1;
 						if((!local || fu > 0) && fu - c_sc.rfe == sc_cur) mask |= 2;
-						if(mask & 1) cur = 2; else if(mask == 2) cur = 5; else { empty = true; }
-					} else {
-						const int sc_cur = mv.get(2, row, col);
-						int mask = 0;
-						if(gapsAllowed) {
-							const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
-							if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) mask |= 1;
-							if((!local || fu > 0) && sc_cur == fu - c_sc.rfe) mask |= 4;
-							if(col > 0) {
-								const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
-								if((!local || hl > 0) && sc_cur == hl - c_sc.rdo) mask |= 2;
-								if((!local || el > 0) && sc_cur == el - c_sc.rde) mask |= 8;
-							}
-						}
-						if(col > 0) {
-							const int hd = mv.get(2, row - 1, col - 1);
-							const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
-							if((!local || hd > 0) && sc_cur == hd + sd) mask |= 16;
-						}
-						if(mask & 16) cur = 1;            // diag > ref open > ref ext > read open > read ext
-						else if(mask & 1) cur = 2;
-						else if(mask & 4) cur = 5;
-						else if(mask & 2) cur = 3;
-						else if(mask & 8) cur = 4;
-						else empty = true;
+						if(mask & 1) cur = 2; else if(mask == 2) cur = 5; else empty = true;
 					}
-					// empty => origMask == 0 here (no stored mask state), so canMoveThru stays true
 				}
-				rp[b >> 3] |= (uint8_t)(1u << (b & 7));
-				if(!canMove) { blocked = true; break; }
-				{
-					const long long diagi = (long long)col - row + (long long)jb.triml;
-					if(diagi >= 0 && (unsigned long long)diagi >= jb.corel && (unsigned long long)diagi <= jb.corer) overlapped = true;
-				}
+				__syncwarp();
+				J.mark(row, col);
+				if(reported) { blocked = true; break; }
+				if(J.on_core(row, col)) overlapped = true;
 				if(empty || row == 0) { trimBeg = row; ok = true; break; }
 				bt2gpu_edit e; e.pad = 0;
-				if(cur == 1) {
-					const int rc = rd[row], rm = rf[col];
-					const int mm = (rm >= 16 || rc > 3) ? -1 : (((1 << rc) & rm) ? 1 : 0);
-					ct = 2;
-					if(mm != 1) {
-						e.pos = (uint32_t)row; e.chr = dev_mask2dna(rm); e.qchr = (uint8_t)"ACGTN"[rc]; e.type = BT2GPU_EDIT_MM;
-						ed[ned++] = e;
-						score -= dev_mm(rc, rm, (int)qu[row] - 33);
-					} else score += c_sc.match;
-					if(mm == -1) ns++;
-					row--; col--;
-				} else if(cur == 2 || cur == 5) {
+				if(cur == 2 || cur == 5) {
 					e.pos = (uint32_t)row; e.chr = '-'; e.qchr = (uint8_t)"ACGTN"[rd[row]]; e.type = BT2GPU_EDIT_REF_GAP;
-					ed[ned++] = e;
-					row--;
+					if(lane == 0) ed[ned] = e;
+					ned++; row--;
 					if(cur == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; }
 					gaps++;
 				} else {
 					e.pos = (uint32_t)row + 1; e.chr = dev_mask2dna(rf[col]); e.qchr = '-'; e.type = BT2GPU_EDIT_READ_GAP;
-					ed[ned++] = e;
-					col--;
+					if(lane == 0) ed[ned] = e;
+					ned++; col--;
 					if(cur == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; }
 					gaps++;
 				}
 			}
+			__syncwarp();
+			if(skipped) { cural++; continue; }
 			if(ok && !blocked) {
 				ok = overlapped;                                           // core-diagonal test
 				if(ok) {
@@ -588,34 +706,39 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					if(mm != 1) {
 						bt2gpu_edit e; e.pad = 0;
 						e.pos = (uint32_t)row; e.chr = dev_mask2dna(rm); e.qchr = (uint8_t)"ACGTN"[rc]; e.type = BT2GPU_EDIT_MM;
-						ed[ned++] = e;
+						if(lane == 0) ed[ned] = e;
+						ned++;
 						score -= dev_mm(rc, rm, (int)qu[row] - 33);
 					} else score += c_sc.match;
 					if(mm == -1) ns++;
 					if(ns > jb.nceil) ok = false;
 				}
 			} else ok = false;
-			if(local) { done[ndone++] = ((uint32_t)c0.row << 16) | (uint32_t)c0.col; }
+			if(local) { if(lane == 0) done[ndone] = ((uint32_t)c0.row << 16) | (uint32_t)c0.col; ndone++; }
+			__syncwarp();
 			if(ok) {
 				out.score = score; out.ns = ns; out.gaps = gaps;
 				out.refoff = (int64_t)col + jb.refl;
 				out.trim5 = (uint32_t)(jb.fw ? trimBeg : trimEnd);
 				out.trim3 = (uint32_t)(jb.fw ? trimEnd : trimBeg);
 				int refns = 0;
-				for(int i = col; i <= origCol; i++) if(rf[i] > 15) refns++;
-				out.refns = refns;
-				const unsigned long long eo = atomicAdd(nedits, (unsigned long long)ned);
-				if(eo + ned > edit_cap) { *errflag = 2; res[ji] = r; return; }
+				for(int i = col + lane; i <= origCol; i += 32) if(rf[i] > 15) refns++;
+				out.refns = __reduce_add_sync(FULL, refns);
+				unsigned long long eo = 0;
+				if(lane == 0) eo = atomicAdd(nedits, (unsigned long long)ned);
+				eo = __shfl_sync(FULL, eo, 0);
+				if(eo + ned > edit_cap) { if(lane == 0) { *errflag = 2; res[ji] = r; } return; }
 				out.edit_off = (uint32_t)eo; out.nedits = (uint32_t)ned;
 				// scratch holds edits in walk order (descending row); reference order after
 				// res.reverse() is ascending; '-' strand then inverts again (edit.cpp:50-78)
 				const int rdex = nrow - trimBeg - trimEnd;
-				for(int i = 0; i < ned; i++) {
+				for(int i = lane; i < ned; i += 32) {
 					bt2gpu_edit e = ed[jb.fw ? (ned - 1 - i) : i];
 					e.pos -= (uint32_t)trimBeg;
 					if(!jb.fw) e.pos = (uint32_t)(rdex - (int)e.pos - (e.type == BT2GPU_EDIT_READ_GAP ? 0 : 1));
 					edits[eo + i] = e;
 				}
+				__syncwarp();
 				got = true;
 				break;
 			}
@@ -624,11 +747,11 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 		if(!got) break;
 		cural++;
 		out.cural = cural; out.tries = tries; tries = 0;
-		alns[(size_t)ji * max_aln + r.naln] = out;
+		if(lane == 0) alns[(size_t)ji * max_aln + r.naln] = out;
 		r.naln++;
 	}
 	r.tail_tries = tries; r.cural = cural;
-	res[ji] = r;
+	if(lane == 0) res[ji] = r;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -786,7 +909,7 @@ extern "C" int bt2gpu_dp_stage(
 			memset(&ch, 0, sizeof(ch)); ch.job0 = (uint32_t)i;
 		}
 		a.mat_off = ch.mat_words; ch.mat_words += mw;
-		a.rep_off = ch.rep_bytes; ch.rep_bytes += ((uint64_t)j.rd_len * j.ncol + 7) / 8;
+		a.rep_off = ch.rep_bytes; ch.rep_bytes += (((uint64_t)j.rd_len * j.ncol + 31) / 32) * 4;   // u32 words (atomicOr)
 		a.bound_off = ch.bound_words; ch.bound_words += 2 * j.ncol;
 		a.escr_off = ch.escr_edits; ch.escr_edits += j.rd_len + j.ncol + 4;
 		if((int)j.ncol > ch.maxcol) ch.maxcol = (int)j.ncol;
@@ -870,7 +993,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 		if(timed) BT2_CUDA(cudaEventRecord(d->ev[2], s));
 		if(phases & 4) {
 			BT2_CUDA(cudaMemsetAsync(d->rep.p, 0, c.rep_bytes, s));
-			k_dp_backtrace<<<(c.njobs + 63) / 64, 64, 0, s>>>(
+			k_dp_backtrace<<<(c.njobs + 3) / 4, 128, 0, s>>>(
 				d->seq.as<uint8_t>(), d->qual.as<uint8_t>(), d->win.as<uint8_t>(), d->jobs.as<bt2gpu_dp_job>(),
 				d->aux.as<DpAux>(), c.job0, c.njobs, d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(),
 				d->cands.as<bt2gpu_dp_cand>(), d->rep.as<uint8_t>(), d->done.as<uint32_t>(), d->alns.as<bt2gpu_dp_aln>(),
