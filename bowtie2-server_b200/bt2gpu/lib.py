@@ -20,7 +20,7 @@ SYMBOLS = [
     "bt2gpu_reads_stage",
     "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
-    "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch",
+    "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
 ]
 
 _lib = None
@@ -221,6 +221,28 @@ class Context:
         h = self._ix.fw if which == "fw" else self._ix.bw
         _check(self.lib.bt2gpu_index_gather_probe(self._h, h, C.c_uint64(nloads), C.byref(g)))
         return float(g.value)
+
+    def hotpath_round0(self, text, seq, qual, reads, minsc, nceil, seed_len=22, ival=(1.0, 1.15), maxgap=15,
+                       max_aln=2, mine_max=2, nthreads=0, out=None):
+        """bt2gpu_hotpath_round0_batch: exactSweep -> seeds -> extend -> pick -> locate -> frame -> DP
+        for a batch of reads, glue in multi-threaded C++.  Returns (out dict, stats dict)."""
+        n = len(reads)
+        if out is None:
+            out = dict(sweep=np.zeros(n, dtype=structs.sweep_result), job_read=np.zeros(n, dtype=np.uint32),
+                       job_start=np.zeros(n, dtype=np.int64), job_fw=np.zeros(n, dtype=np.uint8),
+                       results=np.zeros(n, dtype=structs.dp_result), alns=np.zeros(n * max_aln, dtype=structs.dp_aln),
+                       edits=np.zeros(64 * n + 1024, dtype=structs.edit))
+        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, nthreads)
+        S = structs.HotpathStats()
+        nj, ne = C.c_size_t(0), C.c_size_t(0)
+        _check(self.lib.bt2gpu_hotpath_round0_batch(
+            self._h, self._ix.fw, self._ix.bw, _ptr(text), C.c_uint64(len(text)), _ptr(seq), _ptr(qual),
+            C.c_size_t(len(seq)), _ptr(reads), C.c_size_t(n), _ptr(minsc), _ptr(nceil), C.byref(P),
+            _ptr(out["sweep"]), _ptr(out["job_read"]), _ptr(out["job_start"]), _ptr(out["job_fw"]), C.byref(nj),
+            _ptr(out["results"]), _ptr(out["alns"]), _ptr(out["edits"]), C.c_size_t(len(out["edits"])), C.byref(ne),
+            C.byref(S)))
+        out["njobs"], out["nedits"] = nj.value, ne.value
+        return out, S.as_dict()
 
     def locate_stage(self, rows):
         rows = np.ascontiguousarray(rows, dtype=np.uint32)

@@ -78,3 +78,24 @@ def index_desc(e):
     d.zoff, d.len, d.off_rate, d.ftab_chars, d.is_fw = e.zoff, e.len, e.off_rate, e.ftab_chars, int(e.fw)
     d._keep = e
     return d
+
+
+import ctypes as _ct
+
+_HP_U64 = ("seeds", "seed_bwops", "seed_sides", "seed_hits", "sweep_bwops", "extend_fmops", "locate_rows",
+           "locate_steps", "dp_jobs", "dp_cells", "aligned", "h2d_bytes", "d2h_bytes")
+_HP_F32 = ("ms_sweep", "ms_seed", "ms_extend", "ms_locate", "ms_dp", "ms_dp_fill", "ms_dp_gather", "ms_dp_backtrace")
+
+
+class HotpathParams(_ct.Structure):
+    """bt2gpu_hotpath_params"""
+    _fields_ = [("seed_len", _ct.c_int32), ("ival_const", _ct.c_double), ("ival_coeff", _ct.c_double),
+                ("maxgap", _ct.c_int32), ("max_aln", _ct.c_uint32), ("mine_max", _ct.c_uint32), ("nthreads", _ct.c_int32)]
+
+
+class HotpathStats(_ct.Structure):
+    """bt2gpu_hotpath_stats"""
+    _fields_ = [(k, _ct.c_uint64) for k in _HP_U64] + [(k, _ct.c_float) for k in _HP_F32]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}

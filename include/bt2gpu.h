@@ -259,6 +259,49 @@ int bt2gpu_locate_stage(bt2gpu_ctx *ctx, const uint32_t *rows, size_t n);
 int bt2gpu_locate_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw);
 int bt2gpu_locate_fetch(bt2gpu_ctx *ctx, uint32_t *offs_out, uint32_t *steps_out);
 
+/* ======================================================================== */
+/* ---- batch runtime: one chained pass of the hot path --------------------- */
+
+/* What multiseedSearchWorker + SwDriver::extendSeeds do for one unpaired read in seed round 0
+ * (bt2_search.cpp:3440-4060, aligner_sw_driver.cpp:756-1297), for a whole batch with every
+ * arithmetic step on the GPU and the glue (seed instantiation aligner_seed.cpp:498-587, hit
+ * choice, DynProgFramer::frameSeedExtensionRect dp_framer.cpp:81-129, SwAligner::initRef
+ * window extraction aligner_sw.cpp:155-271) in multi-threaded C++:
+ *   exactSweep -> exact seeds -> extend -> pick one hit per read -> locate -> frame -> DP.
+ * The pick policy is deterministic (narrowest BW range, then longest exact extension, then
+ * first in seed order); the reference's RNG-driven policy (rankSeedHits / prioritizeSATups)
+ * is NOT reproduced here -- this call is the batch runtime's building block and the
+ * measurement path of bench.py, not a replacement of the driver's decisions. */
+typedef struct {
+	int32_t  seed_len;          /* -L (multiseedLen)                                       */
+	double   ival_const, ival_coeff;   /* seed interval S,<const>,<coeff> (msIval, bt2_search.cpp:3391) */
+	int32_t  maxgap;            /* DPRect::maxgap = min(max(rdgaps, rfgaps), maxhalf)      */
+	uint32_t max_aln;           /* nextAlignment() calls per window                        */
+	uint32_t mine_max;          /* exactSweep mineMax                                      */
+	int32_t  nthreads;          /* host threads for the glue (0 = hardware concurrency)    */
+} bt2gpu_hotpath_params;
+
+typedef struct {
+	uint64_t seeds, seed_bwops, seed_sides, seed_hits, sweep_bwops, extend_fmops,
+	         locate_rows, locate_steps, dp_jobs, dp_cells, aligned, h2d_bytes, d2h_bytes;
+	float    ms_sweep, ms_seed, ms_extend, ms_locate, ms_dp, ms_dp_fill, ms_dp_gather, ms_dp_backtrace;
+} bt2gpu_hotpath_stats;
+
+/* text = the joined reference (bytes 0..3, what the index was built over), host memory.
+ * Per read i: minsc[i], nceil[i].  Outputs (all host, caller-owned): sweep[nreads];
+ * job_read[nreads] = read id of DP job k (first *njobs entries valid); job_start[k] = text
+ * offset the oriented read was framed at; results[nreads], alns[nreads*max_aln],
+ * edits[edit_cap] indexed by DP job. */
+int bt2gpu_hotpath_round0_batch(
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+	const uint8_t *text, uint64_t text_len,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
+	const bt2gpu_hotpath_params *params,
+	bt2gpu_sweep_result *sweep, uint32_t *job_read, int64_t *job_start, uint8_t *job_fw, size_t *njobs,
+	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits,
+	bt2gpu_hotpath_stats *stats);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,5 +52,20 @@ def test_hot_path_chain_matches_oracle():
     got = ctx.dp_fetch()          # the chain's batch is still staged: fetch it again with the candidates
     for i in range(len(jobs)):
         assert dpio.results_to_py(*ref, i) == dpio.results_to_py(got[0], got[1], got[2], got[3], i), i
+    # the multi-threaded C++ glue (bt2gpu_hotpath_round0_batch) makes the same choices and gets the same answers
+    n = len(reads)
+    minsc = np.full(n, sc.score_min.f_int(150), dtype=np.int32)
+    nceil = np.full(n, sc.nceil(150), dtype=np.int32)
+    out, st = ctx.hotpath_round0(genome, np.ascontiguousarray(reads.reshape(-1)), np.ascontiguousarray(quals.reshape(-1)),
+                                 pool.reads, minsc, nceil, nthreads=4)
+    nj = out["njobs"]
+    assert nj == len(jobs) and st["dp_jobs"] == nj and st["seeds"] == len(sj)
+    assert np.array_equal(out["job_read"][:nj], L["rid"]) and np.array_equal(out["job_start"][:nj], L["start"])
+    assert np.array_equal(out["job_fw"][:nj].astype(bool), L["fw"])
+    assert out["sweep"].tobytes() == orc.exact_sweep().tobytes()
+    got2 = ctx.dp_fetch()
+    for i in range(nj):
+        assert dpio.results_to_py(*ref, i) == dpio.results_to_py(got2[0], got2[1], got2[2], got2[3], i), i
+    assert st["aligned"] == c["aligned"] and st["seed_bwops"] == c["seed_bwops"] and st["locate_steps"] == c["locate_steps"]
     assert ctx.gather_probe("fw", 1 << 22) > 0
     ctx.close()
