@@ -145,7 +145,11 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 			// 0 local), F(-1,j) = floor  (ee_u8.cpp:920-927, loc_u8.cpp:1066-1075)
 			const uint32_t top0 = pack2(0, fl);
 			if(l == 0) HtopPrev = (st == 0) ? pack2(0, fl) : FLv;
-			uint32_t *rec_base = mat + ax.mat_off + (size_t)st * T * GL * RW + l * 4;
+			// u8 end-to-end jobs (floor -255) store E/F/H as bytes: every value is in [-255, 0], so its low
+			// byte identifies it (0 -> 0, b -> b - 256); halves the matrix stream of the headline path
+			const bool rec8 = (fl == -255);
+			const int rwj = (int)ax.RW;
+			uint32_t *rec_base = mat + ax.mat_off + (size_t)st * T * GL * rwj + l * 4;
 			for(int t = 0; t < T; t++) {
 				const int col_lo = t - 2 * l;
 				int c = 5;
@@ -191,12 +195,32 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 					hdiag = Hprev[k]; Hprev[k] = H; Hup = H; Fup = F;
 				}
 				Hbot = Hup; Fbot = Fup;
+				if(rec8) {
+					constexpr int SH = (S + 1) / 2;               // words per matrix: 2 rows x 2 halves per word
+					constexpr int RW8 = (3 * SH + 3) & ~3;
+					uint32_t r8[RW8];
 #pragma unroll
-				for(int k = 3 * S; k < RW; k++) rec[k] = 0;
-				uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW);
+					for(int m = 0; m < 3; m++)
 #pragma unroll
-				for(int q = 0; q < RW / 4; q++)      // chunk q of the 8 lanes is one contiguous 128-byte line
-					dst[q * GL] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
+						for(int kp = 0; kp < SH; kp++) {
+							const uint32_t a = rec[m * S + 2 * kp];
+							const uint32_t b = (2 * kp + 1 < S) ? rec[m * S + 2 * kp + 1] : 0u;
+							r8[m * SH + kp] = __byte_perm(a, b, 0x6420);   // [lo(k), hi(k), lo(k+1), hi(k+1)] low bytes
+						}
+#pragma unroll
+					for(int k = 3 * SH; k < RW8; k++) r8[k] = 0;
+					uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW8);
+#pragma unroll
+					for(int q = 0; q < RW8 / 4; q++)
+						dst[q * GL] = make_uint4(r8[4 * q], r8[4 * q + 1], r8[4 * q + 2], r8[4 * q + 3]);
+				} else {
+#pragma unroll
+					for(int k = 3 * S; k < RW; k++) rec[k] = 0;
+					uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW);
+#pragma unroll
+					for(int q = 0; q < RW / 4; q++)      // chunk q of the 8 lanes is one contiguous 128-byte line
+						dst[q * GL] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
+				}
 			}
 			if(!lastStripe) __threadfence();   // boundary row visible to lane 0 of the next stripe
 		}
@@ -208,10 +232,11 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 // ---------------------------------------------------------------------------------------
 struct RowRef { int stT, v, k; };    // stripe * T, virtual lane and register of a DP row
 struct MatView {
-	const uint32_t *base; int S, T, RW;
+	const uint32_t *base; int S, T, RW, SH;
 	uint32_t invS, invRS; int stride;     // ceil(2^32 / S), ceil(2^32 / (16 S)), GL * RW
-	__device__ __forceinline__ void init(const uint32_t *b, int S_, int T_, int RW_) {
-		base = b; S = S_; T = T_; RW = RW_;
+	bool rec8;                            // byte records (u8 end-to-end path)
+	__device__ __forceinline__ void init(const uint32_t *b, int S_, int T_, int RW_, bool rec8_) {
+		base = b; S = S_; T = T_; RW = RW_; rec8 = rec8_; SH = (S_ + 1) >> 1;
 		invS = 0xffffffffu / (uint32_t)S + 1u; invRS = 0xffffffffu / (uint32_t)(VL * S) + 1u;
 		stride = GL * RW;
 	}
@@ -222,6 +247,12 @@ struct MatView {
 		return rr;
 	}
 	__device__ __forceinline__ int at(int m, const RowRef &rr, int col) const {
+		if(rec8) {
+			const int idx = m * SH + (rr.k >> 1);
+			const uint32_t w = __ldcg(base + (size_t)(rr.stT + col + rr.v) * stride + ((idx >> 2) * GL + (rr.v >> 1)) * 4 + (idx & 3));
+			const int b = (int)((w >> (8 * (((rr.k & 1) << 1) | (rr.v & 1)))) & 0xffu);
+			return b ? b - 256 : 0;
+		}
 		const int idx = m * S + rr.k;
 		const uint32_t w = __ldcg(base + (size_t)(rr.stT + col + rr.v) * stride + ((idx >> 2) * GL + (rr.v >> 1)) * 4 + (idx & 3));
 		return (rr.v & 1) ? hi16(w) : lo16(w);
@@ -256,7 +287,7 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	const DpAux ax = aux[ji];
 	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol;
 	const int minsc = jb.minsc;
-	MatView mv; mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW);
+	MatView mv; mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW, ax.fl == -255);
 	const uint8_t *rd = seq + jb.rd_off, *qu = qual + jb.rd_off, *rf = win + jb.rf_off;
 	const bool local = !c_sc.monotone;
 	if(EMIT && res[ji].ncand == 0) return;
@@ -534,7 +565,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 	const DpAux ax = aux[ji];
 	BtJob J;
 	J.nrow = (int)jb.rd_len; J.ncol = (int)jb.ncol;
-	J.mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW);
+	J.mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW, ax.fl == -255);
 	J.rd = seq + jb.rd_off; J.qu = qual + jb.rd_off; J.rf = win + jb.rf_off;
 	J.rp32 = reinterpret_cast<uint32_t*>(rep + ax.rep_off);
 	J.local = !c_sc.monotone; J.gapbar = c_sc.gapbar;
@@ -898,10 +929,10 @@ extern "C" int bt2gpu_dp_stage(
 		a.S = (uint32_t)kSClasses[c];
 		a.nstripes = (j.rd_len + 16 * a.S - 1) / (16 * a.S);
 		a.T = j.ncol + 16;
-		a.RW = (3 * a.S + 3) & ~3u;
 		if(local) a.fl = 0;
 		else if(j.enable8 && j.minsc >= -254) a.fl = -255;            // aligner_sw.cpp:518
 		else { a.fl = FL_I16; if(j.minsc < -15000) BT2_FAIL("minsc below the 16-bit end-to-end domain"); }
+		a.RW = (a.fl == -255) ? ((3 * ((a.S + 1) / 2) + 3) & ~3u) : ((3 * a.S + 3) & ~3u);   // byte records on the u8 path
 		const uint64_t mw = (uint64_t)a.nstripes * a.T * GL * a.RW;
 		if(mw > mat_budget_words) BT2_FAIL("single DP problem exceeds the matrix arena");
 		if(ch.mat_words + mw > mat_budget_words || ch.bound_words > 0x70000000u || ch.escr_edits > 0x70000000u) {

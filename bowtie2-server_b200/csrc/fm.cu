@@ -118,6 +118,11 @@ __device__ __forceinline__ void octet_lf(const IndexDev &ix, uint32_t top, uint3
 	topc = h ? oc : c;
 }
 
+// v[c] without dynamic register indexing (keeps t[]/b[] out of local memory)
+__device__ __forceinline__ uint32_t pick4(const uint32_t v[4], int c) {
+	return c == 0 ? v[0] : (c == 1 ? v[1] : (c == 2 ? v[2] : v[3]));
+}
+
 // ftabHi / ftabLo (bt2_idx.h:1425-1554)
 __device__ __forceinline__ uint32_t ftab_hi(const IndexDev &ix, uint32_t i) {
 	const uint32_t v = __ldg(ix.ftab + i);
@@ -171,7 +176,7 @@ static constexpr int SEED_TILE  = 256;
 __global__ void __launch_bounds__(SEED_BLOCK)
 k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seq,
              const bt2gpu_read *__restrict__ reads, const bt2gpu_seed_job *__restrict__ jobs,
-             uint32_t njobs, bt2gpu_seed_hit *__restrict__ out)
+             uint32_t njobs, uint32_t tile_sz, bt2gpu_seed_hit *__restrict__ out)
 {
 	__shared__ unsigned long long s_seq[SEED_TILE];
 	__shared__ int s_len[SEED_TILE];
@@ -179,9 +184,9 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 	const unsigned gmask = 0xffu << (lane & 24);
 	const int oct = threadIdx.x >> 3;                        // octet in block
 	constexpr int NOCT = SEED_BLOCK / 8;
-	for(uint32_t tile = blockIdx.x * SEED_TILE; tile < njobs; tile += gridDim.x * SEED_TILE) {
+	for(uint32_t tile = blockIdx.x * tile_sz; tile < njobs; tile += gridDim.x * tile_sz) {
 		__syncthreads();
-		{   // stage: one job per thread
+		if(threadIdx.x < tile_sz) {   // stage: one job per thread
 			const uint32_t ji = tile + threadIdx.x;
 			unsigned long long p = 0; int len = 0;
 			if(ji < njobs) {
@@ -196,7 +201,7 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 			s_seq[threadIdx.x] = p; s_len[threadIdx.x] = len;
 		}
 		__syncthreads();
-		for(int k = oct; k < SEED_TILE; k += NOCT) {
+		for(int k = oct; k < (int)tile_sz; k += NOCT) {
 			const uint32_t ji = tile + k;
 			if(ji >= njobs) break;
 			const unsigned long long p = s_seq[k];
@@ -231,12 +236,12 @@ k_seed_exact(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ s
 				nsides += (single || topf / 192u == botf / 192u) ? 1 : 2;
 				if(single) {                                    // mapLF1(row, l, c), bt2_idx.h:2420
 					if(topc != c || topf == fw.zoff) { alive = false; break; }
-					topf = t[c]; botf = topf + 1;               // mirror range unchanged
+					topf = pick4(t, c); botf = topf + 1;        // mirror range unchanged
 				} else {                                        // mapBiLFEx, bt2_idx.h:2372
 					uint32_t below = 0;
 #pragma unroll
 					for(int j = 0; j < 3; j++) if(j < c) below += b[j] - t[j];
-					topf = t[c]; botf = b[c];
+					topf = pick4(t, c); botf = pick4(b, c);
 					if(botf == topf) { alive = false; break; }
 					topb += below; botb = topb + (botf - topf);
 				}
@@ -303,8 +308,8 @@ k_exact_sweep(const IndexDev ix, const uint8_t *__restrict__ seq, const bt2gpu_r
 				if(single) {
 					bwops++;
 					if(topc != c || top == ix.zoff) top = bot = 0;
-					else { top = t[c]; bot = top + 1; }
-				} else { bwops += 2; top = t[c]; bot = b[c]; }
+					else { top = pick4(t, c); bot = top + 1; }
+				} else { bwops += 2; top = pick4(t, c); bot = pick4(b, c); }
 			}
 			if(bot <= top) {
 				nedit++;
@@ -341,7 +346,7 @@ k_locate(const IndexDev ix, const uint32_t *__restrict__ rows, uint32_t n,
 		if((row & ix.off_mask) == row) { res = jumps + __ldg(ix.offs + (row >> ix.off_rate)); break; }
 		uint32_t val[4]; int c;
 		quad_lf(ix, row, gmask, q, val, c);                      // mapLF(l), bt2_idx.h:2313
-		row = val[c];
+		row = pick4(val, c);
 		jumps++;
 	}
 	if(q == 0) { offs_out[i] = res; if(steps_out) steps_out[i] = jumps; }
@@ -378,7 +383,7 @@ __device__ __forceinline__ uint32_t extend_dir(const IndexDev &ix, const ReadVie
 			if(abort || (nonz != rdc && rdc <= 3) || bot - top < orig) break;
 		} else {
 			int c = -1;                                         // mapLF1(row&, l), bt2_idx.h:2451
-			if(top != ix.zoff) { c = topc; top = t[c]; }
+			if(top != ix.zoff) { c = topc; top = pick4(t, c); }
 			if(c != rdc && rdc <= 3) break;
 			bot = top + 1;
 		}
@@ -740,12 +745,19 @@ extern "C" int bt2gpu_seed_exact_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw, co
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	FmState *f = ctx->fm;
 	if(f->n_seed_jobs == 0) return 0;
-	uint32_t blocks = (uint32_t)((f->n_seed_jobs + SEED_TILE - 1) / SEED_TILE);
+	// tile = seeds staged per CTA pass: as small as keeps every resident octet busy (latency-bound walk:
+	// parallel seeds beat sequential ones), at most SEED_TILE
+	const uint64_t resident = (uint64_t)ctx->sm_count * 8 * (SEED_BLOCK / 8);   // octets resident on the device
+	uint32_t per_oct = (uint32_t)((f->n_seed_jobs + resident - 1) / resident);
+	if(per_oct < 1) per_oct = 1;
+	if(per_oct > SEED_TILE / (SEED_BLOCK / 8)) per_oct = SEED_TILE / (SEED_BLOCK / 8);
+	const uint32_t tile_sz = per_oct * (SEED_BLOCK / 8);
+	uint32_t blocks = (uint32_t)((f->n_seed_jobs + tile_sz - 1) / tile_sz);
 	const uint32_t maxb = (uint32_t)ctx->sm_count * 8;          // 8 resident CTAs of 256 threads per SM
-	if(blocks > maxb) blocks = maxb;
+	if(blocks > maxb && per_oct == SEED_TILE / (SEED_BLOCK / 8)) blocks = maxb;
 	if(ctx->kstart()) return 1;
 	k_seed_exact<<<blocks, SEED_BLOCK, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
-		f->sjobs.as<bt2gpu_seed_job>(), (uint32_t)f->n_seed_jobs, f->sout.as<bt2gpu_seed_hit>());
+		f->sjobs.as<bt2gpu_seed_job>(), (uint32_t)f->n_seed_jobs, tile_sz, f->sout.as<bt2gpu_seed_hit>());
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
 	if(ctx->kend()) return 1;
