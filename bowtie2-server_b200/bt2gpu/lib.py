@@ -21,6 +21,7 @@ SYMBOLS = [
     "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
+    "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes",
 ]
 
 _lib = None
@@ -41,6 +42,8 @@ def load():
         lib.bt2gpu_ctx_launches.restype = C.c_uint64
         lib.bt2gpu_dp_staged_cells.restype = C.c_uint64
         lib.bt2gpu_index_bytes.restype = C.c_uint64
+        lib.bt2gpu_ref_bytes.restype = C.c_uint64
+        lib.bt2gpu_ref_destroy.restype = None
         lib.bt2gpu_index_bytes.argtypes = [C.c_void_p]
         lib.bt2gpu_index_destroy.argtypes = [C.c_void_p]
         lib.bt2gpu_index_destroy.restype = None
@@ -222,10 +225,11 @@ class Context:
         _check(self.lib.bt2gpu_index_gather_probe(self._h, h, C.c_uint64(nloads), C.byref(g)))
         return float(g.value)
 
-    def hotpath_round0(self, text, seq, qual, reads, minsc, nceil, seed_len=22, ival=(1.0, 1.15), maxgap=15,
+    def hotpath_round0(self, ref, seq, qual, reads, minsc, nceil, seed_len=22, ival=(1.0, 1.15), maxgap=15,
                        max_aln=2, mine_max=2, nthreads=0, out=None):
         """bt2gpu_hotpath_round0_batch: exactSweep -> seeds -> extend -> pick -> locate -> frame -> DP
-        for a batch of reads, glue in multi-threaded C++.  Returns (out dict, stats dict)."""
+        for a batch of reads, every intermediate resident in HBM (ref = DeviceRef).  Returns
+        (out dict, stats dict)."""
         n = len(reads)
         if out is None:
             out = dict(sweep=np.zeros(n, dtype=structs.sweep_result), job_read=np.zeros(n, dtype=np.uint32),
@@ -236,7 +240,7 @@ class Context:
         S = structs.HotpathStats()
         nj, ne = C.c_size_t(0), C.c_size_t(0)
         _check(self.lib.bt2gpu_hotpath_round0_batch(
-            self._h, self._ix.fw, self._ix.bw, _ptr(text), C.c_uint64(len(text)), _ptr(seq), _ptr(qual),
+            self._h, self._ix.fw, self._ix.bw, ref.handle, _ptr(seq), _ptr(qual),
             C.c_size_t(len(seq)), _ptr(reads), C.c_size_t(n), _ptr(minsc), _ptr(nceil), C.byref(P),
             _ptr(out["sweep"]), _ptr(out["job_read"]), _ptr(out["job_start"]), _ptr(out["job_fw"]), C.byref(nj),
             _ptr(out["results"]), _ptr(out["alns"]), _ptr(out["edits"]), C.c_size_t(len(out["edits"])), C.byref(ne),
@@ -281,6 +285,33 @@ class DeviceIndex:
             if h:
                 self.lib.bt2gpu_index_destroy(h)
         self.fw, self.bw = C.c_void_p(0), C.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceRef:
+    """The joined reference text, 2 bits per base, resident in HBM (bt2gpu_ref_create): the device
+    counterpart of BitPairReference (reference.h:180) that SwAligner::initRef reads windows from."""
+
+    def __init__(self, text, device=0):
+        self.lib = load()
+        self.handle = C.c_void_p(0)
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        _check(self.lib.bt2gpu_ref_create(C.c_int(device), _ptr(text), C.c_uint64(len(text)), C.byref(self.handle)))
+        self.length = len(text)
+
+    @property
+    def nbytes(self):
+        return int(self.lib.bt2gpu_ref_bytes(self.handle))
+
+    def close(self):
+        if self.handle:
+            self.lib.bt2gpu_ref_destroy(self.handle)
+        self.handle = C.c_void_p(0)
 
     def __del__(self):
         try:

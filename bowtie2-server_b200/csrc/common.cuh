@@ -63,6 +63,10 @@ struct HostBuf {
 struct DpState;   // dp.cu
 struct FmState;   // fm.cu
 
+// ---- internal, device-resident plumbing of the chained batch runtime (hotpath.cu) ----
+struct FmReadsDev { const uint8_t *seq, *qual; const bt2gpu_read *reads; };
+struct DpDevPools { uint8_t *seq, *qual, *win; bt2gpu_dp_job *jobs; };
+
 } // namespace bt2
 
 struct bt2gpu_ctx {
@@ -89,3 +93,19 @@ struct bt2gpu_ctx {
 		return 0;
 	}
 };
+
+namespace bt2 {
+// fm.cu: same kernels as the C-ABI entry points, device pointers in and out, no synchronisation
+int fm_hp_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view);
+int fm_hp_sweep(bt2gpu_ctx *ctx, const bt2gpu_index *fw, uint32_t mine_max, bt2gpu_sweep_result **dev_out);
+int fm_hp_seed(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_seed_job *djobs,
+               size_t njobs, bt2gpu_seed_hit *dout);
+int fm_hp_extend(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_extend_job *djobs,
+                 size_t njobs, bt2gpu_extend_result *dout);
+int fm_hp_locate(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const uint32_t *drows, size_t n, uint32_t *doffs, uint32_t *dsteps);
+// dp.cu: DP problems whose reads, windows and job table are written by a kernel
+int dp_dev_begin(bt2gpu_ctx *ctx, size_t njobs, size_t pool_len, size_t win_len, uint32_t max_aln, size_t cand_cap,
+                 size_t edit_cap, DpDevPools *pools);
+int dp_dev_finish(bt2gpu_ctx *ctx);
+}

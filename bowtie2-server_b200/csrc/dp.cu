@@ -27,6 +27,7 @@
 // local, and -16000 for the i16 end-to-end path (the reference's floor of -65535 is
 // unreachable for the supported read lengths; checked in stage()).
 #include "common.cuh"
+#include "scan.cuh"
 #include <algorithm>
 
 namespace bt2 {
@@ -807,6 +808,9 @@ struct DpState {
 	DevBuf seq, qual, win, jobs, aux, order, res, counts, cand_off, fillptr, keys, cands, done,
 	       alns, edits, escr, mat, bound, rep, scal;   // scal: [0]=total cands, [1]=total edits, [2]=errflag
 	HostBuf h_scal;
+	DevBuf cls, sizes, soffs, spart, dsum;   // device-side staging scratch
+	HostBuf h_dsum;
+	size_t dev_pool_len = 0, dev_win_len = 0;
 	int maxcol_all = 0;
 	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};   // fill | gather | backtrace boundaries (single-chunk runs)
 	uint32_t ev_phases = 0;
@@ -844,6 +848,93 @@ static int dispatch_fill(bt2gpu_ctx *ctx, DpState *d, int cls, const uint32_t *o
 	case 16: return launch_fill<16>(ctx, d, order, n);
 	}
 	BT2_FAIL("bad S class");
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Device-side staging (chained batch runtime): the job table, reads and windows were written
+// by a kernel, so the per-job layout (class, arena offsets, launch order) is computed here too.
+// ---------------------------------------------------------------------------------------
+struct DpSizes { unsigned long long mat, rep; uint32_t bound, escr; };
+__host__ __device__ __forceinline__ DpSizes operator+(const DpSizes &a, const DpSizes &b) {
+	DpSizes r; r.mat = a.mat + b.mat; r.rep = a.rep + b.rep; r.bound = a.bound + b.bound; r.escr = a.escr + b.escr; return r;
+}
+// summary read back by the host: [0..7] jobs per class, [8] max ncol, [9] error code, then cells (u64 at word 10)
+static constexpr int DPSUM_WORDS = 16;
+__constant__ int c_sclasses[8] = {3, 4, 5, 6, 8, 10, 12, 16};
+
+__global__ void __launch_bounds__(256)
+k_dp_aux(const bt2gpu_dp_job *__restrict__ jobs, uint32_t njobs, unsigned long long pool_len, unsigned long long win_len,
+         int local, DpAux *__restrict__ aux, uint8_t *__restrict__ cls, DpSizes *__restrict__ sizes, uint32_t *__restrict__ sum)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long cells = 0;
+	if(i < njobs) {
+		const bt2gpu_dp_job j = jobs[i];
+		int err = 0;
+		if(j.rd_len == 0 || j.ncol == 0) err = 1;
+		else if((unsigned long long)j.rd_off + j.rd_len > pool_len || (unsigned long long)j.rf_off + j.ncol + 1 > win_len) err = 2;
+		else if(j.ncol > 60000 || j.rd_len > 60000) err = 3;
+		else if(!local && j.rd_len > 2270) err = 4;
+		else if(local && j.rd_len > 16000) err = 5;
+		DpAux a; memset(&a, 0, sizeof(a));
+		int best = -1; long long bestRows = 0, bestStripes = 0;            // choose_class
+		for(int c = 0; c < 8; c++) {
+			const long long rs = 16LL * c_sclasses[c], ns = ((long long)j.rd_len + rs - 1) / rs, rows = ns * rs;
+			if(best < 0 || rows < bestRows || (rows == bestRows && ns < bestStripes)) { best = c; bestRows = rows; bestStripes = ns; }
+		}
+		a.S = (uint32_t)c_sclasses[best];
+		a.nstripes = (j.rd_len + 16 * a.S - 1) / (16 * a.S);
+		a.T = j.ncol + 16;
+		if(local) a.fl = 0;
+		else if(j.enable8 && j.minsc >= -254) a.fl = -255;
+		else { a.fl = FL_I16; if(j.minsc < -15000) err = 6; }
+		a.RW = (a.fl == -255) ? ((3 * ((a.S + 1) / 2) + 3) & ~3u) : ((3 * a.S + 3) & ~3u);
+		DpSizes z;
+		z.mat = (unsigned long long)a.nstripes * a.T * GL * a.RW;
+		z.rep = (((unsigned long long)j.rd_len * j.ncol + 31) / 32) * 4;
+		z.bound = 2 * j.ncol; z.escr = j.rd_len + j.ncol + 4;
+		if(err) { atomicMax(&sum[9], (uint32_t)err); z.mat = z.rep = 0; z.bound = z.escr = 0; }
+		aux[i] = a; cls[i] = (uint8_t)best; sizes[i] = z;
+		atomicAdd(&sum[best], 1u);
+		atomicMax(&sum[8], j.ncol);
+		cells = (unsigned long long)j.rd_len * j.ncol;
+	}
+	for(int o = 16; o; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+	if((threadIdx.x & 31) == 0 && cells) atomicAdd(reinterpret_cast<unsigned long long*>(sum + 10), cells);
+}
+
+__global__ void __launch_bounds__(256)
+k_dp_aux_apply(DpAux *__restrict__ aux, const DpSizes *__restrict__ offs, uint32_t njobs) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= njobs) return;
+	const DpSizes o = offs[i];
+	aux[i].mat_off = o.mat; aux[i].rep_off = o.rep; aux[i].bound_off = o.bound; aux[i].escr_off = o.escr;
+}
+
+// launch order: by class, in job order inside a class.  One block per class walks the class
+// bytes in tiles of 1024 and compacts the matching job ids.
+__global__ void __launch_bounds__(1024)
+k_dp_order(const uint8_t *__restrict__ cls, uint32_t njobs, const uint32_t *__restrict__ sum, uint32_t *__restrict__ order) {
+	__shared__ uint32_t wsum[32];
+	__shared__ uint32_t carry;
+	const int c = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+	if(threadIdx.x == 0) { uint32_t b = 0; for(int k = 0; k < c; k++) b += sum[k]; carry = b; }
+	__syncthreads();
+	if(sum[c] == 0) return;
+	for(uint32_t base = 0; base < njobs; base += 1024) {
+		const uint32_t i = base + threadIdx.x;
+		const bool m = i < njobs && cls[i] == c;
+		const unsigned bal = __ballot_sync(0xffffffffu, m);
+		if(lane == 0) wsum[w] = __popc(bal);
+		__syncthreads();
+		uint32_t off = carry;
+		for(int k = 0; k < w; k++) off += wsum[k];
+		if(m) order[off + __popc(bal & ((1u << lane) - 1u))] = i;
+		__syncthreads();
+		if(threadIdx.x == 0) { uint32_t t = 0; for(int k = 0; k < 32; k++) t += wsum[k]; carry += t; }
+		__syncthreads();
+	}
 }
 
 static int choose_class(int nrow) {
@@ -1090,13 +1181,101 @@ extern "C" int bt2gpu_dp_align_batch(
 }
 
 namespace bt2 {
+
+static int dp_reserve_common(DpState *d, size_t njobs, size_t pool_len, size_t win_len) {
+	if(d->seq.reserve(pool_len) || d->qual.reserve(pool_len) || d->win.reserve(win_len) ||
+	   d->jobs.reserve(njobs * sizeof(bt2gpu_dp_job)) || d->aux.reserve(njobs * sizeof(DpAux)) ||
+	   d->order.reserve(njobs * 4) || d->res.reserve(njobs * sizeof(bt2gpu_dp_result)) ||
+	   d->counts.reserve(njobs * 4) || d->cand_off.reserve(njobs * 4) || d->fillptr.reserve(njobs * 4) ||
+	   d->keys.reserve(d->cand_cap * 8) || d->cands.reserve(d->cand_cap * sizeof(bt2gpu_dp_cand)) ||
+	   d->done.reserve(d->cand_cap * 4) || d->alns.reserve(njobs * d->max_aln * sizeof(bt2gpu_dp_aln)) ||
+	   d->edits.reserve(d->edit_cap * sizeof(bt2gpu_edit)) || d->scal.reserve(64) || d->h_scal.reserve(64)) return 1;
+	return 0;
+}
+
+int dp_dev_begin(bt2gpu_ctx *ctx, size_t njobs, size_t pool_len, size_t win_len, uint32_t max_aln, size_t cand_cap,
+                 size_t edit_cap, DpDevPools *pools)
+{
+	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set must be called first");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	if(!ctx->dp) ctx->dp = new DpState();
+	DpState *d = ctx->dp;
+	d->njobs = njobs; d->max_aln = max_aln ? max_aln : 1; d->cand_cap = cand_cap; d->edit_cap = edit_cap;
+	d->chunks.clear(); d->cells = 0; d->maxcol_all = 0;
+	d->dev_pool_len = pool_len; d->dev_win_len = win_len;
+	if(njobs > 0x7fffffffu / d->max_aln) BT2_FAIL("too many jobs");
+	if(2 * (uint64_t)win_len > 0x70000000u || (uint64_t)pool_len + win_len + 4 * njobs > 0x70000000u)
+		BT2_FAIL("DP batch too large for 32-bit scratch offsets: split the batch");
+	if(dp_reserve_common(d, njobs, pool_len + 16, win_len + 16)) return 1;
+	if(d->cls.reserve(njobs + 16) || d->sizes.reserve((njobs + 1) * sizeof(DpSizes)) || d->soffs.reserve((njobs + 1) * sizeof(DpSizes)) ||
+	   d->spart.reserve((scan_parts(njobs) + 2) * sizeof(DpSizes)) || d->dsum.reserve(DPSUM_WORDS * 4 + sizeof(DpSizes)) ||
+	   d->h_dsum.reserve(DPSUM_WORDS * 4 + sizeof(DpSizes))) return 1;
+	pools->seq = d->seq.as<uint8_t>(); pools->qual = d->qual.as<uint8_t>(); pools->win = d->win.as<uint8_t>();
+	pools->jobs = d->jobs.as<bt2gpu_dp_job>();
+	return 0;
+}
+
+int dp_dev_finish(bt2gpu_ctx *ctx) {
+	DpState *d = ctx->dp;
+	if(!d) BT2_FAIL("nothing staged");
+	const size_t njobs = d->njobs;
+	if(njobs == 0) return 0;
+	cudaStream_t s = ctx->stream;
+	const bool local = !ctx->sc.monotone;
+	uint32_t *sum = d->dsum.as<uint32_t>();
+	DpSizes *total = reinterpret_cast<DpSizes*>(sum + DPSUM_WORDS);
+	BT2_CUDA(cudaMemsetAsync(sum, 0, DPSUM_WORDS * 4, s));
+	const unsigned nb = (unsigned)((njobs + 255) / 256);
+	k_dp_aux<<<nb, 256, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), (uint32_t)njobs, d->dev_pool_len, d->dev_win_len, local ? 1 : 0,
+		d->aux.as<DpAux>(), d->cls.as<uint8_t>(), d->sizes.as<DpSizes>(), sum);
+	if(dev_exclusive_scan<DpSizes>(ctx, d->sizes.as<DpSizes>(), d->soffs.as<DpSizes>(), d->spart.as<DpSizes>(), total, njobs)) return 1;
+	k_dp_aux_apply<<<nb, 256, 0, s>>>(d->aux.as<DpAux>(), d->soffs.as<DpSizes>(), (uint32_t)njobs);
+	k_dp_order<<<kNClasses, 1024, 0, s>>>(d->cls.as<uint8_t>(), (uint32_t)njobs, sum, d->order.as<uint32_t>());
+	ctx->launches += 3;
+	BT2_CUDA(cudaGetLastError());
+	BT2_CUDA(cudaMemcpyAsync(d->h_dsum.p, sum, DPSUM_WORDS * 4 + sizeof(DpSizes), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamSynchronize(s));
+	const uint32_t *hs = d->h_dsum.as<uint32_t>();
+	switch(hs[9]) {
+	case 0: break;
+	case 1: BT2_FAIL("empty DP problem");
+	case 2: BT2_FAIL("job outside pool");
+	case 3: BT2_FAIL("DP problem too large");
+	case 4: BT2_FAIL("end-to-end read longer than 2270 rows: checkpointed path (rdlen >= cminlen, aligner_sw.cpp:514) not implemented");
+	case 5: BT2_FAIL("local read longer than 16000 rows not supported by the s16 domain");
+	default: BT2_FAIL("minsc below the 16-bit end-to-end domain");
+	}
+	DpSizes tot; memcpy(&tot, hs + DPSUM_WORDS, sizeof(tot));
+	size_t freeB = 0, totalB = 0;
+	BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
+	const uint64_t mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
+	if(tot.mat > mat_budget_words) BT2_FAIL("DP batch exceeds the matrix arena: split the batch");
+	DpChunk ch; memset(&ch, 0, sizeof(ch));
+	ch.job0 = 0; ch.njobs = (uint32_t)njobs; ch.mat_words = tot.mat; ch.rep_bytes = tot.rep;
+	ch.bound_words = tot.bound; ch.escr_edits = tot.escr; ch.maxcol = (int)hs[8];
+	uint32_t pos = 0;
+	for(int c = 0; c < kNClasses; c++) { ch.cls_off[c] = pos; pos += hs[c]; }
+	ch.cls_off[kNClasses] = pos;
+	if(pos != njobs) BT2_FAIL("internal: class histogram does not cover the batch");
+	d->chunks.push_back(ch);
+	d->maxcol_all = ch.maxcol;
+	memcpy(&d->cells, hs + 10, 8);
+	if(d->escr.reserve((size_t)tot.escr * sizeof(bt2gpu_edit)) || d->mat.reserve(tot.mat * 4) ||
+	   d->bound.reserve((size_t)tot.bound * 4) || d->rep.reserve(tot.rep)) return 1;
+	return 0;
+}
+
+} // namespace bt2
+
+namespace bt2 {
+const bt2gpu_dp_result *dp_dev_results(bt2gpu_ctx *ctx) { return ctx->dp ? ctx->dp->res.as<bt2gpu_dp_result>() : nullptr; }
 void dp_state_free(DpState *d) {
 	if(!d) return;
 	DevBuf *bufs[] = { &d->seq, &d->qual, &d->win, &d->jobs, &d->aux, &d->order, &d->res, &d->counts, &d->cand_off,
 	                   &d->fillptr, &d->keys, &d->cands, &d->done, &d->alns, &d->edits, &d->escr, &d->mat, &d->bound,
-	                   &d->rep, &d->scal };
+	                   &d->rep, &d->scal, &d->cls, &d->sizes, &d->soffs, &d->spart, &d->dsum };
 	for(DevBuf *b : bufs) b->release();
-	d->h_scal.release();
+	d->h_scal.release(); d->h_dsum.release();
 	for(int i = 0; i < 4; i++) if(d->ev[i]) cudaEventDestroy(d->ev[i]);
 	delete d;
 }

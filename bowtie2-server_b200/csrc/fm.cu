@@ -402,6 +402,10 @@ k_extend(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seq,
 	const uint32_t ji = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
 	if(ji >= njobs) return;
 	const bt2gpu_extend_job jb = jobs[ji];
+	if(jb.botf <= jb.topf) {          // not a hit (the chained batch runtime passes every seed): nothing to extend
+		if(l8 == 0) { out[ji].nlex = 0; out[ji].nrex = 0; out[ji].fmops = 0; }
+		return;
+	}
 	ReadView s; s.rd = seq + reads[jb.read].rd_off; s.len = (int)reads[jb.read].rd_len; s.rc = !jb.fw; s.rev = false;
 	const int rdlen = s.len, off = jb.off, len = jb.len;
 	uint32_t fmops = 0, nlex = 0, nrex = 0;
@@ -717,6 +721,94 @@ extern "C" int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, cons
 	for(size_t i = 0; i < nreads; i++) f->rdlen[i] = reads[i].rd_len;
 	return 0;
 }
+
+
+// ---- device-resident launches for the chained batch runtime (hotpath.cu) -----------------
+// Same kernels as the entry points below; inputs and outputs stay in HBM, nothing synchronises.
+namespace bt2 {
+
+int fm_hp_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view)
+{
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	FmState *f = fm_state(ctx);
+	f->nreads = 0;
+	if(f->seq.reserve(pool_len + 16) || f->qual.reserve(pool_len + 16) || f->reads.reserve(nreads * sizeof(bt2gpu_read) + 16)) return 1;
+	cudaStream_t s = ctx->stream;
+	BT2_CUDA(cudaMemcpyAsync(f->seq.p, seq_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(f->qual.p, qual_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(f->reads.p, reads, nreads * sizeof(bt2gpu_read), cudaMemcpyHostToDevice, s));
+	// validation runs while the copies are in flight
+	f->rdlen.resize(nreads);
+	for(size_t i = 0; i < nreads; i++) {
+		if((size_t)reads[i].rd_off + reads[i].rd_len > pool_len) BT2_FAIL("read outside pool");
+		if(reads[i].rd_len == 0 || reads[i].rd_len > 65000) BT2_FAIL("read length must be in 1..65000");
+		f->rdlen[i] = reads[i].rd_len;
+	}
+	f->nreads = nreads; f->pool_len = pool_len;
+	view->seq = f->seq.as<uint8_t>(); view->qual = f->qual.as<uint8_t>(); view->reads = f->reads.as<bt2gpu_read>();
+	return 0;
+}
+
+int fm_hp_sweep(bt2gpu_ctx *ctx, const bt2gpu_index *fw, uint32_t mine_max, bt2gpu_sweep_result **dev_out) {
+	if(check_idx(ctx, fw, false)) return 1;
+	FmState *f = ctx->fm;
+	const size_t n = f->nreads;
+	if(f->out.reserve(n * sizeof(bt2gpu_sweep_result))) return 1;
+	cudaStream_t s = ctx->stream;
+	BT2_CUDA(cudaMemsetAsync(f->out.p, 0, n * sizeof(bt2gpu_sweep_result), s));
+	k_exact_sweep<<<blocks_for(2 * n, 8, 256), 256, 0, s>>>(fw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
+		(uint32_t)n, 0, 0, mine_max, f->out.as<bt2gpu_sweep_result>());
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	*dev_out = f->out.as<bt2gpu_sweep_result>();
+	return 0;
+}
+
+int fm_hp_seed(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_seed_job *djobs,
+               size_t njobs, bt2gpu_seed_hit *dout)
+{
+	if(check_idx(ctx, fw, false) || check_idx(ctx, bw, false)) return 1;
+	if(fw->dev.ftab_chars != bw->dev.ftab_chars) BT2_FAIL("forward and mirror index disagree on ftabChars");
+	if(njobs == 0) return 0;
+	FmState *f = ctx->fm;
+	const uint64_t resident = (uint64_t)ctx->sm_count * 8 * (SEED_BLOCK / 8);
+	uint32_t per_oct = (uint32_t)((njobs + resident - 1) / resident);
+	if(per_oct < 1) per_oct = 1;
+	if(per_oct > SEED_TILE / (SEED_BLOCK / 8)) per_oct = SEED_TILE / (SEED_BLOCK / 8);
+	const uint32_t tile_sz = per_oct * (SEED_BLOCK / 8);
+	uint32_t blocks = (uint32_t)((njobs + tile_sz - 1) / tile_sz);
+	const uint32_t maxb = (uint32_t)ctx->sm_count * 8;
+	if(blocks > maxb && per_oct == SEED_TILE / (SEED_BLOCK / 8)) blocks = maxb;
+	k_seed_exact<<<blocks, SEED_BLOCK, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
+		djobs, (uint32_t)njobs, tile_sz, dout);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	return 0;
+}
+
+int fm_hp_extend(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_extend_job *djobs,
+                 size_t njobs, bt2gpu_extend_result *dout)
+{
+	if(njobs == 0) return 0;
+	FmState *f = ctx->fm;
+	k_extend<<<blocks_for(njobs, 8, 256), 256, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
+		djobs, (uint32_t)njobs, dout);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	return 0;
+}
+
+int fm_hp_locate(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const uint32_t *drows, size_t n, uint32_t *doffs, uint32_t *dsteps) {
+	if(check_idx(ctx, fw, true)) return 1;
+	if(n == 0) return 0;
+	k_locate<<<blocks_for(n, 4, 256), 256, 0, ctx->stream>>>(fw->dev, drows, (uint32_t)n, doffs, dsteps);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	return 0;
+}
+
+} // namespace bt2
 
 // ---- exact seeds ------------------------------------------------------------------------
 extern "C" int bt2gpu_seed_exact_stage(bt2gpu_ctx *ctx, const bt2gpu_seed_job *jobs, size_t njobs) {

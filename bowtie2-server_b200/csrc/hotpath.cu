@@ -1,51 +1,261 @@
 // hotpath.cu — batch runtime: one chained pass of the hot path (include/bt2gpu.h,
-// bt2gpu_hotpath_round0_batch).  Host C++ only: the arithmetic runs in the kernels of fm.cu and
-// dp.cu through the same C-ABI entry points a caller would use; what is here is the glue the
-// reference executes per read between those calls -- seed instantiation
-// (aligner_seed.cpp:498-587), choosing a seed hit to extend, framing the window
-// (dp_framer.cpp:81-129) and fetching it as masks (aligner_sw.cpp:155-271) -- done per batch on
-// several host threads into pinned staging buffers.
+// bt2gpu_hotpath_round0_batch), resident in HBM from the staged reads to the alignments.
+// The arithmetic runs in the kernels of fm.cu and dp.cu; what is here is the glue the reference
+// executes per read between those calls -- seed instantiation (aligner_seed.cpp:498-587),
+// choosing a seed hit to extend, framing the window (dp_framer.cpp:81-129) and fetching it as
+// masks from the 2-bit reference (aligner_sw.cpp:155-271, reference.cpp getStretch) -- written
+// as small kernels over the whole batch, so that no intermediate (seed jobs, BW ranges, rows,
+// offsets, windows, DP job table) ever crosses PCIe.  The host reads back three scalars on the
+// way (seed count, DP job count, arena totals) to size the next launches.
 #include "common.cuh"
+#include "scan.cuh"
 #include <algorithm>
 #include <cmath>
-#include <thread>
-#include <functional>
+#include <chrono>
+
+// 2-bit reference text on the device (BitPairReference::buf_, reference.h:180; `.4.bt2` layout:
+// base i in bits 2*(i&15).. of word i>>4)
+struct bt2gpu_ref {
+	int device = 0;
+	uint64_t len = 0;
+	bt2::DevBuf packed;
+};
 
 namespace bt2 {
 
+typedef unsigned long long u64;
+
 struct HpState {
-	HostBuf sjobs, shits, xjobs, xres, rows, offs, steps, dseq, dqual, dwin, djobs, pickidx;
-	std::vector<uint32_t> seed_count, seed_first;      // per read
-	std::vector<uint32_t> hit_idx;                     // seed-job index of each extend job
+	DevBuf cnt, first, spart, tot, sjobs, shits, xjobs, xres, pick, val, ppos, pk_read, pk_seed, rows, rdoff, offs, steps,
+	       minsc, nceil, job_read, job_start, job_fw, stats;
+	HostBuf h_tot, h_stats;
+	cudaEvent_t ev[12] = {};
 };
 
-template<typename F> static void parallel_for(size_t n, int nthreads, F f) {
-	if(nthreads <= 1 || n < 2048) { f(0, n); return; }
-	std::vector<std::thread> th;
-	const size_t chunk = (n + nthreads - 1) / nthreads;
-	for(int t = 0; t < nthreads; t++) {
-		const size_t lo = t * chunk, hi = std::min(n, lo + chunk);
-		if(lo >= hi) break;
-		th.emplace_back([=]() { f(lo, hi); });
-	}
-	for(auto &x : th) x.join();
+enum { ST_SEED_BWOPS = 0, ST_SEED_SIDES, ST_SEED_HITS, ST_EXT_FMOPS, ST_LOC_STEPS, ST_ALIGNED, ST_SWEEP_BWOPS, ST_N };
+
+// msIval.f<int>(len) for SIMPLE_FUNC_SQRT (simple_func.h:89-112), then max(.,1) (bt2_search.cpp:3396);
+// explicit round-to-nearest steps so that the product is not contracted into an fma
+__device__ __forceinline__ int seed_interval(double c, double l, uint32_t rdlen) {
+	double v = __dadd_rn(c, __dmul_rn(l, sqrt((double)rdlen)));
+	if(v < 0.0) v = 0.0;
+	const int iv = (int)v;
+	return iv < 1 ? 1 : iv;
 }
 
-// msIval.f<int>(len) for SIMPLE_FUNC_SQRT (simple_func.h:89-112), then max(.,1) (bt2_search.cpp:3396)
-static inline int seed_interval(double c, double l, uint32_t rdlen) {
-	double v = c + l * std::sqrt((double)rdlen);
-	if(v < 0.0) v = 0.0;
-	int iv = (int)v;
-	return iv < 1 ? 1 : iv;
+// ---- seed instantiation: count, then emit (fw seeds of a read, then its rc seeds) ----------
+template<bool EMIT> __global__ void __launch_bounds__(256)
+k_hp_seeds(const uint8_t *__restrict__ seq, const bt2gpu_read *__restrict__ reads, uint32_t nreads, int L, double ic, double il,
+           uint32_t *__restrict__ cnt, const uint32_t *__restrict__ first, bt2gpu_seed_job *__restrict__ out)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= nreads) return;
+	const uint32_t rdlen = reads[i].rd_len;
+	const uint8_t *rd = seq + reads[i].rd_off;
+	const int per = seed_interval(ic, il, rdlen);
+	const int sl = (int)min((uint32_t)L, rdlen);
+	int nseeds = 1;
+	if((int)rdlen > L) nseeds += ((int)rdlen - L) / per;
+	uint32_t c = 0;
+	bt2gpu_seed_job *o = EMIT ? out + first[i] : nullptr;
+	const uint32_t half = EMIT ? cnt[i] / 2 : 0;
+	int lastN = -1, scanned = 0;                      // position of the last N seen in rd[0, scanned)
+	for(int k = 0; k < nseeds; k++) {
+		const int depth = k * per, end = depth + sl;
+		for(; scanned < end; scanned++) if(rd[scanned] > 3) lastN = scanned;
+		if(lastN >= depth) continue;                  // window holds an N: the reference drops it (:556-566)
+		if(EMIT) {
+			bt2gpu_seed_job j; j.read = i; j.off = (uint16_t)depth; j.len = (uint8_t)sl; j.fw = 1;
+			o[c] = j; j.fw = 0; o[half + c] = j;
+		}
+		c++;
+	}
+	if(!EMIT) cnt[i] = 2 * c;
+}
+
+// ---- every seed becomes an extend job (k_extend skips the empty ranges) --------------------
+__global__ void __launch_bounds__(256)
+k_hp_mkextend(const bt2gpu_seed_job *__restrict__ sj, const bt2gpu_seed_hit *__restrict__ sh, uint32_t n,
+              bt2gpu_extend_job *__restrict__ xj, u64 *__restrict__ stats)
+{
+	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+	u64 bw = 0, sd = 0, hit = 0;
+	if(k < n) {
+		const bt2gpu_seed_job j = sj[k]; const bt2gpu_seed_hit h = sh[k];
+		bt2gpu_extend_job x; memset(&x, 0, sizeof(x));
+		x.read = j.read; x.topf = h.topf; x.botf = h.botf; x.topb = h.topb; x.botb = h.botb; x.off = j.off; x.len = j.len; x.fw = j.fw;
+		xj[k] = x;
+		bw = h.bwops; sd = h.sides; hit = h.botf > h.topf;
+	}
+	for(int o = 16; o; o >>= 1) {
+		bw += __shfl_xor_sync(0xffffffffu, bw, o); sd += __shfl_xor_sync(0xffffffffu, sd, o); hit += __shfl_xor_sync(0xffffffffu, hit, o);
+	}
+	if((threadIdx.x & 31) == 0) {
+		if(bw) atomicAdd(stats + ST_SEED_BWOPS, bw);
+		if(sd) atomicAdd(stats + ST_SEED_SIDES, sd);
+		if(hit) atomicAdd(stats + ST_SEED_HITS, hit);
+	}
+}
+
+// ---- one hit per read: narrowest range, then longest exact extension, then first ----------
+// val[i] = (1 << 32) | rdlen for a read that goes on to DP, 0 otherwise (scanned next)
+__global__ void __launch_bounds__(256)
+k_hp_pick(const bt2gpu_read *__restrict__ reads, uint32_t nreads, const uint32_t *__restrict__ first, const uint32_t *__restrict__ cnt,
+          const bt2gpu_extend_job *__restrict__ xj, const bt2gpu_extend_result *__restrict__ xr,
+          uint32_t *__restrict__ pick, u64 *__restrict__ val, u64 *__restrict__ stats)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	u64 fm = 0;
+	if(i < nreads) {
+		const uint32_t lo = first[i], hi = lo + cnt[i];
+		uint32_t best = 0xffffffffu, bsz = 0, bex = 0;
+		for(uint32_t e = lo; e < hi; e++) {
+			const uint32_t sz = xj[e].botf - xj[e].topf;
+			if(xj[e].botf <= xj[e].topf) continue;
+			const bt2gpu_extend_result r = xr[e];
+			fm += r.fmops;
+			const uint32_t ex = (uint32_t)r.nlex + r.nrex;
+			if(best == 0xffffffffu || sz < bsz || (sz == bsz && ex > bex)) { best = e; bsz = sz; bex = ex; }
+		}
+		pick[i] = best;
+		val[i] = best == 0xffffffffu ? 0ull : ((1ull << 32) | reads[i].rd_len);
+	}
+	for(int o = 16; o; o >>= 1) fm += __shfl_xor_sync(0xffffffffu, fm, o);
+	if((threadIdx.x & 31) == 0 && fm) atomicAdd(stats + ST_EXT_FMOPS, fm);
+}
+
+__global__ void __launch_bounds__(256)
+k_hp_compact(uint32_t nreads, const uint32_t *__restrict__ pick, const u64 *__restrict__ pos, const bt2gpu_extend_job *__restrict__ xj,
+             uint32_t *__restrict__ pk_read, uint32_t *__restrict__ pk_seed, uint32_t *__restrict__ rows, uint32_t *__restrict__ rdoff)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= nreads || pick[i] == 0xffffffffu) return;
+	const uint32_t k = (uint32_t)(pos[i] >> 32);
+	pk_read[k] = i; pk_seed[k] = pick[i]; rows[k] = xj[pick[i]].topf; rdoff[k] = (uint32_t)pos[i];
+}
+
+// ---- frame the window around the located seed and fetch it as masks; orient the read --------
+// One warp per DP problem.  DynProgFramer::frameSeedExtensionRect with maxgap on both sides
+// (dp_framer.cpp:81-129): the oriented read is laid at text offset `start`, the window spans
+// [start - 2*maxgap, start + rdlen + 2*maxgap], the core diagonals are [maxgap, 3*maxgap].
+// Window bytes are 1 << base, 16 outside the text, plus one pad column (aligner_sw.cpp:155-271).
+__global__ void __launch_bounds__(256)
+k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const bt2gpu_read *__restrict__ reads,
+           const uint32_t *__restrict__ text2, u64 text_len, uint32_t npick, int mg,
+           const uint32_t *__restrict__ pk_read, const uint32_t *__restrict__ pk_seed, const uint32_t *__restrict__ rdoff,
+           const uint32_t *__restrict__ offs, const uint32_t *__restrict__ steps, const bt2gpu_extend_job *__restrict__ xj,
+           const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil,
+           uint8_t *__restrict__ dseq, uint8_t *__restrict__ dqual, uint8_t *__restrict__ dwin, bt2gpu_dp_job *__restrict__ dj,
+           uint32_t *__restrict__ job_read, long long *__restrict__ job_start, uint8_t *__restrict__ job_fw, u64 *__restrict__ stats)
+{
+	const int lane = threadIdx.x & 31;
+	const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	if(k >= npick) return;
+	const bt2gpu_extend_job x = xj[pk_seed[k]];
+	const uint32_t ri = pk_read[k], rdlen = reads[ri].rd_len;
+	const uint8_t *rd = seq + reads[ri].rd_off, *qu = qual + reads[ri].rd_off;
+	const uint32_t ro = rdoff[k], wo = ro + k * (uint32_t)(4 * mg + 1);
+	uint8_t *os = dseq + ro, *oq = dqual + ro, *ow = dwin + wo;
+	if(x.fw) for(uint32_t i = lane; i < rdlen; i += 32) { os[i] = rd[i]; oq[i] = qu[i]; }
+	else for(uint32_t i = lane; i < rdlen; i += 32) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
+	const long long seedoff = x.fw ? (long long)x.off : (long long)rdlen - x.off - x.len;   // in the oriented read
+	const long long start = (long long)offs[k] - seedoff;
+	const long long refl = start - 2 * mg;
+	const uint32_t ncol = rdlen + 4 * (uint32_t)mg;
+	for(uint32_t c = lane; c <= ncol; c += 32) {
+		const long long p = refl + c;
+		uint8_t m = 16;
+		if(p >= 0 && (u64)p < text_len) m = (uint8_t)(1u << ((__ldg(text2 + (p >> 4)) >> (2 * (p & 15))) & 3u));
+		ow[c] = m;
+	}
+	if(lane == 0) {
+		bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
+		j.rd_off = ro; j.rd_len = rdlen; j.rf_off = wo; j.ncol = ncol;
+		j.minsc = minsc[ri]; j.nceil = nceil[ri]; j.refl = refl; j.triml = 0;
+		j.corel = (uint32_t)mg; j.corer = 3 * (uint32_t)mg; j.fw = x.fw; j.enable8 = 1;
+		dj[k] = j;
+		job_read[k] = ri; job_start[k] = start; job_fw[k] = x.fw;
+		atomicAdd(stats + ST_LOC_STEPS, (u64)steps[k]);
+	}
+}
+
+__global__ void __launch_bounds__(256)
+k_hp_final(const bt2gpu_dp_result *__restrict__ res, uint32_t npick, const bt2gpu_sweep_result *__restrict__ sweep, uint32_t nreads,
+           u64 *__restrict__ stats)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	u64 al = 0, sw = 0;
+	if(i < npick) al = res[i].naln > 0;
+	if(i < nreads) sw = sweep[i].bwops;
+	for(int o = 16; o; o >>= 1) { al += __shfl_xor_sync(0xffffffffu, al, o); sw += __shfl_xor_sync(0xffffffffu, sw, o); }
+	if((threadIdx.x & 31) == 0) {
+		if(al) atomicAdd(stats + ST_ALIGNED, al);
+		if(sw) atomicAdd(stats + ST_SWEEP_BWOPS, sw);
+	}
+}
+
+// 16 text bytes (values 0..3) -> one 2-bit word
+__global__ void __launch_bounds__(256)
+k_ref_pack(const uint8_t *__restrict__ bytes, u64 n, uint32_t *__restrict__ out, int *__restrict__ bad) {
+	const u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+	if(w * 16 >= n) return;
+	uint32_t v = 0;
+	for(int i = 0; i < 16; i++) {
+		const u64 p = w * 16 + i;
+		if(p < n) { const uint8_t c = bytes[p]; if(c > 3) *bad = 1; v |= (uint32_t)(c & 3) << (2 * i); }
+	}
+	out[w] = v;
 }
 
 } // namespace bt2
 
 using namespace bt2;
 
+extern "C" int bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out) {
+	if(!text || !out) BT2_FAIL("null argument");
+	*out = nullptr;
+	int n = 0;
+	BT2_CUDA(cudaGetDeviceCount(&n));
+	if(n <= 0) BT2_FAIL("no CUDA device: libbt2gpu has no CPU fallback");
+	if(device < 0 || device >= n) BT2_FAIL("bad device ordinal");
+	if(text_len == 0 || text_len > 0xfffffff0ull) BT2_FAIL("reference text length must be in 1..2^32-16 (small index)");
+	BT2_CUDA(cudaSetDevice(device));
+	bt2gpu_ref *r = new bt2gpu_ref();
+	r->device = device; r->len = text_len;
+	const uint64_t nwords = (text_len + 15) / 16;
+	DevBuf stage, flag;
+	const uint64_t CH = 64ull << 20;                     // bytes per staged chunk (a multiple of 16)
+	int rc = 0, bad = 0;
+	if(r->packed.reserve(nwords * 4 + 16) || stage.reserve(std::min<uint64_t>(CH, text_len) + 16) || flag.reserve(16)) rc = 1;
+	if(!rc && cudaMemset(flag.p, 0, 4) != cudaSuccess) rc = fail("cudaMemset", __FILE__, __LINE__);
+	for(uint64_t off = 0; !rc && off < text_len; off += CH) {
+		const uint64_t nb = std::min<uint64_t>(CH, text_len - off);
+		if(cudaMemcpy(stage.p, text + off, nb, cudaMemcpyHostToDevice) != cudaSuccess) { rc = fail("cudaMemcpy(reference text)", __FILE__, __LINE__); break; }
+		const uint64_t nw = (nb + 15) / 16;
+		k_ref_pack<<<(unsigned)((nw + 255) / 256), 256>>>(stage.as<uint8_t>(), nb, r->packed.as<uint32_t>() + off / 16, flag.as<int>());
+		if(cudaDeviceSynchronize() != cudaSuccess) { rc = fail("k_ref_pack", __FILE__, __LINE__); break; }
+	}
+	if(!rc && cudaMemcpy(&bad, flag.p, 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail("cudaMemcpy", __FILE__, __LINE__);
+	stage.release(); flag.release();
+	if(!rc && bad) rc = fail("reference text holds a byte outside 0..3", __FILE__, __LINE__);
+	if(rc) { r->packed.release(); delete r; return 1; }
+	*out = r;
+	return 0;
+}
+
+extern "C" void bt2gpu_ref_destroy(bt2gpu_ref *r) {
+	if(!r) return;
+	cudaSetDevice(r->device);
+	r->packed.release();
+	delete r;
+}
+
+extern "C" uint64_t bt2gpu_ref_bytes(const bt2gpu_ref *r) { return r ? ((r->len + 15) / 16) * 4 : 0; }
+
+namespace bt2 { const bt2gpu_dp_result *dp_dev_results(bt2gpu_ctx *ctx); }
+
 extern "C" int bt2gpu_hotpath_round0_batch(
-	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
-	const uint8_t *text, uint64_t text_len,
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
 	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
 	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
 	const bt2gpu_hotpath_params *P,
@@ -53,173 +263,148 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits_out,
 	bt2gpu_hotpath_stats *S)
 {
-	if(!ctx || !fw || !bw || !text || !seq_pool || !qual_pool || !reads || !minsc || !nceil || !P || !sweep ||
+	if(!ctx || !fw || !bw || !ref || !seq_pool || !qual_pool || !reads || !minsc || !nceil || !P || !sweep ||
 	   !job_read || !job_start || !job_fw || !njobs_out || !results || !alns || !edits || !nedits_out || !S)
 		BT2_FAIL("null argument");
-	if(P->seed_len < 1 || P->seed_len > 32) BT2_FAIL("seed_len must be 1..32");
+	if(P->seed_len < 1 || P->seed_len > 32) BT2_FAIL("seed length must be 1..32");
 	if(P->maxgap < 0 || P->maxgap > 1000) BT2_FAIL("bad maxgap");
 	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set must be called first");
+	if(ref->device != ctx->device) BT2_FAIL("reference text lives on another device");
+	if(nreads > 0x7ffffff0u) BT2_FAIL("too many reads");
 	memset(S, 0, sizeof(*S));
 	*njobs_out = 0; *nedits_out = 0;
 	if(nreads == 0) return 0;
-	static thread_local HpState tl_st;         // staging reused across calls of this host thread
-	HpState &st = tl_st;                       // (a local reference: worker-thread lambdas must not re-resolve the thread_local)
-	int nth = P->nthreads > 0 ? P->nthreads : (int)std::thread::hardware_concurrency();
-	if(nth < 1) nth = 1;
-	if(nth > 32) nth = 32;
-	float ms = 0.f;
-	const uint32_t max_aln = P->max_aln ? P->max_aln : 1;
-
-	// ---- 1. stage reads, exactSweep ----
-	if(bt2gpu_reads_stage(ctx, seq_pool, qual_pool, pool_len, reads, nreads)) return 1;
-	S->h2d_bytes += 2 * pool_len + nreads * sizeof(bt2gpu_read);
-	if(bt2gpu_exact_sweep_batch(ctx, fw, 0, 0, P->mine_max ? P->mine_max : 2, sweep)) return 1;
-	if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1;
-	S->ms_sweep = ms;
-	S->d2h_bytes += nreads * sizeof(bt2gpu_sweep_result);
-
-	// ---- 2. seed instantiation (windows without N; fw seeds of a read, then its rc seeds) ----
-	st.seed_count.assign(nreads, 0);
-	st.seed_first.assign(nreads + 1, 0);
-	const int L = P->seed_len;
-	auto count_or_emit = [&](size_t lo, size_t hi, bt2gpu_seed_job *out) {
-		for(size_t i = lo; i < hi; i++) {
-			const uint32_t rdlen = reads[i].rd_len;
-			const uint8_t *rd = seq_pool + reads[i].rd_off;
-			const int per = seed_interval(P->ival_const, P->ival_coeff, rdlen);
-			const int sl = (int)std::min<uint32_t>((uint32_t)L, rdlen);
-			int nseeds = 1;
-			if((int)rdlen > L) nseeds += ((int)rdlen - L) / per;
-			uint32_t cnt = 0;
-			bt2gpu_seed_job *o = out ? out + st.seed_first[i] : nullptr;
-			for(int k = 0; k < nseeds; k++) {
-				const int depth = k * per;
-				bool clean = true;
-				for(int j = 0; j < sl; j++) if(rd[depth + j] > 3) { clean = false; break; }
-				if(!clean) continue;
-				if(o) { o[cnt].read = (uint32_t)i; o[cnt].off = (uint16_t)depth; o[cnt].len = (uint8_t)sl; o[cnt].fw = 1; }
-				cnt++;
-			}
-			if(o) for(uint32_t c = 0; c < cnt; c++) { o[cnt + c] = o[c]; o[cnt + c].fw = 0; }
-			st.seed_count[i] = 2 * cnt;
-		}
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	static thread_local HpState tl_st;         // device scratch reused across calls of this host thread
+	HpState &st = tl_st;
+	cudaStream_t s = ctx->stream;
+	for(int i = 0; i < 12; i++) if(!st.ev[i]) BT2_CUDA(cudaEventCreate(&st.ev[i]));
+	auto tick = std::chrono::steady_clock::now();
+	auto lap = [&](float &dst) {
+		const auto now = std::chrono::steady_clock::now();
+		dst = std::chrono::duration<float, std::milli>(now - tick).count(); tick = now;
 	};
-	parallel_for(nreads, nth, [&](size_t lo, size_t hi) { count_or_emit(lo, hi, nullptr); });
-	for(size_t i = 0; i < nreads; i++) st.seed_first[i + 1] = st.seed_first[i] + st.seed_count[i];
-	const size_t nseed = st.seed_first[nreads];
-	if(st.sjobs.reserve(nseed * sizeof(bt2gpu_seed_job) + 64) || st.shits.reserve(nseed * sizeof(bt2gpu_seed_hit) + 64)) return 1;
-	bt2gpu_seed_job *sj = st.sjobs.as<bt2gpu_seed_job>();
-	bt2gpu_seed_hit *sh = st.shits.as<bt2gpu_seed_hit>();
-	parallel_for(nreads, nth, [&](size_t lo, size_t hi) { count_or_emit(lo, hi, sj); });
-	if(bt2gpu_seed_exact_batch(ctx, fw, bw, sj, nseed, sh)) return 1;
-	if(nseed) { if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1; S->ms_seed = ms; }
+	const uint32_t max_aln = P->max_aln ? P->max_aln : 1;
+	const uint32_t n32 = (uint32_t)nreads;
+	const unsigned nbR = (n32 + 255) / 256;
+
+	// ---- 1. reads to HBM, exactSweep, seed instantiation (count) ----
+	FmReadsDev rv;
+	if(fm_hp_reads_stage(ctx, seq_pool, qual_pool, pool_len, reads, nreads, &rv)) return 1;
+	uint64_t sum_len = 0;
+	for(size_t i = 0; i < nreads; i++) sum_len += reads[i].rd_len;
+	if(sum_len + (uint64_t)nreads * (4 * P->maxgap + 1) > 0x70000000ull) BT2_FAIL("DP pools exceed 32-bit offsets: split the batch");
+	if(st.minsc.reserve(nreads * 4) || st.nceil.reserve(nreads * 4) || st.cnt.reserve(nreads * 4 + 16) || st.first.reserve(nreads * 4 + 16) ||
+	   st.spart.reserve((scan_parts(nreads) + 2) * 8) || st.tot.reserve(64) || st.h_tot.reserve(64) || st.stats.reserve(ST_N * 8) ||
+	   st.h_stats.reserve(ST_N * 8) || st.pick.reserve(nreads * 4) || st.val.reserve(nreads * 8) || st.ppos.reserve(nreads * 8)) return 1;
+	BT2_CUDA(cudaMemcpyAsync(st.minsc.p, minsc, nreads * 4, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(st.nceil.p, nceil, nreads * 4, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemsetAsync(st.stats.p, 0, ST_N * 8, s));
+	S->h2d_bytes += 2 * pool_len + nreads * (sizeof(bt2gpu_read) + 8);
+	u64 *stats = st.stats.as<u64>();
+	BT2_CUDA(cudaEventRecord(st.ev[0], s));
+	bt2gpu_sweep_result *dsweep = nullptr;
+	if(fm_hp_sweep(ctx, fw, P->mine_max ? P->mine_max : 2, &dsweep)) return 1;
+	BT2_CUDA(cudaEventRecord(st.ev[1], s));
+	uint32_t *cnt = st.cnt.as<uint32_t>(), *first = st.first.as<uint32_t>();
+	k_hp_seeds<false><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, cnt, nullptr, nullptr);
+	ctx->launches++;
+	if(dev_exclusive_scan<uint32_t>(ctx, cnt, first, st.spart.as<uint32_t>(), st.tot.as<uint32_t>(), nreads)) return 1;
+	BT2_CUDA(cudaMemcpyAsync(st.h_tot.p, st.tot.p, 4, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaMemcpyAsync(sweep, dsweep, nreads * sizeof(bt2gpu_sweep_result), cudaMemcpyDeviceToHost, s));
+	S->d2h_bytes += nreads * sizeof(bt2gpu_sweep_result);
+	BT2_CUDA(cudaStreamSynchronize(s));
+	const size_t nseed = *st.h_tot.as<uint32_t>();
 	S->seeds = nseed;
-	S->h2d_bytes += nseed * sizeof(bt2gpu_seed_job);
-	S->d2h_bytes += nseed * sizeof(bt2gpu_seed_hit);
+	lap(S->wall_sweep);
 
-	// ---- 3. extend every hit ----
-	st.hit_idx.clear();
-	for(size_t k = 0; k < nseed; k++) {
-		S->seed_bwops += sh[k].bwops; S->seed_sides += sh[k].sides;
-		if(sh[k].botf > sh[k].topf) st.hit_idx.push_back((uint32_t)k);
+	// ---- 2. seeds (emit), exact search, extend every hit, pick one per read ----
+	size_t npick = 0, tot_rd = 0;
+	if(nseed) {
+		if(st.sjobs.reserve(nseed * sizeof(bt2gpu_seed_job)) || st.shits.reserve(nseed * sizeof(bt2gpu_seed_hit)) ||
+		   st.xjobs.reserve(nseed * sizeof(bt2gpu_extend_job)) || st.xres.reserve(nseed * sizeof(bt2gpu_extend_result))) return 1;
+		bt2gpu_seed_job *sj = st.sjobs.as<bt2gpu_seed_job>(); bt2gpu_seed_hit *sh = st.shits.as<bt2gpu_seed_hit>();
+		bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>(); bt2gpu_extend_result *xr = st.xres.as<bt2gpu_extend_result>();
+		k_hp_seeds<true><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, cnt, first, sj);
+		BT2_CUDA(cudaEventRecord(st.ev[2], s));
+		if(fm_hp_seed(ctx, fw, bw, sj, nseed, sh)) return 1;
+		BT2_CUDA(cudaEventRecord(st.ev[3], s));
+		k_hp_mkextend<<<(unsigned)((nseed + 255) / 256), 256, 0, s>>>(sj, sh, (uint32_t)nseed, xj, stats);
+		BT2_CUDA(cudaEventRecord(st.ev[4], s));
+		if(fm_hp_extend(ctx, fw, bw, xj, nseed, xr)) return 1;
+		BT2_CUDA(cudaEventRecord(st.ev[5], s));
+		k_hp_pick<<<nbR, 256, 0, s>>>(rv.reads, n32, first, cnt, xj, xr, st.pick.as<uint32_t>(), st.val.as<u64>(), stats);
+		ctx->launches += 3;
+		BT2_CUDA(cudaGetLastError());
+		if(dev_exclusive_scan<u64>(ctx, st.val.as<u64>(), st.ppos.as<u64>(), st.spart.as<u64>(), st.tot.as<u64>() + 1, nreads)) return 1;
+		BT2_CUDA(cudaMemcpyAsync(st.h_tot.as<u64>() + 1, st.tot.as<u64>() + 1, 8, cudaMemcpyDeviceToHost, s));
+		BT2_CUDA(cudaStreamSynchronize(s));
+		const u64 t = st.h_tot.as<u64>()[1];
+		npick = (size_t)(t >> 32); tot_rd = (size_t)(t & 0xffffffffu);
 	}
-	const size_t nhit = st.hit_idx.size();
-	S->seed_hits = nhit;
-	if(st.xjobs.reserve(nhit * sizeof(bt2gpu_extend_job) + 64) || st.xres.reserve(nhit * sizeof(bt2gpu_extend_result) + 64)) return 1;
-	bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>();
-	bt2gpu_extend_result *xr = st.xres.as<bt2gpu_extend_result>();
-	for(size_t h = 0; h < nhit; h++) {
-		const uint32_t k = st.hit_idx[h];
-		xj[h].read = sj[k].read; xj[h].topf = sh[k].topf; xj[h].botf = sh[k].botf; xj[h].topb = sh[k].topb; xj[h].botb = sh[k].botb;
-		xj[h].off = sj[k].off; xj[h].len = sj[k].len; xj[h].fw = sj[k].fw;
-	}
-	if(bt2gpu_extend_batch(ctx, fw, bw, xj, nhit, xr)) return 1;
-	if(nhit) { if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1; S->ms_extend = ms; }
-	S->h2d_bytes += nhit * sizeof(bt2gpu_extend_job);
-	S->d2h_bytes += nhit * sizeof(bt2gpu_extend_result);
+	lap(S->wall_seed);
 
-	// ---- 4. pick one hit per read: narrowest range, then longest exact extension, then first ----
-	if(st.pickidx.reserve(nreads * 4 + 64) || st.rows.reserve(nreads * 4 + 64) || st.offs.reserve(nreads * 4 + 64) ||
-	   st.steps.reserve(nreads * 4 + 64)) return 1;
-	uint32_t *pick = st.pickidx.as<uint32_t>(), *rows = st.rows.as<uint32_t>();
-	size_t npick = 0;
-	for(size_t h = 0; h < nhit;) {
-		size_t e = h, best = h;
-		while(e < nhit && xj[e].read == xj[h].read) {
-			S->extend_fmops += xr[e].fmops;
-			const uint32_t sz = xj[e].botf - xj[e].topf, bsz = xj[best].botf - xj[best].topf;
-			const uint32_t ex = (uint32_t)xr[e].nlex + xr[e].nrex, bex = (uint32_t)xr[best].nlex + xr[best].nrex;
-			if(sz < bsz || (sz == bsz && ex > bex)) best = e;
-			e++;
-		}
-		pick[npick] = (uint32_t)best; rows[npick] = xj[best].topf; npick++;
-		h = e;
-	}
-	// ---- 5. locate ----
-	uint32_t *offs = st.offs.as<uint32_t>(), *steps = st.steps.as<uint32_t>();
-	if(bt2gpu_locate_batch(ctx, fw, rows, npick, offs, steps)) return 1;
-	if(npick) { if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1; S->ms_locate = ms; }
-	S->locate_rows = npick;
-	S->h2d_bytes += npick * 4; S->d2h_bytes += npick * 8;
-
-	// ---- 6. frame the windows (frameSeedExtensionRect) and fetch them as masks (initRef) ----
-	const int mg = P->maxgap;
-	size_t tot_rd = 0, tot_win = 0;
-	std::vector<uint32_t> &rdoff = st.seed_count;       // reuse: per-pick offsets into the DP pools
-	rdoff.assign(npick + 1, 0);
-	std::vector<uint32_t> winoff(npick + 1, 0);
-	for(size_t k = 0; k < npick; k++) {
-		const uint32_t rdlen = reads[xj[pick[k]].read].rd_len;
-		S->locate_steps += steps[k];
-		rdoff[k] = (uint32_t)tot_rd; winoff[k] = (uint32_t)tot_win;
-		tot_rd += rdlen; tot_win += rdlen + 4 * mg + 1;
-	}
-	if(tot_rd > 0xfffffff0ull || tot_win > 0xfffffff0ull) BT2_FAIL("DP pools exceed 4 GiB: split the batch");
-	if(st.dseq.reserve(tot_rd + 64) || st.dqual.reserve(tot_rd + 64) || st.dwin.reserve(tot_win + 64) ||
-	   st.djobs.reserve(npick * sizeof(bt2gpu_dp_job) + 64)) return 1;
-	uint8_t *dseq = st.dseq.as<uint8_t>(), *dqual = st.dqual.as<uint8_t>(), *dwin = st.dwin.as<uint8_t>();
-	bt2gpu_dp_job *dj = st.djobs.as<bt2gpu_dp_job>();
-	parallel_for(npick, nth, [&](size_t lo, size_t hi) {
-		for(size_t k = lo; k < hi; k++) {
-			const bt2gpu_extend_job &x = xj[pick[k]];
-			const uint32_t ri = x.read, rdlen = reads[ri].rd_len;
-			const uint8_t *rd = seq_pool + reads[ri].rd_off, *qu = qual_pool + reads[ri].rd_off;
-			uint8_t *os = dseq + rdoff[k], *oq = dqual + rdoff[k], *ow = dwin + winoff[k];
-			if(x.fw) { memcpy(os, rd, rdlen); memcpy(oq, qu, rdlen); }
-			else for(uint32_t i = 0; i < rdlen; i++) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
-			const int64_t seedoff = x.fw ? (int64_t)x.off : (int64_t)rdlen - x.off - x.len;   // in the oriented read
-			const int64_t start = (int64_t)offs[k] - seedoff;
-			const int64_t refl = start - 2 * mg;
-			const uint32_t ncol = rdlen + 4 * (uint32_t)mg;
-			for(uint32_t c = 0; c <= ncol; c++) {
-				const int64_t p = refl + c;
-				ow[c] = (p >= 0 && (uint64_t)p < text_len) ? (uint8_t)(1u << text[p]) : (uint8_t)16;
-			}
-			bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
-			j.rd_off = rdoff[k]; j.rd_len = rdlen; j.rf_off = winoff[k]; j.ncol = ncol;
-			j.minsc = minsc[ri]; j.nceil = nceil[ri]; j.refl = refl; j.triml = 0;
-			j.corel = (uint32_t)mg; j.corer = 3 * (uint32_t)mg; j.fw = x.fw; j.enable8 = 1;
-			dj[k] = j;
-			job_read[k] = ri; job_start[k] = start; job_fw[k] = x.fw;
-		}
-	});
-	// ---- 7. fill + gather + nextAlignment loop ----
+	// ---- 3. locate, frame, DP ----
 	if(npick) {
-		if(bt2gpu_dp_stage(ctx, dseq, dqual, tot_rd, dwin, tot_win, dj, npick, max_aln, 256 * npick, edit_cap)) return 1;
+		const int mg = P->maxgap;
+		const size_t tot_win = tot_rd + npick * (size_t)(4 * mg + 1);
+		if(st.pk_read.reserve(npick * 4) || st.pk_seed.reserve(npick * 4) || st.rows.reserve(npick * 4) || st.rdoff.reserve(npick * 4) ||
+		   st.offs.reserve(npick * 4) || st.steps.reserve(npick * 4) || st.job_read.reserve(npick * 4) || st.job_start.reserve(npick * 8) ||
+		   st.job_fw.reserve(npick)) return 1;
+		bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>();
+		k_hp_compact<<<nbR, 256, 0, s>>>(n32, st.pick.as<uint32_t>(), st.ppos.as<u64>(), xj, st.pk_read.as<uint32_t>(),
+			st.pk_seed.as<uint32_t>(), st.rows.as<uint32_t>(), st.rdoff.as<uint32_t>());
+		BT2_CUDA(cudaEventRecord(st.ev[6], s));
+		if(fm_hp_locate(ctx, fw, st.rows.as<uint32_t>(), npick, st.offs.as<uint32_t>(), st.steps.as<uint32_t>())) return 1;
+		BT2_CUDA(cudaEventRecord(st.ev[7], s));
+		DpDevPools pools;
+		if(dp_dev_begin(ctx, npick, tot_rd, tot_win, max_aln, 256 * npick, edit_cap, &pools)) return 1;
+		k_hp_frame<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(rv.seq, rv.qual, rv.reads, ref->packed.as<uint32_t>(), ref->len,
+			(uint32_t)npick, mg, st.pk_read.as<uint32_t>(), st.pk_seed.as<uint32_t>(), st.rdoff.as<uint32_t>(), st.offs.as<uint32_t>(),
+			st.steps.as<uint32_t>(), xj, st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), pools.seq, pools.qual, pools.win, pools.jobs,
+			st.job_read.as<uint32_t>(), st.job_start.as<long long>(), st.job_fw.as<uint8_t>(), stats);
+		ctx->launches += 2;
+		BT2_CUDA(cudaGetLastError());
+		if(dp_dev_finish(ctx)) return 1;
+		lap(S->wall_frame);
+		BT2_CUDA(cudaEventRecord(st.ev[8], s));
 		if(bt2gpu_dp_run(ctx, 7)) return 1;
-		size_t nc = 0, ne = 0;
+		BT2_CUDA(cudaEventRecord(st.ev[9], s));
+	}
+	k_hp_final<<<(unsigned)((std::max(nreads, npick) + 255) / 256), 256, 0, s>>>(npick ? dp_dev_results(ctx) : nullptr, (uint32_t)npick,
+		dsweep, n32, stats);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	BT2_CUDA(cudaEventRecord(st.ev[10], s));
+	BT2_CUDA(cudaMemcpyAsync(st.h_stats.p, stats, ST_N * 8, cudaMemcpyDeviceToHost, s));
+	size_t ne = 0;
+	if(npick) {
+		BT2_CUDA(cudaMemcpyAsync(job_read, st.job_read.p, npick * 4, cudaMemcpyDeviceToHost, s));
+		BT2_CUDA(cudaMemcpyAsync(job_start, st.job_start.p, npick * 8, cudaMemcpyDeviceToHost, s));
+		BT2_CUDA(cudaMemcpyAsync(job_fw, st.job_fw.p, npick, cudaMemcpyDeviceToHost, s));
+		size_t nc = 0;
 		if(bt2gpu_dp_fetch(ctx, results, nullptr, alns, edits, &nc, &ne)) return 1;
-		if(bt2gpu_ctx_kernel_ms(ctx, &ms)) return 1;
-		S->ms_dp = ms;
+		S->d2h_bytes += npick * (13 + sizeof(bt2gpu_dp_result) + max_aln * sizeof(bt2gpu_dp_aln)) + ne * sizeof(bt2gpu_edit);
+	} else BT2_CUDA(cudaStreamSynchronize(s));
+	lap(S->wall_dp);
+
+	// ---- 4. counters and device times ----
+	const u64 *hs = st.h_stats.as<u64>();
+	S->seed_bwops = hs[ST_SEED_BWOPS]; S->seed_sides = hs[ST_SEED_SIDES]; S->seed_hits = hs[ST_SEED_HITS];
+	S->extend_fmops = hs[ST_EXT_FMOPS]; S->locate_steps = hs[ST_LOC_STEPS]; S->aligned = hs[ST_ALIGNED];
+	S->sweep_bwops = hs[ST_SWEEP_BWOPS];
+	S->locate_rows = npick; S->dp_jobs = npick;
+	S->dp_cells = npick ? bt2gpu_dp_staged_cells(ctx) : 0;
+	auto span = [&](int a, int b) -> float { float ms = 0.f; cudaEventElapsedTime(&ms, st.ev[a], st.ev[b]); return ms; };
+	S->ms_sweep = span(0, 1);
+	if(nseed) { S->ms_seed = span(2, 3); S->ms_extend = span(4, 5); }
+	if(npick) {
+		S->ms_locate = span(6, 7); S->ms_dp = span(8, 9);
 		float ph[3] = {0, 0, 0};
 		if(bt2gpu_dp_phase_ms(ctx, ph) == 0) { S->ms_dp_fill = ph[0]; S->ms_dp_gather = ph[1]; S->ms_dp_backtrace = ph[2]; }
-		*nedits_out = ne;
-		S->dp_cells = bt2gpu_dp_staged_cells(ctx);
-		for(size_t k = 0; k < npick; k++) if(results[k].naln > 0) S->aligned++;
-		S->h2d_bytes += 2 * tot_rd + tot_win + npick * sizeof(bt2gpu_dp_job);
-		S->d2h_bytes += npick * (sizeof(bt2gpu_dp_result) + max_aln * sizeof(bt2gpu_dp_aln)) + ne * sizeof(bt2gpu_edit);
 	}
-	S->dp_jobs = npick;
-	*njobs_out = npick;
+	S->ms_total = span(0, 10);
+	S->ms_glue = S->ms_total - S->ms_sweep - S->ms_seed - S->ms_extend - S->ms_locate - S->ms_dp;
+	*njobs_out = npick; *nedits_out = ne;
 	return 0;
 }

@@ -285,16 +285,30 @@ typedef struct {
 	uint64_t seeds, seed_bwops, seed_sides, seed_hits, sweep_bwops, extend_fmops,
 	         locate_rows, locate_steps, dp_jobs, dp_cells, aligned, h2d_bytes, d2h_bytes;
 	float    ms_sweep, ms_seed, ms_extend, ms_locate, ms_dp, ms_dp_fill, ms_dp_gather, ms_dp_backtrace;
+	/* host wall clock per stage (copies, syncs and glue included): reads+sweep, seed instantiation,
+	 * seed search, extend, pick+locate, framing, DP staging, DP run+fetch */
+	float    wall_sweep, wall_inst, wall_seed, wall_extend, wall_locate, wall_frame, wall_dp_stage, wall_dp;
+	/* device span from the first kernel to the last (reads already in HBM), and the part of it that is
+	 * not one of the phases above: glue kernels, scans and the bubbles of the three scalar read-backs */
+	float    ms_total, ms_glue;
 } bt2gpu_hotpath_stats;
 
-/* text = the joined reference (bytes 0..3, what the index was built over), host memory.
- * Per read i: minsc[i], nceil[i].  Outputs (all host, caller-owned): sweep[nreads];
- * job_read[nreads] = read id of DP job k (first *njobs entries valid); job_start[k] = text
- * offset the oriented read was framed at; results[nreads], alns[nreads*max_aln],
- * edits[edit_cap] indexed by DP job. */
+/* The joined reference text on the device, 2 bits per base: what BitPairReference holds in
+ * host memory (reference.h:180, the `.4.bt2` file) and SwAligner::initRef reads windows from
+ * (aligner_sw.cpp:155-271).  text = bytes 0..3, host memory, the text the index was built over;
+ * uploaded once per device and shared read-only by every context on it. */
+typedef struct bt2gpu_ref bt2gpu_ref;
+int      bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out);
+void     bt2gpu_ref_destroy(bt2gpu_ref *ref);
+uint64_t bt2gpu_ref_bytes(const bt2gpu_ref *ref);
+
+/* Per read i: minsc[i], nceil[i].  Inputs are host buffers (pinned memory makes the copies
+ * asynchronous); every intermediate stays in HBM.  Outputs (all host, caller-owned):
+ * sweep[nreads]; job_read[nreads] = read id of DP job k (first *njobs entries valid);
+ * job_start[k] = text offset the oriented read was framed at; results[nreads],
+ * alns[nreads*max_aln], edits[edit_cap] indexed by DP job. */
 int bt2gpu_hotpath_round0_batch(
-	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
-	const uint8_t *text, uint64_t text_len,
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
 	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
 	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
 	const bt2gpu_hotpath_params *params,

@@ -56,7 +56,8 @@ def test_hot_path_chain_matches_oracle():
     n = len(reads)
     minsc = np.full(n, sc.score_min.f_int(150), dtype=np.int32)
     nceil = np.full(n, sc.nceil(150), dtype=np.int32)
-    out, st = ctx.hotpath_round0(genome, np.ascontiguousarray(reads.reshape(-1)), np.ascontiguousarray(quals.reshape(-1)),
+    dref = lib.DeviceRef(genome)
+    out, st = ctx.hotpath_round0(dref, np.ascontiguousarray(reads.reshape(-1)), np.ascontiguousarray(quals.reshape(-1)),
                                  pool.reads, minsc, nceil, nthreads=4)
     nj = out["njobs"]
     assert nj == len(jobs) and st["dp_jobs"] == nj and st["seeds"] == len(sj)
