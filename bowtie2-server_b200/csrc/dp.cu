@@ -542,7 +542,48 @@ struct BtJob {
 		if(mask & 8) return 4;
 		return 0;
 	}
+	// E (ct 0) or F (ct 1) cell in one code path: 3/2 open, 4/5 extend, 0 none
+	__device__ __forceinline__ int g_move(int ct, int row, int col) const {
+		const int pr = row - ct, pc = col - (1 - ct);
+		const int sc_cur = mv.get(ct, row, col);
+		const int hp = mv.get(2, pr, pc), gp = mv.get(ct, pr, pc);
+		const int open = ct ? c_sc.rfo : c_sc.rdo, ext = ct ? c_sc.rfe : c_sc.rde;
+		int mask = 0;
+		if((!local || hp > 0) && hp - open == sc_cur) mask |= 1;
+		if((!local || gp > 0) && gp - ext == sc_cur) mask |= 2;
+		if(mask & 1) return ct ? 2 : 3;
+		return mask == 2 ? (ct ? 5 : 4) : 0;
+	}
+	// move out of an E cell (read gap): 3 open, 4 extend, 0 none;  out of an F cell (ref gap): 2 open, 5 extend
+	__device__ __forceinline__ int e_move(int row, int col) const {
+		const int sc_cur = mv.get(0, row, col);
+		const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
+		int mask = 0;
+		if((!local || hl > 0) && hl - c_sc.rdo == sc_cur) mask |= 1;
+		if((!local || el > 0) && el - c_sc.rde == sc_cur) mask |= 2;
+		return (mask & 1) ? 3 : (mask == 2 ? 4 : 0);
+	}
+	__device__ __forceinline__ int f_move(int row, int col) const {
+		const int sc_cur = mv.get(1, row, col);
+		const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
+		int mask = 0;
+		if((!local || hu > 0) && hu - c_sc.rfo == sc_cur) mask |= 1;
+		if((!local || fu > 0) && fu - c_sc.rfe == sc_cur) mask |= 2;
+		return (mask & 1) ? 2 : (mask == 2 ? 5 : 0);
+	}
 };
+
+// Trial group (end-to-end mode).  After the first alignment of a window, almost every remaining
+// candidate is a neighbour of its end cell whose walk runs a few cells (the gap barrier's rows, then
+// a gap back to the reported path) and dies on a cell that an earlier walk has reported.  The
+// reference tries them one after another; here 32 consecutive candidates walk at once, one per
+// lane, against the bitmap as it stands, each recording its cells.  The reference's order is then
+// replayed over the recorded walks -- candidate q stops at the first of its cells that an earlier
+// candidate of the group has reported -- with a small shared-memory bitmap of the window the walks
+// live in, which is exactly the sequential outcome.  Candidates up to the first one whose walk
+// neither gets skipped nor blocked are committed (bitmap bits, try count); that one goes to the
+// full walker below.
+static constexpr int TR_LMAX = 32;                // recorded cells per trial walk = rows of the window
 
 __global__ void __launch_bounds__(128)
 k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
@@ -580,11 +621,90 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 	const uint32_t ncand = r.ncand;
 	uint32_t SQ = (uint32_t)nrow >> 4; if(SQ == 0) SQ = 1;
 	uint32_t cural = 0, ndone = 0, tries = 0, cbase = 0xffffffffu;
+	__shared__ uint16_t s_tcells[4][TR_LMAX * 32];   // recorded cells of the trial walks: (rows above the last) << 8 | window column
+	__shared__ uint32_t s_twin[4][TR_LMAX * 8];      // cells reported by the group so far: TR_LMAX rows x 256 columns
+	uint16_t *tcells = s_tcells[threadIdx.x >> 5]; uint32_t *twin = s_twin[threadIdx.x >> 5];
+	const bool trial_ok = !local;
+	bool walked = false;                 // a full walk has happened: the bitmap is no longer empty
+	uint32_t trial_at = 0xffffffffu;     // candidate the last trial group stopped at (walked in full next)
 	bt2gpu_dp_cand cc; cc.row = cc.col = 0; cc.score = 0;
 	while(r.naln < max_aln && cural < ncand) {
 		bool got = false;
 		bt2gpu_dp_aln out;
 		while(cural < ncand) {
+			if(trial_ok && walked && cural != trial_at) {
+				// ---- trial group: lanes = candidates cural .. cural+31 ----
+				const uint32_t ci = cural + lane;
+				enum { T_RUN = 0, T_INACTIVE, T_SKIP, T_BLOCKED, T_END, T_HORIZON };
+				int status = T_INACTIVE, row = 0, col = 0, ct = 2, len = 0;
+				int cmin = INT32_MAX, cmax = -1;
+				if(ci < ncand) {
+					const bt2gpu_dp_cand c = cd[ci];
+					row = (int)c.row; col = (int)c.col;
+					status = c.score < jb.minsc ? T_SKIP : T_RUN;
+					cmin = cmax = col;
+					if(row != nrow - 1) cmax = INT32_MAX;          // not an end-to-end candidate: no trial
+				}
+				for(int o = 16; o; o >>= 1) {
+					cmin = min(cmin, __shfl_xor_sync(FULL, cmin, o));
+					cmax = max(cmax, __shfl_xor_sync(FULL, cmax, o));
+				}
+				const int wbase = cmin - TR_LMAX;                   // window: TR_LMAX rows x 256 columns from wbase
+				if(cmax == INT32_MAX || cmax - wbase >= 256) { trial_at = cural; }
+				else {
+					for(int t = 0; t < TR_LMAX; t++) {
+						if(!__any_sync(FULL, status == T_RUN)) break;
+						if(status == T_RUN) {
+							const bool rep = J.reported(row, col);
+							int m = 0;
+							if(!rep && row > 0) m = ct == 2 ? J.h_move(row, col) : J.g_move(ct, row, col);
+							tcells[t * 32 + lane] = (uint16_t)(((nrow - 1 - row) << 8) | (col - wbase));
+							len = t + 1;
+							if(rep) status = t == 0 ? T_SKIP : T_BLOCKED;
+							else if(row == 0 || m == 0) status = T_END;
+							else {
+								if(m == 1) { row--; col--; ct = 2; }
+								else if(m == 2) { row--; ct = 2; }
+								else if(m == 5) { row--; ct = 1; }
+								else if(m == 3) { col--; ct = 2; }
+								else { col--; ct = 0; }
+							}
+						}
+					}
+					if(status == T_RUN) status = T_HORIZON;
+					for(int i = lane; i < TR_LMAX * 8; i += 32) twin[i] = 0;
+					__syncwarp();
+					// the reference's order, replayed over the recorded walks: candidate q stops at the first of
+					// its cells that an earlier candidate of the group has reported
+					int nacc = 0; uint32_t nfail = 0;
+					for(; nacc < 32; nacc++) {
+						const int st = __shfl_sync(FULL, status, nacc), ln = __shfl_sync(FULL, len, nacc);
+						if(st == T_INACTIVE) break;
+						if(st == T_SKIP) continue;
+						uint32_t cell = 0; bool set = false;
+						if(lane < ln) { cell = tcells[lane * 32 + nacc]; set = (twin[cell >> 5] >> (cell & 31)) & 1u; }
+						const int first = __ffs(__ballot_sync(FULL, set)) - 1;
+						int nmark;
+						if(first < 0) {
+							if(st != T_BLOCKED) break;                     // runs to its end or past the horizon: full walk
+							nmark = ln;
+						} else if(first == 0) nmark = 0;                   // start cell already reported: skipped, not a try
+						else nmark = first;                                // cell `first` is set already
+						if(nmark) nfail++;
+						if(lane < nmark) {
+							atomicOr(&twin[cell >> 5], 1u << (cell & 31));
+							const uint32_t b = (uint32_t)(nrow - 1 - (int)(cell >> 8)) * (uint32_t)J.ncol + (uint32_t)(wbase + (int)(cell & 255u));
+							atomicOr(J.rp32 + (b >> 5), 1u << (b & 31));
+						}
+						__syncwarp();
+					}
+					tries += nfail;
+					cural += nacc;
+					trial_at = cural;
+					__syncwarp();
+					if(cural >= ncand) break;
+				}
+			}
 			// candidates are read 32 at a time (one round trip per 32 of them)
 			if(cural < cbase || cural >= cbase + 32) {
 				cbase = cural;
@@ -633,7 +753,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 							}
 							if(__any_sync(FULL, dom)) { skipped = true; break; }
 						}
-						tries++;
+						tries++; walked = true;
 					}
 					// commit lanes [0, nk): diagonal moves
 					{
@@ -1246,10 +1366,12 @@ int dp_dev_finish(bt2gpu_ctx *ctx) {
 	default: BT2_FAIL("minsc below the 16-bit end-to-end domain");
 	}
 	DpSizes tot; memcpy(&tot, hs + DPSUM_WORDS, sizeof(tot));
-	size_t freeB = 0, totalB = 0;
-	BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
-	const uint64_t mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
-	if(tot.mat > mat_budget_words) BT2_FAIL("DP batch exceeds the matrix arena: split the batch");
+	if(tot.mat * 4 > d->mat.cap) {          // the arena has to grow: check the budget first (cudaMemGetInfo is slow, so only then)
+		size_t freeB = 0, totalB = 0;
+		BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
+		const uint64_t mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
+		if(tot.mat > mat_budget_words) BT2_FAIL("DP batch exceeds the matrix arena: split the batch");
+	}
 	DpChunk ch; memset(&ch, 0, sizeof(ch));
 	ch.job0 = 0; ch.njobs = (uint32_t)njobs; ch.mat_words = tot.mat; ch.rep_bytes = tot.rep;
 	ch.bound_words = tot.bound; ch.escr_edits = tot.escr; ch.maxcol = (int)hs[8];
