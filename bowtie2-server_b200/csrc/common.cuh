@@ -102,7 +102,7 @@ int fm_hp_sweep(bt2gpu_ctx *ctx, const bt2gpu_index *fw, uint32_t mine_max, bt2g
 int fm_hp_seed(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_seed_job *djobs,
                size_t njobs, bt2gpu_seed_hit *dout);
 int fm_hp_extend(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_extend_job *djobs,
-                 size_t njobs, bt2gpu_extend_result *dout);
+                 size_t njobs, bt2gpu_extend_result *dout, const uint32_t *dlist, const uint32_t *dnlist);
 int fm_hp_locate(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const uint32_t *drows, size_t n, uint32_t *doffs, uint32_t *dsteps);
 // dp.cu: DP problems whose reads, windows and job table are written by a kernel
 int dp_dev_begin(bt2gpu_ctx *ctx, size_t njobs, size_t pool_len, size_t win_len, uint32_t max_aln, size_t cand_cap,

@@ -477,6 +477,80 @@ k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__r
 	}
 }
 
+// End-to-end windows of at most E2E_CAP columns: count, place, sort and convert in one launch (one
+// warp per job).  The candidates are the last-row cells with H >= minsc (at most ncol of them), so
+// a warp sorts them in its slice of shared memory and takes its slot in the pool with one atomic.
+static constexpr int E2E_CAP = 512;
+__global__ void __launch_bounds__(128)
+k_dp_gather_e2e(const bt2gpu_dp_job *__restrict__ jobs, const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
+                const uint32_t *__restrict__ mat, bt2gpu_dp_result *__restrict__ res, bt2gpu_dp_cand *__restrict__ cands,
+                unsigned long long *__restrict__ total, unsigned long long cap, int *__restrict__ errflag)
+{
+	__shared__ uint64_t s_keys[4][E2E_CAP];
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+	const uint32_t ji = job0 + blockIdx.x * (blockDim.x >> 5) + wib;
+	if(ji >= job0 + njobs) return;
+	const bt2gpu_dp_job jb = jobs[ji];
+	const DpAux ax = aux[ji];
+	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol, minsc = jb.minsc;
+	MatView mv; mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW, ax.fl == -255);
+	uint64_t *a = s_keys[wib];
+	const RowRef rr = mv.rowref(nrow - 1);
+	int best = INT32_MIN; uint32_t cnt = 0;
+	for(int j0 = 0; j0 < ncol; j0 += 32) {
+		const int j = j0 + lane;
+		int h = INT32_MIN;
+		if(j < ncol) h = mv.at(2, rr, j);
+		best = max(best, h);
+		const bool in = j < ncol && h >= minsc;
+		const unsigned bal = __ballot_sync(FULL, in);
+		if(in) a[cnt + __popc(bal & ((1u << lane) - 1u))] = cand_key(h, nrow - 1, j);
+		cnt += __popc(bal);
+	}
+	for(int o = 16; o; o >>= 1) best = max(best, __shfl_xor_sync(FULL, best, o));
+	bt2gpu_dp_result r; memset(&r, 0, sizeof(r));
+	const bool w8 = (ax.fl == -255);
+	int64_t b = best; bool ok = true;
+	if(ncol <= 0) { b = INT64_MIN; ok = false; }                 // !found
+	else if(best < minsc) ok = false;                            // flag -1, returns score
+	else if(w8 && best == -255) { b = INT64_MIN; ok = false; }   // flag -2 (ee_u8.cpp:1137)
+	r.best = b; r.width = ok ? (w8 ? 8 : 16) : 0;
+	r.ncand = ok ? cnt : 0; r.aligned = (ok && cnt > 0) ? 1 : 0;
+	const uint32_t n = r.ncand;
+	if(n) {
+		// bitonic sort of the warp's keys (ascending key == DpBtCandidate::operator<)
+		uint32_t np2 = 1; while(np2 < n) np2 <<= 1;
+		__syncwarp();
+		for(uint32_t size = 2; size <= np2; size <<= 1) {
+			for(uint32_t i = lane; i < np2 / 2; i += 32) {
+				const uint32_t blk = i / (size / 2), off = i % (size / 2);
+				const uint32_t x = blk * size + off, y = blk * size + size - 1 - off;
+				if(y < n) { const uint64_t kx = a[x], ky = a[y]; if(kx > ky) { a[x] = ky; a[y] = kx; } }
+			}
+			__syncwarp();
+			for(uint32_t stride = size / 4; stride > 0; stride >>= 1) {
+				for(uint32_t i = lane; i < np2 / 2; i += 32) {
+					const uint32_t x = (i / stride) * stride * 2 + (i % stride), y = x + stride;
+					if(y < n) { const uint64_t kx = a[x], ky = a[y]; if(kx > ky) { a[x] = ky; a[y] = kx; } }
+				}
+				__syncwarp();
+			}
+		}
+		unsigned long long off = 0;
+		if(lane == 0) off = atomicAdd(total, (unsigned long long)n);
+		off = __shfl_sync(FULL, off, 0);
+		if(off + n > cap) { if(lane == 0) { *errflag = 1; r.ncand = 0; r.aligned = 0; res[ji] = r; } return; }
+		r.cand_off = (uint32_t)off;
+		for(uint32_t i = lane; i < n; i += 32) {
+			const uint64_t k = ~a[i];
+			bt2gpu_dp_cand c; c.score = (int32_t)(uint32_t)(k >> 32) - 32768; c.row = (uint32_t)((k >> 16) & 0xffff); c.col = (uint32_t)(k & 0xffff);
+			cands[off + i] = c;
+		}
+	}
+	if(lane == 0) res[ji] = r;
+}
+
 // ---------------------------------------------------------------------------------------
 // Backtrace.  One WARP per job replays SwAligner::nextAlignment (aligner_sw.cpp:737-1146)
 // over the sorted candidates.  The walk is backtraceNucleotides* (ee_u8.cpp:1283-1877).
@@ -1211,7 +1285,13 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 			}
 		}
 		if(timed) BT2_CUDA(cudaEventRecord(d->ev[1], s));
-		if(phases & 2) {
+		if((phases & 2) && !local && c.maxcol <= E2E_CAP) {
+			k_dp_gather_e2e<<<(c.njobs + 3) / 4, 128, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), d->aux.as<DpAux>(), c.job0, c.njobs,
+				d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
+				(unsigned long long)d->cand_cap, errflag);
+			ctx->launches++;
+			BT2_CUDA(cudaGetLastError());
+		} else if(phases & 2) {
 			const uint32_t gb = (c.njobs + 3) / 4;
 			const size_t gsm = local ? (size_t)4 * 2 * c.maxcol * sizeof(int) : 0;
 			if(gsm > 48 * 1024) {

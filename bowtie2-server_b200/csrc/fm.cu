@@ -395,17 +395,16 @@ __device__ __forceinline__ uint32_t extend_dir(const IndexDev &ix, const ReadVie
 __global__ void __launch_bounds__(256)
 k_extend(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seq,
          const bt2gpu_read *__restrict__ reads, const bt2gpu_extend_job *__restrict__ jobs, uint32_t njobs,
-         bt2gpu_extend_result *__restrict__ out)
+         bt2gpu_extend_result *__restrict__ out, const uint32_t *__restrict__ list, const uint32_t *__restrict__ nlist)
 {
 	const int lane = threadIdx.x & 31, l8 = lane & 7;
 	const unsigned gmask = 0xffu << (lane & 24);
-	const uint32_t ji = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-	if(ji >= njobs) return;
+	// list mode (chained batch runtime): the jobs to run are list[0 .. *nlist), a count only the device knows
+	const uint32_t n = list ? *nlist : njobs;
+	const uint32_t noct = (gridDim.x * blockDim.x) >> 3;
+	for(uint32_t it = (blockIdx.x * blockDim.x + threadIdx.x) >> 3; it < n; it += noct) {
+	const uint32_t ji = list ? list[it] : it;
 	const bt2gpu_extend_job jb = jobs[ji];
-	if(jb.botf <= jb.topf) {          // not a hit (the chained batch runtime passes every seed): nothing to extend
-		if(l8 == 0) { out[ji].nlex = 0; out[ji].nrex = 0; out[ji].fmops = 0; }
-		return;
-	}
 	ReadView s; s.rd = seq + reads[jb.read].rd_off; s.len = (int)reads[jb.read].rd_len; s.rc = !jb.fw; s.rev = false;
 	const int rdlen = s.len, off = jb.off, len = jb.len;
 	uint32_t fmops = 0, nlex = 0, nrex = 0;
@@ -414,6 +413,7 @@ k_extend(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seq,
 	lim = jb.fw ? rdlen - len - off : off;
 	if(lim > 0) nrex = extend_dir(bw, s, jb.topb, jb.botb, jb.fw, off, len, lim, false, gmask, l8, fmops);
 	if(l8 == 0) { out[ji].nlex = (uint16_t)nlex; out[ji].nrex = (uint16_t)nrex; out[ji].fmops = fmops; }
+	}
 }
 
 // ---------------------------------------------------------------------------------------
@@ -788,12 +788,15 @@ int fm_hp_seed(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, 
 }
 
 int fm_hp_extend(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_extend_job *djobs,
-                 size_t njobs, bt2gpu_extend_result *dout)
+                 size_t njobs, bt2gpu_extend_result *dout, const uint32_t *dlist, const uint32_t *dnlist)
 {
 	if(njobs == 0) return 0;
 	FmState *f = ctx->fm;
-	k_extend<<<blocks_for(njobs, 8, 256), 256, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
-		djobs, (uint32_t)njobs, dout);
+	uint32_t blocks = blocks_for(njobs, 8, 256);
+	const uint32_t maxb = (uint32_t)ctx->sm_count * 8;
+	if(blocks > maxb) blocks = maxb;
+	k_extend<<<blocks, 256, 0, ctx->stream>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
+		djobs, (uint32_t)njobs, dout, dlist, dnlist);
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
 	return 0;
@@ -972,7 +975,7 @@ extern "C" int bt2gpu_extend_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, cons
 	BT2_CUDA(cudaMemcpyAsync(f->jobs.p, jobs, njobs * sizeof(bt2gpu_extend_job), cudaMemcpyHostToDevice, s));
 	if(ctx->kstart()) return 1;
 	k_extend<<<blocks_for(njobs, 8, 256), 256, 0, s>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->reads.as<bt2gpu_read>(),
-		f->jobs.as<bt2gpu_extend_job>(), (uint32_t)njobs, f->out.as<bt2gpu_extend_result>());
+		f->jobs.as<bt2gpu_extend_job>(), (uint32_t)njobs, f->out.as<bt2gpu_extend_result>(), nullptr, nullptr);
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
 	if(ctx->kend()) return 1;

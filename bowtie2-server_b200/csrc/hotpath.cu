@@ -26,7 +26,7 @@ namespace bt2 {
 typedef unsigned long long u64;
 
 struct HpState {
-	DevBuf cnt, first, spart, tot, sjobs, shits, xjobs, xres, pick, val, ppos, pk_read, pk_seed, rows, rdoff, offs, steps,
+	DevBuf cnt, first, spart, tot, hitlist, sjobs, shits, xjobs, xres, pick, val, ppos, pk_read, pk_seed, rows, rdoff, offs, steps,
 	       minsc, nceil, job_read, job_start, job_fw, stats;
 	HostBuf h_tot, h_stats;
 	cudaEvent_t ev[12] = {};
@@ -76,7 +76,7 @@ k_hp_seeds(const uint8_t *__restrict__ seq, const bt2gpu_read *__restrict__ read
 // ---- every seed becomes an extend job (k_extend skips the empty ranges) --------------------
 __global__ void __launch_bounds__(256)
 k_hp_mkextend(const bt2gpu_seed_job *__restrict__ sj, const bt2gpu_seed_hit *__restrict__ sh, uint32_t n,
-              bt2gpu_extend_job *__restrict__ xj, u64 *__restrict__ stats)
+              bt2gpu_extend_job *__restrict__ xj, uint32_t *__restrict__ hitlist, uint32_t *__restrict__ nhit, u64 *__restrict__ stats)
 {
 	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
 	u64 bw = 0, sd = 0, hit = 0;
@@ -86,6 +86,13 @@ k_hp_mkextend(const bt2gpu_seed_job *__restrict__ sj, const bt2gpu_seed_hit *__r
 		x.read = j.read; x.topf = h.topf; x.botf = h.botf; x.topb = h.topb; x.botb = h.botb; x.off = j.off; x.len = j.len; x.fw = j.fw;
 		xj[k] = x;
 		bw = h.bwops; sd = h.sides; hit = h.botf > h.topf;
+	}
+	{   // the hits, compacted (order is irrelevant: results land at the seed's own slot)
+		const unsigned bal = __ballot_sync(0xffffffffu, hit != 0);
+		uint32_t base = 0;
+		if((threadIdx.x & 31) == 0 && bal) base = atomicAdd(nhit, (uint32_t)__popc(bal));
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if(hit) hitlist[base + __popc(bal & ((1u << (threadIdx.x & 31)) - 1u))] = k;
 	}
 	for(int o = 16; o; o >>= 1) {
 		bw += __shfl_xor_sync(0xffffffffu, bw, o); sd += __shfl_xor_sync(0xffffffffu, sd, o); hit += __shfl_xor_sync(0xffffffffu, hit, o);
@@ -322,16 +329,19 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 	size_t npick = 0, tot_rd = 0;
 	if(nseed) {
 		if(st.sjobs.reserve(nseed * sizeof(bt2gpu_seed_job)) || st.shits.reserve(nseed * sizeof(bt2gpu_seed_hit)) ||
-		   st.xjobs.reserve(nseed * sizeof(bt2gpu_extend_job)) || st.xres.reserve(nseed * sizeof(bt2gpu_extend_result))) return 1;
+		   st.xjobs.reserve(nseed * sizeof(bt2gpu_extend_job)) || st.xres.reserve(nseed * sizeof(bt2gpu_extend_result)) ||
+		   st.hitlist.reserve(nseed * 4)) return 1;
+		BT2_CUDA(cudaMemsetAsync(st.tot.as<uint32_t>() + 8, 0, 4, s));
 		bt2gpu_seed_job *sj = st.sjobs.as<bt2gpu_seed_job>(); bt2gpu_seed_hit *sh = st.shits.as<bt2gpu_seed_hit>();
 		bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>(); bt2gpu_extend_result *xr = st.xres.as<bt2gpu_extend_result>();
 		k_hp_seeds<true><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, cnt, first, sj);
 		BT2_CUDA(cudaEventRecord(st.ev[2], s));
 		if(fm_hp_seed(ctx, fw, bw, sj, nseed, sh)) return 1;
 		BT2_CUDA(cudaEventRecord(st.ev[3], s));
-		k_hp_mkextend<<<(unsigned)((nseed + 255) / 256), 256, 0, s>>>(sj, sh, (uint32_t)nseed, xj, stats);
+		k_hp_mkextend<<<(unsigned)((nseed + 255) / 256), 256, 0, s>>>(sj, sh, (uint32_t)nseed, xj, st.hitlist.as<uint32_t>(),
+			st.tot.as<uint32_t>() + 8, stats);
 		BT2_CUDA(cudaEventRecord(st.ev[4], s));
-		if(fm_hp_extend(ctx, fw, bw, xj, nseed, xr)) return 1;
+		if(fm_hp_extend(ctx, fw, bw, xj, nseed, xr, st.hitlist.as<uint32_t>(), st.tot.as<uint32_t>() + 8)) return 1;
 		BT2_CUDA(cudaEventRecord(st.ev[5], s));
 		k_hp_pick<<<nbR, 256, 0, s>>>(rv.reads, n32, first, cnt, xj, xr, st.pick.as<uint32_t>(), st.val.as<u64>(), stats);
 		ctx->launches += 3;

@@ -33,13 +33,18 @@ def test_cuda_matches_reference_dump(ctx, name, local):
     assert H.compare_with_dump(probs, *res) == len(probs)
 
 
-def _random_batch(rng, sc, n, local, rdlen_range, mutate=0.06):
+def _random_batch(rng, sc, n, local, rdlen_range, mutate=0.06, tandem=False):
     b = dpio.DpBatch()
     for _ in range(n):
         rdlen = int(rng.integers(*rdlen_range))
         maxgap = int(rng.integers(0, 16))
         width = rdlen + 2 * maxgap
         ref = rng.integers(0, 4, size=width + 1).astype(np.uint8)
+        if tandem:   # tandem repeat: many equally good placements, long runs of tied moves, many candidates
+            unit = rng.integers(0, 4, size=int(rng.integers(1, 9))).astype(np.uint8)
+            ref = np.resize(unit, width + 1).copy()
+            drift = rng.random(width + 1) < 0.02
+            ref[drift] = rng.integers(0, 4, size=int(drift.sum()))
         start = int(rng.integers(0, 2 * maxgap + 1))
         read = ref[start:start + rdlen].copy()
         # substitutions, a deletion and an insertion now and then, a few Ns
@@ -83,6 +88,25 @@ def test_cuda_matches_oracle_random(ctx, local, rdlen_range, n, seed):
         a = dpio.results_to_py(*ref, i)
         b = dpio.results_to_py(*got, i)
         assert a == b, (i, a[0]["best"], b[0]["best"], a[2], b[2])
+
+
+@pytest.mark.parametrize("seed,gapbar", [(21, 4), (22, 1), (23, 8)])
+def test_cuda_matches_oracle_tandem_repeats(ctx, seed, gapbar):
+    # end-to-end windows over tandem repeats: dozens of candidates per window whose walks cross each
+    # other, so the order in which nextAlignment tries them (and what each one marks) decides the answer
+    rng = np.random.default_rng(seed)
+    sc = scoring.Scoring(local=False, gapbar=gapbar)
+    ctx.set_scoring(sc)
+    seq, qual, win, jobs = _random_batch(rng, sc, 300, False, (30, 180), mutate=0.03, tandem=True)
+    ref = H.oracle_dp(sc.to_struct(), seq, qual, win, jobs, max_aln=16, cand_cap=30_000_000, edit_cap=2_000_000)
+    got = ctx.dp_align_batch(seq, qual, win, jobs, max_aln=16, cand_cap=30_000_000, edit_cap=2_000_000)
+    ntries = 0
+    for i in range(len(jobs)):
+        a = dpio.results_to_py(*ref, i)
+        b = dpio.results_to_py(*got, i)
+        assert a == b, (i, a[0], b[0])
+        ntries += a[0]["ncand"]
+    assert ntries > 15 * len(jobs)
 
 
 def test_non_default_scoring(ctx):
