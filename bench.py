@@ -273,7 +273,9 @@ def run_ours(args, rank, world, local_rank):
     ok = np.abs(o["job_start"][:nj] - pos[o["job_read"][:nj]]) <= 64
     frac_true = float(ok.mean()) if nj else 0.0
     cnt = {k: (int(v) if not k.startswith(("ms_", "wall_")) else float(v)) for k, v in cnt.items()}
-    probe = ctx.gather_probe("fw", 1 << 27)
+    probe_ix = ctx.gather_probe("fw", 1 << 27)                # random sides of the index itself (L2 helps when it fits)
+    probe = ctx.probe_random_gather(8 << 30, 1 << 27)         # random 64-B gathers over 8 GiB: the HBM random-access ceiling
+    dpx_peak = ctx.probe_dpx()                                # G thread-instr/s of packed s16x2 DPX
 
     t = torch.tensor([dev_ms, wall_e2e], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -300,18 +302,26 @@ def run_ours(args, rank, world, local_rank):
     # algorithmic bytes per launch: 64 B per distinct BWT side + 16 B of ftab per seed;
     # 64 B per LF step (+4 B offs) in locate; 64 B per side in sweep/extend (bwops counts sides);
     # E, F, H of every DP cell (3 B/cell in the u8 path) for the fill
+    def fm(kernel, sides, extra_bytes, ms, steps=None):
+        d = rl(kernel, 64.0 * sides + extra_bytes, ms)
+        d.update({"random_gather_peak_gbs": probe, "index_gather_gbs": probe_ix,
+                  "frac_of_random_gather": (d["achieved"] / probe) if probe else 0.0})
+        if steps is not None and ms > 0:
+            d["lf_steps_per_s"] = steps / (ms / 1e3)
+        return d
+    fill_ms = kms["dp_fill"] / K
+    dpx = 2.5 * cnt["dp_cells"] / (fill_ms / 1e3) / 1e9 if fill_ms > 0 else 0.0   # 5 DPX instr per packed pair of cells
     rls = [
-        rl("k_seed_exact", 64.0 * cnt["seed_sides"] + 16.0 * cnt["seeds"], kms["seed"] / K,
-           {"lf_steps_per_s": cnt["seed_bwops"] / (kms["seed"] / K / 1e3), "random_gather_peak_gbs": probe,
-            "frac_of_random_gather": (64.0 * cnt["seed_sides"] / (kms["seed"] / K / 1e3) / 1e9) / probe}),
-        rl("k_exact_sweep", 64.0 * cnt["sweep_bwops"], kms["sweep"] / K,
-           {"lf_steps_per_s": cnt["sweep_bwops"] / (kms["sweep"] / K / 1e3), "random_gather_peak_gbs": probe}),
-        rl("k_extend", 64.0 * cnt["extend_fmops"], kms["extend"] / K),
-        rl("k_locate", 68.0 * cnt["locate_steps"] + 4.0 * cnt["locate_rows"], kms["locate"] / K),
-        rl("k_dp_fill", 3.0 * cnt["dp_cells"], kms["dp_fill"] / K,
-           {"gcups": cnt["dp_cells"] / (kms["dp_fill"] / K / 1e3) / 1e9}),
-        rl("k_dp_backtrace", 0.0, kms["dp_backtrace"] / K),
-        rl("k_dp_gather+sort", 0.0, kms["dp_gather"] / K),
+        fm("k_seed_exact", cnt["seed_sides"], 16.0 * cnt["seeds"], kms["seed"] / K, cnt["seed_bwops"]),
+        fm("k_exact_sweep", cnt["sweep_bwops"], 0.0, kms["sweep"] / K, cnt["sweep_bwops"]),
+        fm("k_extend", cnt["extend_fmops"], 0.0, kms["extend"] / K, cnt["extend_fmops"]),
+        fm("k_locate", cnt["locate_steps"], 4.0 * cnt["locate_steps"] + 4.0 * cnt["locate_rows"], kms["locate"] / K, cnt["locate_steps"]),
+        rl("k_dp_fill", 3.0 * cnt["dp_cells"], fill_ms,
+           {"gcups": cnt["dp_cells"] / (fill_ms / 1e3) / 1e9 if fill_ms > 0 else 0.0,
+            "dpx_ginstr_per_s": dpx, "dpx_peak_ginstr_per_s": dpx_peak, "dpx_frac": dpx / dpx_peak if dpx_peak else 0.0}),
+        rl("k_dp_backtrace", 0.0, kms["dp_backtrace"] / K,
+           {"note": "latency/issue-bound walk over the stored matrices; no byte roofline applies"}),
+        rl("k_dp_gather_e2e", 1.0 * cnt["dp_jobs"] * (RDLEN + 4 * MAXGAP), kms["dp_gather"] / K),
     ]
     dominant = max(rls, key=lambda r: r["ms"])
     line = {

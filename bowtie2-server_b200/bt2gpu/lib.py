@@ -21,7 +21,7 @@ SYMBOLS = [
     "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
-    "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes",
+    "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx",
 ]
 
 _lib = None
@@ -224,6 +224,18 @@ class Context:
         h = self._ix.fw if which == "fw" else self._ix.bw
         _check(self.lib.bt2gpu_index_gather_probe(self._h, h, C.c_uint64(nloads), C.byref(g)))
         return float(g.value)
+
+    def probe_random_gather(self, table_bytes=8 << 30, nloads=1 << 27):
+        """GB/s of independent random 64-byte gathers over a scratch table far larger than L2."""
+        g = C.c_double(0)
+        _check(self.lib.bt2gpu_probe_random_gather(self._h, C.c_uint64(table_bytes), C.c_uint64(nloads), C.byref(g)))
+        return g.value
+
+    def probe_dpx(self):
+        """G thread-instructions/s of packed s16x2 DPX (VIADDMNMX / VIMNMX3)."""
+        g = C.c_double(0)
+        _check(self.lib.bt2gpu_probe_dpx(self._h, C.byref(g)))
+        return g.value
 
     def hotpath_round0(self, ref, seq, qual, reads, minsc, nceil, seed_len=22, ival=(1.0, 1.15), maxgap=15,
                        max_aln=2, mine_max=2, nthreads=0, out=None):

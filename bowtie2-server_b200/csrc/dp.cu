@@ -231,32 +231,37 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 // ---------------------------------------------------------------------------------------
 // Matrix access for gather / backtrace: cell (row, col) of matrix m (0=E, 1=F, 2=H).
 // ---------------------------------------------------------------------------------------
-struct RowRef { int stT, v, k; };    // stripe * T, virtual lane and register of a DP row
+// A DP row resolved once: its step offset (stripe * T + virtual lane) and the byte offset of its
+// E, F and H elements inside a lane-step record chunk; a cell is then one byte/halfword load at
+// base + (tv + col) * record bytes + off[m].
+struct RowRef { int tv; int off[3]; };
 struct MatView {
 	const uint32_t *base; int S, T, RW, SH;
-	uint32_t invS, invRS; int stride;     // ceil(2^32 / S), ceil(2^32 / (16 S)), GL * RW
+	uint32_t invS, invRS; int stride;     // ceil(2^32 / S), ceil(2^32 / (16 S)), record bytes of one step (GL * RW * 4)
 	bool rec8;                            // byte records (u8 end-to-end path)
 	__device__ __forceinline__ void init(const uint32_t *b, int S_, int T_, int RW_, bool rec8_) {
 		base = b; S = S_; T = T_; RW = RW_; rec8 = rec8_; SH = (S_ + 1) >> 1;
 		invS = 0xffffffffu / (uint32_t)S + 1u; invRS = 0xffffffffu / (uint32_t)(VL * S) + 1u;
-		stride = GL * RW;
+		stride = GL * RW * 4;
 	}
 	// row -> (stripe, virtual lane, register) by multiply-high: exact for rows < 2^16
 	__device__ __forceinline__ RowRef rowref(int row) const {
 		const int st = (int)__umulhi((uint32_t)row, invRS), r = row - st * (VL * S);
-		RowRef rr; rr.v = (int)__umulhi((uint32_t)r, invS); rr.k = r - rr.v * S; rr.stT = st * T;
+		const int v = (int)__umulhi((uint32_t)r, invS), k = r - v * S;
+		RowRef rr; rr.tv = st * T + v;
+		const int lane_b = (v >> 1) * 16;
+#pragma unroll
+		for(int m = 0; m < 3; m++) {
+			const int idx = rec8 ? m * SH + (k >> 1) : m * S + k;
+			const int sub = rec8 ? (((k & 1) << 1) | (v & 1)) : ((v & 1) << 1);
+			rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + sub;
+		}
 		return rr;
 	}
 	__device__ __forceinline__ int at(int m, const RowRef &rr, int col) const {
-		if(rec8) {
-			const int idx = m * SH + (rr.k >> 1);
-			const uint32_t w = __ldcg(base + (size_t)(rr.stT + col + rr.v) * stride + ((idx >> 2) * GL + (rr.v >> 1)) * 4 + (idx & 3));
-			const int b = (int)((w >> (8 * (((rr.k & 1) << 1) | (rr.v & 1)))) & 0xffu);
-			return b ? b - 256 : 0;
-		}
-		const int idx = m * S + rr.k;
-		const uint32_t w = __ldcg(base + (size_t)(rr.stT + col + rr.v) * stride + ((idx >> 2) * GL + (rr.v >> 1)) * 4 + (idx & 3));
-		return (rr.v & 1) ? hi16(w) : lo16(w);
+		const unsigned char *p = reinterpret_cast<const unsigned char*>(base) + (size_t)(rr.tv + col) * (size_t)stride + rr.off[m];
+		if(rec8) { const int b = (int)__ldcg(p); return b ? b - 256 : 0; }
+		return (int)__ldcg(reinterpret_cast<const short*>(p));
 	}
 	__device__ __forceinline__ int get(int m, int row, int col) const { return at(m, rowref(row), col); }
 };
@@ -333,7 +338,7 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	int cnt = 0;
 	for(int rix = lane; rix < nrec; rix += 32) {
 		const int l = rix & (GL - 1), t = (rix >> 3) % T, st = (rix >> 3) / T;
-		const uint32_t *rp = mv.base + (size_t)(rix >> 3) * GL * mv.RW;
+		const uint32_t *rp = mv.base + (size_t)(rix >> 3) * GL * mv.RW;   // whole records, word-addressed (s16 layout: local mode)
 		for(int k = 0; k < S; k++) {
 			const int idx = 2 * S + k;
 			const uint32_t w = __ldcg(rp + ((idx >> 2) * GL + l) * 4 + (idx & 3));

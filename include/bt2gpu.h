@@ -186,6 +186,11 @@ uint64_t bt2gpu_index_bytes(const bt2gpu_index *idx);
 /* Roofline probe: bandwidth (GB/s) of `nloads` independent random 64-byte side gathers over this
  * index at full occupancy -- the HBM random-access ceiling of the seed kernels. */
 int bt2gpu_index_gather_probe(bt2gpu_ctx *ctx, const bt2gpu_index *idx, uint64_t nloads, double *gbs);
+/* Roofline probes on this device (probe.cu): independent random 64-byte gathers over a scratch table of
+ * `table_bytes` (choose it far larger than the 126 MB L2), and the issue rate of the packed s16x2 DPX
+ * instructions the DP fill is made of, in G thread-instructions/s. */
+int bt2gpu_probe_random_gather(bt2gpu_ctx *ctx, uint64_t table_bytes, uint64_t nloads, double *gbs);
+int bt2gpu_probe_dpx(bt2gpu_ctx *ctx, double *ginstr_per_s);
 
 /* A read in the pools: bytes 0..4 (A,C,G,T,N), forward strand (Read::patFw);
  * quality bytes Phred+33 (Read::qual).  The kernels derive patRc/patFwRev/... */
