@@ -82,6 +82,20 @@ __device__ __forceinline__ int dev_mm(int rdc, int refm, int q) {
 // ---------------------------------------------------------------------------------------
 // Fill.  One 8-lane group per job; jobs of one S class per launch, taken in `order`.
 // ---------------------------------------------------------------------------------------
+// a[idx] for a register array (idx is not a compile-time constant): a tree of selects on the bits of idx
+template<int N> __device__ __forceinline__ uint32_t pick_reg(const uint32_t *a, int idx) {
+	uint32_t t[N];
+#pragma unroll
+	for(int i = 0; i < N; i++) t[i] = a[i];
+#pragma unroll
+	for(int bit = 0, n = N; n > 1; bit++, n = (n + 1) / 2) {
+		const bool b = (idx >> bit) & 1;
+#pragma unroll
+		for(int i = 0; i < (n + 1) / 2; i++) t[i] = (b && 2 * i + 1 < n) ? t[2 * i + 1] : t[2 * i];
+	}
+	return t[0];
+}
+
 template<int S>
 __global__ void __launch_bounds__(128)
 k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
@@ -142,6 +156,12 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 			const uint32_t *bin = (st & 1) ? bnd1 : bnd0;      // written by stripe st-1
 			uint32_t *bout = (st & 1) ? bnd0 : bnd1;
 			const bool lastStripe = (st + 1 == (int)ax.nstripes);
+			// the matrix's last row (end-to-end candidates, gatherCellsNucleotidesEnd2End*) lives in one half of one
+			// lane of the last stripe; that lane copies its H values, column by column, into the boundary buffer the
+			// last stripe leaves free, so the gather reads one contiguous row instead of one sector per column
+			const int rlast = nrow - 1 - st * (VL * S);
+			const int vlast = lastStripe ? rlast / S : -1, klast = lastStripe ? rlast - vlast * S : 0;
+			const bool ownLast = lastStripe && (vlast >> 1) == l;
 			// top boundary of the matrix: H(-1,j) = 0 in both modes (0xff / 0x7fff raw end-to-end,
 			// 0 local), F(-1,j) = floor  (ee_u8.cpp:920-927, loc_u8.cpp:1066-1075)
 			const uint32_t top0 = pack2(0, fl);
@@ -196,8 +216,17 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 					hdiag = Hprev[k]; Hprev[k] = H; Hup = H; Fup = F;
 				}
 				Hbot = Hup; Fbot = Fup;
+				if(ownLast) {
+					const int cl = t - vlast;
+					if(cl >= 0 && cl < ncol) {
+						const uint32_t hw = pick_reg<S>(rec + 2 * S, klast);
+						bout[cl] = (uint32_t)((vlast & 1) ? hi16(hw) : lo16(hw));
+					}
+				}
 				if(rec8) {
-					constexpr int SH = (S + 1) / 2;               // words per matrix: 2 rows x 2 halves per word
+					// byte records: word m * SH + k / 2 holds the low bytes of [lo(k), hi(k), lo(k+1), hi(k+1)] of
+					// matrix m (one PRMT per word; a cell-major order costs three and did not pay off downstream)
+					constexpr int SH = (S + 1) / 2;
 					constexpr int RW8 = (3 * SH + 3) & ~3;
 					uint32_t r8[RW8];
 #pragma unroll
@@ -206,7 +235,7 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 						for(int kp = 0; kp < SH; kp++) {
 							const uint32_t a = rec[m * S + 2 * kp];
 							const uint32_t b = (2 * kp + 1 < S) ? rec[m * S + 2 * kp + 1] : 0u;
-							r8[m * SH + kp] = __byte_perm(a, b, 0x6420);   // [lo(k), hi(k), lo(k+1), hi(k+1)] low bytes
+							r8[m * SH + kp] = __byte_perm(a, b, 0x6420);
 						}
 #pragma unroll
 					for(int k = 3 * SH; k < RW8; k++) r8[k] = 0;
@@ -250,16 +279,25 @@ struct MatView {
 		const int v = (int)__umulhi((uint32_t)r, invS), k = r - v * S;
 		RowRef rr; rr.tv = st * T + v;
 		const int lane_b = (v >> 1) * 16;
+		if(rec8) {       // byte records: word m * SH + k / 2, byte (k & 1) * 2 + (v & 1)
+			const int sub = ((k & 1) << 1) | (v & 1);
+#pragma unroll
+			for(int m = 0; m < 3; m++) {
+				const int idx = m * SH + (k >> 1);
+				rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + sub;
+			}
+			return rr;
+		}
 #pragma unroll
 		for(int m = 0; m < 3; m++) {
-			const int idx = rec8 ? m * SH + (k >> 1) : m * S + k;
-			const int sub = rec8 ? (((k & 1) << 1) | (v & 1)) : ((v & 1) << 1);
-			rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + sub;
+			const int idx = m * S + k;
+			rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + ((v & 1) << 1);
 		}
 		return rr;
 	}
 	__device__ __forceinline__ int at(int m, const RowRef &rr, int col) const {
-		const unsigned char *p = reinterpret_cast<const unsigned char*>(base) + (size_t)(rr.tv + col) * (size_t)stride + rr.off[m];
+		// a job's matrix is far below 4 GiB (dp_stage bounds rows and columns): 32-bit offset, one IMAD
+		const unsigned char *p = reinterpret_cast<const unsigned char*>(base) + (uint32_t)((rr.tv + col) * stride + rr.off[m]);
 		if(rec8) { const int b = (int)__ldcg(p); return b ? b - 256 : 0; }
 		return (int)__ldcg(reinterpret_cast<const short*>(p));
 	}
@@ -488,7 +526,7 @@ k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__r
 static constexpr int E2E_CAP = 512;
 __global__ void __launch_bounds__(128)
 k_dp_gather_e2e(const bt2gpu_dp_job *__restrict__ jobs, const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
-                const uint32_t *__restrict__ mat, bt2gpu_dp_result *__restrict__ res, bt2gpu_dp_cand *__restrict__ cands,
+                const uint32_t *__restrict__ bound, bt2gpu_dp_result *__restrict__ res, bt2gpu_dp_cand *__restrict__ cands,
                 unsigned long long *__restrict__ total, unsigned long long cap, int *__restrict__ errflag)
 {
 	__shared__ uint64_t s_keys[4][E2E_CAP];
@@ -499,14 +537,14 @@ k_dp_gather_e2e(const bt2gpu_dp_job *__restrict__ jobs, const DpAux *__restrict_
 	const bt2gpu_dp_job jb = jobs[ji];
 	const DpAux ax = aux[ji];
 	const int nrow = (int)jb.rd_len, ncol = (int)jb.ncol, minsc = jb.minsc;
-	MatView mv; mv.init(mat + ax.mat_off, (int)ax.S, (int)ax.T, (int)ax.RW, ax.fl == -255);
 	uint64_t *a = s_keys[wib];
-	const RowRef rr = mv.rowref(nrow - 1);
+	// last row of H, left by the fill in the boundary buffer its last stripe does not use
+	const int32_t *lastrow = reinterpret_cast<const int32_t*>(bound + ax.bound_off + (((ax.nstripes - 1) & 1) ? 0 : ncol));
 	int best = INT32_MIN; uint32_t cnt = 0;
 	for(int j0 = 0; j0 < ncol; j0 += 32) {
 		const int j = j0 + lane;
 		int h = INT32_MIN;
-		if(j < ncol) h = mv.at(2, rr, j);
+		if(j < ncol) h = __ldcg(lastrow + j);
 		best = max(best, h);
 		const bool in = j < ncol && h >= minsc;
 		const unsigned bal = __ballot_sync(FULL, in);
@@ -595,7 +633,7 @@ struct BtJob {
 	// move out of an H cell: 0 = none (empty mask), 1 diag, 2 ref-open, 5 ref-ext, 3 read-open, 4 read-ext
 	__device__ __forceinline__ int h_move(int row, int col) const {
 		const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
-		const RowRef rc = mv.rowref(row), ru = mv.rowref(row - 1);
+		const RowRef rc = mv.rowref(row), ru = mv.rowref(row > 0 ? row - 1 : 0);   // row 0: callers discard the result
 		// all neighbours are fetched up front (independent loads, one round trip)
 		const int sc_cur = mv.at(2, rc, col);
 		const int hu = mv.at(2, ru, col), fu = mv.at(1, ru, col);
@@ -623,7 +661,7 @@ struct BtJob {
 	}
 	// E (ct 0) or F (ct 1) cell in one code path: 3/2 open, 4/5 extend, 0 none
 	__device__ __forceinline__ int g_move(int ct, int row, int col) const {
-		const int pr = row - ct, pc = col - (1 - ct);
+		const int pr = max(row - ct, 0), pc = max(col - (1 - ct), 0);      // clamped: callers discard row 0 / col 0 results
 		const int sc_cur = mv.get(ct, row, col);
 		const int hp = mv.get(2, pr, pc), gp = mv.get(ct, pr, pc);
 		const int open = ct ? c_sc.rfo : c_sc.rdo, ext = ct ? c_sc.rfe : c_sc.rde;
@@ -664,7 +702,7 @@ struct BtJob {
 // full walker below.
 static constexpr int TR_LMAX = 32;                // recorded cells per trial walk = rows of the window
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 8)
 k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
                const uint8_t *__restrict__ win, const bt2gpu_dp_job *__restrict__ jobs,
                const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
@@ -1292,7 +1330,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 		if(timed) BT2_CUDA(cudaEventRecord(d->ev[1], s));
 		if((phases & 2) && !local && c.maxcol <= E2E_CAP) {
 			k_dp_gather_e2e<<<(c.njobs + 3) / 4, 128, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), d->aux.as<DpAux>(), c.job0, c.njobs,
-				d->mat.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
+				d->bound.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
 				(unsigned long long)d->cand_cap, errflag);
 			ctx->launches++;
 			BT2_CUDA(cudaGetLastError());
