@@ -258,6 +258,9 @@ class Context:
             _ptr(out["results"]), _ptr(out["alns"]), _ptr(out["edits"]), C.c_size_t(len(out["edits"])), C.byref(ne),
             C.byref(S)))
         out["njobs"], out["nedits"] = nj.value, ne.value
+        # the batch stays staged on the device: dp_fetch() can read it again (with the candidate pool)
+        self._dp_n, self._dp_k = nj.value, max_aln
+        self._cand_cap, self._edit_cap = 256 * max(nj.value, 1), len(out["edits"])
         return out, S.as_dict()
 
     def locate_stage(self, rows):

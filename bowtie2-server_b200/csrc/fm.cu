@@ -355,41 +355,33 @@ k_locate(const IndexDev ix, const uint32_t *__restrict__ rows, uint32_t n,
 // ---------------------------------------------------------------------------------------
 // Kernel 1d: SwDriver::extend (aligner_sw_driver.cpp:299-484).  One octet per seed hit.
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t extend_dir(const IndexDev &ix, const ReadView &s, uint32_t top, uint32_t bot,
-                                               int fw, int off, int len, int lim, bool left, unsigned gmask,
-                                               int l8, uint32_t &fmops)
+// One step of SwDriver::extend's loop in one direction (:332-404 left over the forward index,
+// :405-484 right over the mirror): false when the extension stops before this character.
+__device__ __forceinline__ bool extend_step(const IndexDev &ix, const ReadView &s, uint32_t &top, uint32_t &bot,
+                                            int i, unsigned gmask, int l8)
 {
-	uint32_t nex = 0;
-	const int rdlen = s.len;
-	for(int ii = 0; ii < lim; ii++) {
-		int i;
-		if(left) i = fw ? off - ii - 1 : rdlen - off - len - 1 - ii;
-		else     i = fw ? ii + len + off : rdlen - off + ii;
-		const int rdc = s.at(i);
-		uint32_t t[4], b[4]; int topc;
-		const bool single = (bot - top == 1);
-		octet_lf(ix, top, single ? top : bot, gmask, l8, t, b, topc);
-		fmops++;
-		if(!single) {
-			int nonz = -1; bool abort = false;
-			const uint32_t orig = bot - top;
+	const int rdc = s.at(i);
+	uint32_t t[4], b[4]; int topc;
+	const bool single = (bot - top == 1);
+	octet_lf(ix, top, single ? top : bot, gmask, l8, t, b, topc);
+	if(!single) {
+		int nonz = -1; bool abort = false;
+		const uint32_t orig = bot - top;
 #pragma unroll
-			for(int j = 0; j < 4; j++) {
-				if(!abort && b[j] > t[j]) {
-					if(nonz >= 0) abort = true;
-					else { nonz = j; top = t[j]; bot = b[j]; }
-				}
+		for(int j = 0; j < 4; j++) {
+			if(!abort && b[j] > t[j]) {
+				if(nonz >= 0) abort = true;
+				else { nonz = j; top = t[j]; bot = b[j]; }
 			}
-			if(abort || (nonz != rdc && rdc <= 3) || bot - top < orig) break;
-		} else {
-			int c = -1;                                         // mapLF1(row&, l), bt2_idx.h:2451
-			if(top != ix.zoff) { c = topc; top = pick4(t, c); }
-			if(c != rdc && rdc <= 3) break;
-			bot = top + 1;
 		}
-		if(++nex == 255) break;
+		if(abort || (nonz != rdc && rdc <= 3) || bot - top < orig) return false;
+	} else {
+		int c = -1;                                         // mapLF1(row&, l), bt2_idx.h:2451
+		if(top != ix.zoff) { c = topc; top = pick4(t, c); }
+		if(c != rdc && rdc <= 3) return false;
+		bot = top + 1;
 	}
-	return nex;
+	return true;
 }
 
 __global__ void __launch_bounds__(256)
@@ -397,22 +389,45 @@ k_extend(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seq,
          const bt2gpu_read *__restrict__ reads, const bt2gpu_extend_job *__restrict__ jobs, uint32_t njobs,
          bt2gpu_extend_result *__restrict__ out, const uint32_t *__restrict__ list, const uint32_t *__restrict__ nlist)
 {
+	// Persistent octets: extensions run 0..255 characters each way, so an octet that is done takes the next
+	// hit at once (one flat loop, one rank step per iteration; octets diverge freely -- the walk is
+	// latency-bound and independently scheduled octets hide more of it than a converged warp does).
+	// list mode (chained batch runtime): the jobs to run are list[0 .. *nlist), a count only the device knows.
 	const int lane = threadIdx.x & 31, l8 = lane & 7;
 	const unsigned gmask = 0xffu << (lane & 24);
-	// list mode (chained batch runtime): the jobs to run are list[0 .. *nlist), a count only the device knows
 	const uint32_t n = list ? *nlist : njobs;
 	const uint32_t noct = (gridDim.x * blockDim.x) >> 3;
-	for(uint32_t it = (blockIdx.x * blockDim.x + threadIdx.x) >> 3; it < n; it += noct) {
-	const uint32_t ji = list ? list[it] : it;
-	const bt2gpu_extend_job jb = jobs[ji];
-	ReadView s; s.rd = seq + reads[jb.read].rd_off; s.len = (int)reads[jb.read].rd_len; s.rc = !jb.fw; s.rev = false;
-	const int rdlen = s.len, off = jb.off, len = jb.len;
-	uint32_t fmops = 0, nlex = 0, nrex = 0;
-	int lim = jb.fw ? off : rdlen - len - off;
-	if(lim > 0) nlex = extend_dir(fw, s, jb.topf, jb.botf, jb.fw, off, len, lim, true, gmask, l8, fmops);
-	lim = jb.fw ? rdlen - len - off : off;
-	if(lim > 0) nrex = extend_dir(bw, s, jb.topb, jb.botb, jb.fw, off, len, lim, false, gmask, l8, fmops);
-	if(l8 == 0) { out[ji].nlex = (uint16_t)nlex; out[ji].nrex = (uint16_t)nrex; out[ji].fmops = fmops; }
+	uint32_t next = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+	bt2gpu_extend_job jb; memset(&jb, 0, sizeof(jb));
+	ReadView s; s.rd = seq; s.len = 0; s.rc = false; s.rev = false;
+	uint32_t ji = 0, top = 0, bot = 0, fmops = 0, nex = 0, nlex = 0;
+	int phase = 2, ii = 0, lim = 0;          // 0 = left over fw, 1 = right over bw, 2 = no job
+	for(;;) {
+		if(phase == 2) {
+			if(next >= n) break;
+			ji = list ? list[next] : next; next += noct;
+			jb = jobs[ji];
+			s.rd = seq + reads[jb.read].rd_off; s.len = (int)reads[jb.read].rd_len; s.rc = !jb.fw;
+			fmops = 0; nlex = 0;
+			phase = 0; ii = 0; nex = 0; top = jb.topf; bot = jb.botf;
+			lim = jb.fw ? (int)jb.off : s.len - (int)jb.len - (int)jb.off;
+		}
+		if(ii < lim) {
+			const int rdlen = s.len, off = jb.off, len = jb.len;
+			int i;
+			if(phase == 0) i = jb.fw ? off - ii - 1 : rdlen - off - len - 1 - ii;
+			else           i = jb.fw ? ii + len + off : rdlen - off + ii;
+			fmops++;
+			if(extend_step(phase == 0 ? fw : bw, s, top, bot, i, gmask, l8)) { ii++; if(++nex == 255) ii = lim; }
+			else ii = lim;
+		} else if(phase == 0) {
+			nlex = nex;
+			phase = 1; ii = 0; nex = 0; top = jb.topb; bot = jb.botb;
+			lim = jb.fw ? s.len - (int)jb.len - (int)jb.off : (int)jb.off;
+		} else {
+			if(l8 == 0) { out[ji].nlex = (uint16_t)nlex; out[ji].nrex = (uint16_t)nex; out[ji].fmops = fmops; }
+			phase = 2;
+		}
 	}
 }
 

@@ -70,3 +70,118 @@ def test_hot_path_chain_matches_oracle():
     assert st["aligned"] == c["aligned"] and st["seed_bwops"] == c["seed_bwops"] and st["locate_steps"] == c["locate_steps"]
     assert ctx.gather_probe("fw", 1 << 22) > 0
     ctx.close()
+
+
+def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, max_aln=2):
+    """The batch runtime's chain restated with the CPU oracle stage by stage (ragged reads)."""
+    orc = H.FmOracle(ix, sc.to_struct())
+    orc.stage_reads(pool)
+    sweep = orc.exact_sweep()
+    sj, _ = fmio.instantiate_exact_seeds(pool, seed_len)
+    sh = orc.seed_exact(sj) if len(sj) else np.zeros(0, dtype=structs.seed_hit)
+    hit = np.nonzero(sh["botf"] > sh["topf"])[0]
+    xj = np.zeros(len(hit), dtype=structs.extend_job)
+    for f in ("read", "off", "len", "fw"):
+        xj[f] = sj[f][hit]
+    for f in ("topf", "botf", "topb", "botb"):
+        xj[f] = sh[f][hit]
+    xr = orc.extend(xj) if len(xj) else np.zeros(0, dtype=structs.extend_result)
+    picks = []
+    h = 0
+    while h < len(xj):
+        e, best = h, h
+        while e < len(xj) and xj["read"][e] == xj["read"][h]:
+            sz, bsz = int(xj["botf"][e]) - int(xj["topf"][e]), int(xj["botf"][best]) - int(xj["topf"][best])
+            ex, bex = int(xr["nlex"][e]) + int(xr["nrex"][e]), int(xr["nlex"][best]) + int(xr["nrex"][best])
+            if sz < bsz or (sz == bsz and ex > bex):
+                best = e
+            e += 1
+        picks.append(best)
+        h = e
+    picks = np.array(picks, dtype=np.int64)
+    offs, steps = orc.locate(xj["topf"][picks]) if len(picks) else (np.zeros(0, np.uint32), np.zeros(0, np.uint32))
+    b_seq, b_qual, b_win, jobs, rid, starts, fws = [], [], [], np.zeros(len(picks), dtype=structs.dp_job), [], [], []
+    G = len(genome)
+    ro = wo = 0
+    comp = np.array([3, 2, 1, 0, 4], np.uint8)
+    for k, p in enumerate(picks):
+        x = xj[p]
+        ri = int(x["read"]); rdlen = int(pool.reads["rd_len"][ri]); o = int(pool.reads["rd_off"][ri])
+        rd, qu = pool.seq[o:o + rdlen], pool.qual[o:o + rdlen]
+        if not x["fw"]:
+            rd, qu = comp[rd[::-1]], qu[::-1]
+        seedoff = int(x["off"]) if x["fw"] else rdlen - int(x["off"]) - int(x["len"])
+        start = int(offs[k]) - seedoff
+        refl = start - 2 * maxgap
+        ncol = rdlen + 4 * maxgap
+        cols = refl + np.arange(ncol + 1)
+        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
+        b_seq.append(rd); b_qual.append(qu); b_win.append((1 << codes).astype(np.uint8))
+        j = jobs[k]
+        j["rd_off"], j["rd_len"], j["rf_off"], j["ncol"] = ro, rdlen, wo, ncol
+        j["minsc"], j["nceil"], j["refl"], j["triml"] = minsc[ri], nceil[ri], refl, 0
+        j["corel"], j["corer"], j["fw"], j["enable8"] = maxgap, 3 * maxgap, x["fw"], 1
+        ro += rdlen; wo += ncol + 1
+        rid.append(ri); starts.append(start); fws.append(int(x["fw"]))
+    cat = lambda a: np.ascontiguousarray(np.concatenate(a)) if a else np.zeros(0, np.uint8)
+    ref = H.oracle_dp(sc.to_struct(), cat(b_seq), cat(b_qual), cat(b_win), jobs, max_aln=max_aln) if len(jobs) else None
+    return dict(sweep=sweep, nseeds=len(sj), rid=np.array(rid), start=np.array(starts), fw=np.array(fws), dp=ref, njobs=len(jobs),
+                steps=int(steps.sum()) if len(picks) else 0)
+
+
+def test_batch_runtime_ragged_reads_match_oracle():
+    # reads of every length from 1 up (shorter than the seed, shorter than the ftab jump), all-N reads,
+    # reads off both ends of the text: the device glue (seed instantiation, pick, compaction, framing,
+    # device-side DP staging with several stripe classes) against the oracle chained stage by stage
+    rng = np.random.default_rng(7)
+    genome = synth.random_genome(rng, 1 << 18)
+    ix, _ = build.build_index([genome], ["chr1"])
+    sc = scoring.Scoring(local=False)
+    ctx = lib.Context(0)
+    ctx.set_scoring(sc)
+    dix = lib.DeviceIndex(ix, 0)
+    ctx.bind_index(dix)
+    dref = lib.DeviceRef(genome)
+    seqs, quals = [], []
+    lens = list(range(1, 40)) + [int(x) for x in rng.integers(22, 420, size=700)]
+    for i, L in enumerate(lens):
+        p = int(rng.integers(0, len(genome) - L))
+        if i % 97 == 0:
+            p = 0 if (i // 97) % 2 == 0 else len(genome) - L          # windows hang off the text
+        r = genome[p:p + L].copy()
+        mm = rng.random(L) < 0.02
+        r[mm] = rng.integers(0, 4, size=int(mm.sum()))
+        if i % 11 == 0:
+            r[rng.integers(0, L)] = 4
+        if i % 53 == 0:
+            r[:] = 4
+        if rng.random() < 0.5:
+            r = np.array([3, 2, 1, 0, 4], np.uint8)[r[::-1]]
+        seqs.append(r.astype(np.uint8)); quals.append((rng.integers(2, 41, size=L) + 33).astype(np.uint8))
+    pool = fmio.ReadPool.__new__(fmio.ReadPool)
+    pool.seq, pool.qual = np.concatenate(seqs), np.concatenate(quals)
+    pool.reads = np.zeros(len(lens), dtype=structs.read)
+    pool.reads["rd_len"] = lens
+    pool.reads["rd_off"] = np.concatenate([[0], np.cumsum(lens)[:-1]])
+    minsc = np.array([sc.score_min.f_int(L) for L in lens], dtype=np.int32)
+    nceil = np.array([sc.nceil(L) for L in lens], dtype=np.int32)
+    want = _oracle_round0(ix, genome, sc, pool, minsc, nceil)
+    out, st = ctx.hotpath_round0(dref, pool.seq, pool.qual, pool.reads, minsc, nceil)
+    nj = out["njobs"]
+    assert out["sweep"].tobytes() == want["sweep"].tobytes()
+    assert st["seeds"] == want["nseeds"] and nj == want["njobs"] and nj > 400
+    assert np.array_equal(out["job_read"][:nj], want["rid"]) and np.array_equal(out["job_start"][:nj], want["start"])
+    assert np.array_equal(out["job_fw"][:nj], want["fw"]) and st["locate_steps"] == want["steps"]
+    got = ctx.dp_fetch()
+    for i in range(nj):
+        assert dpio.results_to_py(*want["dp"], i) == dpio.results_to_py(got[0], got[1], got[2], got[3], i), i
+    # an empty batch and a batch without a single seed are not errors
+    e = np.zeros(0, dtype=np.uint8)
+    out0, st0 = ctx.hotpath_round0(dref, np.zeros(1, np.uint8), np.zeros(1, np.uint8), np.zeros(0, dtype=structs.read),
+                                   np.zeros(0, np.int32), np.zeros(0, np.int32))
+    assert out0["njobs"] == 0
+    rdN = np.zeros(2, dtype=structs.read); rdN["rd_len"] = 30; rdN["rd_off"] = [0, 30]
+    outN, stN = ctx.hotpath_round0(dref, np.full(60, 4, np.uint8), np.full(60, 73, np.uint8), rdN,
+                                   np.full(2, -18, np.int32), np.full(2, 1, np.int32))
+    assert outN["njobs"] == 0 and stN["seeds"] == 0
+    ctx.close()
