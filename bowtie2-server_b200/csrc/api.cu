@@ -34,6 +34,9 @@ extern "C" int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
 	c->sm_count = prop.multiProcessorCount;
 	cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 	if(e != cudaSuccess) { delete c; return fail("cudaStreamCreate", __FILE__, __LINE__, e); }
+	e = cudaStreamCreateWithFlags(&c->cstream, cudaStreamNonBlocking);
+	if(e != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return fail("cudaStreamCreate", __FILE__, __LINE__, e); }
+	for(int i = 0; i < 2; i++) cudaEventCreateWithFlags(&c->cev[i], cudaEventDisableTiming);
 	*out = c;
 	return 0;
 }
@@ -45,6 +48,8 @@ extern "C" void bt2gpu_ctx_destroy(bt2gpu_ctx *ctx) {
 	dp_state_free(ctx->dp);
 	fm_state_free(ctx->fm);
 	for(int i = 0; i < 2; i++) if(ctx->kev[i]) cudaEventDestroy(ctx->kev[i]);
+	for(int i = 0; i < 2; i++) if(ctx->cev[i]) cudaEventDestroy(ctx->cev[i]);
+	if(ctx->cstream) { cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream); }
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }

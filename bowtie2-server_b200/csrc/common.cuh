@@ -72,6 +72,8 @@ struct DpDevPools { uint8_t *seq, *qual, *win; bt2gpu_dp_job *jobs; };
 struct bt2gpu_ctx {
 	int device = 0;
 	cudaStream_t stream = nullptr;
+	cudaStream_t cstream = nullptr;       // copy stream of the batch runtime (transfers that overlap kernels)
+	cudaEvent_t cev[2] = {nullptr, nullptr};
 	uint64_t launches = 0;
 	int sm_count = 0;
 	bt2gpu_scoring sc;
@@ -97,7 +99,7 @@ struct bt2gpu_ctx {
 namespace bt2 {
 // fm.cu: same kernels as the C-ABI entry points, device pointers in and out, no synchronisation
 int fm_hp_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
-                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view);
+                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view, cudaStream_t qual_stream);
 int fm_hp_sweep(bt2gpu_ctx *ctx, const bt2gpu_index *fw, uint32_t mine_max, bt2gpu_sweep_result **dev_out);
 int fm_hp_seed(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_seed_job *djobs,
                size_t njobs, bt2gpu_seed_hit *dout);

@@ -1097,7 +1097,7 @@ __host__ __device__ __forceinline__ DpSizes operator+(const DpSizes &a, const Dp
 	DpSizes r; r.mat = a.mat + b.mat; r.rep = a.rep + b.rep; r.bound = a.bound + b.bound; r.escr = a.escr + b.escr; return r;
 }
 // summary read back by the host: [0..7] jobs per class, [8] max ncol, [9] error code, then cells (u64 at word 10)
-static constexpr int DPSUM_WORDS = 16;
+static constexpr int DPSUM_WORDS = 24;    // [16..23]: per-class fill counters of k_dp_order
 __constant__ int c_sclasses[8] = {3, 4, 5, 6, 8, 10, 12, 16};
 
 __global__ void __launch_bounds__(256)
@@ -1106,6 +1106,7 @@ k_dp_aux(const bt2gpu_dp_job *__restrict__ jobs, uint32_t njobs, unsigned long l
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	unsigned long long cells = 0;
+	int mycls = -1; uint32_t mycol = 0;
 	if(i < njobs) {
 		const bt2gpu_dp_job j = jobs[i];
 		int err = 0;
@@ -1133,12 +1134,21 @@ k_dp_aux(const bt2gpu_dp_job *__restrict__ jobs, uint32_t njobs, unsigned long l
 		z.bound = 2 * j.ncol; z.escr = j.rd_len + j.ncol + 4;
 		if(err) { atomicMax(&sum[9], (uint32_t)err); z.mat = z.rep = 0; z.bound = z.escr = 0; }
 		aux[i] = a; cls[i] = (uint8_t)best; sizes[i] = z;
-		atomicAdd(&sum[best], 1u);
-		atomicMax(&sum[8], j.ncol);
+		mycls = best; mycol = j.ncol;
 		cells = (unsigned long long)j.rd_len * j.ncol;
 	}
-	for(int o = 16; o; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
-	if((threadIdx.x & 31) == 0 && cells) atomicAdd(reinterpret_cast<unsigned long long*>(sum + 10), cells);
+	// one atomic per warp and class (a batch is mostly one class: 65 us of same-address atomics otherwise)
+	const int lane = threadIdx.x & 31;
+#pragma unroll
+	for(int c = 0; c < 8; c++) {
+		const unsigned bal = __ballot_sync(0xffffffffu, mycls == c);
+		if(lane == 0 && bal) atomicAdd(&sum[c], (uint32_t)__popc(bal));
+	}
+	for(int o = 16; o; o >>= 1) {
+		cells += __shfl_xor_sync(0xffffffffu, cells, o);
+		mycol = max(mycol, __shfl_xor_sync(0xffffffffu, mycol, o));
+	}
+	if(lane == 0 && cells) { atomicAdd(reinterpret_cast<unsigned long long*>(sum + 10), cells); atomicMax(&sum[8], mycol); }
 }
 
 __global__ void __launch_bounds__(256)
@@ -1149,28 +1159,26 @@ k_dp_aux_apply(DpAux *__restrict__ aux, const DpSizes *__restrict__ offs, uint32
 	aux[i].mat_off = o.mat; aux[i].rep_off = o.rep; aux[i].bound_off = o.bound; aux[i].escr_off = o.escr;
 }
 
-// launch order: by class, in job order inside a class.  One block per class walks the class
-// bytes in tiles of 1024 and compacts the matching job ids.
-__global__ void __launch_bounds__(1024)
-k_dp_order(const uint8_t *__restrict__ cls, uint32_t njobs, const uint32_t *__restrict__ sum, uint32_t *__restrict__ order) {
-	__shared__ uint32_t wsum[32];
-	__shared__ uint32_t carry;
-	const int c = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-	if(threadIdx.x == 0) { uint32_t b = 0; for(int k = 0; k < c; k++) b += sum[k]; carry = b; }
-	__syncthreads();
-	if(sum[c] == 0) return;
-	for(uint32_t base = 0; base < njobs; base += 1024) {
-		const uint32_t i = base + threadIdx.x;
-		const bool m = i < njobs && cls[i] == c;
-		const unsigned bal = __ballot_sync(0xffffffffu, m);
-		if(lane == 0) wsum[w] = __popc(bal);
-		__syncthreads();
-		uint32_t off = carry;
-		for(int k = 0; k < w; k++) off += wsum[k];
-		if(m) order[off + __popc(bal & ((1u << lane) - 1u))] = i;
-		__syncthreads();
-		if(threadIdx.x == 0) { uint32_t t = 0; for(int k = 0; k < 32; k++) t += wsum[k]; carry += t; }
-		__syncthreads();
+// launch order: by class; inside a class in (nearly) job order -- a warp takes its slots with one atomic per
+// class.  `order` only schedules the fill, results are addressed by job.  fillc[8] must be zero on entry.
+__global__ void __launch_bounds__(256)
+k_dp_order(const uint8_t *__restrict__ cls, uint32_t njobs, const uint32_t *__restrict__ sum, uint32_t *__restrict__ fillc,
+           uint32_t *__restrict__ order) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int lane = threadIdx.x & 31;
+	const int c = i < njobs ? (int)cls[i] : -1;
+#pragma unroll
+	for(int k = 0; k < 8; k++) {
+		const unsigned bal = __ballot_sync(0xffffffffu, c == k);
+		if(!bal) continue;
+		uint32_t base = 0;
+		if(lane == 0) base = atomicAdd(&fillc[k], (uint32_t)__popc(bal));
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if(c == k) {
+			uint32_t cb = 0;
+			for(int q = 0; q < k; q++) cb += sum[q];
+			order[cb + base + __popc(bal & ((1u << lane) - 1u))] = i;
+		}
 	}
 }
 
@@ -1473,7 +1481,7 @@ int dp_dev_finish(bt2gpu_ctx *ctx) {
 		d->aux.as<DpAux>(), d->cls.as<uint8_t>(), d->sizes.as<DpSizes>(), sum);
 	if(dev_exclusive_scan<DpSizes>(ctx, d->sizes.as<DpSizes>(), d->soffs.as<DpSizes>(), d->spart.as<DpSizes>(), total, njobs)) return 1;
 	k_dp_aux_apply<<<nb, 256, 0, s>>>(d->aux.as<DpAux>(), d->soffs.as<DpSizes>(), (uint32_t)njobs);
-	k_dp_order<<<kNClasses, 1024, 0, s>>>(d->cls.as<uint8_t>(), (uint32_t)njobs, sum, d->order.as<uint32_t>());
+	k_dp_order<<<nb, 256, 0, s>>>(d->cls.as<uint8_t>(), (uint32_t)njobs, sum, sum + 16, d->order.as<uint32_t>());
 	ctx->launches += 3;
 	BT2_CUDA(cudaGetLastError());
 	BT2_CUDA(cudaMemcpyAsync(d->h_dsum.p, sum, DPSUM_WORDS * 4 + sizeof(DpSizes), cudaMemcpyDeviceToHost, s));

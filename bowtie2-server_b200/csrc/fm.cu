@@ -743,16 +743,17 @@ extern "C" int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, cons
 namespace bt2 {
 
 int fm_hp_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
-                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view)
+                      const bt2gpu_read *reads, size_t nreads, FmReadsDev *view, cudaStream_t qual_stream)
 {
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	FmState *f = fm_state(ctx);
 	f->nreads = 0;
 	if(f->seq.reserve(pool_len + 16) || f->qual.reserve(pool_len + 16) || f->reads.reserve(nreads * sizeof(bt2gpu_read) + 16)) return 1;
 	cudaStream_t s = ctx->stream;
-	BT2_CUDA(cudaMemcpyAsync(f->seq.p, seq_pool, pool_len, cudaMemcpyHostToDevice, s));
-	BT2_CUDA(cudaMemcpyAsync(f->qual.p, qual_pool, pool_len, cudaMemcpyHostToDevice, s));
 	BT2_CUDA(cudaMemcpyAsync(f->reads.p, reads, nreads * sizeof(bt2gpu_read), cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(f->seq.p, seq_pool, pool_len, cudaMemcpyHostToDevice, s));
+	// qualities are first read by the DP framing: their copy rides a second stream under the FM kernels
+	BT2_CUDA(cudaMemcpyAsync(f->qual.p, qual_pool, pool_len, cudaMemcpyHostToDevice, qual_stream ? qual_stream : s));
 	// validation runs while the copies are in flight
 	f->rdlen.resize(nreads);
 	for(size_t i = 0; i < nreads; i++) {

@@ -261,7 +261,7 @@ extern "C" uint64_t bt2gpu_ref_bytes(const bt2gpu_ref *r) { return r ? ((r->len 
 
 namespace bt2 { const bt2gpu_dp_result *dp_dev_results(bt2gpu_ctx *ctx); }
 
-extern "C" int bt2gpu_hotpath_round0_batch(
+static int hotpath_round0(
 	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
 	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
 	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
@@ -297,15 +297,17 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 
 	// ---- 1. reads to HBM, exactSweep, seed instantiation (count) ----
 	FmReadsDev rv;
-	if(fm_hp_reads_stage(ctx, seq_pool, qual_pool, pool_len, reads, nreads, &rv)) return 1;
+	cudaStream_t cs = ctx->cstream;
+	if(fm_hp_reads_stage(ctx, seq_pool, qual_pool, pool_len, reads, nreads, &rv, cs)) return 1;
 	uint64_t sum_len = 0;
 	for(size_t i = 0; i < nreads; i++) sum_len += reads[i].rd_len;
 	if(sum_len + (uint64_t)nreads * (4 * P->maxgap + 1) > 0x70000000ull) BT2_FAIL("DP pools exceed 32-bit offsets: split the batch");
 	if(st.minsc.reserve(nreads * 4) || st.nceil.reserve(nreads * 4) || st.cnt.reserve(nreads * 4 + 16) || st.first.reserve(nreads * 4 + 16) ||
 	   st.spart.reserve((scan_parts(nreads) + 2) * 8) || st.tot.reserve(64) || st.h_tot.reserve(64) || st.stats.reserve(ST_N * 8) ||
 	   st.h_stats.reserve(ST_N * 8) || st.pick.reserve(nreads * 4) || st.val.reserve(nreads * 8) || st.ppos.reserve(nreads * 8)) return 1;
-	BT2_CUDA(cudaMemcpyAsync(st.minsc.p, minsc, nreads * 4, cudaMemcpyHostToDevice, s));
-	BT2_CUDA(cudaMemcpyAsync(st.nceil.p, nceil, nreads * 4, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(st.minsc.p, minsc, nreads * 4, cudaMemcpyHostToDevice, cs));
+	BT2_CUDA(cudaMemcpyAsync(st.nceil.p, nceil, nreads * 4, cudaMemcpyHostToDevice, cs));
+	BT2_CUDA(cudaEventRecord(ctx->cev[0], cs));        // qualities, minsc, nceil in HBM
 	BT2_CUDA(cudaMemsetAsync(st.stats.p, 0, ST_N * 8, s));
 	S->h2d_bytes += 2 * pool_len + nreads * (sizeof(bt2gpu_read) + 8);
 	u64 *stats = st.stats.as<u64>();
@@ -318,7 +320,8 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 	ctx->launches++;
 	if(dev_exclusive_scan<uint32_t>(ctx, cnt, first, st.spart.as<uint32_t>(), st.tot.as<uint32_t>(), nreads)) return 1;
 	BT2_CUDA(cudaMemcpyAsync(st.h_tot.p, st.tot.p, 4, cudaMemcpyDeviceToHost, s));
-	BT2_CUDA(cudaMemcpyAsync(sweep, dsweep, nreads * sizeof(bt2gpu_sweep_result), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamWaitEvent(cs, st.ev[1], 0));       // sweep results go home under the kernels that follow
+	BT2_CUDA(cudaMemcpyAsync(sweep, dsweep, nreads * sizeof(bt2gpu_sweep_result), cudaMemcpyDeviceToHost, cs));
 	S->d2h_bytes += nreads * sizeof(bt2gpu_sweep_result);
 	BT2_CUDA(cudaStreamSynchronize(s));
 	const size_t nseed = *st.h_tot.as<uint32_t>();
@@ -369,6 +372,7 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 		BT2_CUDA(cudaEventRecord(st.ev[7], s));
 		DpDevPools pools;
 		if(dp_dev_begin(ctx, npick, tot_rd, tot_win, max_aln, 256 * npick, edit_cap, &pools)) return 1;
+		BT2_CUDA(cudaStreamWaitEvent(s, ctx->cev[0], 0));
 		k_hp_frame<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(rv.seq, rv.qual, rv.reads, ref->packed.as<uint32_t>(), ref->len,
 			(uint32_t)npick, mg, st.pk_read.as<uint32_t>(), st.pk_seed.as<uint32_t>(), st.rdoff.as<uint32_t>(), st.offs.as<uint32_t>(),
 			st.steps.as<uint32_t>(), xj, st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), pools.seq, pools.qual, pools.win, pools.jobs,
@@ -396,6 +400,7 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 		if(bt2gpu_dp_fetch(ctx, results, nullptr, alns, edits, &nc, &ne)) return 1;
 		S->d2h_bytes += npick * (13 + sizeof(bt2gpu_dp_result) + max_aln * sizeof(bt2gpu_dp_aln)) + ne * sizeof(bt2gpu_edit);
 	} else BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(cudaStreamSynchronize(cs));
 	lap(S->wall_dp);
 
 	// ---- 4. counters and device times ----
@@ -417,4 +422,22 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 	S->ms_glue = S->ms_total - S->ms_sweep - S->ms_seed - S->ms_extend - S->ms_locate - S->ms_dp;
 	*njobs_out = npick; *nedits_out = ne;
 	return 0;
+}
+
+extern "C" int bt2gpu_hotpath_round0_batch(
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
+	const bt2gpu_hotpath_params *P,
+	bt2gpu_sweep_result *sweep, uint32_t *job_read, int64_t *job_start, uint8_t *job_fw, size_t *njobs_out,
+	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits_out,
+	bt2gpu_hotpath_stats *S)
+{
+	const int rc = hotpath_round0(ctx, fw, bw, ref, seq_pool, qual_pool, pool_len, reads, nreads, minsc, nceil, P, sweep,
+	                              job_read, job_start, job_fw, njobs_out, results, alns, edits, edit_cap, nedits_out, S);
+	if(rc && ctx) {          // failed part-way: nothing may still be copying from / into the caller's buffers
+		cudaStreamSynchronize(ctx->stream);
+		if(ctx->cstream) cudaStreamSynchronize(ctx->cstream);
+	}
+	return rc;
 }
