@@ -354,10 +354,19 @@ def run_ours(args, rank, world, local_rank):
         rl("k_dp_fill", 3.0 * cnt["dp_cells"], fill_ms,
            {"gcups": cnt["dp_cells"] / (fill_ms / 1e3) / 1e9 if fill_ms > 0 else 0.0,
             "dpx_ginstr_per_s": dpx, "dpx_peak_ginstr_per_s": dpx_peak, "dpx_frac": dpx / dpx_peak if dpx_peak else 0.0}),
-        rl("k_dp_backtrace", 0.0, kms["dp_backtrace"] / K,
-           {"note": "latency/issue-bound walk over the stored matrices; no byte roofline applies"}),
+        rl("k_dp_backtrace", 3.0 * cnt["bt_cells"] + 12.0 * cnt["dp_cands"], kms["dp_backtrace"] / K,
+           {"note": "dependent walk over the stored matrices (E,F,H of each visited cell + the candidate list): "
+                    "latency/issue-bound, a byte roofline does not describe it",
+            "walked_cells_per_job": cnt["bt_cells"] / max(cnt["dp_jobs"], 1), "candidates_per_job": cnt["dp_cands"] / max(cnt["dp_jobs"], 1)}),
         rl("k_dp_gather_e2e", 1.0 * cnt["dp_jobs"] * (RDLEN + 4 * MAXGAP), kms["dp_gather"] / K),
     ]
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
+    # command at its default workload (profiles/r1z_summary.md); other workloads: not captured
+    if args.batch == 262144 and args.genome_mbp == 1024:
+        traffic = {"k_exact_sweep": 0.409e9, "k_seed_exact": 0.710e9, "k_extend": 0.526e9, "k_locate": 0.159e9,
+                   "k_dp_fill": 10.582e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 9.806e9}
+        for r_ in rls:
+            r_["traffic"] = traffic.get(r_["kernel"])
     dominant = max(rls, key=lambda r: r["ms"])
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

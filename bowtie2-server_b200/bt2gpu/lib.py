@@ -21,7 +21,7 @@ SYMBOLS = [
     "bt2gpu_seed_exact_batch", "bt2gpu_exact_sweep_batch", "bt2gpu_onemm_batch", "bt2gpu_extend_batch",
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
-    "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx",
+    "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
 ]
 
 _lib = None
@@ -41,6 +41,7 @@ def load():
         lib.bt2gpu_ctx_stream.restype = C.c_void_p
         lib.bt2gpu_ctx_launches.restype = C.c_uint64
         lib.bt2gpu_dp_staged_cells.restype = C.c_uint64
+        lib.bt2gpu_dp_walked_cells.restype = C.c_uint64
         lib.bt2gpu_index_bytes.restype = C.c_uint64
         lib.bt2gpu_ref_bytes.restype = C.c_uint64
         lib.bt2gpu_ref_destroy.restype = None

@@ -83,7 +83,7 @@ def index_desc(e):
 import ctypes as _ct
 
 _HP_U64 = ("seeds", "seed_bwops", "seed_sides", "seed_hits", "sweep_bwops", "extend_fmops", "locate_rows",
-           "locate_steps", "dp_jobs", "dp_cells", "aligned", "h2d_bytes", "d2h_bytes")
+           "locate_steps", "dp_jobs", "dp_cells", "aligned", "h2d_bytes", "d2h_bytes", "bt_cells", "dp_cands")
 _HP_F32 = ("ms_sweep", "ms_seed", "ms_extend", "ms_locate", "ms_dp", "ms_dp_fill", "ms_dp_gather", "ms_dp_backtrace",
            "wall_sweep", "wall_inst", "wall_seed", "wall_extend", "wall_locate", "wall_frame", "wall_dp_stage", "wall_dp", "ms_total", "ms_glue")
 

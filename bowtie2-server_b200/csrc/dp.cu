@@ -738,6 +738,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 	const uint32_t ncand = r.ncand;
 	uint32_t SQ = (uint32_t)nrow >> 4; if(SQ == 0) SQ = 1;
 	uint32_t cural = 0, ndone = 0, tries = 0, cbase = 0xffffffffu;
+	uint32_t btcells = 0;                // matrix cells the walks visited (the reference's SSEMetrics.btcell)
 	__shared__ uint16_t s_tcells[4][TR_LMAX * 32];   // recorded cells of the trial walks: (rows above the last) << 8 | window column
 	__shared__ uint32_t s_twin[4][TR_LMAX * 8];      // cells reported by the group so far: TR_LMAX rows x 256 columns
 	uint16_t *tcells = s_tcells[threadIdx.x >> 5]; uint32_t *twin = s_twin[threadIdx.x >> 5];
@@ -808,6 +809,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 						} else if(first == 0) nmark = 0;                   // start cell already reported: skipped, not a try
 						else nmark = first;                                // cell `first` is set already
 						if(nmark) nfail++;
+						btcells += nmark;
 						if(lane < nmark) {
 							atomicOr(&twin[cell >> 5], 1u << (cell & 31));
 							const uint32_t b = (uint32_t)(nrow - 1 - (int)(cell >> 8)) * (uint32_t)J.ncol + (uint32_t)(wbase + (int)(cell & 255u));
@@ -894,7 +896,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 						ns += __popc(__ballot_sync(FULL, mine && mm == -1));
 						if(__any_sync(FULL, mine && J.on_core(ri, ci))) overlapped = true;
 					}
-					row -= nk; col -= nk;
+					row -= nk; col -= nk; btcells += nk;
 					if(nk == 32) continue;
 					// ---- event at lane nk: cell (row, col), still in the H state ----
 					if(col < 0) {
@@ -904,7 +906,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					}
 					const bool e_rep = __shfl_sync(FULL, (int)rep_i, nk) != 0;
 					const int e_mv = __shfl_sync(FULL, mv_i, nk);
-					J.mark(row, col);
+					J.mark(row, col); btcells++;
 					if(e_rep) { blocked = true; break; }
 					if(J.on_core(row, col)) overlapped = true;
 					if(row == 0 || e_mv == 0) { trimBeg = row; ok = true; break; }
@@ -946,7 +948,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					}
 				}
 				__syncwarp();
-				J.mark(row, col);
+				J.mark(row, col); btcells++;
 				if(reported) { blocked = true; break; }
 				if(J.on_core(row, col)) overlapped = true;
 				if(empty || row == 0) { trimBeg = row; ok = true; break; }
@@ -1020,7 +1022,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 		r.naln++;
 	}
 	r.tail_tries = tries; r.cural = cural;
-	if(lane == 0) res[ji] = r;
+	if(lane == 0) { res[ji] = r; atomicAdd(nedits + 2, (unsigned long long)btcells); }   // scal[3]
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1419,6 +1421,8 @@ extern "C" int bt2gpu_dp_fetch(
 }
 
 extern "C" uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx) { return (ctx && ctx->dp) ? ctx->dp->cells : 0; }
+/* matrix cells the nextAlignment walks visited in the last fetched run (the reference's SSEMetrics.btcell) */
+extern "C" uint64_t bt2gpu_dp_walked_cells(bt2gpu_ctx *ctx) { return (ctx && ctx->dp && ctx->dp->h_scal.p) ? ctx->dp->h_scal.as<unsigned long long>()[3] : 0; }
 
 extern "C" int bt2gpu_dp_align_batch(
 	bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,

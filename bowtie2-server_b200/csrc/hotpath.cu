@@ -391,13 +391,12 @@ static int hotpath_round0(
 	BT2_CUDA(cudaGetLastError());
 	BT2_CUDA(cudaEventRecord(st.ev[10], s));
 	BT2_CUDA(cudaMemcpyAsync(st.h_stats.p, stats, ST_N * 8, cudaMemcpyDeviceToHost, s));
-	size_t ne = 0;
+	size_t ne = 0, nc_total = 0;
 	if(npick) {
 		BT2_CUDA(cudaMemcpyAsync(job_read, st.job_read.p, npick * 4, cudaMemcpyDeviceToHost, s));
 		BT2_CUDA(cudaMemcpyAsync(job_start, st.job_start.p, npick * 8, cudaMemcpyDeviceToHost, s));
 		BT2_CUDA(cudaMemcpyAsync(job_fw, st.job_fw.p, npick, cudaMemcpyDeviceToHost, s));
-		size_t nc = 0;
-		if(bt2gpu_dp_fetch(ctx, results, nullptr, alns, edits, &nc, &ne)) return 1;
+		if(bt2gpu_dp_fetch(ctx, results, nullptr, alns, edits, &nc_total, &ne)) return 1;
 		S->d2h_bytes += npick * (13 + sizeof(bt2gpu_dp_result) + max_aln * sizeof(bt2gpu_dp_aln)) + ne * sizeof(bt2gpu_edit);
 	} else BT2_CUDA(cudaStreamSynchronize(s));
 	BT2_CUDA(cudaStreamSynchronize(cs));
@@ -410,6 +409,8 @@ static int hotpath_round0(
 	S->sweep_bwops = hs[ST_SWEEP_BWOPS];
 	S->locate_rows = npick; S->dp_jobs = npick;
 	S->dp_cells = npick ? bt2gpu_dp_staged_cells(ctx) : 0;
+	S->bt_cells = npick ? bt2gpu_dp_walked_cells(ctx) : 0;
+	S->dp_cands = nc_total;
 	auto span = [&](int a, int b) -> float { float ms = 0.f; cudaEventElapsedTime(&ms, st.ev[a], st.ev[b]); return ms; };
 	S->ms_sweep = span(0, 1);
 	if(nseed) { S->ms_seed = span(2, 3); S->ms_extend = span(4, 5); }

@@ -157,6 +157,8 @@ int bt2gpu_dp_fetch(
 int bt2gpu_dp_phase_ms(bt2gpu_ctx *ctx, float *ms3);
 /* DP cells (rows x cols, the bowtie2-dp CUPS numerator bt2_dp.cpp:744) of the staged batch. */
 uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx);
+/* matrix cells visited by the nextAlignment walks of the last fetched run (SSEMetrics.btcell) */
+uint64_t bt2gpu_dp_walked_cells(bt2gpu_ctx *ctx);
 
 /* ======================================================================== */
 /* ---- FM index (replaces Ebwt's search-side state, bt2_idx.h:2530-2570) --- */
@@ -288,7 +290,7 @@ typedef struct {
 
 typedef struct {
 	uint64_t seeds, seed_bwops, seed_sides, seed_hits, sweep_bwops, extend_fmops,
-	         locate_rows, locate_steps, dp_jobs, dp_cells, aligned, h2d_bytes, d2h_bytes;
+	         locate_rows, locate_steps, dp_jobs, dp_cells, aligned, h2d_bytes, d2h_bytes, bt_cells, dp_cands;
 	float    ms_sweep, ms_seed, ms_extend, ms_locate, ms_dp, ms_dp_fill, ms_dp_gather, ms_dp_backtrace;
 	/* host wall clock per stage (copies, syncs and glue included): reads+sweep, seed instantiation,
 	 * seed search, extend, pick+locate, framing, DP staging, DP run+fetch */
