@@ -239,7 +239,7 @@ class Context:
         return g.value
 
     def hotpath_round0(self, ref, seq, qual, reads, minsc, nceil, seed_len=22, ival=(1.0, 1.15), maxgap=15,
-                       max_aln=2, mine_max=2, nthreads=0, out=None):
+                       max_aln=2, mine_max=2, nthreads=0, out=None, cand_per_job=0):
         """bt2gpu_hotpath_round0_batch: exactSweep -> seeds -> extend -> pick -> locate -> frame -> DP
         for a batch of reads, every intermediate resident in HBM (ref = DeviceRef).  Returns
         (out dict, stats dict)."""
@@ -249,7 +249,7 @@ class Context:
                        job_start=np.zeros(n, dtype=np.int64), job_fw=np.zeros(n, dtype=np.uint8),
                        results=np.zeros(n, dtype=structs.dp_result), alns=np.zeros(n * max_aln, dtype=structs.dp_aln),
                        edits=np.zeros(64 * n + 1024, dtype=structs.edit))
-        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, nthreads)
+        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, nthreads, cand_per_job)
         S = structs.HotpathStats()
         nj, ne = C.c_size_t(0), C.c_size_t(0)
         _check(self.lib.bt2gpu_hotpath_round0_batch(
@@ -261,7 +261,7 @@ class Context:
         out["njobs"], out["nedits"] = nj.value, ne.value
         # the batch stays staged on the device: dp_fetch() can read it again (with the candidate pool)
         self._dp_n, self._dp_k = nj.value, max_aln
-        self._cand_cap, self._edit_cap = 256 * max(nj.value, 1), len(out["edits"])
+        self._cand_cap, self._edit_cap = 4096 * max(nj.value, 1), len(out["edits"])
         return out, S.as_dict()
 
     def locate_stage(self, rows):

@@ -371,7 +371,8 @@ static int hotpath_round0(
 		if(fm_hp_locate(ctx, fw, st.rows.as<uint32_t>(), npick, st.offs.as<uint32_t>(), st.steps.as<uint32_t>())) return 1;
 		BT2_CUDA(cudaEventRecord(st.ev[7], s));
 		DpDevPools pools;
-		if(dp_dev_begin(ctx, npick, tot_rd, tot_win, max_aln, 256 * npick, edit_cap, &pools)) return 1;
+		const size_t cpj = P->cand_per_job ? P->cand_per_job : (ctx->sc.monotone ? 256 : 4096);
+		if(dp_dev_begin(ctx, npick, tot_rd, tot_win, max_aln, cpj * npick, edit_cap, &pools)) return 1;
 		BT2_CUDA(cudaStreamWaitEvent(s, ctx->cev[0], 0));
 		k_hp_frame<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(rv.seq, rv.qual, rv.reads, ref->packed.as<uint32_t>(), ref->len,
 			(uint32_t)npick, mg, st.pk_read.as<uint32_t>(), st.pk_seed.as<uint32_t>(), st.rdoff.as<uint32_t>(), st.offs.as<uint32_t>(),

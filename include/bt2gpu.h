@@ -285,7 +285,8 @@ typedef struct {
 	int32_t  maxgap;            /* DPRect::maxgap = min(max(rdgaps, rfgaps), maxhalf)      */
 	uint32_t max_aln;           /* nextAlignment() calls per window                        */
 	uint32_t mine_max;          /* exactSweep mineMax                                      */
-	int32_t  nthreads;          /* host threads for the glue (0 = hardware concurrency)    */
+	int32_t  nthreads;          /* unused since the glue moved to the device (kept for layout) */
+	uint32_t cand_per_job;      /* candidate pool = this many cells per DP window (0: 256 end-to-end, 4096 local) */
 } bt2gpu_hotpath_params;
 
 typedef struct {
