@@ -39,15 +39,18 @@ import numpy as np  # noqa: E402
 RDLEN = 150
 MAXGAP = 15
 SEED_LEN = 22
+IVAL = (1.0, 1.15)
+LOCAL = False
 METRIC = "aligned reads/sec (2x150 end-to-end)"
 UNIT = "reads/s"
 
 
 def workload_name(batch, gmbp):
-    return ("synthetic 150 bp reads (simulate.pl model) vs FM index of a random %d Mbp genome: exactSweep + "
-            "exact seeds (-L 22, S,1,1.15) + extend + locate + one seed-extension DP window (150 x %d, "
-            "end-to-end u8: fill + gather + nextAlignment loop) per read, %d reads per step per GPU"
-            % (gmbp, RDLEN + 4 * MAXGAP, batch))
+    return ("synthetic %d bp reads (simulate.pl model) vs FM index of a random %d Mbp genome: exactSweep + "
+            "exact seeds (-L %d, S,%g,%g) + extend + locate + one seed-extension DP window (%d x %d, "
+            "%s: fill + gather + nextAlignment loop) per read, %d reads per step per GPU"
+            % (RDLEN, gmbp, SEED_LEN, IVAL[0], IVAL[1], RDLEN, RDLEN + 4 * MAXGAP,
+               "local u8 with i16 re-runs" if LOCAL else "end-to-end u8", batch))
 
 
 def make_genome(seed, gmbp):
@@ -209,7 +212,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1 and rank == 0:
         dist.barrier()
     torch.cuda.empty_cache()
-    sc = scoring.Scoring(local=False)
+    sc = scoring.Scoring(local=LOCAL)
     dix = lib.DeviceIndex(ix, local_rank)
     dref = lib.DeviceRef(genome, local_rank)                  # 2-bit text in HBM (windows are cut on the device)
     # C worker contexts per GPU, each with its own stream and arenas and a contiguous shard of the batch -- the
@@ -246,7 +249,8 @@ def run_ours(args, rank, world, local_rank):
         rd["rd_off"] = np.arange(m, dtype=np.int64) * RDLEN
         rd["rd_len"] = RDLEN
         return dict(seq=hseq[lo * RDLEN:hi * RDLEN], qual=hqual[lo * RDLEN:hi * RDLEN], rd=rd, lo=lo,
-                    minsc=np.full(m, sc.score_min.f_int(RDLEN), dtype=np.int32), nceil=np.full(m, sc.nceil(RDLEN), dtype=np.int32),
+                    minsc=np.full(m, max(1, sc.score_min.f_int(RDLEN)) if LOCAL else sc.score_min.f_int(RDLEN), dtype=np.int32),
+                    nceil=np.full(m, sc.nceil(RDLEN), dtype=np.int32),
                     out=dict(sweep=pin(np.zeros(m, dtype=structs.sweep_result)), job_read=np.zeros(m, dtype=np.uint32),
                              job_start=np.zeros(m, dtype=np.int64), job_fw=np.zeros(m, dtype=np.uint8),
                              results=pin(np.zeros(m, dtype=structs.dp_result)),
@@ -258,7 +262,7 @@ def run_ours(args, rank, world, local_rank):
 
     def run(c_, io):
         return c_.hotpath_round0(dref, io["seq"], io["qual"], io["rd"], io["minsc"], io["nceil"], seed_len=SEED_LEN,
-                                 ival=(1.0, 1.15), maxgap=MAXGAP, max_aln=max_aln, mine_max=2, nthreads=0, out=io["out"])
+                                 ival=IVAL, maxgap=MAXGAP, max_aln=max_aln, mine_max=2, nthreads=0, out=io["out"])
 
     def step():
         if C == 1:
@@ -351,7 +355,7 @@ def run_ours(args, rank, world, local_rank):
         fm("k_exact_sweep", cnt["sweep_bwops"], 0.0, kms["sweep"] / K, cnt["sweep_bwops"]),
         fm("k_extend", cnt["extend_fmops"], 0.0, kms["extend"] / K, cnt["extend_fmops"]),
         fm("k_locate", cnt["locate_steps"], 4.0 * cnt["locate_steps"] + 4.0 * cnt["locate_rows"], kms["locate"] / K, cnt["locate_steps"]),
-        rl("k_dp_fill", 3.0 * cnt["dp_cells"], fill_ms,
+        rl("k_dp_fill", (6.0 if LOCAL else 3.0) * cnt["dp_cells"], fill_ms,
            {"gcups": cnt["dp_cells"] / (fill_ms / 1e3) / 1e9 if fill_ms > 0 else 0.0,
             "dpx_ginstr_per_s": dpx, "dpx_peak_ginstr_per_s": dpx_peak, "dpx_frac": dpx / dpx_peak if dpx_peak else 0.0}),
         rl("k_dp_backtrace", 3.0 * cnt["bt_cells"] + 12.0 * cnt["dp_cands"], kms["dp_backtrace"] / K,
@@ -416,10 +420,19 @@ def main():
     ap.add_argument("--batch", type=int, default=262144)
     ap.add_argument("--contexts", type=int, default=1, help="worker contexts (streams) per GPU; more than one did not pay (DESIGN.md 5)")
     ap.add_argument("--genome-mbp", type=int, default=1024)
+    ap.add_argument("--mode", default="e2e", choices=["e2e", "local"],
+                    help="local: 250 bp reads, --sensitive-local seeds (-L 20, S,1,0.75), u8 local DP with i16 re-runs (config C4); our arm only")
     ap.add_argument("--cpu-sample", type=int, default=40000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()
+    if args.mode == "local":
+        global RDLEN, SEED_LEN, IVAL, LOCAL
+        RDLEN, SEED_LEN, IVAL, LOCAL = 250, 20, (1.0, 0.75), True
+        args.no_cpu_baseline = True
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "the reference arm times the end-to-end workload only"}))
+            return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -824,6 +824,27 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					if(cural >= ncand) break;
 				}
 			}
+			if(local) {
+				// Skip scan (local mode: thousands of candidates per window, nearly all dropped untried).  The next 32
+				// candidates are tested at once for the three reasons nextAlignment drops one without a walk -- score
+				// below minsc, start cell already reported, within SQ rows and columns of a tried one -- and, as
+				// dropping a candidate changes no state, everything before the first survivor goes in one step.
+				const uint32_t ci = cural + lane;
+				bool keepc = false;
+				if(ci < ncand) {
+					const bt2gpu_dp_cand c = cd[ci];
+					keepc = c.score >= jb.minsc && !J.reported((int)c.row, (int)c.col);
+					for(uint32_t i = 0; keepc && i < ndone; i++) {
+						const uint32_t dv = done[i];
+						const uint32_t dr = dv >> 16, dc = dv & 0xffff;
+						const uint32_t rh = max(c.row, dr), rl = min(c.row, dr), ch = max(c.col, dc), cl = min(c.col, dc);
+						if(ch - cl <= SQ && rh - rl <= SQ) keepc = false;
+					}
+				}
+				const unsigned keep = __ballot_sync(FULL, keepc);
+				if(keep == 0) { cural += min(32u, ncand - cural); continue; }
+				cural += (uint32_t)(__ffs(keep) - 1);
+			}
 			// candidates are read 32 at a time (one round trip per 32 of them)
 			if(cural < cbase || cural >= cbase + 32) {
 				cbase = cural;
