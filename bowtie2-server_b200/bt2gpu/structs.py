@@ -50,6 +50,24 @@ assert sweep_result.itemsize == 28 and onemm_job.itemsize == 12 and ee_hit.items
 assert onemm_result.itemsize == 12 and extend_job.itemsize == 24 and extend_result.itemsize == 8
 
 
+# framing / paired-end geometry (include/bt2gpu.h "framing" section; DPRect dp_framer.h:34-90)
+rect = np.dtype([("refl", "<i8"), ("refr", "<i8"), ("refl_pretrim", "<i8"), ("refr_pretrim", "<i8"),
+                 ("triml", "<u8"), ("trimr", "<u8"), ("corel", "<u8"), ("corer", "<u8"), ("maxgap", "<u8")], align=True)
+pe_policy = np.dtype([("pol", "<i4"), ("trim_to_ref", "<i4"), ("maxfrag", "<u8"), ("minfrag", "<u8"),
+                      ("local", "u1"), ("flip_ok", "u1"), ("dovetail_ok", "u1"), ("contain_ok", "u1"),
+                      ("olap_ok", "u1"), ("expand_to_fit", "u1"), ("pad", "u1", (2,))], align=True)
+o_pe_policy = pe_policy       # oracle/frame_oracle.c reads the same layout (trim_to_ref sits in its padding)
+frame_job = np.dtype([("off", "<i8"), ("reflen", "<i8"), ("maxns", "<i8"), ("rdlen", "<u4"), ("maxrdgap", "<u4"),
+                      ("maxrfgap", "<u4"), ("maxhalf", "<u4")], align=True)
+mate_job = np.dtype([("off", "<i8"), ("maxalcols", "<i8"), ("reflen", "<i8"), ("maxns", "<i8"),
+                     ("len1", "<u4"), ("len2", "<u4"), ("maxrdgap", "<u4"), ("maxrfgap", "<u4"), ("maxhalf", "<u4"),
+                     ("is1", "u1"), ("fw", "u1"), ("pad", "u1", (2,))], align=True)
+mate_frame = np.dtype([("rect", rect), ("oll", "<i8"), ("olr", "<i8"), ("orl", "<i8"), ("orr", "<i8"),
+                       ("found", "u1"), ("ok", "u1"), ("oleft", "u1"), ("ofw", "u1"), ("pad", "u1", (4,))], align=True)
+pair_job = np.dtype([("off1", "<i8"), ("off2", "<i8"), ("len1", "<u4"), ("len2", "<u4"),
+                     ("fw1", "u1"), ("fw2", "u1"), ("pad", "u1", (6,))], align=True)
+
+
 class IndexDesc(__import__("ctypes").Structure):
     """bt2gpu_index_desc"""
     import ctypes as _C

@@ -27,7 +27,7 @@ def oracle_lib():
     global _oracle
     if _oracle is None:
         so = os.path.join(ROOT, "oracle", "libbt2oracle.so")
-        srcs = [os.path.join(ROOT, "oracle", f) for f in ("dp_oracle.c", "fm_oracle.c")]
+        srcs = [os.path.join(ROOT, "oracle", f) for f in ("dp_oracle.c", "fm_oracle.c", "frame_oracle.c")]
         srcs = [s for s in srcs if os.path.exists(s)]
         if (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
             subprocess.check_call(["gcc", "-O2", "-shared", "-fPIC", "-o", so] + srcs)
@@ -260,3 +260,89 @@ def compare_fm_with_dump(eng, recs, sc, local, seed_len, interval_fn):
     assert [int(x) for x in offs] == lexp, "locate"
     checks += len(lrows)
     return checks
+
+
+# ---------------------------------------------------------------------------------------
+# framing / paired-end geometry: golden vectors of the reference (oracle/ref_frame_dump.cpp)
+# ---------------------------------------------------------------------------------------
+def parse_frame_vectors(path=None):
+    """-> dict kind -> list of (inputs, outputs) integer tuples; flag strings become tuples of 0/1."""
+    path = path or os.path.join(GOLDEN, "frame_vectors.txt")
+    out = {k: [] for k in "SMCGJ"}
+
+    def ints(tok):
+        r = []
+        for t in tok:
+            if len(t) == 6 and set(t) <= {"0", "1"}:
+                r.append(tuple(int(c) for c in t))
+            else:
+                r.append(int(t))
+        return r
+    with open(path) as fh:
+        for ln in fh:
+            kind, rest = ln[0], ln[2:]
+            lhs, rhs = rest.split(" -> ")
+            parts = [ints(p.split()) for p in lhs.split(" | ")]
+            out[kind].append((parts, ints(rhs.split())))
+    return out
+
+
+class FrameOracle:
+    """ctypes face of oracle/frame_oracle.c."""
+
+    def __init__(self):
+        self.lib = oracle_lib()
+        L = self.lib
+        i64, u64, ci = C.c_int64, C.c_uint64, C.c_int
+        L.bt2o_frame_seed_ext.argtypes = [i64, u64, i64, u64, u64, i64, u64, ci, C.c_void_p]
+        L.bt2o_frame_mate.argtypes = [ci, i64, i64, i64, i64, u64, i64, u64, u64, i64, u64, ci, C.c_void_p]
+        L.bt2o_pe_other_mate.argtypes = [C.c_void_p, ci, ci, i64, i64, u64, u64, u64] + [C.c_void_p] * 6
+        L.bt2o_pe_classify.argtypes = [C.c_void_p, i64, u64, ci, i64, u64, ci]
+        L.bt2o_max_read_gaps.argtypes = [i64, u64, i64, i64, i64]
+        L.bt2o_max_ref_gaps.argtypes = [i64, u64, i64, i64, i64]
+        L.bt2o_joined_to_text_off.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, ci, C.c_uint32, C.c_uint32, ci] + [C.c_void_p] * 4
+
+    @staticmethod
+    def policy(pol, maxfrag, minfrag, flags):
+        p = np.zeros(1, dtype=structs.o_pe_policy)
+        p["pol"], p["maxfrag"], p["minfrag"] = pol, maxfrag, minfrag
+        for k, v in zip(("local", "flip_ok", "dovetail_ok", "contain_ok", "olap_ok", "expand_to_fit"), flags):
+            p[k] = v
+        return p
+
+    @staticmethod
+    def rect_tuple(r):
+        r = r.reshape(-1)[0]
+        return tuple(int(r[k]) for k in ("refl", "refr", "refl_pretrim", "refr_pretrim", "triml", "trimr", "corel", "corer", "maxgap"))
+
+    def frame_seed_ext(self, off, rdlen, reflen, rdgap, rfgap, maxns, maxhalf, trim):
+        r = np.zeros(1, dtype=structs.rect)
+        ok = self.lib.bt2o_frame_seed_ext(off, rdlen, reflen, rdgap, rfgap, maxns, maxhalf, trim, _ptr(r))
+        return ok, self.rect_tuple(r)
+
+    def frame_mate(self, anchor_left, ll, lr, rl, rr, rdlen, reflen, rdgap, rfgap, maxns, maxhalf, trim):
+        r = np.zeros(1, dtype=structs.rect)
+        ok = self.lib.bt2o_frame_mate(anchor_left, ll, lr, rl, rr, rdlen, reflen, rdgap, rfgap, maxns, maxhalf, trim, _ptr(r))
+        return ok, self.rect_tuple(r)
+
+    def other_mate(self, pol, is1, fw, off, maxalcols, reflen, len1, len2):
+        o = np.zeros(4, dtype=np.int64)
+        fl = np.zeros(2, dtype=np.int32)
+        found = self.lib.bt2o_pe_other_mate(_ptr(pol), is1, fw, off, maxalcols, reflen, len1, len2,
+                                            fl[0:].ctypes.data_as(C.c_void_p), o[0:].ctypes.data_as(C.c_void_p),
+                                            o[1:].ctypes.data_as(C.c_void_p), o[2:].ctypes.data_as(C.c_void_p),
+                                            o[3:].ctypes.data_as(C.c_void_p), fl[1:].ctypes.data_as(C.c_void_p))
+        return found, int(fl[0]), [int(x) for x in o], int(fl[1])
+
+    def classify(self, pol, off1, len1, fw1, off2, len2, fw2):
+        return self.lib.bt2o_pe_classify(_ptr(pol), off1, len1, fw1, off2, len2, fw2)
+
+    def joined_to_text_off(self, e, qlen, off, reject):
+        o = np.zeros(3, dtype=np.uint32)
+        st = np.zeros(1, dtype=np.int32)
+        rs = np.ascontiguousarray(e.rstarts, dtype=np.uint32)
+        pl = np.ascontiguousarray(e.plen, dtype=np.uint32)
+        self.lib.bt2o_joined_to_text_off(_ptr(rs), len(rs), _ptr(pl), e.len, 1 if e.fw else 0, qlen, off, reject,
+                                         o[0:].ctypes.data_as(C.c_void_p), o[1:].ctypes.data_as(C.c_void_p),
+                                         o[2:].ctypes.data_as(C.c_void_p), _ptr(st))
+        return int(o[0]), int(o[1]), int(o[2]), int(st[0])
