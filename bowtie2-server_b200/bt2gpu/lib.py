@@ -22,6 +22,8 @@ SYMBOLS = [
     "bt2gpu_locate_batch", "bt2gpu_seed_exact_stage", "bt2gpu_seed_exact_run", "bt2gpu_seed_exact_fetch",
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
+    "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
+    "bt2gpu_joined_to_text_off_batch",
 ]
 
 _lib = None
@@ -263,6 +265,52 @@ class Context:
         self._dp_n, self._dp_k = nj.value, max_aln
         self._cand_cap, self._edit_cap = 4096 * max(nj.value, 1), len(out["edits"])
         return out, S.as_dict()
+
+    # ---- framing / paired-end geometry (frame.cu) ----
+    def frame_seed_ext(self, jobs, trim_to_ref=True):
+        """DynProgFramer::frameSeedExtensionRect per job -> (rects, ok)."""
+        jobs = np.ascontiguousarray(jobs, dtype=structs.frame_job)
+        rects = np.zeros(len(jobs), dtype=structs.rect)
+        ok = np.zeros(len(jobs), dtype=np.uint8)
+        _check(self.lib.bt2gpu_frame_seed_ext_batch(self._h, C.c_int(int(trim_to_ref)), _ptr(jobs), C.c_size_t(len(jobs)),
+                                                    _ptr(rects), _ptr(ok)))
+        return rects, ok
+
+    def frame_mate(self, pol, jobs):
+        """PairedEndPolicy::otherMate + DynProgFramer::frameFindMateRect per anchor -> mate_frame records."""
+        jobs = np.ascontiguousarray(jobs, dtype=structs.mate_job)
+        out = np.zeros(len(jobs), dtype=structs.mate_frame)
+        _check(self.lib.bt2gpu_frame_mate_batch(self._h, _ptr(pol), _ptr(jobs), C.c_size_t(len(jobs)), _ptr(out)))
+        return out
+
+    def pe_classify(self, pol, jobs):
+        jobs = np.ascontiguousarray(jobs, dtype=structs.pair_job)
+        cls = np.zeros(len(jobs), dtype=np.int32)
+        _check(self.lib.bt2gpu_pe_classify_batch(self._h, _ptr(pol), _ptr(jobs), C.c_size_t(len(jobs)), _ptr(cls)))
+        return cls
+
+    def max_gaps(self, minsc, rdlen):
+        minsc = np.ascontiguousarray(minsc, dtype=np.int64)
+        rdlen = np.ascontiguousarray(rdlen, dtype=np.uint32)
+        a = np.zeros(len(minsc), dtype=np.int32)
+        b = np.zeros(len(minsc), dtype=np.int32)
+        _check(self.lib.bt2gpu_max_gaps_batch(self._h, _ptr(minsc), _ptr(rdlen), C.c_size_t(len(minsc)), _ptr(a), _ptr(b)))
+        return a, b
+
+    def joined_to_text_off(self, e, qlen, off, reject_straddle=True):
+        """Ebwt::joinedToTextOff over EbwtData `e` -> (tidx, textoff, tlen, straddled)."""
+        rs = np.ascontiguousarray(e.rstarts, dtype=np.uint32)
+        pl = np.ascontiguousarray(e.plen, dtype=np.uint32)
+        qlen = np.ascontiguousarray(qlen, dtype=np.uint32)
+        off = np.ascontiguousarray(off, dtype=np.uint32)
+        n = len(off)
+        o = [np.zeros(n, dtype=np.uint32) for _ in range(3)]
+        st = np.zeros(n, dtype=np.uint8)
+        _check(self.lib.bt2gpu_joined_to_text_off_batch(self._h, _ptr(rs), C.c_uint32(len(rs)), _ptr(pl), C.c_uint32(len(pl)),
+                                                        C.c_uint32(e.len), C.c_int(1 if e.fw else 0), _ptr(qlen), _ptr(off),
+                                                        C.c_size_t(n), C.c_int(int(reject_straddle)),
+                                                        _ptr(o[0]), _ptr(o[1]), _ptr(o[2]), _ptr(st)))
+        return o[0], o[1], o[2], st
 
     def locate_stage(self, rows):
         rows = np.ascontiguousarray(rows, dtype=np.uint32)

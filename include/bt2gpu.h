@@ -266,6 +266,85 @@ int bt2gpu_locate_stage(bt2gpu_ctx *ctx, const uint32_t *rows, size_t n);
 int bt2gpu_locate_run(bt2gpu_ctx *ctx, const bt2gpu_index *fw);
 int bt2gpu_locate_fetch(bt2gpu_ctx *ctx, uint32_t *offs_out, uint32_t *steps_out);
 
+/* ---- window framing and paired-end geometry (between the FM and the DP kernels) -------- */
+
+/* DPRect (dp_framer.h:34-90). */
+typedef struct {
+	int64_t  refl, refr;                 /* inclusive reference columns after trimming         */
+	int64_t  refl_pretrim, refr_pretrim; /* ... before trimming                                */
+	uint64_t triml, trimr;               /* columns trimmed off either side                    */
+	uint64_t corel, corer;               /* core diagonals, w.r.t. the untrimmed rectangle     */
+	uint64_t maxgap;
+} bt2gpu_rect;
+
+/* PairedEndPolicy (pe.h:169-321) + DynProgFramer::trimToRef_ (= !gReportOverhangs). */
+#define BT2GPU_PE_FF 1   /* PE_POLICY_FF (pe.h:38-54) */
+#define BT2GPU_PE_RR 2
+#define BT2GPU_PE_FR 3
+#define BT2GPU_PE_RF 4
+#define BT2GPU_PE_ALS_NORMAL   1   /* PE_ALS_* (pe.h:62-95) */
+#define BT2GPU_PE_ALS_OVERLAP  2
+#define BT2GPU_PE_ALS_CONTAIN  3
+#define BT2GPU_PE_ALS_DOVETAIL 4
+#define BT2GPU_PE_ALS_DISCORD  5
+typedef struct {
+	int32_t  pol;            /* BT2GPU_PE_*                                   */
+	int32_t  trim_to_ref;    /* DynProgFramer(trimToRef)                      */
+	uint64_t maxfrag;        /* -X (gMaxInsert)                               */
+	uint64_t minfrag;        /* -I (gMinInsert)                               */
+	uint8_t  local, flip_ok, dovetail_ok, contain_ok, olap_ok, expand_to_fit;
+	uint8_t  pad[2];
+} bt2gpu_pe_policy;
+
+/* DynProgFramer::frameSeedExtensionRect (dp_framer.cpp:81-129), one call per job. */
+typedef struct {
+	int64_t  off;            /* reference offset of the read implied by the seed hit */
+	int64_t  reflen;
+	int64_t  maxns;
+	uint32_t rdlen, maxrdgap, maxrfgap, maxhalf;
+} bt2gpu_frame_job;
+int bt2gpu_frame_seed_ext_batch(bt2gpu_ctx *ctx, int trim_to_ref, const bt2gpu_frame_job *jobs, size_t n,
+                                bt2gpu_rect *rects, uint8_t *ok);
+
+/* PairedEndPolicy::otherMate (pe.cpp:161-353) followed by DynProgFramer::frameFindMateRect
+ * (dp_framer.h:155-197) -- the call pair of SwDriver::extendSeedsPaired
+ * (aligner_sw_driver.cpp:1994-2023).  len1/len2 = mate lengths; the opposite mate's length
+ * (orows) is len2 when is1, else len1. */
+typedef struct {
+	int64_t  off;            /* anchor alignment's reference offset (AlnRes::refoff) */
+	int64_t  maxalcols;      /* orows + oreadGaps, or -1                             */
+	int64_t  reflen;
+	int64_t  maxns;          /* opposite mate's N ceiling                            */
+	uint32_t len1, len2, maxrdgap, maxrfgap, maxhalf;
+	uint8_t  is1, fw, pad[2];
+} bt2gpu_mate_job;
+typedef struct {
+	bt2gpu_rect rect;
+	int64_t  oll, olr, orl, orr;
+	uint8_t  found;          /* otherMate's return value                  */
+	uint8_t  ok;             /* found && frameFindMateRect's return value */
+	uint8_t  oleft, ofw;
+	uint8_t  pad[4];
+} bt2gpu_mate_frame;
+int bt2gpu_frame_mate_batch(bt2gpu_ctx *ctx, const bt2gpu_pe_policy *pol, const bt2gpu_mate_job *jobs, size_t n,
+                            bt2gpu_mate_frame *out);
+
+/* PairedEndPolicy::peClassifyPair (pe.cpp:37-136): cls[i] = BT2GPU_PE_ALS_*. */
+typedef struct { int64_t off1, off2; uint32_t len1, len2; uint8_t fw1, fw2, pad[6]; } bt2gpu_pair_job;
+int bt2gpu_pe_classify_batch(bt2gpu_ctx *ctx, const bt2gpu_pe_policy *pol, const bt2gpu_pair_job *jobs, size_t n,
+                             int32_t *cls);
+
+/* Scoring::maxReadGaps / maxRefGaps (scoring.cpp:42-105) with the context's scoring scheme. */
+int bt2gpu_max_gaps_batch(bt2gpu_ctx *ctx, const int64_t *minsc, const uint32_t *rdlen, size_t n,
+                          int32_t *rdgaps, int32_t *rfgaps);
+
+/* Ebwt::joinedToTextOff (bt2_idx.cpp:54-124).  rstarts = nfrag triples (Ebwt::rstarts()), plen = text
+ * lengths, len = EbwtParams::_len, fw = Ebwt::fw().  tidx = 0xffffffff for rejected straddlers. */
+int bt2gpu_joined_to_text_off_batch(bt2gpu_ctx *ctx, const uint32_t *rstarts, uint32_t nfrag, const uint32_t *plen,
+                                    uint32_t npat, uint32_t len, int fw, const uint32_t *qlen, const uint32_t *off,
+                                    size_t n, int reject_straddle,
+                                    uint32_t *tidx, uint32_t *textoff, uint32_t *tlen, uint8_t *straddled);
+
 /* ======================================================================== */
 /* ---- batch runtime: one chained pass of the hot path --------------------- */
 
