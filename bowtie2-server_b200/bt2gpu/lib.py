@@ -23,7 +23,7 @@ SYMBOLS = [
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
-    "bt2gpu_joined_to_text_off_batch",
+    "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch",
 ]
 
 _lib = None
@@ -265,6 +265,35 @@ class Context:
         self._dp_n, self._dp_k = nj.value, max_aln
         self._cand_cap, self._edit_cap = 4096 * max(nj.value, 1), len(out["edits"])
         return out, S.as_dict()
+
+    def hotpath_pairs(self, ref, seq, qual, reads, minsc, nceil, pol, maxhalf=15, seed_len=22, ival=(1.0, 1.15), maxgap=15,
+                      max_aln=2, mine_max=2, out=None, cand_per_job=0):
+        """bt2gpu_hotpath_pairs_batch: the anchor pass of hotpath_round0 over reads[2i] = mate 1, reads[2i+1] = mate 2,
+        then otherMate -> frameFindMateRect -> DP of the opposite mate -> peClassifyPair for every anchor alignment.
+        Returns (out dict, anchor-pass stats, mate-pass stats)."""
+        n = len(reads)
+        if out is None:
+            out = dict(sweep=np.zeros(n, dtype=structs.sweep_result), job_read=np.zeros(n, dtype=np.uint32),
+                       job_start=np.zeros(n, dtype=np.int64), job_fw=np.zeros(n, dtype=np.uint8),
+                       results=np.zeros(n, dtype=structs.dp_result), alns=np.zeros(n * max_aln, dtype=structs.dp_aln),
+                       edits=np.zeros(64 * n + 1024, dtype=structs.edit),
+                       mates=np.zeros(n, dtype=structs.mate_info), mresults=np.zeros(n, dtype=structs.dp_result),
+                       malns=np.zeros(n * max_aln, dtype=structs.dp_aln), medits=np.zeros(64 * n + 1024, dtype=structs.edit))
+        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, 0, cand_per_job)
+        S, PS = structs.HotpathStats(), structs.PairsStats()
+        nj, ne, nm, nme = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
+        _check(self.lib.bt2gpu_hotpath_pairs_batch(
+            self._h, self._ix.fw, self._ix.bw, ref.handle, _ptr(seq), _ptr(qual),
+            C.c_size_t(len(seq)), _ptr(reads), C.c_size_t(n), _ptr(minsc), _ptr(nceil), C.byref(P), _ptr(pol), C.c_uint32(maxhalf),
+            _ptr(out["sweep"]), _ptr(out["job_read"]), _ptr(out["job_start"]), _ptr(out["job_fw"]), C.byref(nj),
+            _ptr(out["results"]), _ptr(out["alns"]), _ptr(out["edits"]), C.c_size_t(len(out["edits"])), C.byref(ne),
+            C.byref(S),
+            _ptr(out["mates"]), C.byref(nm), _ptr(out["mresults"]), _ptr(out["malns"]), _ptr(out["medits"]),
+            C.c_size_t(len(out["medits"])), C.byref(nme), C.byref(PS)))
+        out["njobs"], out["nedits"], out["nmates"], out["nmedits"] = nj.value, ne.value, nm.value, nme.value
+        self._dp_n, self._dp_k = nm.value, max_aln          # the mate pass is what stays staged
+        self._cand_cap, self._edit_cap = 4096 * max(nm.value, 1), len(out["medits"])
+        return out, S.as_dict(), PS.as_dict()
 
     # ---- framing / paired-end geometry (frame.cu) ----
     def frame_seed_ext(self, jobs, trim_to_ref=True):

@@ -64,6 +64,8 @@ mate_job = np.dtype([("off", "<i8"), ("maxalcols", "<i8"), ("reflen", "<i8"), ("
                      ("is1", "u1"), ("fw", "u1"), ("pad", "u1", (2,))], align=True)
 mate_frame = np.dtype([("rect", rect), ("oll", "<i8"), ("olr", "<i8"), ("orl", "<i8"), ("orr", "<i8"),
                        ("found", "u1"), ("ok", "u1"), ("oleft", "u1"), ("ofw", "u1"), ("pad", "u1", (4,))], align=True)
+mate_info = np.dtype([("anchor_job", "<u4"), ("read", "<u4"), ("cls", "<i4"), ("ofw", "u1"), ("oleft", "u1"), ("pad", "u1", (2,)),
+                      ("anchor_refoff", "<i8"), ("anchor_extent", "<u4"), ("mate_extent", "<u4"), ("rect", rect)], align=True)
 pair_job = np.dtype([("off1", "<i8"), ("off2", "<i8"), ("len1", "<u4"), ("len2", "<u4"),
                      ("fw1", "u1"), ("fw2", "u1"), ("pad", "u1", (6,))], align=True)
 
@@ -116,6 +118,18 @@ class HotpathParams(_ct.Structure):
 class HotpathStats(_ct.Structure):
     """bt2gpu_hotpath_stats"""
     _fields_ = [(k, _ct.c_uint64) for k in _HP_U64] + [(k, _ct.c_float) for k in _HP_F32]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_PS_U64 = ("mate_jobs", "mate_cells", "mate_aligned", "concordant", "bt_cells", "dp_cands", "d2h_bytes")
+_PS_F32 = ("ms_frame", "ms_dp", "ms_dp_fill", "ms_dp_gather", "ms_dp_backtrace", "ms_total")
+
+
+class PairsStats(_ct.Structure):
+    """bt2gpu_pairs_stats"""
+    _fields_ = [(k, _ct.c_uint64) for k in _PS_U64] + [(k, _ct.c_float) for k in _PS_F32]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -523,7 +523,7 @@ k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__r
 // End-to-end windows of at most E2E_CAP columns: count, place, sort and convert in one launch (one
 // warp per job).  The candidates are the last-row cells with H >= minsc (at most ncol of them), so
 // a warp sorts them in its slice of shared memory and takes its slot in the pool with one atomic.
-static constexpr int E2E_CAP = 512;
+static constexpr int E2E_CAP = 1024;   // mate windows of -X 500 are ~700 columns wide
 __global__ void __launch_bounds__(128)
 k_dp_gather_e2e(const bt2gpu_dp_job *__restrict__ jobs, const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
                 const uint32_t *__restrict__ bound, bt2gpu_dp_result *__restrict__ res, bt2gpu_dp_cand *__restrict__ cands,
@@ -1547,6 +1547,8 @@ int dp_dev_finish(bt2gpu_ctx *ctx) {
 
 namespace bt2 {
 const bt2gpu_dp_result *dp_dev_results(bt2gpu_ctx *ctx) { return ctx->dp ? ctx->dp->res.as<bt2gpu_dp_result>() : nullptr; }
+const bt2gpu_dp_aln *dp_dev_alns(bt2gpu_ctx *ctx) { return ctx->dp ? ctx->dp->alns.as<bt2gpu_dp_aln>() : nullptr; }
+const bt2gpu_edit *dp_dev_edits(bt2gpu_ctx *ctx) { return ctx->dp ? ctx->dp->edits.as<bt2gpu_edit>() : nullptr; }
 void dp_state_free(DpState *d) {
 	if(!d) return;
 	DevBuf *bufs[] = { &d->seq, &d->qual, &d->win, &d->jobs, &d->aux, &d->order, &d->res, &d->counts, &d->cand_off,

@@ -9,6 +9,7 @@
 // way (seed count, DP job count, arena totals) to size the next launches.
 #include "common.cuh"
 #include "scan.cuh"
+#include "frame.cuh"
 #include <algorithm>
 #include <cmath>
 #include <chrono>
@@ -30,7 +31,14 @@ struct HpState {
 	       minsc, nceil, job_read, job_start, job_fw, stats;
 	HostBuf h_tot, h_stats;
 	cudaEvent_t ev[12] = {};
+	// paired-end pass (bt2gpu_hotpath_pairs_batch): what pass 1 left behind, and the mate-pass scratch
+	FmReadsDev rv = {nullptr, nullptr, nullptr};
+	size_t last_npick = 0; uint32_t last_max_aln = 0;
+	DevBuf anc, mtmp, mval, mpos, wval, wpos, minfo, mstats;
+	HostBuf h_mstats;
+	cudaEvent_t mev[6] = {};
 };
+static thread_local HpState tl_st;         // device scratch reused across calls of this host thread
 
 enum { ST_SEED_BWOPS = 0, ST_SEED_SIDES, ST_SEED_HITS, ST_EXT_FMOPS, ST_LOC_STEPS, ST_ALIGNED, ST_SWEEP_BWOPS, ST_N };
 
@@ -143,8 +151,8 @@ k_hp_compact(uint32_t nreads, const uint32_t *__restrict__ pick, const u64 *__re
 
 // ---- frame the window around the located seed and fetch it as masks; orient the read --------
 // One warp per DP problem.  DynProgFramer::frameSeedExtensionRect with maxgap on both sides
-// (dp_framer.cpp:81-129): the oriented read is laid at text offset `start`, the window spans
-// [start - 2*maxgap, start + rdlen + 2*maxgap], the core diagonals are [maxgap, 3*maxgap].
+// (dp_framer.cpp:81-129, frame.cuh): the oriented read is laid at text offset `start`, the window spans
+// [start - 2*maxgap, start + rdlen + 2*maxgap] trimmed to the text, the core diagonals are [maxgap, 3*maxgap].
 // Window bytes are 1 << base, 16 outside the text, plus one pad column (aligner_sw.cpp:155-271).
 __global__ void __launch_bounds__(256)
 k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const bt2gpu_read *__restrict__ reads,
@@ -167,8 +175,10 @@ k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, co
 	else for(uint32_t i = lane; i < rdlen; i += 32) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
 	const long long seedoff = x.fw ? (long long)x.off : (long long)rdlen - x.off - x.len;   // in the oriented read
 	const long long start = (long long)offs[k] - seedoff;
-	const long long refl = start - 2 * mg;
-	const uint32_t ncol = rdlen + 4 * (uint32_t)mg;
+	bt2gpu_rect rect;         // trimToRef_ = !gReportOverhangs = true (bt2_search.cpp:188); the window holds the located seed, so it is never empty
+	frame_seed_ext(start, rdlen, (long long)text_len, (u64)mg, (u64)mg, nceil[ri], (u64)mg, true, rect);
+	const long long refl = rect.refl;
+	const uint32_t ncol = (uint32_t)(rect.refr - rect.refl + 1);
 	for(uint32_t c = lane; c <= ncol; c += 32) {
 		const long long p = refl + c;
 		uint8_t m = 16;
@@ -178,8 +188,8 @@ k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, co
 	if(lane == 0) {
 		bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
 		j.rd_off = ro; j.rd_len = rdlen; j.rf_off = wo; j.ncol = ncol;
-		j.minsc = minsc[ri]; j.nceil = nceil[ri]; j.refl = refl; j.triml = 0;
-		j.corel = (uint32_t)mg; j.corer = 3 * (uint32_t)mg; j.fw = x.fw; j.enable8 = 1;
+		j.minsc = minsc[ri]; j.nceil = nceil[ri]; j.refl = refl; j.triml = (uint32_t)rect.triml;
+		j.corel = (uint32_t)rect.corel; j.corer = (uint32_t)rect.corer; j.fw = x.fw; j.enable8 = 1;
 		dj[k] = j;
 		job_read[k] = ri; job_start[k] = start; job_fw[k] = x.fw;
 		atomicAdd(stats + ST_LOC_STEPS, (u64)steps[k]);
@@ -282,8 +292,8 @@ static int hotpath_round0(
 	*njobs_out = 0; *nedits_out = 0;
 	if(nreads == 0) return 0;
 	BT2_CUDA(cudaSetDevice(ctx->device));
-	static thread_local HpState tl_st;         // device scratch reused across calls of this host thread
 	HpState &st = tl_st;
+	st.last_npick = 0;
 	cudaStream_t s = ctx->stream;
 	for(int i = 0; i < 12; i++) if(!st.ev[i]) BT2_CUDA(cudaEventCreate(&st.ev[i]));
 	auto tick = std::chrono::steady_clock::now();
@@ -423,6 +433,7 @@ static int hotpath_round0(
 	S->ms_total = span(0, 10);
 	S->ms_glue = S->ms_total - S->ms_sweep - S->ms_seed - S->ms_extend - S->ms_locate - S->ms_dp;
 	*njobs_out = npick; *nedits_out = ne;
+	st.rv = rv; st.last_npick = npick; st.last_max_aln = max_aln;
 	return 0;
 }
 
@@ -438,6 +449,240 @@ extern "C" int bt2gpu_hotpath_round0_batch(
 	const int rc = hotpath_round0(ctx, fw, bw, ref, seq_pool, qual_pool, pool_len, reads, nreads, minsc, nceil, P, sweep,
 	                              job_read, job_start, job_fw, njobs_out, results, alns, edits, edit_cap, nedits_out, S);
 	if(rc && ctx) {          // failed part-way: nothing may still be copying from / into the caller's buffers
+		cudaStreamSynchronize(ctx->stream);
+		if(ctx->cstream) cudaStreamSynchronize(ctx->cstream);
+	}
+	return rc;
+}
+
+// =======================================================================================
+// Paired-end pass: anchor alignments -> mate windows -> DP -> pair classes
+// =======================================================================================
+namespace bt2 {
+const bt2gpu_dp_aln *dp_dev_alns(bt2gpu_ctx *ctx);
+const bt2gpu_edit *dp_dev_edits(bt2gpu_ctx *ctx);
+int check_pe_policy(const bt2gpu_pe_policy *pol);
+
+enum { MS_ALIGNED = 0, MS_CONCORDANT, MS_BADWIN, MS_N };
+
+struct AnchorSum { long long refoff; uint32_t extent; int32_t score; };
+
+// AlnRes::refExtent(): read characters aligned, minus those opposite a reference gap, plus the
+// reference characters opposite a read gap
+__device__ __forceinline__ uint32_t ref_extent(uint32_t rdlen, const bt2gpu_dp_aln &a, const bt2gpu_edit *__restrict__ edits) {
+	int ext = (int)rdlen - (int)a.trim5 - (int)a.trim3;
+	for(uint32_t e = 0; e < a.nedits; e++) {
+		const uint8_t t = edits[a.edit_off + e].type;
+		if(t == BT2GPU_EDIT_REF_GAP) ext--;
+		else if(t == BT2GPU_EDIT_READ_GAP) ext++;
+	}
+	return (uint32_t)ext;
+}
+
+// One thread per pass-1 DP job: the first alignment of the job is the anchor; compute where the opposite
+// mate may lie (otherMate) and the rectangle to search (frameFindMateRect).
+// mval[k] = (1 << 32) | opposite read length, wval[k] = window bytes (ncol + 1), both 0 without a window.
+__global__ void __launch_bounds__(256)
+k_hp_anchor(const bt2gpu_dp_result *__restrict__ res, const bt2gpu_dp_aln *__restrict__ alns, const bt2gpu_edit *__restrict__ edits,
+            uint32_t max_aln, uint32_t njobs, const uint32_t *__restrict__ job_read, const uint8_t *__restrict__ job_fw,
+            const bt2gpu_read *__restrict__ reads, const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil,
+            bt2gpu_pe_policy pol, uint32_t maxhalf, long long reflen, int match, int rdo, int rde, int rfo, int rfe,
+            AnchorSum *__restrict__ anc, bt2gpu_mate_frame *__restrict__ mtmp, u64 *__restrict__ mval, u64 *__restrict__ wval,
+            u64 *__restrict__ mstats)
+{
+	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+	if(k >= njobs) return;
+	u64 mv = 0, wv = 0;
+	if(res[k].naln > 0) {
+		const bt2gpu_dp_aln a = alns[(size_t)k * max_aln];
+		const uint32_t ri = job_read[k], mate = ri ^ 1u;
+		const bool is1 = (ri & 1u) == 0, fw = job_fw[k] != 0;
+		const uint32_t len_a = reads[ri].rd_len, len_o = reads[mate].rd_len;
+		AnchorSum s; s.refoff = a.refoff; s.extent = ref_extent(len_a, a, edits); s.score = a.score;
+		anc[k] = s;
+		const long long ominsc = minsc[mate];
+		const int ordg = max_gaps(ominsc, len_o, match, rdo, rde, false), orfg = max_gaps(ominsc, len_o, match, rfo, rfe, true);
+		bt2gpu_mate_frame f; memset(&f, 0, sizeof(f));
+		MateWin w;
+		bool ok = len_o > 0 && ordg >= 0 && orfg >= 0 &&
+		          other_mate(pol, is1, fw, a.refoff, (long long)len_o + ordg, is1 ? len_a : len_o, is1 ? len_o : len_a, w);
+		if(ok) {
+			f.found = 1; f.oleft = w.oleft; f.ofw = w.ofw; f.oll = w.oll; f.olr = w.olr; f.orl = w.orl; f.orr = w.orr;
+			ok = frame_mate(!w.oleft, w.oll, w.olr, w.orl, w.orr, len_o, reflen, (u64)ordg, (u64)orfg, nceil[mate], maxhalf,
+			                pol.trim_to_ref != 0, f.rect);
+		}
+		if(ok) {
+			const long long ncol = f.rect.refr - f.rect.refl + 1;
+			if(ncol > 60000 || f.rect.corer > 0xffffffffull) { atomicAdd(mstats + MS_BADWIN, 1ull); ok = false; }
+			else { f.ok = 1; mv = (1ull << 32) | len_o; wv = (u64)ncol + 1; }
+		}
+		mtmp[k] = f;
+	}
+	mval[k] = mv; wval[k] = wv;
+}
+
+// One warp per anchor job that has a window: orient the opposite mate, fetch the window as masks
+// (16 outside the text, plus the pad column, aligner_sw.cpp:155-271), write the DP job and its description.
+__global__ void __launch_bounds__(256)
+k_hp_mateframe(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const bt2gpu_read *__restrict__ reads,
+               const uint32_t *__restrict__ text2, u64 text_len, uint32_t njobs, const uint32_t *__restrict__ job_read,
+               const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil, const AnchorSum *__restrict__ anc,
+               const bt2gpu_mate_frame *__restrict__ mtmp, const u64 *__restrict__ mval, const u64 *__restrict__ mpos,
+               const u64 *__restrict__ wpos, uint8_t *__restrict__ dseq, uint8_t *__restrict__ dqual, uint8_t *__restrict__ dwin,
+               bt2gpu_dp_job *__restrict__ dj, bt2gpu_mate_info *__restrict__ info)
+{
+	const int lane = threadIdx.x & 31;
+	const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	if(k >= njobs || mval[k] == 0) return;
+	const uint32_t m = (uint32_t)(mpos[k] >> 32), ro = (uint32_t)mpos[k], wo = (uint32_t)wpos[k];
+	const uint32_t mate = job_read[k] ^ 1u, rdlen = reads[mate].rd_len;
+	const bt2gpu_mate_frame f = mtmp[k];
+	const uint8_t *rd = seq + reads[mate].rd_off, *qu = qual + reads[mate].rd_off;
+	uint8_t *os = dseq + ro, *oq = dqual + ro, *ow = dwin + wo;
+	if(f.ofw) for(uint32_t i = lane; i < rdlen; i += 32) { os[i] = rd[i]; oq[i] = qu[i]; }
+	else for(uint32_t i = lane; i < rdlen; i += 32) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
+	const long long refl = f.rect.refl;
+	const uint32_t ncol = (uint32_t)(f.rect.refr - f.rect.refl + 1);
+	for(uint32_t c = lane; c <= ncol; c += 32) {
+		const long long p = refl + c;
+		uint8_t v = 16;
+		if(p >= 0 && (u64)p < text_len) v = (uint8_t)(1u << ((__ldg(text2 + (p >> 4)) >> (2 * (p & 15))) & 3u));
+		ow[c] = v;
+	}
+	if(lane == 0) {
+		bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
+		j.rd_off = ro; j.rd_len = rdlen; j.rf_off = wo; j.ncol = ncol;
+		j.minsc = minsc[mate]; j.nceil = nceil[mate]; j.refl = refl; j.triml = (uint32_t)f.rect.triml;
+		j.corel = (uint32_t)f.rect.corel; j.corer = (uint32_t)f.rect.corer; j.fw = f.ofw; j.enable8 = 1;
+		dj[m] = j;
+		bt2gpu_mate_info o; memset(&o, 0, sizeof(o));
+		o.anchor_job = k; o.read = mate; o.ofw = f.ofw; o.oleft = f.oleft;
+		o.anchor_refoff = anc[k].refoff; o.anchor_extent = anc[k].extent; o.rect = f.rect;
+		info[m] = o;
+	}
+}
+
+// One thread per mate job: peClassifyPair of the anchor alignment and the first mate alignment.
+__global__ void __launch_bounds__(256)
+k_hp_pairs(const bt2gpu_dp_result *__restrict__ res, const bt2gpu_dp_aln *__restrict__ alns, const bt2gpu_edit *__restrict__ edits,
+           uint32_t max_aln, uint32_t nmates, const bt2gpu_read *__restrict__ reads, const uint8_t *__restrict__ job_fw,
+           bt2gpu_pe_policy pol, bt2gpu_mate_info *__restrict__ info, u64 *__restrict__ mstats)
+{
+	const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+	u64 al = 0, cc = 0;
+	if(m < nmates && res[m].naln > 0) {
+		bt2gpu_mate_info o = info[m];
+		const bt2gpu_dp_aln a = alns[(size_t)m * max_aln];
+		const uint32_t ext = ref_extent(reads[o.read].rd_len, a, edits);
+		const bool mate_is1 = (o.read & 1u) == 0, afw = job_fw[o.anchor_job] != 0;
+		const long long off1 = mate_is1 ? a.refoff : o.anchor_refoff, off2 = mate_is1 ? o.anchor_refoff : a.refoff;
+		const uint32_t len1 = mate_is1 ? ext : o.anchor_extent, len2 = mate_is1 ? o.anchor_extent : ext;
+		const bool fw1 = mate_is1 ? (o.ofw != 0) : afw, fw2 = mate_is1 ? afw : (o.ofw != 0);
+		const int cls = pe_classify(pol, off1, len1, fw1, off2, len2, fw2);
+		info[m].cls = cls; info[m].mate_extent = ext;
+		al = 1; cc = cls != BT2GPU_PE_ALS_DISCORD;
+	}
+	for(int o = 16; o; o >>= 1) { al += __shfl_xor_sync(0xffffffffu, al, o); cc += __shfl_xor_sync(0xffffffffu, cc, o); }
+	if((threadIdx.x & 31) == 0) {
+		if(al) atomicAdd(mstats + MS_ALIGNED, al);
+		if(cc) atomicAdd(mstats + MS_CONCORDANT, cc);
+	}
+}
+
+} // namespace bt2
+
+static int hotpath_mates(
+	bt2gpu_ctx *ctx, const bt2gpu_ref *ref, size_t nreads, const bt2gpu_hotpath_params *P, const bt2gpu_pe_policy *pol, uint32_t maxhalf,
+	bt2gpu_mate_info *mates, size_t *nmates_out, bt2gpu_dp_result *mresults, bt2gpu_dp_aln *malns, bt2gpu_edit *medits,
+	size_t medit_cap, size_t *nmedits_out, bt2gpu_pairs_stats *S)
+{
+	HpState &st = tl_st;
+	cudaStream_t s = ctx->stream;
+	const size_t npick = st.last_npick;
+	const uint32_t max_aln = st.last_max_aln;
+	if(npick == 0) return 0;
+	for(int i = 0; i < 6; i++) if(!st.mev[i]) BT2_CUDA(cudaEventCreate(&st.mev[i]));
+	if(st.anc.reserve(npick * sizeof(AnchorSum)) || st.mtmp.reserve(npick * sizeof(bt2gpu_mate_frame)) || st.mval.reserve(npick * 8) ||
+	   st.mpos.reserve(npick * 8) || st.wval.reserve(npick * 8) || st.wpos.reserve(npick * 8) || st.minfo.reserve(npick * sizeof(bt2gpu_mate_info)) ||
+	   st.mstats.reserve(MS_N * 8) || st.h_mstats.reserve(MS_N * 8) || st.spart.reserve((scan_parts(std::max(npick, nreads)) + 2) * 8)) return 1;
+	u64 *mstats = st.mstats.as<u64>();
+	BT2_CUDA(cudaMemsetAsync(mstats, 0, MS_N * 8, s));
+	BT2_CUDA(cudaEventRecord(st.mev[0], s));
+	const bt2gpu_scoring &sc = ctx->sc;
+	const unsigned nbJ = (unsigned)((npick + 255) / 256);
+	k_hp_anchor<<<nbJ, 256, 0, s>>>(dp_dev_results(ctx), dp_dev_alns(ctx), dp_dev_edits(ctx), max_aln, (uint32_t)npick,
+		st.job_read.as<uint32_t>(), st.job_fw.as<uint8_t>(), st.rv.reads, st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), *pol, maxhalf,
+		(long long)ref->len, sc.match_bonus, sc.rd_gap_open, sc.rd_gap_ext, sc.rf_gap_open, sc.rf_gap_ext,
+		st.anc.as<AnchorSum>(), st.mtmp.as<bt2gpu_mate_frame>(), st.mval.as<u64>(), st.wval.as<u64>(), mstats);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	if(dev_exclusive_scan<u64>(ctx, st.mval.as<u64>(), st.mpos.as<u64>(), st.spart.as<u64>(), st.tot.as<u64>() + 2, npick)) return 1;
+	if(dev_exclusive_scan<u64>(ctx, st.wval.as<u64>(), st.wpos.as<u64>(), st.spart.as<u64>(), st.tot.as<u64>() + 3, npick)) return 1;
+	BT2_CUDA(cudaMemcpyAsync(st.h_tot.as<u64>() + 2, st.tot.as<u64>() + 2, 16, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaMemcpyAsync(st.h_mstats.p, mstats, MS_N * 8, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamSynchronize(s));
+	if(st.h_mstats.as<u64>()[MS_BADWIN]) BT2_FAIL("mate window wider than 60000 columns: lower the maximum fragment length");
+	const u64 t = st.h_tot.as<u64>()[2];
+	const size_t nm = (size_t)(t >> 32), tot_rd = (size_t)(t & 0xffffffffu), tot_win = (size_t)st.h_tot.as<u64>()[3];
+	*nmates_out = nm;
+	S->mate_jobs = nm;
+	if(nm == 0) return 0;
+	DpDevPools pools;
+	const size_t cpj = std::max<size_t>(P->cand_per_job ? P->cand_per_job : (ctx->sc.monotone ? 256 : 4096), ctx->sc.monotone ? 1024 : 4096);
+	if(dp_dev_begin(ctx, nm, tot_rd, tot_win, max_aln, cpj * nm, medit_cap, &pools)) return 1;
+	k_hp_mateframe<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(st.rv.seq, st.rv.qual, st.rv.reads, ref->packed.as<uint32_t>(), ref->len,
+		(uint32_t)npick, st.job_read.as<uint32_t>(), st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), st.anc.as<AnchorSum>(),
+		st.mtmp.as<bt2gpu_mate_frame>(), st.mval.as<u64>(), st.mpos.as<u64>(), st.wpos.as<u64>(), pools.seq, pools.qual, pools.win, pools.jobs,
+		st.minfo.as<bt2gpu_mate_info>());
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	BT2_CUDA(cudaEventRecord(st.mev[1], s));
+	if(dp_dev_finish(ctx)) return 1;
+	BT2_CUDA(cudaEventRecord(st.mev[2], s));
+	if(bt2gpu_dp_run(ctx, 7)) return 1;
+	BT2_CUDA(cudaEventRecord(st.mev[3], s));
+	k_hp_pairs<<<(unsigned)((nm + 255) / 256), 256, 0, s>>>(dp_dev_results(ctx), dp_dev_alns(ctx), dp_dev_edits(ctx), max_aln, (uint32_t)nm,
+		st.rv.reads, st.job_fw.as<uint8_t>(), *pol, st.minfo.as<bt2gpu_mate_info>(), mstats);
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	BT2_CUDA(cudaEventRecord(st.mev[4], s));
+	BT2_CUDA(cudaMemcpyAsync(st.h_mstats.p, mstats, MS_N * 8, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaMemcpyAsync(mates, st.minfo.p, nm * sizeof(bt2gpu_mate_info), cudaMemcpyDeviceToHost, s));
+	size_t ne = 0, nc_total = 0;
+	if(bt2gpu_dp_fetch(ctx, mresults, nullptr, malns, medits, &nc_total, &ne)) return 1;
+	*nmedits_out = ne;
+	const u64 *hs = st.h_mstats.as<u64>();
+	S->mate_aligned = hs[MS_ALIGNED]; S->concordant = hs[MS_CONCORDANT];
+	S->mate_cells = bt2gpu_dp_staged_cells(ctx); S->bt_cells = bt2gpu_dp_walked_cells(ctx); S->dp_cands = nc_total;
+	S->d2h_bytes = nm * (sizeof(bt2gpu_mate_info) + sizeof(bt2gpu_dp_result) + max_aln * sizeof(bt2gpu_dp_aln)) + ne * sizeof(bt2gpu_edit);
+	auto span = [&](int a, int b) -> float { float ms = 0.f; cudaEventElapsedTime(&ms, st.mev[a], st.mev[b]); return ms; };
+	S->ms_frame = span(0, 2); S->ms_dp = span(2, 3); S->ms_total = span(0, 4);
+	float ph[3] = {0, 0, 0};
+	if(bt2gpu_dp_phase_ms(ctx, ph) == 0) { S->ms_dp_fill = ph[0]; S->ms_dp_gather = ph[1]; S->ms_dp_backtrace = ph[2]; }
+	return 0;
+}
+
+extern "C" int bt2gpu_hotpath_pairs_batch(
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
+	const bt2gpu_hotpath_params *P, const bt2gpu_pe_policy *pol, uint32_t maxhalf,
+	bt2gpu_sweep_result *sweep, uint32_t *job_read, int64_t *job_start, uint8_t *job_fw, size_t *njobs_out,
+	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits_out,
+	bt2gpu_hotpath_stats *S,
+	bt2gpu_mate_info *mates, size_t *nmates_out,
+	bt2gpu_dp_result *mresults, bt2gpu_dp_aln *malns, bt2gpu_edit *medits, size_t medit_cap, size_t *nmedits_out,
+	bt2gpu_pairs_stats *PS)
+{
+	if(!mates || !nmates_out || !mresults || !malns || !medits || !nmedits_out || !PS) BT2_FAIL("null argument");
+	if(nreads & 1) BT2_FAIL("paired batch needs an even number of reads (mate 1, mate 2, mate 1, ...)");
+	if(check_pe_policy(pol)) return 1;
+	memset(PS, 0, sizeof(*PS));
+	*nmates_out = 0; *nmedits_out = 0;
+	int rc = hotpath_round0(ctx, fw, bw, ref, seq_pool, qual_pool, pool_len, reads, nreads, minsc, nceil, P, sweep,
+	                        job_read, job_start, job_fw, njobs_out, results, alns, edits, edit_cap, nedits_out, S);
+	if(!rc) rc = hotpath_mates(ctx, ref, nreads, P, pol, maxhalf, mates, nmates_out, mresults, malns, medits, medit_cap, nmedits_out, PS);
+	if(rc && ctx) {
 		cudaStreamSynchronize(ctx->stream);
 		if(ctx->cstream) cudaStreamSynchronize(ctx->cstream);
 	}

@@ -403,6 +403,47 @@ int bt2gpu_hotpath_round0_batch(
 	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits,
 	bt2gpu_hotpath_stats *stats);
 
+/* ---- batch runtime, paired-end: anchor pass + mate search ------------------------------- */
+
+/* What SwDriver::extendSeedsPaired adds to the unpaired flow (aligner_sw_driver.cpp:1925-2240):
+ * for every anchor alignment, PairedEndPolicy::otherMate -> DynProgFramer::frameFindMateRect ->
+ * SwAligner::initRef/align/nextAlignment of the OPPOSITE mate in that window -> peClassifyPair.
+ * reads[2i] is mate 1 and reads[2i+1] mate 2 of pair i.  Pass 1 is exactly
+ * bt2gpu_hotpath_round0_batch over all 2*npairs reads (every mate is tried as an anchor; its
+ * outputs have the same meaning).  Pass 2 takes the FIRST alignment of every anchor DP job, frames
+ * the opposite mate's window on the device and runs the DP kernels on those windows; mate job m
+ * is described by mates[m] and answered by mresults[m], malns[m*max_aln..], medits.
+ * The whole joined text is treated as one reference sequence (tidx 0, reflen = text length). */
+typedef struct {
+	uint32_t anchor_job;     /* pass-1 DP job this window was framed from                     */
+	uint32_t read;           /* read id of the opposite mate (the one aligned in this window)  */
+	int32_t  cls;            /* BT2GPU_PE_ALS_* of (anchor, first mate alignment); 0 if the mate did not align */
+	uint8_t  ofw, oleft, pad[2];
+	int64_t  anchor_refoff;  /* AlnRes::refoff() of the anchor alignment                       */
+	uint32_t anchor_extent;  /* AlnRes::refExtent() of the anchor alignment                    */
+	uint32_t mate_extent;    /* ... of the first mate alignment (0 if none)                    */
+	bt2gpu_rect rect;
+} bt2gpu_mate_info;
+
+typedef struct {
+	uint64_t mate_jobs, mate_cells, mate_aligned, concordant, bt_cells, dp_cands, d2h_bytes;
+	float    ms_frame, ms_dp, ms_dp_fill, ms_dp_gather, ms_dp_backtrace, ms_total;
+} bt2gpu_pairs_stats;
+
+int bt2gpu_hotpath_pairs_batch(
+	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const bt2gpu_read *reads, size_t nreads, const int32_t *minsc, const int32_t *nceil,
+	const bt2gpu_hotpath_params *params, const bt2gpu_pe_policy *pol, uint32_t maxhalf,
+	/* pass 1 (anchors), as bt2gpu_hotpath_round0_batch */
+	bt2gpu_sweep_result *sweep, uint32_t *job_read, int64_t *job_start, uint8_t *job_fw, size_t *njobs,
+	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits,
+	bt2gpu_hotpath_stats *stats,
+	/* pass 2 (mates): arrays of nreads entries (at most one mate job per anchor job) */
+	bt2gpu_mate_info *mates, size_t *nmates,
+	bt2gpu_dp_result *mresults, bt2gpu_dp_aln *malns, bt2gpu_edit *medits, size_t medit_cap, size_t *nmedits,
+	bt2gpu_pairs_stats *pstats);
+
 #ifdef __cplusplus
 }
 #endif

@@ -102,6 +102,7 @@ def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, m
     offs, steps = orc.locate(xj["topf"][picks]) if len(picks) else (np.zeros(0, np.uint32), np.zeros(0, np.uint32))
     b_seq, b_qual, b_win, jobs, rid, starts, fws = [], [], [], np.zeros(len(picks), dtype=structs.dp_job), [], [], []
     G = len(genome)
+    fo = H.FrameOracle()
     ro = wo = 0
     comp = np.array([3, 2, 1, 0, 4], np.uint8)
     for k, p in enumerate(picks):
@@ -112,21 +113,22 @@ def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, m
             rd, qu = comp[rd[::-1]], qu[::-1]
         seedoff = int(x["off"]) if x["fw"] else rdlen - int(x["off"]) - int(x["len"])
         start = int(offs[k]) - seedoff
-        refl = start - 2 * maxgap
-        ncol = rdlen + 4 * maxgap
+        ok, rect = fo.frame_seed_ext(start, rdlen, G, maxgap, maxgap, int(nceil[ri]), maxgap, 1)   # trimToRef (the reference default)
+        assert ok
+        refl, ncol = rect[0], rect[1] - rect[0] + 1
         cols = refl + np.arange(ncol + 1)
         codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
         b_seq.append(rd); b_qual.append(qu); b_win.append((1 << codes).astype(np.uint8))
         j = jobs[k]
         j["rd_off"], j["rd_len"], j["rf_off"], j["ncol"] = ro, rdlen, wo, ncol
-        j["minsc"], j["nceil"], j["refl"], j["triml"] = minsc[ri], nceil[ri], refl, 0
-        j["corel"], j["corer"], j["fw"], j["enable8"] = maxgap, 3 * maxgap, x["fw"], 1
+        j["minsc"], j["nceil"], j["refl"], j["triml"] = minsc[ri], nceil[ri], refl, rect[4]
+        j["corel"], j["corer"], j["fw"], j["enable8"] = rect[6], rect[7], x["fw"], 1
         ro += rdlen; wo += ncol + 1
         rid.append(ri); starts.append(start); fws.append(int(x["fw"]))
     cat = lambda a: np.ascontiguousarray(np.concatenate(a)) if a else np.zeros(0, np.uint8)
     ref = H.oracle_dp(sc.to_struct(), cat(b_seq), cat(b_qual), cat(b_win), jobs, max_aln=max_aln) if len(jobs) else None
     return dict(sweep=sweep, nseeds=len(sj), rid=np.array(rid), start=np.array(starts), fw=np.array(fws), dp=ref, njobs=len(jobs),
-                steps=int(steps.sum()) if len(picks) else 0)
+                steps=int(steps.sum()) if len(picks) else 0, jobs=jobs)
 
 
 @pytest.mark.parametrize("local", [False, True])
