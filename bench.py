@@ -41,11 +41,22 @@ MAXGAP = 15
 SEED_LEN = 22
 IVAL = (1.0, 1.15)
 LOCAL = False
+PAIRED = False            # --mode pairs: reads are 2 x RDLEN pairs (mate 1, mate 2 interleaved), -I 0 -X 500 --fr
+MAXFRAG, MINFRAG, MAXHALF = 500, 0, 15
+PE_FLAGS = (0, 0, 0, 1, 1, 1)   # local, flip, dovetail, contain, overlap, expand-to-fit: the reference defaults (bt2_search.cpp:381-385)
 METRIC = "aligned reads/sec (2x150 end-to-end)"
 UNIT = "reads/s"
 
 
 def workload_name(batch, gmbp):
+    if PAIRED:
+        return ("synthetic 2x%d bp --fr pairs (simulate.pl model, fragments N(250,45) >= 2x%d) vs FM index of a random %d Mbp "
+                "genome, -I %d -X %d: every mate through exactSweep + exact seeds (-L %d, S,%g,%g) + extend + locate + one "
+                "seed-extension DP window (%d x %d, end-to-end u8: fill + gather + nextAlignment loop); then, per anchor "
+                "alignment, otherMate + frameFindMateRect + the opposite mate's DP in the mate window (%d x ~%d) + "
+                "peClassifyPair; %d reads (%d pairs) per step per GPU"
+                % (RDLEN, RDLEN, gmbp, MINFRAG, MAXFRAG, SEED_LEN, IVAL[0], IVAL[1], RDLEN, RDLEN + 4 * MAXGAP, RDLEN,
+                   MAXFRAG + RDLEN + 56, batch, batch // 2))
     return ("synthetic %d bp reads (simulate.pl model) vs FM index of a random %d Mbp genome: exactSweep + "
             "exact seeds (-L %d, S,%g,%g) + extend + locate + one seed-extension DP window (%d x %d, "
             "%s: fill + gather + nextAlignment loop) per read, %d reads per step per GPU"
@@ -75,6 +86,9 @@ def get_index(genome, seed, gmbp, need_files):
 def make_reads(seed, genome, n):
     from bt2gpu import synth
     rng = np.random.default_rng(seed)
+    if PAIRED:
+        reads, quals, pos, fw = synth.simulate_pairs(rng, genome, n // 2, RDLEN)
+        return np.ascontiguousarray(reads), np.ascontiguousarray(quals), pos, fw
     reads, quals, pos, _ = synth.simulate_reads(rng, genome, n, RDLEN)
     # strand coin-flip as simulate.pl does: half of the reads are given reverse-complemented
     rc = rng.random(n) < 0.5
@@ -125,46 +139,91 @@ def write_fastq(path, reads, quals):
             fh.write(b"@r%d\n" % i + c2a[reads[i]].tobytes() + b"\n+\n" + quals[i].tobytes() + b"\n")
 
 
+def _dp_problem_file(path, genome, sc, items):
+    """items: (oriented read, oriented quals, rect tuple (refl, refr, ..., triml, trimr, corel, corer, maxgap)) per problem
+    -> "P" lines for ref_dp_dump (window fetched like SwAligner::initRef: N outside the text, one pad column)."""
+    from bt2gpu import synth, structs
+    G = len(genome)
+    n = len(items)
+    jobs = np.zeros(n, dtype=structs.dp_job)
+    seqs, quals, wins = [], [], []
+    ro = wo = 0
+    for k, (rd, qu, rect) in enumerate(items):
+        refl, ncol = rect[0], rect[1] - rect[0] + 1
+        cols = refl + np.arange(ncol + 1)
+        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
+        seqs.append(rd); quals.append(qu); wins.append((1 << codes).astype(np.uint8))
+        j = jobs[k]
+        j["rd_off"], j["rd_len"], j["rf_off"], j["ncol"] = ro, len(rd), wo, ncol
+        j["minsc"], j["nceil"] = sc.score_min.f_int(len(rd)), sc.nceil(len(rd))
+        j["refl"], j["triml"], j["corel"], j["corer"] = refl, rect[4], rect[6], rect[7]
+        j["fw"], j["enable8"] = 1, 1        # the window is framed for the oriented read; '+' keeps it as given
+        ro += len(rd); wo += ncol + 1
+    synth.problems_to_plines(np.concatenate(seqs), np.concatenate(quals), np.concatenate(wins), jobs, path, reflen=G)
+    return n
+
+
 def reference_step(base, genome, reads, quals, pos, fw, threads, td):
-    """One bounded step through the reference's own code: ref_seed_dump --bench (exactSweep,
-    searchAllSeeds, extend, getOffset) + ref_dp_dump --bench (SwAligner) with `threads` threads.
-    Returns (seconds, detail)."""
-    from bt2gpu import synth, scoring, structs
+    """One bounded step through the reference's own code with `threads` threads:
+      ref_seed_dump --bench   exactSweep, searchAllSeeds, SwDriver::extend, getOffset for every read; it also reports
+                              which reads had an exact seed hit (--hits-out) -- the reads the chain takes to DP;
+      ref_dp_dump --bench     SwAligner (initRead, initRef, align, nextAlignment x2) on the seed-extension window of
+                              each of those reads, framed on the read's origin;
+      --mode pairs            ... and on the mate window (otherMate + frameFindMateRect from that anchor) of the
+                              opposite mate, again through ref_dp_dump --bench.
+    The windows are framed with oracle/frame_oracle.c (pinned on the reference's DynProgFramer / PairedEndPolicy);
+    framing is not timed on either arm's DP kernels.  Returns (seconds, detail)."""
+    from bt2gpu import scoring
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers as H
     bin_ = os.path.join(ROOT, "oracle", "_ref")
     fq = os.path.join(td, "reads.fq")
+    hits = os.path.join(td, "hits.bin")
     if not os.path.exists(fq):
         write_fastq(fq, reads, quals)
     o1 = json.loads(subprocess.check_output([os.path.join(bin_, "ref_seed_dump"), "--index", base, "--reads", fq,
-                                             "--bench", "--threads", str(threads)]).decode())
-    pf = os.path.join(td, "p.txt")
+                                             "--bench", "--threads", str(threads), "--hits-out", hits]).decode())
+    pf, mf = os.path.join(td, "p.txt"), os.path.join(td, "m.txt")
+    sc = scoring.Scoring(local=False)
     if not os.path.exists(pf):
-        sc = scoring.Scoring(local=False)
-        n = len(reads)
-        comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
-        orient = np.where(fw[:, None], reads, comp[reads[:, ::-1]])
-        oq = np.where(fw[:, None], quals, quals[:, ::-1])
-        ncol = RDLEN + 4 * MAXGAP
-        refl = pos - 2 * MAXGAP
-        cols = refl[:, None] + np.arange(ncol + 1)[None, :]
+        hit = np.fromfile(hits, dtype=np.uint8).astype(bool)
+        fo = H.FrameOracle()
         G = len(genome)
-        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
-        jobs = np.zeros(n, dtype=structs.dp_job)
-        jobs["rd_off"] = np.arange(n, dtype=np.int64) * RDLEN
-        jobs["rd_len"] = RDLEN
-        jobs["rf_off"] = np.arange(n, dtype=np.int64) * (ncol + 1)
-        jobs["ncol"] = ncol
-        jobs["minsc"] = sc.score_min.f_int(RDLEN)
-        jobs["nceil"] = sc.nceil(RDLEN)
-        jobs["refl"] = refl
-        jobs["corel"], jobs["corer"] = MAXGAP, 3 * MAXGAP
-        jobs["fw"] = 1          # the window is framed for the oriented read; '+' keeps it as given
-        jobs["enable8"] = 1
-        synth.problems_to_plines(orient.reshape(-1), oq.reshape(-1), (1 << codes).astype(np.uint8).reshape(-1), jobs, pf)
+        comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
+        scs = sc.to_struct().reshape(-1)[0]
+        minsc, nceil = sc.score_min.f_int(RDLEN), sc.nceil(RDLEN)
+        rdg = fo.lib.bt2o_max_read_gaps(minsc, RDLEN, int(scs["match_bonus"]), int(scs["rd_gap_open"]), int(scs["rd_gap_ext"]))
+        rfg = fo.lib.bt2o_max_ref_gaps(minsc, RDLEN, int(scs["match_bonus"]), int(scs["rf_gap_open"]), int(scs["rf_gap_ext"]))
+        pol = fo.policy(3, MAXFRAG, MINFRAG, PE_FLAGS)
+        anchors, mates = [], []
+        for i in np.nonzero(hit)[0]:
+            rd, qu = (reads[i], quals[i]) if fw[i] else (comp[reads[i][::-1]], quals[i][::-1])
+            ok, rect = fo.frame_seed_ext(int(pos[i]), RDLEN, G, MAXGAP, MAXGAP, nceil, MAXGAP, 1)
+            if ok:
+                anchors.append((rd, qu, rect))
+            if PAIRED and ok:
+                m = i ^ 1
+                is1 = int(i % 2 == 0)
+                found, oleft, o4, ofw = fo.other_mate(pol, is1, int(fw[i]), int(pos[i]), RDLEN + rdg, G, RDLEN, RDLEN)
+                if found:
+                    ok2, mrect = fo.frame_mate(int(not oleft), *o4, RDLEN, G, rdg, rfg, nceil, MAXHALF, 1)
+                    if ok2:
+                        mrd, mqu = (reads[m], quals[m]) if ofw else (comp[reads[m][::-1]], quals[m][::-1])
+                        mates.append((mrd, mqu, mrect))
+        _dp_problem_file(pf, genome, sc, anchors)
+        if PAIRED:
+            _dp_problem_file(mf, genome, sc, mates)
     o2 = json.loads(subprocess.check_output([os.path.join(bin_, "ref_dp_dump"), "--problems", pf, "--bench",
                                              "--threads", str(threads)]).decode())
-    return o1["seconds"] + o2["seconds"], {"seed_s": o1["seconds"], "dp_s": o2["seconds"],
-                                           "lf_steps_per_s": o1["lf_steps_per_s"],
-                                           "gcups": o2["cells"] / o2["seconds"] / 1e9}
+    det = {"seed_s": o1["seconds"], "dp_s": o2["seconds"], "lf_steps_per_s": o1["lf_steps_per_s"],
+           "dp_problems": o2.get("problems"), "gcups": o2["cells"] / o2["seconds"] / 1e9}
+    tot = o1["seconds"] + o2["seconds"]
+    if PAIRED:
+        o3 = json.loads(subprocess.check_output([os.path.join(bin_, "ref_dp_dump"), "--problems", mf, "--bench",
+                                                 "--threads", str(threads)]).decode())
+        det.update({"mate_dp_s": o3["seconds"], "mate_dp_problems": o3.get("problems"), "mate_gcups": o3["cells"] / o3["seconds"] / 1e9})
+        tot += o3["seconds"]
+    return tot, det
 
 
 def run_reference(args, rank, world):
@@ -255,12 +314,29 @@ def run_ours(args, rank, world, local_rank):
                              job_start=np.zeros(m, dtype=np.int64), job_fw=np.zeros(m, dtype=np.uint8),
                              results=pin(np.zeros(m, dtype=structs.dp_result)),
                              alns=pin(np.zeros(m * max_aln, dtype=structs.dp_aln)),
-                             edits=pin(np.zeros(64 * m + 1024, dtype=structs.edit))))
+                             edits=pin(np.zeros(64 * m + 1024, dtype=structs.edit)),
+                             **(dict(mates=pin(np.zeros(m, dtype=structs.mate_info)), mresults=pin(np.zeros(m, dtype=structs.dp_result)),
+                                     malns=pin(np.zeros(m * max_aln, dtype=structs.dp_aln)),
+                                     medits=pin(np.zeros(64 * m + 1024, dtype=structs.edit))) if PAIRED else {})))
     bounds = [n * i // C for i in range(C + 1)]
     shards = [make_io(bounds[i], bounds[i + 1]) for i in range(C)]
     pool = ThreadPoolExecutor(max_workers=C)
 
+    pe_pol = np.zeros(1, dtype=structs.pe_policy)
+    pe_pol["pol"], pe_pol["trim_to_ref"], pe_pol["maxfrag"], pe_pol["minfrag"] = 3, 1, MAXFRAG, MINFRAG
+    for k_, v_ in zip(("local", "flip_ok", "dovetail_ok", "contain_ok", "olap_ok", "expand_to_fit"), PE_FLAGS):
+        pe_pol[k_] = v_
+
     def run(c_, io):
+        if PAIRED:
+            o_, st_, ps_ = c_.hotpath_pairs(dref, io["seq"], io["qual"], io["rd"], io["minsc"], io["nceil"], pe_pol, maxhalf=MAXHALF,
+                                            seed_len=SEED_LEN, ival=IVAL, maxgap=MAXGAP, max_aln=max_aln, mine_max=2, out=io["out"])
+            st_ = dict(st_)
+            st_.update({("mate_" + k_ if not k_.startswith("mate_") else k_): v_ for k_, v_ in ps_.items()})
+            st_["ms_anchor_total"] = st_["ms_total"]
+            st_["ms_total"] = st_["ms_total"] + ps_["ms_total"]          # device span of both passes
+            st_["d2h_bytes"] += ps_["d2h_bytes"]
+            return o_, st_
         return c_.hotpath_round0(dref, io["seq"], io["qual"], io["rd"], io["minsc"], io["nceil"], seed_len=SEED_LEN,
                                  ival=IVAL, maxgap=MAXGAP, max_aln=max_aln, mine_max=2, nthreads=0, out=io["out"])
 
@@ -307,11 +383,14 @@ def run_ours(args, rank, world, local_rank):
         o, cnt = run(ctx, solo)
         for k in ("sweep", "seed", "extend", "locate", "dp", "dp_fill", "dp_gather", "dp_backtrace", "glue", "total"):
             kms[k] = kms.get(k, 0.0) + cnt["ms_" + k]
+        if PAIRED:
+            for k in ("frame", "dp", "dp_fill", "dp_gather", "dp_backtrace", "total"):
+                kms["mate_" + k] = kms.get("mate_" + k, 0.0) + cnt["mate_ms_" + k]
     # sanity: the located diagonal of a read is its simulated origin (indel shifts aside)
     nj = o["njobs"]
     ok = np.abs(o["job_start"][:nj] - pos[o["job_read"][:nj]]) <= 64
     frac_true = float(ok.mean()) if nj else 0.0
-    cnt = {k: (int(v) if not k.startswith(("ms_", "wall_")) else float(v)) for k, v in cnt.items()}
+    cnt = {k: (int(v) if not k.startswith(("ms_", "wall_", "mate_ms_")) else float(v)) for k, v in cnt.items()}
     probe_ix = ctx.gather_probe("fw", 1 << 27)                # random sides of the index itself (L2 helps when it fits)
     probe = ctx.probe_random_gather(8 << 30, 1 << 27)         # random 64-B gathers over 8 GiB: the HBM random-access ceiling
     dpx_peak = ctx.probe_dpx()                                # G thread-instr/s of packed s16x2 DPX
@@ -364,11 +443,30 @@ def run_ours(args, rank, world, local_rank):
             "walked_cells_per_job": cnt["bt_cells"] / max(cnt["dp_jobs"], 1), "candidates_per_job": cnt["dp_cands"] / max(cnt["dp_jobs"], 1)}),
         rl("k_dp_gather_e2e", 1.0 * cnt["dp_jobs"] * (RDLEN + 4 * MAXGAP), kms["dp_gather"] / K),
     ]
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
-    # command at its default workload (profiles/r1z_summary.md); other workloads: not captured
-    if args.batch == 262144 and args.genome_mbp == 1024:
-        traffic = {"k_exact_sweep": 0.409e9, "k_seed_exact": 0.710e9, "k_extend": 0.526e9, "k_locate": 0.159e9,
-                   "k_dp_fill": 10.582e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 9.806e9}
+    if PAIRED:          # the same DP kernels on the mate windows (second launch of each per step)
+        mfill = kms["mate_dp_fill"] / K
+        mdpx = 2.5 * cnt["mate_cells"] / (mfill / 1e3) / 1e9 if mfill > 0 else 0.0
+        rls += [
+            rl("k_dp_fill[mate windows]", 3.0 * cnt["mate_cells"], mfill,
+               {"gcups": cnt["mate_cells"] / (mfill / 1e3) / 1e9 if mfill > 0 else 0.0, "dpx_ginstr_per_s": mdpx,
+                "dpx_peak_ginstr_per_s": dpx_peak, "dpx_frac": mdpx / dpx_peak if dpx_peak else 0.0}),
+            rl("k_dp_backtrace[mate windows]", 3.0 * cnt["mate_bt_cells"] + 12.0 * cnt["mate_dp_cands"], kms["mate_dp_backtrace"] / K,
+               {"walked_cells_per_job": cnt["mate_bt_cells"] / max(cnt["mate_jobs"], 1),
+                "candidates_per_job": cnt["mate_dp_cands"] / max(cnt["mate_jobs"], 1)}),
+            rl("k_dp_gather_e2e[mate windows]", 4.0 * cnt["mate_cells"] / RDLEN, kms["mate_dp_gather"] / K),
+        ]
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures of this
+    # command at its default batch and genome (profiles/r1p_summary.md for --mode pairs, profiles/r1z_summary.md for
+    # --mode e2e); other workloads: not captured
+    if args.batch == 262144 and args.genome_mbp == 1024 and not LOCAL:
+        if PAIRED:
+            traffic = {"k_exact_sweep": 0.413e9, "k_seed_exact": 0.712e9, "k_extend": 0.532e9, "k_locate": 0.162e9,
+                       "k_dp_fill": 10.627e9, "k_dp_gather_e2e": 0.115e9, "k_dp_backtrace": 9.885e9,
+                       "k_dp_fill[mate windows]": 33.918e9, "k_dp_gather_e2e[mate windows]": 0.304e9,
+                       "k_dp_backtrace[mate windows]": 10.411e9}
+        else:
+            traffic = {"k_exact_sweep": 0.409e9, "k_seed_exact": 0.710e9, "k_extend": 0.526e9, "k_locate": 0.159e9,
+                       "k_dp_fill": 10.582e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 9.806e9}
         for r_ in rls:
             r_["traffic"] = traffic.get(r_["kernel"])
     dominant = max(rls, key=lambda r: r["ms"])
@@ -420,14 +518,17 @@ def main():
     ap.add_argument("--batch", type=int, default=262144)
     ap.add_argument("--contexts", type=int, default=1, help="worker contexts (streams) per GPU; more than one did not pay (DESIGN.md 5)")
     ap.add_argument("--genome-mbp", type=int, default=1024)
-    ap.add_argument("--mode", default="e2e", choices=["e2e", "local"],
-                    help="local: 250 bp reads, --sensitive-local seeds (-L 20, S,1,0.75), u8 local DP with i16 re-runs (config C4); our arm only")
+    ap.add_argument("--mode", default="pairs", choices=["pairs", "e2e", "local"],
+                    help="pairs: 2x150 --fr pairs, anchor pass + mate-window pass (the metric's own shape); e2e: unpaired 150 bp reads, anchor pass only; local: 250 bp reads, --sensitive-local seeds (-L 20, S,1,0.75), u8 local DP with i16 re-runs (config C4); our arm only")
     ap.add_argument("--cpu-sample", type=int, default=40000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()
+    global RDLEN, SEED_LEN, IVAL, LOCAL, PAIRED
+    if args.mode == "pairs":
+        PAIRED = True
+        args.batch -= args.batch % 2
     if args.mode == "local":
-        global RDLEN, SEED_LEN, IVAL, LOCAL
         RDLEN, SEED_LEN, IVAL, LOCAL = 250, 20, (1.0, 0.75), True
         args.no_cpu_baseline = True
         if args.impl == "reference":

@@ -11,10 +11,11 @@ def random_genome(rng, n):
     return rng.integers(0, 4, size=n, dtype=np.uint8)
 
 
-def simulate_reads(rng, genome, nreads, rdlen):
-    """Return (reads[n, rdlen] codes, quals[n, rdlen] phred+33, pos[n], fw[n])."""
+def simulate_reads(rng, genome, nreads, rdlen, pos=None):
+    """Return (reads[n, rdlen] codes, quals[n, rdlen] phred+33, pos[n], fw[n]).  `pos`: given origins."""
     G = len(genome)
-    pos = rng.integers(0, G - rdlen - 64, size=nreads)
+    if pos is None:
+        pos = rng.integers(0, G - rdlen - 64, size=nreads)
     idx = pos[:, None] + np.arange(rdlen + 48)[None, :]
     frag = genome[idx]                                   # true fragment with slack for deletions
     reads = frag[:, :rdlen].copy()
@@ -43,6 +44,32 @@ def simulate_reads(rng, genome, nreads, rdlen):
     reads[err] = alphabet[rng.integers(0, 10, size=int(err.sum()))]
     fw = rng.random(nreads) < 0.5
     return reads, (q + 33).astype(np.uint8), pos, fw
+
+
+def simulate_pairs(rng, genome, npairs, rdlen, frag_av=250.0, frag_sd=45.0):
+    """simulate.pl --fr pairs (:191-207): fragment length N(frag_av, frag_sd) raised to at least 2 * rdlen, fragment
+    strand by coin flip, mate 1 = the fragment's first rdlen bases, mate 2 = the reverse complement of its last rdlen.
+    Returns (reads[2n, rdlen] with mate 1 / mate 2 interleaved, quals, pos[2n] = leftmost genome offset of each mate,
+    fw[2n] = mate given in genome orientation)."""
+    G = len(genome)
+    flen = np.maximum(rng.normal(frag_av, frag_sd, size=npairs).astype(np.int64), 2 * rdlen)
+    fs = rng.integers(0, G - flen - rdlen - 64, size=npairs)
+    posl, posr = fs, fs + flen - rdlen
+    rl, ql, _, _ = simulate_reads(rng, genome, npairs, rdlen, pos=posl)
+    rr, qr, _, _ = simulate_reads(rng, genome, npairs, rdlen, pos=posr)
+    comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
+    frag_fw = rng.random(npairs) < 0.5
+    reads = np.empty((2 * npairs, rdlen), dtype=np.uint8)
+    quals = np.empty((2 * npairs, rdlen), dtype=np.uint8)
+    pos = np.empty(2 * npairs, dtype=np.int64)
+    fw = np.empty(2 * npairs, dtype=bool)
+    rc_r, rcq_r = comp[rr[:, ::-1]], qr[:, ::-1]
+    # Watson fragment: mate 1 = left piece as is, mate 2 = rc(right piece); Crick fragment: mate 1 = rc(right piece), mate 2 = left piece
+    reads[0::2] = np.where(frag_fw[:, None], rl, rc_r); quals[0::2] = np.where(frag_fw[:, None], ql, rcq_r)
+    reads[1::2] = np.where(frag_fw[:, None], rc_r, rl); quals[1::2] = np.where(frag_fw[:, None], rcq_r, ql)
+    pos[0::2] = np.where(frag_fw, posl, posr); pos[1::2] = np.where(frag_fw, posr, posl)
+    fw[0::2] = frag_fw; fw[1::2] = ~frag_fw
+    return reads, quals, pos, fw
 
 
 def dp_extend_batch(rng, genome, nreads, rdlen, sc, maxgap=15):

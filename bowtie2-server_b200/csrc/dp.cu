@@ -523,13 +523,13 @@ k_dp_sort(uint32_t job0, const bt2gpu_dp_result *__restrict__ res, uint64_t *__r
 // End-to-end windows of at most E2E_CAP columns: count, place, sort and convert in one launch (one
 // warp per job).  The candidates are the last-row cells with H >= minsc (at most ncol of them), so
 // a warp sorts them in its slice of shared memory and takes its slot in the pool with one atomic.
-static constexpr int E2E_CAP = 1024;   // mate windows of -X 500 are ~700 columns wide
-__global__ void __launch_bounds__(128)
+static constexpr int E2E_CAP = 1024;   // mate windows of -X 500 are ~700 columns wide; seed-extension windows use the 512 instance
+template<int CAP> __global__ void __launch_bounds__(128)
 k_dp_gather_e2e(const bt2gpu_dp_job *__restrict__ jobs, const DpAux *__restrict__ aux, uint32_t job0, uint32_t njobs,
                 const uint32_t *__restrict__ bound, bt2gpu_dp_result *__restrict__ res, bt2gpu_dp_cand *__restrict__ cands,
                 unsigned long long *__restrict__ total, unsigned long long cap, int *__restrict__ errflag)
 {
-	__shared__ uint64_t s_keys[4][E2E_CAP];
+	__shared__ uint64_t s_keys[4][CAP];
 	const unsigned FULL = 0xffffffffu;
 	const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
 	const uint32_t ji = job0 + blockIdx.x * (blockDim.x >> 5) + wib;
@@ -1360,9 +1360,14 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 		}
 		if(timed) BT2_CUDA(cudaEventRecord(d->ev[1], s));
 		if((phases & 2) && !local && c.maxcol <= E2E_CAP) {
-			k_dp_gather_e2e<<<(c.njobs + 3) / 4, 128, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), d->aux.as<DpAux>(), c.job0, c.njobs,
-				d->bound.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
-				(unsigned long long)d->cand_cap, errflag);
+			if(c.maxcol <= 512)
+				k_dp_gather_e2e<512><<<(c.njobs + 3) / 4, 128, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), d->aux.as<DpAux>(), c.job0, c.njobs,
+					d->bound.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
+					(unsigned long long)d->cand_cap, errflag);
+			else
+				k_dp_gather_e2e<E2E_CAP><<<(c.njobs + 3) / 4, 128, 0, s>>>(d->jobs.as<bt2gpu_dp_job>(), d->aux.as<DpAux>(), c.job0, c.njobs,
+					d->bound.as<uint32_t>(), d->res.as<bt2gpu_dp_result>(), d->cands.as<bt2gpu_dp_cand>(), scal,
+					(unsigned long long)d->cand_cap, errflag);
 			ctx->launches++;
 			BT2_CUDA(cudaGetLastError());
 		} else if(phases & 2) {

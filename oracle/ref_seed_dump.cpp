@@ -61,7 +61,7 @@ static Ebwt* loadEbwt(const string& base, bool fw) {
 }
 
 int main(int argc, char** argv) {
-	string idx, reads;
+	string idx, reads, hitsOut;   // --hits-out FILE (bench mode): one byte per read, 1 = an exact seed of the read hit the index
 	size_t limit = (size_t)-1, maxloc = 16;
 	int seedLen = 22, nthreads = 1, reps = 1;
 	double ivC = 1.0, ivL = 1.15;     // default end-to-end interval S,1,1.15 (--sensitive)
@@ -78,6 +78,7 @@ int main(int argc, char** argv) {
 		else if(a == "--bench") bench = true;
 		else if(a == "--threads") nthreads = atoi(argv[++i]);
 		else if(a == "--reps") reps = atoi(argv[++i]);
+		else if(a == "--hits-out") hitsOut = argv[++i];
 		else { cerr << "unknown arg " << a << endl; return 2; }
 	}
 	Ebwt* ebwtFw = loadEbwt(idx, true);
@@ -100,6 +101,7 @@ int main(int argc, char** argv) {
 		atomic<size_t> next(0);
 		atomic<uint64_t> totOps(0), totSeeds(0), totLoc(0);
 		const size_t total = fq.size() * (size_t)reps;
+		vector<uint8_t> hitflag(fq.size(), 0);
 		auto t0 = chrono::steady_clock::now();
 		vector<thread> th;
 		for(int t = 0; t < nthreads; t++) th.emplace_back([&]() {
@@ -146,7 +148,7 @@ int main(int argc, char** argv) {
 								if(bestSz == 0 || sz < bestSz) { bestSz = sz; bestTop = satups[k].topf; }
 							}
 						}
-						if(bestSz > 0) { sink += ebwtFw->getOffset(bestTop); nloc++; }
+						if(bestSz > 0) { sink += ebwtFw->getOffset(bestTop); nloc++; hitflag[q % fq.size()] = 1; }
 					}
 				}
 			}
@@ -154,6 +156,7 @@ int main(int argc, char** argv) {
 		});
 		for(auto& t : th) t.join();
 		double sec = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
+		if(!hitsOut.empty()) { ofstream ho(hitsOut.c_str(), ios::binary); ho.write((const char*)hitflag.data(), (streamsize)hitflag.size()); }
 		printf("{\"reads\": %zu, \"seconds\": %.6f, \"reads_per_s\": %.1f, \"lf_steps\": %llu, \"lf_steps_per_s\": %.1f, \"seeds\": %llu, \"located\": %llu, \"threads\": %d}\n",
 		       total, sec, total / sec, (unsigned long long)totOps.load(), totOps.load() / sec,
 		       (unsigned long long)totSeeds.load(), (unsigned long long)totLoc.load(), nthreads);

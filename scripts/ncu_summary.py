@@ -44,7 +44,7 @@ for r in rr[2:]:
     name = r[hh.index("Kernel Name")].split("(")[0]
     seen[name] += 1
     if seen[name] > 1:
-        continue
+        name += " [launch %d]" % seen[name]
     md.append("| %s | " % name + " | ".join("%s %s" % (r[i][:12], units[i]) for i, _ in idx) + " |")
 open(out, "w").write("\n".join(md) + "\n")
 print("\n".join(md))
