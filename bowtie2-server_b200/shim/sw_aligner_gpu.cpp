@@ -1,0 +1,188 @@
+// sw_aligner_gpu.cpp — reference-side shim: SwAligner::align / SwAligner::nextAlignment bodies that run the
+// dynamic programming on the GPU through the C ABI (include/bt2gpu.h) instead of aligner_swsse_*.cpp.
+//
+// Compiled against the reference's own headers (-I<reference tree>) and linked into the unmodified reference in
+// place of the two member functions it replaces (aligner_sw.cpp:500-729 align, :737-1146 nextAlignment); every
+// other member of SwAligner (initRead, initRef, ungappedAlign, done(), reset(), the metrics) is the reference's.
+// SwDriver, AlnSinkWrap, the SAM writer and the client/server front end are untouched, so the SAM the binary
+// prints is the parity statement: it must be byte-identical to the stock reference's.
+//
+// Per call the shim sends ONE problem (the batch-of-one binding; the batched runtime is bt2gpu_hotpath_*).  The
+// GPU runs initRef's window + fill + gather + the whole nextAlignment loop at once; nextAlignment() then hands
+// the alignments out one per call and replays the reference's RNG protocol (one rnd.nextU32() re-seed per
+// attempted backtrace: aligner_sw.cpp:794-795,877-879,974,1062) so the caller's RandomSource is in the same
+// state as after the reference's call.
+//
+// No CPU fallback: anything the CUDA path does not cover (checkpointed reads >= cperMinlen_, ABI errors) throws,
+// which bowtie() reports as a fatal error (bt2_search.cpp:5604-5611).
+#include <cstdio>
+#include <cstdlib>
+#include <atomic>
+#include <fcntl.h>
+#include <unistd.h>
+#include <unordered_map>
+#include <vector>
+#include <limits>
+#include "aligner_sw.h"
+#include "bt2gpu.h"
+
+namespace {
+
+struct ShimState {               // what align() got back for one SwAligner instance
+	bt2gpu_dp_result res;
+	std::vector<bt2gpu_dp_aln> alns;
+	std::vector<bt2gpu_edit> edits;
+	uint32_t next = 0;           // next alignment to hand out
+	TAlScore minsc = 0;
+};
+
+struct ShimThread {              // one bt2gpu_ctx per worker thread (bt2_search.cpp:3128-3130)
+	bt2gpu_ctx *ctx = NULL;
+	const Scoring *sc = NULL;
+	std::unordered_map<const SwAligner*, ShimState> st;
+	std::vector<uint8_t> seq, qual, win;
+	std::vector<bt2gpu_dp_cand> cands;
+	uint64_t launches = 0;
+	~ShimThread() { if(ctx != NULL) bt2gpu_ctx_destroy(ctx); }
+};
+thread_local ShimThread g_t;
+
+// Evidence counters (the worker threads are detached and the server is stopped by a signal, so nothing can be
+// printed at exit): with BT2GPU_SHIM_STATS=<file> the totals are rewritten in place after every align() call.
+std::atomic<uint64_t> g_calls(0), g_alns(0), g_launches(0);
+void noteCall(ShimThread& t) {
+	static const char *path = getenv("BT2GPU_SHIM_STATS");
+	static int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
+	uint64_t l = bt2gpu_ctx_launches(t.ctx);
+	g_launches += l - t.launches; t.launches = l;
+	uint64_t c = ++g_calls;
+	if(fd >= 0) {
+		char buf[160];
+		int n = snprintf(buf, sizeof buf, "align_calls_on_gpu %20llu alignments %20llu kernel_launches %20llu\n",
+		                 (unsigned long long)c, (unsigned long long)g_alns.load(), (unsigned long long)g_launches.load());
+		if(pwrite(fd, buf, (size_t)n, 0) < 0) { /* evidence only */ }
+	}
+}
+
+void fail(const char *what) {
+	fprintf(stderr, "bt2gpu shim: %s: %s\n", what, bt2gpu_last_error());
+	throw 1;                     // the reference's fatal-error convention
+}
+
+void bindScoring(const Scoring& sc) {
+	if(g_t.ctx == NULL) {
+		const char *dev = getenv("BT2GPU_DEVICE");
+		if(bt2gpu_ctx_create(dev ? atoi(dev) : 0, &g_t.ctx)) fail("bt2gpu_ctx_create");
+	}
+	if(g_t.sc == &sc) return;
+	bt2gpu_scoring s;
+	for(int q = 0; q < 256; q++) { s.mmpens[q] = sc.mmpens[q]; s.npens[q] = sc.npens[q]; }
+	s.match_bonus = (int32_t)sc.match(30);
+	s.rd_gap_open = sc.readGapOpen();  s.rd_gap_ext = sc.readGapExtend();
+	s.rf_gap_open = sc.refGapOpen();   s.rf_gap_ext = sc.refGapExtend();
+	s.gapbar = sc.gapbar;              s.monotone = sc.monotone ? 1 : 0;
+	if(bt2gpu_scoring_set(g_t.ctx, &s)) fail("bt2gpu_scoring_set");
+	g_t.sc = &sc;
+}
+
+} // namespace
+
+/**
+ * SwAligner::align (aligner_sw.cpp:500-729): same contract — `best` = best score in the matrix (MIN_I64 when the
+ * fill found nothing valid), returns true iff there is at least one backtrace candidate; leaves btncand_ sorted,
+ * sse8succ_/sse16succ_ and cural_ as the reference does.
+ */
+bool SwAligner::align(TAlScore& best) {
+	assert(initedRef() && initedRead());
+	state_ = STATE_ALIGNED;
+	btncand_.clear();
+	btncanddone_.clear();
+	btncanddoneSucc_ = btncanddoneFail_ = 0;
+	best = std::numeric_limits<TAlScore>::min();
+	sse8succ_ = sse16succ_ = false;
+	cural_ = 0;
+	const size_t rdlen = rdf_ - rdi_;
+	const size_t ncol = (size_t)(rff_ - rfi_);
+	if(rdlen >= cperMinlen_) {
+		fprintf(stderr, "bt2gpu shim: checkpointed DP (read of %zu rows >= %zu) is not on the CUDA path\n", rdlen, cperMinlen_);
+		throw 1;
+	}
+	bindScoring(*sc_);
+	ShimThread& t = g_t;
+	ShimState& st = t.st[this];
+	// the oriented read, rows rdi_..rdf_-1 (bytes 0..4 + Phred+33), and the window incl. the extra column of initRef
+	t.seq.resize(rdlen); t.qual.resize(rdlen); t.win.resize(ncol + 1);
+	for(size_t i = 0; i < rdlen; i++) { t.seq[i] = (uint8_t)(*rd_)[rdi_ + i]; t.qual[i] = (uint8_t)(*qu_)[rdi_ + i]; }
+	for(size_t i = 0; i <= ncol; i++) t.win[i] = (uint8_t)rf_[rfi_ + i];
+	bt2gpu_dp_job job;
+	job.rd_off = 0; job.rd_len = (uint32_t)rdlen; job.rf_off = 0; job.ncol = (uint32_t)ncol;
+	job.minsc = (int32_t)minsc_; job.nceil = nceil_;
+	job.refl = rect_->refl; job.triml = (uint32_t)rect_->triml;
+	job.corel = (uint32_t)rect_->corel; job.corer = (uint32_t)rect_->corer;
+	job.fw = fw_ ? 1 : 0; job.enable8 = (enable8_ && !readSse16_) ? 1 : 0;
+	job.reserved[0] = job.reserved[1] = 0;
+	const uint32_t maxAln = 1024;
+	size_t candCap = rdlen * ncol + 64, editCap = (size_t)1 << 18;
+	if(sc_->monotone) candCap = ncol + 64;
+	t.cands.resize(candCap); st.alns.resize(maxAln); st.edits.resize(editCap);
+	if(bt2gpu_dp_align_batch(t.ctx, t.seq.data(), t.qual.data(), rdlen, t.win.data(), ncol + 1, &job, 1, maxAln,
+	                         &st.res, t.cands.data(), candCap, st.alns.data(), st.edits.data(), editCap))
+		fail("bt2gpu_dp_align_batch");
+	if(st.res.naln >= maxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", maxAln); throw 1; }
+	noteCall(t);
+	st.next = 0; st.minsc = minsc_;
+	sse8succ_ = st.res.width == 8; sse16succ_ = st.res.width == 16;
+	best = st.res.best;                      // INT64_MIN == MIN_I64
+	if(best == MIN_I64 || best < minsc_) {   // aligner_sw.cpp:681-686
+		if(dpLog_ != NULL) (*dpLog_) << ",0,0";
+		return false;
+	}
+	if(dpLog_ != NULL) (*dpLog_) << ",1," << best;
+	for(uint32_t i = 0; i < st.res.ncand; i++) {
+		const bt2gpu_dp_cand& c = t.cands[st.res.cand_off + i];
+		btncand_.push_back(DpBtCandidate(c.row, c.col, c.score));
+	}
+	return st.res.aligned != 0;
+}
+
+/**
+ * SwAligner::nextAlignment (aligner_sw.cpp:737-1146): hands out the alignments of the candidate loop the GPU
+ * already ran, in order, leaving `res`, cural_ and `rnd` exactly as the reference's call would.
+ */
+bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) {
+	assert(initedRead() && initedRef());
+	if(done()) { res.reset(); return false; }
+	ShimState& st = g_t.st[this];
+	if(minsc != st.minsc) { fprintf(stderr, "bt2gpu shim: nextAlignment minsc differs from initRef's\n"); throw 1; }
+	const bt2gpu_dp_aln *a = (st.next < st.res.naln) ? &st.alns[st.res.aln_off + st.next] : NULL;
+	const uint32_t tries = a ? a->tries : st.res.tail_tries;
+	for(uint32_t k = 0; k < tries; k++) {    // u8: init(reseed) ... init(reseed+1); i16: ... init(reseed)
+		uint32_t reseed = rnd.nextU32() + 1;
+		rnd.init(sse8succ_ ? reseed + 1 : reseed);
+	}
+	res.reset();
+	if(a == NULL) { cural_ = btncand_.size(); return false; }
+	const size_t rdlen = rdf_ - rdi_;
+	const size_t trimBeg = fw_ ? a->trim5 : a->trim3;
+	EList<Edit>& ned = res.alres.ned();
+	for(uint32_t i = 0; i < a->nedits; i++) {
+		const bt2gpu_edit& e = st.edits[a->edit_off + i];
+		ned.push_back(Edit(e.pos, (int)e.chr, (int)e.qchr, (int)e.type));
+	}
+	// back to the backtrace's frame (w.r.t. the upstream end, before AlnRes::setShape's trim shift), so that
+	// setShape and invertEdits below run exactly as in the reference (ee_u8.cpp:1819-1847, aligner_sw.cpp:1137)
+	if(!fw_) Edit::invertPoss(ned, rdlen - a->trim5 - a->trim3, false);
+	for(size_t i = 0; i < ned.size(); i++) ned[i].pos += (uint32_t)trimBeg;
+	AlnScore score;
+	score.score_ = a->score; score.ns_ = a->ns; score.gaps_ = a->gaps;
+	score.edits_ = (int)a->nedits;
+	score.basesAligned_ = (int)(rdlen - a->trim5 - a->trim3 - a->nedits);
+	res.alres.setScore(score);
+	res.alres.setShape(refidx_, a->refoff, reflen_, fw_, rdlen, true, 0, 0, true, a->trim5, a->trim3);
+	res.alres.setRefNs(a->refns);
+	if(!fw_) res.alres.invertEdits();
+	cural_ = a->cural;
+	st.next++;
+	g_alns++;
+	return true;
+}

@@ -1,0 +1,93 @@
+"""Drop-in harness (test infrastructure): runs the unmodified reference server/client pair (oracle/_ref, built from
+/root/reference by oracle/Makefile) and the same reference linked against libbt2gpu.so through the shim in
+bowtie2-server_b200/shim/ (oracle/_ref/bowtie2-align-server-s-gpu) on the same reads, and returns both SAM outputs."""
+import os
+import socket
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "oracle", "_ref")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, os.path.join(ROOT, "bowtie2-server_b200"))
+
+CPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s")
+GPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s-gpu")
+CLIENT = os.path.join(BIN, "bowtie2-align-l")
+
+
+def have_binaries():
+    return all(os.path.exists(p) for p in (CPU_SERVER, GPU_SERVER, CLIENT, os.path.join(BIN, "bowtie2-build-s")))
+
+
+def read_fasta(path):
+    names, seqs, cur = [], [], []
+    for ln in open(path):
+        if ln.startswith(">"):
+            if cur:
+                seqs.append("".join(cur)); cur = []
+            names.append(ln[1:].strip())
+        else:
+            cur.append(ln.strip())
+    seqs.append("".join(cur))
+    return names, seqs
+
+
+def build_index(fasta, base):
+    subprocess.check_call([os.path.join(BIN, "bowtie2-build-s"), "-q", fasta, base], stdout=subprocess.DEVNULL)
+
+
+def write_fastq(path, reads, quals, prefix, lens=None):
+    """reads/quals: [n, L] code / phred+33 arrays; lens: optional per-read length (ragged)."""
+    with open(path, "w") as fh:
+        for i in range(len(reads)):
+            n = reads.shape[1] if lens is None else int(lens[i])
+            fh.write("@%s%d\n%s\n+\n%s\n" % (prefix, i, "".join("ACGTN"[c] for c in reads[i, :n]),
+                                               bytes(quals[i, :n]).decode()))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def run(server, base, server_args, client_args, sam, threads=2, timeout=600, env=None):
+    """One server + one client run; returns (sorted alignment lines, server stderr)."""
+    port = _free_port()
+    errp, outp = sam + ".server.err", sam + ".server.out"
+    e = dict(os.environ)
+    e.update(env or {})
+    with open(errp, "w") as err, open(outp, "w") as out:
+        srv = subprocess.Popen([server, "--server-port", str(port), "-x", base, "-p", str(threads), "--seed", "0"]
+                               + server_args, stdout=out, stderr=err, env=e)
+        try:
+            t0 = time.time()
+            while "ready to process" not in open(errp).read():
+                if srv.poll() is not None or time.time() - t0 > 120:
+                    raise RuntimeError("server did not start: " + open(errp).read()[-2000:])
+                time.sleep(0.05)
+            subprocess.check_call([CLIENT, "--server-port", str(port), "-x", base] + client_args + ["-S", sam],
+                                  stderr=open(sam + ".client.err", "w"), timeout=timeout)
+        finally:
+            srv.terminate()
+            try:
+                srv.wait(timeout=30)
+            except subprocess.TimeoutExpired:
+                srv.kill()
+    lines = sorted(ln for ln in open(sam) if not ln.startswith("@"))
+    return lines, open(errp).read()
+
+
+def lambda_genome():
+    _, seqs = read_fasta(os.path.join(GOLDEN, "lambda.fa"))
+    lut = np.full(256, 4, np.uint8)
+    for i, c in enumerate("ACGT"):
+        lut[ord(c)] = i
+        lut[ord(c.lower())] = i
+    return lut[np.frombuffer(seqs[0].encode(), np.uint8)]

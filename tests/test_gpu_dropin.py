@@ -1,0 +1,88 @@
+"""GPU: the drop-in statement.  The unmodified reference (oracle/_ref/bowtie2-align-server-s + client) and the same
+reference with SwAligner::align / nextAlignment bound to libbt2gpu.so through bowtie2-server_b200/shim/
+(bowtie2-align-server-s-gpu) must print byte-identical SAM records for the same reads, --seed 0.
+SwDriver, AlnSinkWrap and the SAM writer are the reference's in both runs (SURVEY §8b, §8d parity gate)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import dropin as D
+from bt2gpu import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def work(tmp_path_factory):
+    if not D.have_binaries():
+        pytest.fail("oracle/_ref binaries missing: run __graft_entry__.build() where /root/reference is mounted")
+    w = str(tmp_path_factory.mktemp("dropin"))
+    D.build_index(os.path.join(D.GOLDEN, "lambda.fa"), os.path.join(w, "lambda"))
+    return w
+
+
+def _both(work, tag, server_args, client_args):
+    base = os.path.join(work, "lambda")
+    cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"))
+    stats = os.path.join(work, tag + "_shim_stats.txt")
+    gpu, err = D.run(D.GPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_gpu.sam"),
+                     env={"BT2GPU_SHIM_STATS": stats})
+    m = re.match(r"align_calls_on_gpu\s+(\d+) alignments\s+(\d+) kernel_launches\s+(\d+)", open(stats).read())
+    assert m and int(m.group(1)) > 0 and int(m.group(3)) > 0, "the DP did not run on the GPU:\n" + err[-2000:]
+    print("%s: %s SwAligner::align calls on the GPU, %s alignments handed out, %s kernel launches"
+          % (tag, m.group(1), m.group(2), m.group(3)))
+    return cpu, gpu, int(m.group(1))
+
+
+def _check(cpu, gpu):
+    assert len(cpu) == len(gpu)
+    bad = [(a, b) for a, b in zip(cpu, gpu) if a != b]
+    assert not bad, "%d of %d SAM records differ, first:\n%s%s" % (len(bad), len(cpu), bad[0][0], bad[0][1])
+    aligned = sum(1 for ln in cpu if ln.split("\t")[2] != "*")
+    assert aligned > len(cpu) // 4
+
+
+def test_paired_end_to_end_sam_identical(work):
+    """C2 shape: paired-end, end-to-end, default options (u8 path, mate-window DP through osw)."""
+    rng = np.random.default_rng(11)
+    r, q, _, _ = synth.simulate_pairs(rng, D.lambda_genome(), 1500, 100)
+    f1, f2 = os.path.join(work, "pe_1.fq"), os.path.join(work, "pe_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "pair")
+    D.write_fastq(f2, r[1::2], q[1::2], "pair")
+    cpu, gpu, calls = _both(work, "pe", [], ["-1", f1, "-2", f2])
+    assert calls > 500
+    _check(cpu, gpu)
+
+
+def test_unpaired_ragged_sensitive_sam_identical(work):
+    """C1 shape: unpaired reads of 30..700 bp, --sensitive (u8 and, for minsc < -254, the i16 end-to-end path)."""
+    rng = np.random.default_rng(12)
+    L = 700
+    r, q, _, _ = synth.simulate_reads(rng, D.lambda_genome(), 600, L)
+    lens = rng.integers(30, L + 1, size=600)
+    f = os.path.join(work, "long.fq")
+    D.write_fastq(f, r, q, "long", lens)
+    cpu, gpu, _ = _both(work, "long", ["--sensitive"], ["-U", f])
+    _check(cpu, gpu)
+
+
+def test_unpaired_local_sam_identical(work):
+    """C4 shape: --local (u8 local DP, i16 re-run on saturation, local candidate gather and SQ filter)."""
+    rng = np.random.default_rng(13)
+    r, q, _, _ = synth.simulate_reads(rng, D.lambda_genome(), 800, 250)
+    f = os.path.join(work, "loc.fq")
+    D.write_fastq(f, r, q, "loc")
+    cpu, gpu, _ = _both(work, "loc", ["--local"], ["-U", f])
+    _check(cpu, gpu)
+
+
+def test_paired_local_sam_identical(work):
+    rng = np.random.default_rng(14)
+    r, q, _, _ = synth.simulate_pairs(rng, D.lambda_genome(), 600, 150)
+    f1, f2 = os.path.join(work, "pl_1.fq"), os.path.join(work, "pl_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "pl")
+    D.write_fastq(f2, r[1::2], q[1::2], "pl")
+    cpu, gpu, _ = _both(work, "pl", ["--local"], ["-1", f1, "-2", f2])
+    _check(cpu, gpu)
