@@ -1,0 +1,114 @@
+// gpu_shim.cpp — see gpu_shim.h.  Our code, compiled against the reference's headers.
+#include <cstdio>
+#include <cstdlib>
+#include <atomic>
+#include <mutex>
+#include <unordered_map>
+#include <fcntl.h>
+#include <unistd.h>
+#include "bt2_idx.h"
+#include "scoring.h"
+#include "read.h"
+#include <vector>
+#include "gpu_shim.h"
+
+namespace bt2shim {
+namespace {
+
+struct Thread {
+	bt2gpu_ctx *ctx = NULL;
+	const Scoring *sc = NULL;
+	uint64_t launches = 0;
+	std::vector<uint8_t> seq, qual;           // the staged read
+	const Read *rd = NULL; uint64_t rdid = 0; int mate = 0;
+	~Thread() { if(ctx != NULL) bt2gpu_ctx_destroy(ctx); }
+};
+thread_local Thread g_t;
+
+std::mutex g_ixmu;
+std::unordered_map<const Ebwt*, bt2gpu_index*> g_ix;
+std::atomic<uint64_t> g_cnt[C_NCOUNTERS], g_launches(0);
+
+int device() { const char *d = getenv("BT2GPU_DEVICE"); return d ? atoi(d) : 0; }
+
+} // namespace
+
+void fail(const char *what) {
+	fprintf(stderr, "bt2gpu shim: %s: %s\n", what, bt2gpu_last_error());
+	throw 1;
+}
+
+bt2gpu_ctx *ctx() {
+	if(g_t.ctx == NULL && bt2gpu_ctx_create(device(), &g_t.ctx)) fail("bt2gpu_ctx_create");
+	return g_t.ctx;
+}
+
+void bindScoring(const Scoring& sc) {
+	bt2gpu_ctx *c = ctx();
+	if(g_t.sc == &sc) return;
+	bt2gpu_scoring s;
+	for(int q = 0; q < 256; q++) { s.mmpens[q] = sc.mmpens[q]; s.npens[q] = sc.npens[q]; }
+	s.match_bonus = (int32_t)sc.match(30);
+	s.rd_gap_open = sc.readGapOpen();  s.rd_gap_ext = sc.readGapExtend();
+	s.rf_gap_open = sc.refGapOpen();   s.rf_gap_ext = sc.refGapExtend();
+	s.gapbar = sc.gapbar;              s.monotone = sc.monotone ? 1 : 0;
+	if(bt2gpu_scoring_set(c, &s)) fail("bt2gpu_scoring_set");
+	g_t.sc = &sc;
+}
+
+// Read::patFw (codes 0..4) + Read::qual (Phred+33) -> the context's read pool.  The reference hands the same Read to
+// exactSweep, oneMmSearch, searchAllSeeds and every SwDriver::extend call; it is staged once.
+void stageRead(const Read& rd) {
+	Thread& t = g_t;
+	bt2gpu_ctx *c = ctx();
+	const size_t len = rd.length();
+	if(t.rd == &rd && t.rdid == (uint64_t)rd.rdid && t.mate == rd.mate && t.seq.size() == len) {
+		bool same = true;
+		for(size_t i = 0; i < len && same; i++) same = t.seq[i] == (uint8_t)rd.patFw[i] && t.qual[i] == (uint8_t)rd.qual[i];
+		if(same) return;
+	}
+	t.seq.resize(len); t.qual.resize(len);
+	for(size_t i = 0; i < len; i++) { t.seq[i] = (uint8_t)rd.patFw[i]; t.qual[i] = (uint8_t)rd.qual[i]; }
+	bt2gpu_read r; r.rd_off = 0; r.rd_len = (uint32_t)len;
+	if(bt2gpu_reads_stage(c, t.seq.data(), t.qual.data(), len, &r, 1)) fail("bt2gpu_reads_stage");
+	t.rd = &rd; t.rdid = (uint64_t)rd.rdid; t.mate = rd.mate;
+}
+
+// Ebwt as loaded by Ebwt::readIntoMemory (bt2_io.cpp:131-614) -> bt2gpu_index_desc, field for field
+bt2gpu_index *index(const Ebwt& e) {
+	std::lock_guard<std::mutex> lk(g_ixmu);
+	auto it = g_ix.find(&e);
+	if(it != g_ix.end()) return it->second;
+	bt2gpu_index_desc d;
+	d.ebwt = e.ebwt();             d.ebwt_bytes = e.eh().ebwtTotLen();
+	d.offs = e.offs();             d.n_offs = e.offs() ? e.eh().offsLen() : 0;
+	d.ftab = e.ftab();             d.eftab = e.eftab();
+	for(int i = 0; i < 5; i++) d.fchr[i] = e.fchr()[i];
+	d.zoff = e.zOff();             d.len = e.eh().len();
+	d.off_rate = e.eh().offRate(); d.ftab_chars = e.eh().ftabChars();
+	d.is_fw = e.fw() ? 1 : 0;
+	bt2gpu_index *h = NULL;
+	if(bt2gpu_index_create(device(), &d, &h)) fail("bt2gpu_index_create");
+	g_ix[&e] = h;
+	return h;
+}
+
+void note(Counter c, uint64_t n) {
+	static const char *path = getenv("BT2GPU_SHIM_STATS");
+	static int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
+	g_cnt[c] += n;
+	if(g_t.ctx != NULL) {
+		uint64_t l = bt2gpu_ctx_launches(g_t.ctx);
+		g_launches += l - g_t.launches; g_t.launches = l;
+	}
+	if(fd < 0) return;
+	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
+	                                          "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu" };
+	char buf[512]; int n2 = 0;
+	for(int i = 0; i < C_NCOUNTERS; i++)
+		n2 += snprintf(buf + n2, sizeof buf - n2, "%s %12llu ", names[i], (unsigned long long)g_cnt[i].load());
+	n2 += snprintf(buf + n2, sizeof buf - n2, "kernel_launches %12llu\n", (unsigned long long)g_launches.load());
+	if(pwrite(fd, buf, (size_t)n2, 0) < 0) { /* evidence only */ }
+}
+
+} // namespace bt2shim

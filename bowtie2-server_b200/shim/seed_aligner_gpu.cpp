@@ -1,0 +1,180 @@
+// seed_aligner_gpu.cpp — reference-side shim: SeedAligner::exactSweep / oneMmSearch / searchAllSeeds bodies that
+// run the FM-index searches on the GPU through the C ABI (include/bt2gpu.h) instead of Ebwt::mapLF*/mapBiLFEx.
+//
+// Compiled against the reference's own headers and linked into the unmodified reference in place of the three
+// member functions it replaces (aligner_seed.cpp:854-968, :973-1323, :597-718).  instantiateSeeds, the
+// AlignmentCache protocol, SeedResults and every caller are the reference's.  Batch-of-one binding: each call
+// stages its one read and sends that read's searches; the batched runtime is bt2gpu_hotpath_*.
+// No CPU fallback: seed policies the CUDA path does not cover (-N 1/2 multi-zone seeds) throw.
+#include <cstdio>
+#include <vector>
+#include "aligner_seed.h"
+#include "gpu_shim.h"
+
+namespace {
+
+struct SeedThread {
+	std::vector<bt2gpu_seed_job> jobs;
+	std::vector<bt2gpu_seed_hit> out;
+	std::vector<bt2gpu_ee_hit> ee;
+};
+thread_local SeedThread g_s;
+
+} // namespace
+
+/**
+ * SeedAligner::exactSweep (aligner_seed.cpp:854-968): same contract — returns the number of BW elements of the exact
+ * end-to-end hits, sets mineFw/mineRc as exactSweepStep / the final loop do, installs the exact hits in `hits`.
+ */
+size_t SeedAligner::exactSweep(
+	const Ebwt& ebwt, const Read& read, const Scoring& sc, bool nofw, bool norc, size_t mineMax,
+	size_t& mineFw, size_t& mineRc, bool repex, SeedResults& hits, SeedSearchMetrics& met)
+{
+	bt2shim::bindScoring(sc);
+	bt2shim::stageRead(read);
+	bt2gpu_sweep_result r;
+	if(bt2gpu_exact_sweep_batch(bt2shim::ctx(), bt2shim::index(ebwt), nofw ? 1 : 0, norc ? 1 : 0, (uint32_t)mineMax, &r))
+		bt2shim::fail("bt2gpu_exact_sweep_batch");
+	bt2shim::note(bt2shim::C_SWEEP, 1);
+	bwops_ += r.bwops;
+	const size_t len = read.length();
+	size_t nelt = 0;
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		if(fw ? nofw : norc) continue;
+		// stopped at the bound (exactSweepStep :837-841) or ran to the end of the read (:944): either way the
+		// reference leaves nedit in mineFw/mineRc
+		if(r.done[fwi]) { (fw ? mineFw : mineRc) = r.nedit[fwi]; continue; }
+		(fw ? mineFw : mineRc) = r.nedit[fwi];
+		if(r.nedit[fwi] == 0 && r.bot[fwi] > r.top[fwi]) {
+			if(repex) {
+				int64_t score = len * sc.match();
+				if(fw) hits.addExactEeFw(r.top[fwi], r.bot[fwi], NULL, NULL, fw, score);
+				else   hits.addExactEeRc(r.top[fwi], r.bot[fwi], NULL, NULL, fw, score);
+			}
+			nelt += (r.bot[fwi] - r.top[fwi]);
+		}
+	}
+	return nelt;
+}
+
+/**
+ * SeedAligner::oneMmSearch (aligner_seed.cpp:973-1323): end-to-end alignments with exactly one mismatch (and, with
+ * repex, the exact ones), installed in `hits` in the reference's order of add1mmEe / addExactEe* calls.
+ * The return value ("found something", ignored by the reference's only caller, bt2_search.cpp:3654) is true iff
+ * a hit was installed.
+ */
+bool SeedAligner::oneMmSearch(
+	const Ebwt* ebwtFw, const Ebwt* ebwtBw, const Read& read, const Scoring& sc, int64_t minsc, bool nofw, bool norc,
+	bool local, bool repex, bool rep1mm, SeedResults& hits, SeedSearchMetrics& met)
+{
+	const size_t len = read.length();
+	size_t ns = read.ns();
+	if(ns > 1) return false;                 // :990-997
+	else if(ns == 1 && !rep1mm) return false;
+	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: oneMmSearch needs the mirror index\n"); throw 1; }
+	bt2shim::bindScoring(sc);
+	bt2shim::stageRead(read);
+	bt2gpu_onemm_job job;
+	job.minsc = (int32_t)minsc; job.nceil = sc.nCeil.f<int>((double)len);
+	job.nofw = nofw ? 1 : 0; job.norc = norc ? 1 : 0; job.pad[0] = job.pad[1] = 0;
+	bt2gpu_onemm_result res;
+	SeedThread& t = g_s;
+	size_t cap = 8 * len + 64, n = 0;
+	t.ee.resize(cap);
+	if(bt2gpu_onemm_batch(bt2shim::ctx(), bt2shim::index(*ebwtFw), bt2shim::index(*ebwtBw), &job, local ? 1 : 0,
+	                      repex ? 1 : 0, rep1mm ? 1 : 0, &res, t.ee.data(), cap, &n))
+		bt2shim::fail("bt2gpu_onemm_batch");
+	bt2shim::note(bt2shim::C_ONEMM, 1);
+	bwops_ += res.bwops;
+	for(uint32_t k = 0; k < res.nhits; k++) {
+		const bt2gpu_ee_hit& h = t.ee[res.hit_off + k];
+		const bool fw = h.fw != 0;
+		if(h.pos == 0xffff) {
+			int64_t score = len * sc.match();
+			if(fw) hits.addExactEeFw(h.top, h.bot, NULL, NULL, fw, score);
+			else   hits.addExactEeRc(h.top, h.bot, NULL, NULL, fw, score);
+		} else {
+			Edit e((uint32_t)h.pos, (int)h.chr, (int)h.qchr, EDIT_TYPE_MM, true);   // = Edit(off5p, j, rdc, MM, false), :1226
+			hits.add1mmEe(h.top, h.bot, &e, NULL, fw, h.score);
+		}
+	}
+	return res.nhits > 0;
+}
+
+/**
+ * SeedAligner::searchAllSeeds (aligner_seed.cpp:597-718) for exact seeds (-N 0): every instantiated seed of the read
+ * goes to the GPU in one bt2gpu_seed_exact_batch call (ftab jump + mapBiLFEx / mapLF1 steps, startSearchSeedBi :1633,
+ * searchSeedBi :1854); the hits then go through the reference's own cache protocol (reportHit :1575 -> addOnTheFly,
+ * beginAlign / addAllCached / finishAlign, SeedResults::add) in the reference's order: forward seeds by offset,
+ * then reverse-complement seeds by offset.  The searches themselves never touch the cache, so running them all
+ * before the first beginAlign leaves the cache in the same state as the reference's batches of eight.
+ */
+void SeedAligner::searchAllSeeds(
+	const EList<Seed>& seeds, const Ebwt* ebwtFw, const Ebwt* ebwtBw, const Read& read, const Scoring& pens,
+	AlignmentCacheIface& cache, SeedResults& sr, SeedSearchMetrics& met, PerReadMetrics& prm)
+{
+	ebwtFw_ = ebwtFw; ebwtBw_ = ebwtBw; sc_ = &pens; read_ = &read;
+	bwops_ = bwedits_ = 0;
+	uint64_t possearches = 0, seedsearches = 0, ooms = 0;
+	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: searchAllSeeds needs the mirror index\n"); throw 1; }
+	SeedThread& t = g_s;
+	t.jobs.clear();
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		for(size_t i = 0; i < sr.numOffs(); i++) {
+			EList<InstantiatedSeed>& iss = sr.instantiatedSeeds(fw, i);
+			if(iss.empty()) continue;              // seed window with an N, or a cross-read cache hit
+			possearches++;
+			if(iss.size() != 1 || seeds[iss[0].seedtypeidx].type != SEED_TYPE_EXACT) {
+				fprintf(stderr, "bt2gpu shim: only exact seeds (-N 0) are on the CUDA path\n");
+				throw 1;
+			}
+			seedsearches++;
+			bt2gpu_seed_job j;
+			j.read = 0; j.off = (uint16_t)iss[0].seedoff; j.len = (uint8_t)sr.seqs(fw)[i].length(); j.fw = fw ? 1 : 0;
+			t.jobs.push_back(j);
+		}
+	}
+	t.out.resize(t.jobs.size());
+	if(!t.jobs.empty()) {
+		bt2shim::bindScoring(pens);
+		bt2shim::stageRead(read);
+		if(bt2gpu_seed_exact_batch(bt2shim::ctx(), bt2shim::index(*ebwtFw), bt2shim::index(*ebwtBw),
+		                           t.jobs.data(), t.jobs.size(), t.out.data()))
+			bt2shim::fail("bt2gpu_seed_exact_batch");
+		bt2shim::note(bt2shim::C_SEEDS, t.jobs.size());
+	}
+	size_t k = 0;
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		for(size_t i = 0; i < sr.numOffs(); i++) {
+			if(sr.instantiatedSeeds(fw, i).empty()) continue;
+			const bt2gpu_seed_hit& h = t.out[k++];
+			bwops_ += h.bwops;
+			const BTDnaString& seq = sr.seqs(fw)[i];
+			SeedSearchCache srcache(seq, sr.quals(fw)[i]);
+			if(h.botf > h.topf) srcache.addOnTheFly(seq, h.topf, h.botf, h.topb, h.botb);   // reportHit, exact: rf = seq
+			if(srcache.beginAlign(cache) == -1) { ooms++; continue; }
+			if(!srcache.addAllCached()) { ooms++; continue; }
+			srcache.finishAlign();
+			if(srcache.qvValid()) sr.add(srcache.getQv(), cache.current(), (uint32_t)i, fw);
+		}
+	}
+	prm.nSeedRanges = sr.numRanges();
+	prm.nSeedElts = sr.numElts();
+	prm.nSeedRangesFw = sr.numRangesFw();
+	prm.nSeedRangesRc = sr.numRangesRc();
+	prm.nSeedEltsFw = sr.numEltsFw();
+	prm.nSeedEltsRc = sr.numEltsRc();
+	prm.seedMedian = (uint64_t)(sr.medianHitsPerSeed() + 0.5);
+	prm.seedMean = (uint64_t)sr.averageHitsPerSeed();
+	prm.nSdFmops += bwops_;
+	met.seedsearch += seedsearches;
+	met.nrange += sr.numRanges();
+	met.nelt += sr.numElts();
+	met.possearch += possearches;
+	met.ooms += ooms;
+	met.bwops += bwops_;
+	met.bweds += bwedits_;
+}

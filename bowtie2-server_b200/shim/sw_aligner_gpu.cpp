@@ -16,15 +16,11 @@
 // No CPU fallback: anything the CUDA path does not cover (checkpointed reads >= cperMinlen_, ABI errors) throws,
 // which bowtie() reports as a fatal error (bt2_search.cpp:5604-5611).
 #include <cstdio>
-#include <cstdlib>
-#include <atomic>
-#include <fcntl.h>
-#include <unistd.h>
 #include <unordered_map>
 #include <vector>
 #include <limits>
 #include "aligner_sw.h"
-#include "bt2gpu.h"
+#include "gpu_shim.h"
 
 namespace {
 
@@ -36,54 +32,12 @@ struct ShimState {               // what align() got back for one SwAligner inst
 	TAlScore minsc = 0;
 };
 
-struct ShimThread {              // one bt2gpu_ctx per worker thread (bt2_search.cpp:3128-3130)
-	bt2gpu_ctx *ctx = NULL;
-	const Scoring *sc = NULL;
+struct ShimThread {
 	std::unordered_map<const SwAligner*, ShimState> st;
 	std::vector<uint8_t> seq, qual, win;
 	std::vector<bt2gpu_dp_cand> cands;
-	uint64_t launches = 0;
-	~ShimThread() { if(ctx != NULL) bt2gpu_ctx_destroy(ctx); }
 };
 thread_local ShimThread g_t;
-
-// Evidence counters (the worker threads are detached and the server is stopped by a signal, so nothing can be
-// printed at exit): with BT2GPU_SHIM_STATS=<file> the totals are rewritten in place after every align() call.
-std::atomic<uint64_t> g_calls(0), g_alns(0), g_launches(0);
-void noteCall(ShimThread& t) {
-	static const char *path = getenv("BT2GPU_SHIM_STATS");
-	static int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
-	uint64_t l = bt2gpu_ctx_launches(t.ctx);
-	g_launches += l - t.launches; t.launches = l;
-	uint64_t c = ++g_calls;
-	if(fd >= 0) {
-		char buf[160];
-		int n = snprintf(buf, sizeof buf, "align_calls_on_gpu %20llu alignments %20llu kernel_launches %20llu\n",
-		                 (unsigned long long)c, (unsigned long long)g_alns.load(), (unsigned long long)g_launches.load());
-		if(pwrite(fd, buf, (size_t)n, 0) < 0) { /* evidence only */ }
-	}
-}
-
-void fail(const char *what) {
-	fprintf(stderr, "bt2gpu shim: %s: %s\n", what, bt2gpu_last_error());
-	throw 1;                     // the reference's fatal-error convention
-}
-
-void bindScoring(const Scoring& sc) {
-	if(g_t.ctx == NULL) {
-		const char *dev = getenv("BT2GPU_DEVICE");
-		if(bt2gpu_ctx_create(dev ? atoi(dev) : 0, &g_t.ctx)) fail("bt2gpu_ctx_create");
-	}
-	if(g_t.sc == &sc) return;
-	bt2gpu_scoring s;
-	for(int q = 0; q < 256; q++) { s.mmpens[q] = sc.mmpens[q]; s.npens[q] = sc.npens[q]; }
-	s.match_bonus = (int32_t)sc.match(30);
-	s.rd_gap_open = sc.readGapOpen();  s.rd_gap_ext = sc.readGapExtend();
-	s.rf_gap_open = sc.refGapOpen();   s.rf_gap_ext = sc.refGapExtend();
-	s.gapbar = sc.gapbar;              s.monotone = sc.monotone ? 1 : 0;
-	if(bt2gpu_scoring_set(g_t.ctx, &s)) fail("bt2gpu_scoring_set");
-	g_t.sc = &sc;
-}
 
 } // namespace
 
@@ -107,7 +61,7 @@ bool SwAligner::align(TAlScore& best) {
 		fprintf(stderr, "bt2gpu shim: checkpointed DP (read of %zu rows >= %zu) is not on the CUDA path\n", rdlen, cperMinlen_);
 		throw 1;
 	}
-	bindScoring(*sc_);
+	bt2shim::bindScoring(*sc_);
 	ShimThread& t = g_t;
 	ShimState& st = t.st[this];
 	// the oriented read, rows rdi_..rdf_-1 (bytes 0..4 + Phred+33), and the window incl. the extra column of initRef
@@ -125,11 +79,11 @@ bool SwAligner::align(TAlScore& best) {
 	size_t candCap = rdlen * ncol + 64, editCap = (size_t)1 << 18;
 	if(sc_->monotone) candCap = ncol + 64;
 	t.cands.resize(candCap); st.alns.resize(maxAln); st.edits.resize(editCap);
-	if(bt2gpu_dp_align_batch(t.ctx, t.seq.data(), t.qual.data(), rdlen, t.win.data(), ncol + 1, &job, 1, maxAln,
+	if(bt2gpu_dp_align_batch(bt2shim::ctx(), t.seq.data(), t.qual.data(), rdlen, t.win.data(), ncol + 1, &job, 1, maxAln,
 	                         &st.res, t.cands.data(), candCap, st.alns.data(), st.edits.data(), editCap))
-		fail("bt2gpu_dp_align_batch");
+		bt2shim::fail("bt2gpu_dp_align_batch");
 	if(st.res.naln >= maxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", maxAln); throw 1; }
-	noteCall(t);
+	bt2shim::note(bt2shim::C_ALIGN, 1);
 	st.next = 0; st.minsc = minsc_;
 	sse8succ_ = st.res.width == 8; sse16succ_ = st.res.width == 16;
 	best = st.res.best;                      // INT64_MIN == MIN_I64
@@ -183,6 +137,6 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 	if(!fw_) res.alres.invertEdits();
 	cural_ = a->cural;
 	st.next++;
-	g_alns++;
+	bt2shim::note(bt2shim::C_ALN, 1);
 	return true;
 }

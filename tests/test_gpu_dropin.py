@@ -1,5 +1,6 @@
 """GPU: the drop-in statement.  The unmodified reference (oracle/_ref/bowtie2-align-server-s + client) and the same
-reference with SwAligner::align / nextAlignment bound to libbt2gpu.so through bowtie2-server_b200/shim/
+reference with SeedAligner::exactSweep / oneMmSearch / searchAllSeeds and SwAligner::align / nextAlignment bound
+to libbt2gpu.so through bowtie2-server_b200/shim/
 (bowtie2-align-server-s-gpu) must print byte-identical SAM records for the same reads, --seed 0.
 SwDriver, AlnSinkWrap and the SAM writer are the reference's in both runs (SURVEY §8b, §8d parity gate)."""
 import os
@@ -29,11 +30,11 @@ def _both(work, tag, server_args, client_args):
     stats = os.path.join(work, tag + "_shim_stats.txt")
     gpu, err = D.run(D.GPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_gpu.sam"),
                      env={"BT2GPU_SHIM_STATS": stats})
-    m = re.match(r"align_calls_on_gpu\s+(\d+) alignments\s+(\d+) kernel_launches\s+(\d+)", open(stats).read())
-    assert m and int(m.group(1)) > 0 and int(m.group(3)) > 0, "the DP did not run on the GPU:\n" + err[-2000:]
-    print("%s: %s SwAligner::align calls on the GPU, %s alignments handed out, %s kernel launches"
-          % (tag, m.group(1), m.group(2), m.group(3)))
-    return cpu, gpu, int(m.group(1))
+    st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
+    print(tag, st)
+    for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "kernel_launches"):
+        assert st.get(k, 0) > 0, "%s: nothing ran on the GPU:\n%s\n%s" % (k, st, err[-2000:])
+    return cpu, gpu, st["align_calls_on_gpu"]
 
 
 def _check(cpu, gpu):
@@ -86,3 +87,34 @@ def test_paired_local_sam_identical(work):
     D.write_fastq(f2, r[1::2], q[1::2], "pl")
     cpu, gpu, _ = _both(work, "pl", ["--local"], ["-1", f1, "-2", f2])
     _check(cpu, gpu)
+
+
+def test_near_exact_reads_one_mismatch_path(work):
+    """High-quality reads with zero or one substitution, both strands: exactSweep's exact end-to-end hits and the
+    up-front oneMmSearch (bt2_search.cpp:3634-3668) decide these reads; a third carry several substitutions so the
+    seed / extend / DP path runs too."""
+    rng = np.random.default_rng(15)
+    g = D.lambda_genome()
+    n, L = 900, 80
+    pos = rng.integers(0, len(g) - L, size=n)
+    r = g[pos[:, None] + np.arange(L)[None, :]].copy()
+    nsub = rng.choice([0, 1, 1, 3], size=n)
+    for i in range(n):
+        for p in rng.choice(L, size=int(nsub[i]), replace=False):
+            r[i, p] = (r[i, p] + rng.integers(1, 4)) % 4
+    rc = rng.random(n) < 0.5
+    comp = np.array([3, 2, 1, 0, 4], dtype=np.uint8)
+    r[rc] = comp[r[rc, ::-1]]
+    q = np.full((n, L), ord("I"), dtype=np.uint8)
+    f = os.path.join(work, "near.fq")
+    D.write_fastq(f, r, q, "near")
+    for tag, args in (("near", []), ("nearloc", ["--local"])):
+        base = os.path.join(work, "lambda")
+        cpu, _ = D.run(D.CPU_SERVER, base, args, ["-U", f], os.path.join(work, tag + "_cpu.sam"))
+        stats = os.path.join(work, tag + "_shim_stats.txt")
+        gpu, err = D.run(D.GPU_SERVER, base, args, ["-U", f], os.path.join(work, tag + "_gpu.sam"),
+                         env={"BT2GPU_SHIM_STATS": stats})
+        st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
+        print(tag, st)
+        assert st.get("onemm_calls_on_gpu", 0) > 0 and st.get("sweep_calls_on_gpu", 0) > 0, st
+        _check(cpu, gpu)
