@@ -32,7 +32,8 @@ def _both(work, tag, server_args, client_args):
                      env={"BT2GPU_SHIM_STATS": stats})
     st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
     print(tag, st)
-    for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "kernel_launches"):
+    for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "frame_calls_on_gpu",
+              "joined_to_text_off_on_gpu", "kernel_launches"):
         assert st.get(k, 0) > 0, "%s: nothing ran on the GPU:\n%s\n%s" % (k, st, err[-2000:])
     return cpu, gpu, st["align_calls_on_gpu"]
 
@@ -54,6 +55,8 @@ def test_paired_end_to_end_sam_identical(work):
     D.write_fastq(f2, r[1::2], q[1::2], "pair")
     cpu, gpu, calls = _both(work, "pe", [], ["-1", f1, "-2", f2])
     assert calls > 500
+    st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(os.path.join(work, "pe_shim_stats.txt")).read()))
+    assert st["pe_classify_on_gpu"] > 0, st
     _check(cpu, gpu)
 
 
