@@ -29,15 +29,25 @@ struct ShimState {               // what align() got back for one SwAligner inst
 	std::vector<bt2gpu_dp_aln> alns;
 	std::vector<bt2gpu_edit> edits;
 	uint32_t next = 0;           // next alignment to hand out
-	TAlScore minsc = 0;
+	TAlScore minsc = 0;          // initRef's minsc_
+	bt2gpu_dp_job job;           // the problem, kept for the raised-minsc replay of nextAlignment()
+	std::vector<uint8_t> seq, qual, win;
 };
 
 struct ShimThread {
 	std::unordered_map<const SwAligner*, ShimState> st;
-	std::vector<uint8_t> seq, qual, win;
 	std::vector<bt2gpu_dp_cand> cands;
+	std::vector<bt2gpu_dp_aln> alns2;
+	std::vector<bt2gpu_edit> edits2;
 };
 thread_local ShimThread g_t;
+
+const uint32_t kMaxAln = 1024;
+const size_t kEditCap = (size_t)1 << 18;
+
+size_t candCap(const bt2gpu_dp_job& j, bool monotone) {
+	return monotone ? (size_t)j.ncol + 64 : (size_t)j.rd_len * j.ncol + 64;
+}
 
 } // namespace
 
@@ -65,24 +75,22 @@ bool SwAligner::align(TAlScore& best) {
 	ShimThread& t = g_t;
 	ShimState& st = t.st[this];
 	// the oriented read, rows rdi_..rdf_-1 (bytes 0..4 + Phred+33), and the window incl. the extra column of initRef
-	t.seq.resize(rdlen); t.qual.resize(rdlen); t.win.resize(ncol + 1);
-	for(size_t i = 0; i < rdlen; i++) { t.seq[i] = (uint8_t)(*rd_)[rdi_ + i]; t.qual[i] = (uint8_t)(*qu_)[rdi_ + i]; }
-	for(size_t i = 0; i <= ncol; i++) t.win[i] = (uint8_t)rf_[rfi_ + i];
-	bt2gpu_dp_job job;
+	st.seq.resize(rdlen); st.qual.resize(rdlen); st.win.resize(ncol + 1);
+	for(size_t i = 0; i < rdlen; i++) { st.seq[i] = (uint8_t)(*rd_)[rdi_ + i]; st.qual[i] = (uint8_t)(*qu_)[rdi_ + i]; }
+	for(size_t i = 0; i <= ncol; i++) st.win[i] = (uint8_t)rf_[rfi_ + i];
+	bt2gpu_dp_job& job = st.job;
 	job.rd_off = 0; job.rd_len = (uint32_t)rdlen; job.rf_off = 0; job.ncol = (uint32_t)ncol;
 	job.minsc = (int32_t)minsc_; job.nceil = nceil_;
 	job.refl = rect_->refl; job.triml = (uint32_t)rect_->triml;
 	job.corel = (uint32_t)rect_->corel; job.corer = (uint32_t)rect_->corer;
 	job.fw = fw_ ? 1 : 0; job.enable8 = (enable8_ && !readSse16_) ? 1 : 0;
 	job.reserved[0] = job.reserved[1] = 0;
-	const uint32_t maxAln = 1024;
-	size_t candCap = rdlen * ncol + 64, editCap = (size_t)1 << 18;
-	if(sc_->monotone) candCap = ncol + 64;
-	t.cands.resize(candCap); st.alns.resize(maxAln); st.edits.resize(editCap);
-	if(bt2gpu_dp_align_batch(bt2shim::ctx(), t.seq.data(), t.qual.data(), rdlen, t.win.data(), ncol + 1, &job, 1, maxAln,
-	                         &st.res, t.cands.data(), candCap, st.alns.data(), st.edits.data(), editCap))
+	const size_t cc = candCap(job, sc_->monotone);
+	t.cands.resize(cc); st.alns.resize(kMaxAln); st.edits.resize(kEditCap);
+	if(bt2gpu_dp_align_batch(bt2shim::ctx(), st.seq.data(), st.qual.data(), rdlen, st.win.data(), ncol + 1, &job, 1, kMaxAln,
+	                         &st.res, t.cands.data(), cc, st.alns.data(), st.edits.data(), kEditCap))
 		bt2shim::fail("bt2gpu_dp_align_batch");
-	if(st.res.naln >= maxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", maxAln); throw 1; }
+	if(st.res.naln >= kMaxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", kMaxAln); throw 1; }
 	bt2shim::note(bt2shim::C_ALIGN, 1);
 	st.next = 0; st.minsc = minsc_;
 	sse8succ_ = st.res.width == 8; sse16succ_ = st.res.width == 16;
@@ -107,9 +115,35 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 	assert(initedRead() && initedRef());
 	if(done()) { res.reset(); return false; }
 	ShimState& st = g_t.st[this];
-	if(minsc != st.minsc) { fprintf(stderr, "bt2gpu shim: nextAlignment minsc differs from initRef's\n"); throw 1; }
+	if(minsc < st.minsc) { fprintf(stderr, "bt2gpu shim: nextAlignment minsc below initRef's\n"); throw 1; }
 	const bt2gpu_dp_aln *a = (st.next < st.res.naln) ? &st.alns[st.res.aln_off + st.next] : NULL;
-	const uint32_t tries = a ? a->tries : st.res.tail_tries;
+	uint32_t tries = a ? a->tries : st.res.tail_tries;
+	if(minsc > st.minsc) {
+		// The driver tightened minsc after reporting an alignment (aligner_sw_driver.cpp:1255-1284).  nextAlignment only
+		// uses its minsc argument to drop candidates (aligner_sw.cpp:762); btncand_ is sorted by score, so from the
+		// first candidate below the new minsc on, everything is dropped without a backtrace or an RNG draw.
+		if(btncand_[cural_].score < minsc) { res.reset(); cural_ = btncand_.size(); return false; }
+		if(a == NULL || btncand_[a->cural - 1].score < minsc) {
+			// The GPU loop's next success (or its tail) lies beyond that point: the backtraces attempted before it are
+			// those of the same problem with minsc raised from the start (candidates >= the new minsc come first and
+			// see the same history) -- replay it and take its tail count.
+			ShimThread& t = g_t;
+			bt2gpu_dp_job j2 = st.job; bt2gpu_dp_result r2;
+			j2.minsc = (int32_t)minsc; j2.enable8 = sse8succ_ ? 1 : 0;
+			const size_t cc = candCap(j2, sc_->monotone);
+			t.cands.resize(cc); t.alns2.resize(kMaxAln); t.edits2.resize(kEditCap);
+			bt2shim::bindScoring(*sc_);
+			if(bt2gpu_dp_align_batch(bt2shim::ctx(), st.seq.data(), st.qual.data(), j2.rd_len, st.win.data(), j2.ncol + 1, &j2, 1,
+			                         kMaxAln, &r2, t.cands.data(), cc, t.alns2.data(), t.edits2.data(), kEditCap))
+				bt2shim::fail("bt2gpu_dp_align_batch (raised minsc)");
+			bt2shim::note(bt2shim::C_ALIGN, 1);
+			if(r2.naln != st.next || (r2.width != 0 && r2.width != st.res.width)) {
+				fprintf(stderr, "bt2gpu shim: raised-minsc replay diverged (%u alignments, expected %u)\n", r2.naln, st.next);
+				throw 1;
+			}
+			a = NULL; tries = r2.tail_tries;
+		}
+	}
 	for(uint32_t k = 0; k < tries; k++) {    // u8: init(reseed) ... init(reseed+1); i16: ... init(reseed)
 		uint32_t reseed = rnd.nextU32() + 1;
 		rnd.init(sse8succ_ ? reseed + 1 : reseed);

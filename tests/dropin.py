@@ -72,8 +72,11 @@ def run(server, base, server_args, client_args, sam, threads=2, timeout=600, env
                 if srv.poll() is not None or time.time() - t0 > 120:
                     raise RuntimeError("server did not start: " + open(errp).read()[-2000:])
                 time.sleep(0.05)
-            subprocess.check_call([CLIENT, "--server-port", str(port), "-x", base] + client_args + ["-S", sam],
-                                  stderr=open(sam + ".client.err", "w"), timeout=timeout)
+            rc = subprocess.call([CLIENT, "--server-port", str(port), "-x", base] + client_args + ["-S", sam],
+                                 stderr=open(sam + ".client.err", "w"), timeout=timeout)
+            if rc != 0:
+                raise RuntimeError("client exit %d; client stderr:\n%s\nserver stderr:\n%s"
+                                   % (rc, open(sam + ".client.err").read()[-1500:], open(errp).read()[-1500:]))
         finally:
             srv.terminate()
             try:
@@ -84,10 +87,15 @@ def run(server, base, server_args, client_args, sam, threads=2, timeout=600, env
     return lines, open(errp).read()
 
 
-def lambda_genome():
-    _, seqs = read_fasta(os.path.join(GOLDEN, "lambda.fa"))
+def genome_codes(fasta="lambda.fa"):
+    """All sequences of a golden FASTA as code arrays (0..3, 4 = N)."""
+    _, seqs = read_fasta(os.path.join(GOLDEN, fasta))
     lut = np.full(256, 4, np.uint8)
     for i, c in enumerate("ACGT"):
         lut[ord(c)] = i
         lut[ord(c.lower())] = i
-    return lut[np.frombuffer(seqs[0].encode(), np.uint8)]
+    return [lut[np.frombuffer(x.encode(), np.uint8)] for x in seqs]
+
+
+def lambda_genome():
+    return genome_codes("lambda.fa")[0]

@@ -24,8 +24,8 @@ def work(tmp_path_factory):
     return w
 
 
-def _both(work, tag, server_args, client_args):
-    base = os.path.join(work, "lambda")
+def _both(work, tag, server_args, client_args, index="lambda"):
+    base = os.path.join(work, index)
     cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"))
     stats = os.path.join(work, tag + "_shim_stats.txt")
     gpu, err = D.run(D.GPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_gpu.sam"),
@@ -121,3 +121,30 @@ def test_near_exact_reads_one_mismatch_path(work):
         print(tag, st)
         assert st.get("onemm_calls_on_gpu", 0) > 0 and st.get("sweep_calls_on_gpu", 0) > 0, st
         _check(cpu, gpu)
+
+
+def test_repeat_genome_three_chromosomes(work):
+    """tests/golden/rep.fa: three sequences with tandem and dispersed repeats and an N gap -- wide BW ranges (RowSampler,
+    redundant-alignment filters, many nextAlignment candidates), reads hanging over sequence ends and across the gap
+    (joinedToTextOff straddle rejection, window trimming), -k 5 so several alignments per read are printed."""
+    D.build_index(os.path.join(D.GOLDEN, "rep.fa"), os.path.join(work, "rep"))
+    rng = np.random.default_rng(16)
+    chroms = D.genome_codes("rep.fa")
+    rs, qs = [], []
+    for c in chroms:
+        r, q, _, _ = synth.simulate_pairs(rng, c, 400, 120)
+        rs.append(r); qs.append(q)
+        # reads hanging over both ends of the sequence (soft ends / trimmed windows)
+        edge = np.concatenate([c[:90], c[-90:]])
+        for k in range(12):
+            o = 6 * k
+            x = np.concatenate([rng.integers(0, 4, size=30 - 2 * k).astype(np.uint8), edge[o:o + 90 + 2 * k]])
+            rs.append(np.stack([x, x[::-1].copy()])); qs.append(np.full((2, 120), ord("F"), dtype=np.uint8))
+    r, q = np.concatenate(rs), np.concatenate(qs)
+    f1, f2 = os.path.join(work, "rep_1.fq"), os.path.join(work, "rep_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "rep")
+    D.write_fastq(f2, r[1::2], q[1::2], "rep")
+    cpu, gpu, _ = _both(work, "rep", ["-k", "5"], ["-1", f1, "-2", f2], index="rep")
+    _check(cpu, gpu)
+    cpu, gpu, _ = _both(work, "repl", ["--local", "--very-sensitive-local"], ["-U", f1 + "," + f2], index="rep")
+    _check(cpu, gpu)
