@@ -148,3 +148,33 @@ def test_repeat_genome_three_chromosomes(work):
     _check(cpu, gpu)
     cpu, gpu, _ = _both(work, "repl", ["--local", "--very-sensitive-local"], ["-U", f1 + "," + f2], index="rep")
     _check(cpu, gpu)
+
+
+def _gunzip(work, name):
+    import gzip
+    import shutil
+    dst = os.path.join(work, name[:-3])
+    with gzip.open(os.path.join(D.GOLDEN, name), "rb") as src, open(dst, "wb") as out:
+        shutil.copyfileobj(src, out)
+    return dst
+
+
+def test_config_c1_example_longreads(work):
+    """BASELINE.json configs[0]: lambda_virus + example/reads/longreads.fq, unpaired end-to-end --sensitive (the first
+    500 reads shorter than the checkpointing threshold, scripts/make_example_fixtures.py)."""
+    f = _gunzip(work, "example_longreads.fq.gz")
+    cpu, gpu, _ = _both(work, "c1", ["--sensitive"], ["-U", f])
+    _check(cpu, gpu)
+
+
+def test_config_c2_example_pairs(work):
+    """BASELINE.json configs[1]: lambda_virus paired-end example/reads/reads_{1,2}.fq, end-to-end u8 path (first 1200
+    pairs)."""
+    f1, f2 = _gunzip(work, "example_reads_1.fq.gz"), _gunzip(work, "example_reads_2.fq.gz")
+    cpu, gpu, _ = _both(work, "c2", [], ["-1", f1, "-2", f2])
+    st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(os.path.join(work, "c2_shim_stats.txt")).read()))
+    assert st["pe_classify_on_gpu"] > 0, st
+    _check(cpu, gpu)
+    # the same pairs in --local mode (the C4 policy on the C2 reads)
+    cpu, gpu, _ = _both(work, "c2l", ["--local"], ["-1", f1, "-2", f2])
+    _check(cpu, gpu)
