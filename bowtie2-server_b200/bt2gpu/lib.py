@@ -23,7 +23,7 @@ SYMBOLS = [
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
-    "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch",
+    "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch",
 ]
 
 _lib = None
@@ -160,6 +160,18 @@ class Context:
         self.dp_run(7)
         r = self.dp_fetch()
         return r[0], r[1], r[2], r[3]
+
+    def ungapped_batch(self, seq, qual, win, jobs, edit_cap=None):
+        """bt2gpu_ungapped_batch: SwAligner::ungappedAlign for a batch -> (results, edits)."""
+        n = len(jobs)
+        edit_cap = edit_cap if edit_cap is not None else int(jobs["rd_len"].sum()) + 16
+        res = np.zeros(n, dtype=structs.ungap_result)
+        edits = np.zeros(edit_cap, dtype=structs.edit)
+        ne = C.c_size_t(0)
+        _check(self.lib.bt2gpu_ungapped_batch(self._h, _ptr(seq), _ptr(qual), C.c_size_t(len(seq)), _ptr(win),
+                                              C.c_size_t(len(win)), _ptr(jobs), C.c_size_t(n), _ptr(res), _ptr(edits),
+                                              C.c_size_t(edit_cap), C.byref(ne)))
+        return res, edits[: ne.value]
 
     # ---- FM index (seed side) ---------------------------------------------------------------
     def stage_reads(self, pool):

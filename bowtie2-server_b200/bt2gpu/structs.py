@@ -133,3 +133,10 @@ class PairsStats(_ct.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+# SwAligner::ungappedAlign (bt2gpu_ungapped_batch)
+ungap_job = np.dtype([("rd_off", "<u4"), ("rd_len", "<u4"), ("rf_off", "<u4"), ("minsc", "<i4"), ("nceil", "<i4"),
+                      ("fw", "u1"), ("ohang", "u1"), ("pad", "u1", (2,)), ("off", "<i8"), ("reflen", "<i8")], align=True)
+ungap_result = np.dtype([("ret", "<i4"), ("score", "<i4"), ("ns", "<i4"), ("refns", "<i4"), ("refoff", "<i8"),
+                         ("trim5", "<u4"), ("trim3", "<u4"), ("nedits", "<u4"), ("edit_off", "<u4")], align=True)
+assert ungap_job.itemsize == 40 and ungap_result.itemsize == 40

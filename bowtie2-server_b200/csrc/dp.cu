@@ -1565,3 +1565,171 @@ void dp_state_free(DpState *d) {
 	delete d;
 }
 }
+
+// ---------------------------------------------------------------------------------------
+// SwAligner::ungappedAlign (aligner_sw.cpp:286-494): the read laid on one diagonal.  A warp per job.
+//   pass 1  lanes score 32 positions at a time (coalesced byte loads of read, quality, window).  End-to-end: every
+//           term is <= 0 and the N count only grows, so the reference's per-prefix bail-out (score < minsc || ns >
+//           nceil, :391-396) is the test on the totals -- two warp reductions.  Local: the running score with its
+//           floor at 0 and the (scoreMax, rowf, rowi, sols) bookkeeping (:399-424) is a sequential state machine;
+//           the lanes' terms are broadcast one by one and every lane steps the same scalar state (no divergence).
+//   pass 2  mismatch edits of rows rowi..rowf, compacted with ballots, written in their final form (after
+//           AlnRes::setShape's trim shift and, for the '-' strand, invertEdits) into a range of the edit pool
+//           reserved with one atomic per job.
+__global__ void __launch_bounds__(128)
+k_ungapped(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const uint8_t *__restrict__ win,
+           const bt2gpu_ungap_job *__restrict__ jobs, uint32_t njobs, bt2gpu_ungap_result *__restrict__ res,
+           bt2gpu_edit *__restrict__ edits, unsigned long long *__restrict__ nedits, unsigned long long edit_cap,
+           int *__restrict__ errflag)
+{
+	const uint32_t FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	const uint32_t ji = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if(ji >= njobs) return;
+	const bt2gpu_ungap_job j = jobs[ji];
+	bt2gpu_ungap_result r;
+	r.ret = 0; r.score = r.ns = r.refns = 0; r.refoff = 0; r.trim5 = r.trim3 = r.nedits = r.edit_off = 0;
+	const int len = (int)j.rd_len;
+	const uint8_t *rd = seq + j.rd_off, *qu = qual + j.rd_off, *rf = win + j.rf_off;
+	const long long rfi = j.off, rff = j.off + len;
+	long long leftNs = 0, rightNs = 0;
+	bool ok = true;
+	if(rfi < 0) { if(j.ohang) leftNs = -rfi; else ok = false; }
+	if(rff > j.reflen) { if(j.ohang) rightNs = rff - j.reflen; else ok = false; }
+	if(leftNs + rightNs > (long long)j.nceil) ok = false;
+	int rowi = 0, rowf = len - 1, score = 0, ns = 0;
+	if(ok) {
+		if(c_sc.monotone) {
+			int tot = 0;
+			for(int i = lane; i < len; i += 32) {
+				const int rdc = rd[i], c = rf[i];
+				ns += (rdc > 3 || c > 3);
+				tot += dev_score(rdc, c, (int)qu[i] - 33);
+			}
+			for(int o = 16; o; o >>= 1) { tot += __shfl_xor_sync(FULL, tot, o); ns += __shfl_xor_sync(FULL, ns, o); }
+			score = tot;
+			ok = !(score < j.minsc || ns > j.nceil);
+		} else {
+			int scoreMax = 0, lastfloor = 0, sols = 0, run = 0;
+			rowi = -1;
+			for(int base = 0; base < len; base += 32) {
+				const int i = base + lane;
+				int s = 0, isn = 0;
+				if(i < len) {
+					const int rdc = rd[i], c = rf[i];
+					isn = (rdc > 3 || c > 3);
+					s = dev_score(rdc, c, (int)qu[i] - 33);
+				}
+				ns += __popc(__ballot_sync(FULL, isn));
+				const int cnt = min(32, len - base);
+				for(int k = 0; k < cnt; k++) {
+					run += __shfl_sync(FULL, s, k);
+					if(run >= j.minsc && run >= scoreMax) {
+						scoreMax = run; rowf = base + k;
+						if(rowi != lastfloor) { rowi = lastfloor; sols++; }
+					}
+					if(run <= 0) { run = 0; lastfloor = base + k + 1; }
+				}
+			}
+			if(ns > j.nceil || scoreMax < j.minsc || rowi < 0) ok = false;
+			else if(sols > 1) { ok = false; r.ret = -1; }
+			score = scoreMax;
+		}
+	}
+	if(ok) {
+		// count, reserve, write
+		uint32_t n = 0, refns = 0;
+		for(int base = rowi; base <= rowf; base += 32) {
+			const int i = base + lane;
+			bool e = false, rn = false;
+			if(i <= rowf) { const int c = rf[i]; rn = c > 3; e = rn || rd[i] != c; }
+			n += __popc(__ballot_sync(FULL, e));
+			refns += __popc(__ballot_sync(FULL, rn));
+		}
+		unsigned long long e0 = 0;
+		if(lane == 0 && n) e0 = atomicAdd(nedits, (unsigned long long)n);
+		e0 = __shfl_sync(FULL, e0, 0);
+		if(e0 + n > edit_cap) { if(lane == 0) { *errflag = 2; res[ji] = r; } return; }
+		uint32_t k0 = 0;
+		for(int base = rowi; base <= rowf; base += 32) {
+			const int i = base + lane;
+			bool e = false; int c = 0, rdc = 0;
+			if(i <= rowf) { c = rf[i]; rdc = rd[i]; e = c > 3 || rdc != c; }
+			const uint32_t m = __ballot_sync(FULL, e);
+			if(e) {
+				const uint32_t k = k0 + __popc(m & ((1u << lane) - 1u));
+				bt2gpu_edit ed;
+				ed.pos = j.fw ? (uint32_t)(i - rowi) : (uint32_t)(rowf - i);
+				ed.chr = (uint8_t)"ACGTN"[c]; ed.qchr = (uint8_t)"ACGTN"[rdc];
+				ed.type = BT2GPU_EDIT_MM; ed.pad = 0;
+				edits[e0 + (j.fw ? k : n - 1 - k)] = ed;
+			}
+			k0 += __popc(m);
+		}
+		const int trimEnd = (len - 1) - rowf;
+		r.ret = 1; r.score = score; r.ns = ns; r.refns = (int32_t)refns;
+		r.refoff = j.off + rowi;
+		r.trim5 = (uint32_t)(j.fw ? rowi : trimEnd); r.trim3 = (uint32_t)(j.fw ? trimEnd : rowi);
+		r.nedits = n; r.edit_off = (uint32_t)e0;
+	}
+	if(lane == 0) res[ji] = r;
+}
+
+extern "C" int bt2gpu_ungapped_batch(
+	bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len, const bt2gpu_ungap_job *jobs, size_t njobs,
+	bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits)
+{
+	using namespace bt2;
+	if(!ctx) BT2_FAIL("null context");
+	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set has not been called");
+	if(nedits) *nedits = 0;
+	if(njobs == 0) return 0;
+	if(!seq_pool || !qual_pool || !win_pool || !jobs || !results || (!edits && edit_cap)) BT2_FAIL("null argument");
+	if(njobs > 0x7fffffffu) BT2_FAIL("too many jobs");
+	for(size_t i = 0; i < njobs; i++) {
+		const bt2gpu_ungap_job& j = jobs[i];
+		if(j.rd_len == 0) BT2_FAIL("empty read");
+		if((size_t)j.rd_off + j.rd_len > pool_len || (size_t)j.rf_off + j.rd_len > win_len) BT2_FAIL("job outside its pool");
+	}
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	DevBuf buf;
+	auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+	const size_t o_seq = 0, o_qual = o_seq + al(pool_len), o_win = o_qual + al(pool_len), o_jobs = o_win + al(win_len),
+	             o_res = o_jobs + al(njobs * sizeof(bt2gpu_ungap_job)), o_ed = o_res + al(njobs * sizeof(bt2gpu_ungap_result)),
+	             o_scal = o_ed + al(edit_cap * sizeof(bt2gpu_edit)), total = o_scal + 256;
+	if(buf.reserve(total)) return 1;
+	uint8_t *b = buf.as<uint8_t>();
+	int rc = 0;
+	do {
+		cudaStream_t s = ctx->stream;
+		cudaError_t e = cudaMemcpyAsync(b + o_seq, seq_pool, pool_len, cudaMemcpyHostToDevice, s);
+		if(e == cudaSuccess) e = cudaMemcpyAsync(b + o_qual, qual_pool, pool_len, cudaMemcpyHostToDevice, s);
+		if(e == cudaSuccess) e = cudaMemcpyAsync(b + o_win, win_pool, win_len, cudaMemcpyHostToDevice, s);
+		if(e == cudaSuccess) e = cudaMemcpyAsync(b + o_jobs, jobs, njobs * sizeof(bt2gpu_ungap_job), cudaMemcpyHostToDevice, s);
+		if(e == cudaSuccess) e = cudaMemsetAsync(b + o_scal, 0, 256, s);
+		if(e != cudaSuccess) { rc = fail("ungapped H2D", __FILE__, __LINE__, e); break; }
+		ctx->kstart();
+		const unsigned wpb = 4;
+		k_ungapped<<<(unsigned)((njobs + wpb - 1) / wpb), wpb * 32, 0, s>>>(
+			b + o_seq, b + o_qual, b + o_win, reinterpret_cast<const bt2gpu_ungap_job*>(b + o_jobs), (uint32_t)njobs,
+			reinterpret_cast<bt2gpu_ungap_result*>(b + o_res), reinterpret_cast<bt2gpu_edit*>(b + o_ed),
+			reinterpret_cast<unsigned long long*>(b + o_scal), (unsigned long long)edit_cap,
+			reinterpret_cast<int*>(b + o_scal + 8));
+		ctx->launches++;
+		ctx->kend();
+		unsigned long long scal[2] = {0, 0};
+		e = cudaMemcpyAsync(results, b + o_res, njobs * sizeof(bt2gpu_ungap_result), cudaMemcpyDeviceToHost, s);
+		if(e == cudaSuccess) e = cudaMemcpyAsync(scal, b + o_scal, sizeof scal, cudaMemcpyDeviceToHost, s);
+		if(e == cudaSuccess) e = cudaStreamSynchronize(s);
+		if(e != cudaSuccess) { rc = fail("ungapped", __FILE__, __LINE__, e); break; }
+		if((int)(scal[1] & 0xffffffffu) == 2 || scal[0] > edit_cap) { rc = fail("edit pool overflow (raise edit_cap)", __FILE__, __LINE__); break; }
+		if(scal[0]) {
+			e = cudaMemcpy(edits, b + o_ed, (size_t)scal[0] * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost);
+			if(e != cudaSuccess) { rc = fail("ungapped D2H", __FILE__, __LINE__, e); break; }
+		}
+		if(nedits) *nedits = (size_t)scal[0];
+	} while(0);
+	buf.release();
+	return rc;
+}

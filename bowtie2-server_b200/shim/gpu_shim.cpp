@@ -102,7 +102,7 @@ void note(Counter c, uint64_t n) {
 		g_launches += l - g_t.launches; g_t.launches = l;
 	}
 	if(fd < 0) return;
-	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
+	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapped_calls_on_gpu", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
 	                                          "seeds_on_gpu", "extend_calls_on_gpu", "frame_calls_on_gpu", "pe_classify_on_gpu",
 	                                          "joined_to_text_off_on_gpu" };
 	char buf[512]; int n2 = 0;

@@ -20,6 +20,7 @@
 #include <vector>
 #include <limits>
 #include "aligner_sw.h"
+#include "reference.h"
 #include "gpu_shim.h"
 
 namespace {
@@ -39,6 +40,8 @@ struct ShimThread {
 	std::vector<bt2gpu_dp_cand> cands;
 	std::vector<bt2gpu_dp_aln> alns2;
 	std::vector<bt2gpu_edit> edits2;
+	std::vector<uint8_t> useq, uqual, uwin;   // ungappedAlign
+	std::vector<bt2gpu_edit> uedits;
 };
 thread_local ShimThread g_t;
 
@@ -173,4 +176,63 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 	st.next++;
 	bt2shim::note(bt2shim::C_ALN, 1);
 	return true;
+}
+
+/**
+ * SwAligner::ungappedAlign (aligner_sw.cpp:286-494): the single-diagonal alignment SwDriver tries when no gap is
+ * affordable.  The window is cut out of the BitPairReference here (Ns off the ends, as :326-360); the overhang
+ * rules, the scoring scan, the soft trims and the edit list come from bt2gpu_ungapped_batch.
+ */
+int SwAligner::ungappedAlign(
+	const BTDnaString& rd, const BTString& qu, const Coord& coord, const BitPairReference& refs, size_t reflen,
+	const Scoring& sc, bool ohang, TAlScore minsc, SwResult& res)
+{
+	const size_t len = rd.length();
+	bt2shim::bindScoring(sc);
+	ShimThread& t = g_t;
+	std::vector<uint8_t>& seq = t.useq; std::vector<uint8_t>& qual = t.uqual; std::vector<uint8_t>& win = t.uwin;
+	seq.resize(len); qual.resize(len); win.resize(len);
+	const TRefOff rfi = coord.off();
+	for(size_t i = 0; i < len; i++) {
+		seq[i] = (uint8_t)rd[i]; qual[i] = (uint8_t)qu[i];
+		const TRefOff p = rfi + (TRefOff)i;
+		win[i] = (p < 0 || (size_t)p >= reflen) ? 4 : (uint8_t)refs.getBase(coord.ref(), (size_t)p);
+	}
+	bt2gpu_ungap_job j;
+	j.rd_off = 0; j.rd_len = (uint32_t)len; j.rf_off = 0; j.minsc = (int32_t)minsc;
+	j.nceil = sc.nCeil.f<int>((double)len);
+	j.fw = coord.fw() ? 1 : 0; j.ohang = ohang ? 1 : 0; j.pad[0] = j.pad[1] = 0;
+	j.off = rfi; j.reflen = (int64_t)reflen;
+	bt2gpu_ungap_result r; size_t ne = 0;
+	t.uedits.resize(len + 1);
+	if(bt2gpu_ungapped_batch(bt2shim::ctx(), seq.data(), qual.data(), len, win.data(), len, &j, 1, &r, t.uedits.data(),
+	                         len + 1, &ne))
+		bt2shim::fail("bt2gpu_ungapped_batch");
+	bt2shim::note(bt2shim::C_UNGAPPED, 1);
+	if(r.ret != 1) {
+		// the reference has reset res.alres by the time it scores (:386); before that it returns with res untouched
+		bool early = false;
+		if(rfi < 0 && !ohang) early = true;
+		if(rfi + (TRefOff)len > (TRefOff)reflen && !ohang) early = true;
+		size_t leftNs = rfi < 0 ? (size_t)(-rfi) : 0, rightNs = rfi + (TRefOff)len > (TRefOff)reflen ? (size_t)(rfi + (TRefOff)len - (TRefOff)reflen) : 0;
+		if(leftNs + rightNs > (size_t)j.nceil) early = true;
+		if(!early) res.alres.reset();
+		return r.ret;
+	}
+	res.alres.reset();
+	const bool fw = coord.fw();
+	const size_t rowi = fw ? r.trim5 : r.trim3, trimEnd = fw ? r.trim3 : r.trim5;
+	EList<Edit>& ned = res.alres.ned();
+	for(uint32_t i = 0; i < r.nedits; i++) {
+		const bt2gpu_edit& e = t.uedits[r.edit_off + i];
+		ned.push_back(Edit(e.pos, (int)e.chr, (int)e.qchr, (int)e.type));
+	}
+	// back to row coordinates so that setShape / invertEdits below run as in the reference (:456-490)
+	if(!fw) Edit::invertPoss(ned, len - rowi - trimEnd, false);
+	for(size_t i = 0; i < ned.size(); i++) ned[i].pos += (uint32_t)rowi;
+	res.alres.setScore(AlnScore(r.score, (int)(len - ned.size()), (int)ned.size(), r.ns, 0));
+	res.alres.setShape(coord.ref(), r.refoff, reflen, fw, len, true, 0, 0, true, r.trim5, r.trim3);
+	res.alres.setRefNs(r.refns);
+	if(!fw) res.alres.invertEdits();
+	return 1;
 }

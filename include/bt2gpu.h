@@ -160,6 +160,38 @@ uint64_t bt2gpu_dp_staged_cells(bt2gpu_ctx *ctx);
 /* matrix cells visited by the nextAlignment walks of the last fetched run (SSEMetrics.btcell) */
 uint64_t bt2gpu_dp_walked_cells(bt2gpu_ctx *ctx);
 
+/* ---- SwAligner::ungappedAlign (aligner_sw.cpp:286-494) --------------------
+ * The single-diagonal alignment SwDriver tries when the score budget affords no gap
+ * (aligner_sw_driver.cpp:1031-1060): the read laid on the reference at `off`.
+ * The window is given as reference codes 0..3 (4 = N), rd_len bytes, with 4 at
+ * positions off the ends of the reference (the reference pads with Ns, :342-360).
+ * ret: 1 = alignment, 0 = none, -1 = more than one local solution on the diagonal
+ * (the caller falls through to the DP, :447-450). */
+typedef struct {
+	uint32_t rd_off, rd_len;   /* oriented read (rd/qu arguments) in seq_pool/qual_pool  */
+	uint32_t rf_off;           /* window in win_pool                                      */
+	int32_t  minsc;            /* minsc argument                                          */
+	int32_t  nceil;            /* sc.nCeil.f(len)  (:297)                                 */
+	uint8_t  fw;               /* coord.fw()                                              */
+	uint8_t  ohang;            /* allow overhang? (:307-322)                              */
+	uint8_t  pad[2];
+	int64_t  off;              /* coord.off()                                             */
+	int64_t  reflen;           /* length of the reference sequence                        */
+} bt2gpu_ungap_job;
+typedef struct {
+	int32_t  ret;
+	int32_t  score, ns, refns; /* AlnScore::score_/ns_, AlnRes::refNs()                   */
+	int64_t  refoff;           /* coord.off() + rowi                                      */
+	uint32_t trim5, trim3;     /* soft trims w.r.t. the read's 5'/3' ends                 */
+	uint32_t nedits, edit_off; /* mismatch edits, pos w.r.t. the 5' end after invertEdits */
+} bt2gpu_ungap_result;
+int bt2gpu_ungapped_batch(
+	bt2gpu_ctx *ctx,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len,
+	const bt2gpu_ungap_job *jobs, size_t njobs,
+	bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits);
+
 /* ======================================================================== */
 /* ---- FM index (replaces Ebwt's search-side state, bt2_idx.h:2530-2570) --- */
 

@@ -575,3 +575,83 @@ uint64_t bt2oracle_dp_cells(const bt2gpu_dp_job *jobs, size_t njobs) {
 	for(size_t i = 0; i < njobs; i++) c += (uint64_t)jobs[i].rd_len * jobs[i].ncol;
 	return c;
 }
+
+/* ---- SwAligner::ungappedAlign (aligner_sw.cpp:286-494) ------------------------------------
+ * Pinned against tests/golden/ungapped_{ee,loc}.txt (oracle/make_ungapped_goldens.py: dumps of
+ * the unmodified reference through ref_dp_dump --ungapped). */
+static int ungap_one(const bt2gpu_scoring *sc, const uint8_t *rd, const uint8_t *qu, const uint8_t *rf,
+                     const bt2gpu_ungap_job *j, bt2gpu_ungap_result *r, bt2gpu_edit *ed, size_t cap, size_t *ne)
+{
+	const int64_t len = j->rd_len;
+	int ns = 0;
+	memset(r, 0, sizeof *r);
+	int64_t rfi = j->off, rff = rfi + len;
+	int64_t leftNs = 0, rightNs = 0;
+	if(rfi < 0) { if(j->ohang) leftNs = -rfi; else return 0; }                    /* :307-314 */
+	if(rff > j->reflen) { if(j->ohang) rightNs = rff - j->reflen; else return 0; } /* :315-322 */
+	if(leftNs + rightNs > (int64_t)j->nceil) return 0;                             /* :323-325 */
+	int64_t score = 0, rowi = 0, rowf = len - 1;
+	if(sc->monotone) {                                                             /* :387-398 */
+		for(int64_t i = 0; i < len; i++) {
+			const int rdc = rd[i], refm = 1 << rf[i], q = qu[i] - 33;
+			if(rdc > 3 || refm > 15) ns++;
+			score += sc_score(sc, rdc, refm, q);
+			if(score < j->minsc || ns > j->nceil) return 0;
+		}
+	} else {                                                                       /* :399-435 */
+		int64_t scoreMax = 0, lastfloor = 0, sols = 0;
+		rowi = -1;
+		for(int64_t i = 0; i < len; i++) {
+			const int rdc = rd[i], refm = 1 << rf[i], q = qu[i] - 33;
+			if(rdc > 3 || refm > 15) ns++;
+			score += sc_score(sc, rdc, refm, q);
+			if(score >= j->minsc && score >= scoreMax) {
+				scoreMax = score; rowf = i;
+				if(rowi != lastfloor) { rowi = lastfloor; sols++; }
+			}
+			if(score <= 0) { score = 0; lastfloor = i + 1; }
+		}
+		if(ns > j->nceil || scoreMax < j->minsc || rowi < 0) return 0;   /* rowi < 0: minsc <= 0 and no cell reached it */
+		if(sols > 1) { r->ret = -1; return 0; }
+		score = scoreMax;
+	}
+	const size_t e0 = *ne;
+	uint32_t n = 0; int refns = 0;
+	for(int64_t i = rowi; i <= rowf; i++) {                                        /* :441-455 */
+		if(rf[i] > 3 || rd[i] != rf[i]) {
+			if(e0 + n >= cap) return 1;
+			bt2gpu_edit *e = &ed[e0 + n++];
+			e->pos = (uint32_t)i; e->chr = (uint8_t)"ACGTN"[rf[i]]; e->qchr = (uint8_t)"ACGTN"[rd[i]];
+			e->type = BT2GPU_EDIT_MM; e->pad = 0;
+			if(rf[i] > 3) refns++;
+		}
+	}
+	const int64_t trimEnd = (len - 1) - rowf;
+	/* setShape's trim shift (aligner_result.cpp:101-108) then, for the '-' strand, invertEdits (:489) */
+	for(uint32_t k = 0; k < n; k++) ed[e0 + k].pos -= (uint32_t)rowi;
+	if(!j->fw) {
+		const uint32_t ext = (uint32_t)(rowf - rowi + 1);
+		for(uint32_t k = 0; k < n / 2; k++) { bt2gpu_edit t = ed[e0 + k]; ed[e0 + k] = ed[e0 + n - 1 - k]; ed[e0 + n - 1 - k] = t; }
+		for(uint32_t k = 0; k < n; k++) ed[e0 + k].pos = ext - ed[e0 + k].pos - 1;
+	}
+	*ne = e0 + n;
+	r->ret = 1; r->score = (int32_t)score; r->ns = ns; r->refns = refns;
+	r->refoff = j->off + rowi;
+	r->trim5 = (uint32_t)(j->fw ? rowi : trimEnd); r->trim3 = (uint32_t)(j->fw ? trimEnd : rowi);
+	r->nedits = n; r->edit_off = (uint32_t)e0;
+	return 0;
+}
+
+int bt2oracle_ungapped_batch(const bt2gpu_scoring *sc, const uint8_t *seq_pool, const uint8_t *qual_pool,
+                             const uint8_t *win_pool, const bt2gpu_ungap_job *jobs, size_t njobs,
+                             bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits)
+{
+	size_t ne = 0;
+	for(size_t i = 0; i < njobs; i++) {
+		const bt2gpu_ungap_job *j = &jobs[i];
+		if(ungap_one(sc, seq_pool + j->rd_off, qual_pool + j->rd_off, win_pool + j->rf_off, j, &results[i], edits, edit_cap, &ne))
+			return 1;
+	}
+	*nedits = ne;
+	return 0;
+}

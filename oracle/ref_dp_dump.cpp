@@ -80,7 +80,7 @@ static pair<int,int> parsePair(const char* s) {
 }
 
 int main(int argc, char** argv) {
-	string logfn, idx, probfn;
+	string logfn, idx, probfn, ungfn;
 	bool local = false, enable8 = true;
 	int ma = -1, mpmax = DEFAULT_MM_PENALTY_MAX, mpmin = DEFAULT_MM_PENALTY_MIN;
 	int np = DEFAULT_N_PENALTY, gbar = 4;
@@ -94,6 +94,7 @@ int main(int argc, char** argv) {
 		if(a == "--log") logfn = argv[++i];
 		else if(a == "--index") idx = argv[++i];
 		else if(a == "--problems") probfn = argv[++i];
+		else if(a == "--ungapped") ungfn = argv[++i];
 		else if(a == "--local") local = true;
 		else if(a == "--no-sse8") enable8 = false;
 		else if(a == "--ma") ma = atoi(argv[++i]);
@@ -120,6 +121,51 @@ int main(int argc, char** argv) {
 	BitPairReference* refs = NULL;
 	if(!idx.empty()) {
 		refs = new BitPairReference(idx, false, false, NULL, NULL, false, false, false, false, false, false);
+	}
+
+	if(!ungfn.empty()) {
+		// --ungapped FILE --index BASE: SwAligner::ungappedAlign (aligner_sw.cpp:286-494) on lines
+		//   U <rd as passed (oriented)> <qual> <+/-> <refidx> <off> <ohang 0/1> <minsc>
+		// prints the line back with reflen and the window the reference scored against (codes as ACGTN,
+		// overhang = N), then  UR ret [score ns refns refoff trim5 trim3 nedits edits]
+		if(refs == NULL) { cerr << "need --index" << endl; return 2; }
+		ifstream uin(ungfn.c_str());
+		string ul;
+		SwAligner usw(NULL);
+		BTDnaString rd; BTString qu;
+		while(getline(uin, ul)) {
+			EList<string> b; tokenize(ul, '\t', b);
+			if(b.size() < 8 || b[0] != "U") continue;
+			rd.install(b[1].c_str(), true); qu = b[2];
+			bool fw = (b[3] == "+");
+			TRefId refidx = (TRefId)atol(b[4].c_str());
+			TRefOff off = (TRefOff)atoll(b[5].c_str());
+			bool ohang = atoi(b[6].c_str()) != 0;
+			TAlScore minsc = (TAlScore)atoll(b[7].c_str());
+			size_t reflen = refs->approxLen(refidx);
+			Coord coord(refidx, off, fw);
+			SwResult res;
+			int ret = usw.ungappedAlign(rd, qu, coord, *refs, reflen, sc, ohang, minsc, res);
+			cout << "U\t" << b[1] << '\t' << b[2] << '\t' << b[3] << '\t' << refidx << '\t' << off << '\t'
+			     << (ohang ? 1 : 0) << '\t' << minsc << '\t' << reflen << '\t';
+			for(size_t i = 0; i < rd.length(); i++) {
+				TRefOff p = off + (TRefOff)i;
+				cout << ((p < 0 || (size_t)p >= reflen) ? 'N' : "ACGTN"[refs->getBase(refidx, (size_t)p)]);
+			}
+			cout << '\n' << "UR\t" << ret;
+			if(ret == 1) {
+				const AlnRes& r = res.alres;
+				cout << '\t' << r.score().score() << '\t' << r.score().ns() << '\t' << r.refNs() << '\t' << r.refoff()
+				     << '\t' << r.trimmed5p(true) << '\t' << r.trimmed3p(true) << '\t' << r.ned().size() << '\t';
+				for(size_t i = 0; i < r.ned().size(); i++) {
+					const Edit& e = r.ned()[i];
+					if(i) cout << ';';
+					cout << e.pos << ':' << (char)e.chr << ':' << (char)e.qchr << ':' << (int)e.type;
+				}
+			}
+			cout << '\n';
+		}
+		return 0;
 	}
 
 	if(bench) {

@@ -54,6 +54,55 @@ def oracle_dp(sc_struct, seq, qual, win, jobs, max_aln=8, cand_cap=None, edit_ca
     return results, cands[: nc.value], alns, edits[: ne.value]
 
 
+def oracle_ungapped(sc_struct, seq, qual, win, jobs):
+    lib = oracle_lib()
+    n = len(jobs)
+    cap = int(jobs["rd_len"].sum()) + 16
+    res = np.zeros(n, dtype=structs.ungap_result)
+    edits = np.zeros(cap, dtype=structs.edit)
+    ne = C.c_size_t(0)
+    rc = lib.bt2oracle_ungapped_batch(_ptr(sc_struct), _ptr(seq), _ptr(qual), _ptr(win), _ptr(jobs), C.c_size_t(n),
+                                      _ptr(res), _ptr(edits), C.c_size_t(cap), C.byref(ne))
+    assert rc == 0
+    return res, edits[: ne.value]
+
+
+def parse_ungapped_golden(path, sc):
+    """tests/golden/ungapped_*.txt (oracle/ref_dp_dump --ungapped) -> (seq, qual, win, jobs, expected)."""
+    code = {c: i for i, c in enumerate("ACGTN")}
+    seqs, quals, wins, jobs, exp = [], [], [], [], []
+    off = 0
+    for ln in open(path):
+        t = ln.rstrip("\n").split("\t")
+        if t[0] == "U":
+            rd = np.array([code[c] for c in t[1]], dtype=np.uint8)
+            seqs.append(rd); quals.append(np.frombuffer(t[2].encode(), dtype=np.uint8))
+            wins.append(np.array([code[c] for c in t[9]], dtype=np.uint8))
+            jobs.append((off, len(rd), off, int(t[7]), sc.nceil(len(rd)), 1 if t[3] == "+" else 0, int(t[6]),
+                         int(t[5]), int(t[8])))
+            off += len(rd)
+        elif t[0] == "UR":
+            if int(t[1]) == 1:
+                ed = [] if not t[9] else [(int(a), b, c, int(d)) for a, b, c, d in (x.split(":") for x in t[9].split(";"))]
+                exp.append((1, int(t[2]), int(t[3]), int(t[4]), int(t[5]), int(t[6]), int(t[7]), ed))
+            else:
+                exp.append((int(t[1]),))
+    j = np.zeros(len(jobs), dtype=structs.ungap_job)
+    a = np.array(jobs, dtype=np.int64)
+    for c, name in enumerate(("rd_off", "rd_len", "rf_off", "minsc", "nceil", "fw", "ohang", "off", "reflen")):
+        j[name] = a[:, c]
+    return np.concatenate(seqs), np.concatenate(quals), np.concatenate(wins), j, exp
+
+
+def ungapped_to_py(res, edits, i):
+    r = res[i]
+    if int(r["ret"]) != 1:
+        return (int(r["ret"]),)
+    e = edits[int(r["edit_off"]): int(r["edit_off"]) + int(r["nedits"])]
+    return (1, int(r["score"]), int(r["ns"]), int(r["refns"]), int(r["refoff"]), int(r["trim5"]), int(r["trim3"]),
+            [(int(x["pos"]), chr(x["chr"]), chr(x["qchr"]), int(x["type"])) for x in e])
+
+
 class RandomSource:
     """random_source.h:33-63 (LCG); used to replay SwAligner::nextAlignment's re-seed protocol."""
     A, Cc = 1664525, 1013904223

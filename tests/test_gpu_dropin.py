@@ -111,7 +111,10 @@ def test_near_exact_reads_one_mismatch_path(work):
     q = np.full((n, L), ord("I"), dtype=np.uint8)
     f = os.path.join(work, "near.fq")
     D.write_fastq(f, r, q, "near")
-    for tag, args in (("near", []), ("nearloc", ["--local"])):
+    # the last two leave no room for a gap in the score budget: SwDriver goes through ungappedAlign
+    # (aligner_sw_driver.cpp:1031-1060) before / instead of the DP
+    for tag, args in (("near", []), ("nearloc", ["--local"]), ("nearung", ["--score-min", "L,0,-0.2", "--rdg", "20,3", "--rfg", "20,3"]),
+                      ("nearungloc", ["--local", "--score-min", "L,0,1.95"])):
         base = os.path.join(work, "lambda")
         cpu, _ = D.run(D.CPU_SERVER, base, args, ["-U", f], os.path.join(work, tag + "_cpu.sam"))
         stats = os.path.join(work, tag + "_shim_stats.txt")
@@ -120,6 +123,8 @@ def test_near_exact_reads_one_mismatch_path(work):
         st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
         print(tag, st)
         assert st.get("onemm_calls_on_gpu", 0) > 0 and st.get("sweep_calls_on_gpu", 0) > 0, st
+        if "ung" in tag:
+            assert st.get("ungapped_calls_on_gpu", 0) > 0, st
         _check(cpu, gpu)
 
 
