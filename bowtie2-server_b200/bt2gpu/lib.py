@@ -23,7 +23,7 @@ SYMBOLS = [
     "bt2gpu_locate_stage", "bt2gpu_locate_run", "bt2gpu_locate_fetch", "bt2gpu_hotpath_round0_batch",
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
-    "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch",
+    "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch", "bt2gpu_frame_mate_rect_batch",
 ]
 
 _lib = None
@@ -323,6 +323,15 @@ class Context:
         out = np.zeros(len(jobs), dtype=structs.mate_frame)
         _check(self.lib.bt2gpu_frame_mate_batch(self._h, _ptr(pol), _ptr(jobs), C.c_size_t(len(jobs)), _ptr(out)))
         return out
+
+    def frame_mate_rect(self, trim_to_ref, jobs):
+        """DynProgFramer::frameFindMateRect for given otherMate windows -> (rects, ok)."""
+        jobs = np.ascontiguousarray(jobs, dtype=structs.mate_rect_job)
+        rects = np.zeros(len(jobs), dtype=structs.rect)
+        ok = np.zeros(len(jobs), dtype=np.uint8)
+        _check(self.lib.bt2gpu_frame_mate_rect_batch(self._h, C.c_int(1 if trim_to_ref else 0), _ptr(jobs),
+                                                     C.c_size_t(len(jobs)), _ptr(rects), _ptr(ok)))
+        return rects, ok
 
     def pe_classify(self, pol, jobs):
         jobs = np.ascontiguousarray(jobs, dtype=structs.pair_job)

@@ -140,3 +140,8 @@ ungap_job = np.dtype([("rd_off", "<u4"), ("rd_len", "<u4"), ("rf_off", "<u4"), (
 ungap_result = np.dtype([("ret", "<i4"), ("score", "<i4"), ("ns", "<i4"), ("refns", "<i4"), ("refoff", "<i8"),
                          ("trim5", "<u4"), ("trim3", "<u4"), ("nedits", "<u4"), ("edit_off", "<u4")], align=True)
 assert ungap_job.itemsize == 40 and ungap_result.itemsize == 40
+
+mate_rect_job = np.dtype([("ll", "<i8"), ("lr", "<i8"), ("rl", "<i8"), ("rr", "<i8"), ("reflen", "<i8"), ("maxns", "<i8"),
+                          ("rdlen", "<u4"), ("maxrdgap", "<u4"), ("maxrfgap", "<u4"), ("maxhalf", "<u4"),
+                          ("anchor_left", "u1"), ("pad", "u1", (7,))], align=True)
+assert mate_rect_job.itemsize == 72

@@ -41,6 +41,19 @@ k_frame_mate(const bt2gpu_mate_job *__restrict__ jobs, uint32_t n, bt2gpu_pe_pol
 }
 
 __global__ void __launch_bounds__(256)
+k_frame_mate_rect(const bt2gpu_mate_rect_job *__restrict__ jobs, uint32_t n, int trim, bt2gpu_rect *__restrict__ rects,
+                  uint8_t *__restrict__ ok)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n) return;
+	const bt2gpu_mate_rect_job j = jobs[i];
+	bt2gpu_rect r; memset(&r, 0, sizeof(r));
+	ok[i] = frame_mate(j.anchor_left != 0, j.ll, j.lr, j.rl, j.rr, j.rdlen, j.reflen, j.maxrdgap, j.maxrfgap, j.maxns,
+	                   j.maxhalf, trim != 0, r) ? 1 : 0;
+	rects[i] = r;
+}
+
+__global__ void __launch_bounds__(256)
 k_pe_classify(const bt2gpu_pair_job *__restrict__ jobs, uint32_t n, bt2gpu_pe_policy pol, int32_t *__restrict__ cls)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -140,6 +153,31 @@ extern "C" int bt2gpu_frame_mate_batch(bt2gpu_ctx *ctx, const bt2gpu_pe_policy *
 		cudaMemcpyAsync(out, dout, n * sizeof(*out), cudaMemcpyDeviceToHost, ctx->stream);
 		cudaError_t e = cudaStreamSynchronize(ctx->stream);
 		if(e != cudaSuccess) rc = fail("frame_mate", __FILE__, __LINE__, e);
+	} while(0);
+	buf.release();
+	return rc;
+}
+
+extern "C" int bt2gpu_frame_mate_rect_batch(bt2gpu_ctx *ctx, int trim_to_ref, const bt2gpu_mate_rect_job *jobs, size_t n,
+                                            bt2gpu_rect *rects, uint8_t *ok)
+{
+	FRAME_PROLOGUE(n);
+	if(n == 0) return 0;
+	DevBuf buf;
+	if(buf.reserve(carve_size({n * sizeof(*jobs), n * sizeof(*rects), n}))) return 1;
+	Carve c{buf.as<uint8_t>()};
+	auto *dj = c.take<bt2gpu_mate_rect_job>(n); auto *dr = c.take<bt2gpu_rect>(n); auto *dk = c.take<uint8_t>(n);
+	int rc = 0;
+	do {
+		if(cudaMemcpyAsync(dj, jobs, n * sizeof(*jobs), cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) { rc = fail("H2D", __FILE__, __LINE__); break; }
+		ctx->kstart();
+		k_frame_mate_rect<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(dj, (uint32_t)n, trim_to_ref, dr, dk);
+		ctx->launches++;
+		ctx->kend();
+		cudaMemcpyAsync(rects, dr, n * sizeof(*rects), cudaMemcpyDeviceToHost, ctx->stream);
+		cudaMemcpyAsync(ok, dk, n, cudaMemcpyDeviceToHost, ctx->stream);
+		cudaError_t e = cudaStreamSynchronize(ctx->stream);
+		if(e != cudaSuccess) rc = fail("frame_mate_rect", __FILE__, __LINE__, e);
 	} while(0);
 	buf.release();
 	return rc;

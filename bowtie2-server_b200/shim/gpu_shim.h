@@ -13,7 +13,7 @@ struct Read;
 
 namespace bt2shim {
 
-enum Counter { C_ALIGN = 0, C_ALN, C_UNGAPPED, C_SWEEP, C_ONEMM, C_SEEDS, C_EXTEND, C_FRAME, C_PECLASS, C_JOINED, C_NCOUNTERS };
+enum Counter { C_ALIGN = 0, C_ALN, C_UNGAPPED, C_SWEEP, C_ONEMM, C_SEEDS, C_EXTEND, C_LOCATE, C_FRAME, C_OTHERMATE, C_MATERECT, C_PECLASS, C_JOINED, C_NCOUNTERS };
 
 bt2gpu_ctx   *ctx();                         // this thread's context (created on first use; throws 1 on failure)
 void          bindScoring(const Scoring& sc);// bt2gpu_scoring_set once per (thread, Scoring object)

@@ -361,6 +361,18 @@ typedef struct {
 int bt2gpu_frame_mate_batch(bt2gpu_ctx *ctx, const bt2gpu_pe_policy *pol, const bt2gpu_mate_job *jobs, size_t n,
                             bt2gpu_mate_frame *out);
 
+/* DynProgFramer::frameFindMateRect alone (dp_framer.h:155-197 -> frameFindMateAnchorLeftRect /
+ * frameFindMateAnchorRightRect, dp_framer.cpp:177-357), for callers that already hold otherMate's
+ * window (ll, lr, rl, rr): the per-call seam of the reference-side shim. */
+typedef struct {
+	int64_t  ll, lr, rl, rr;
+	int64_t  reflen, maxns;
+	uint32_t rdlen, maxrdgap, maxrfgap, maxhalf;
+	uint8_t  anchor_left, pad[7];
+} bt2gpu_mate_rect_job;
+int bt2gpu_frame_mate_rect_batch(bt2gpu_ctx *ctx, int trim_to_ref, const bt2gpu_mate_rect_job *jobs, size_t n,
+                                 bt2gpu_rect *rects, uint8_t *ok);
+
 /* PairedEndPolicy::peClassifyPair (pe.cpp:37-136): cls[i] = BT2GPU_PE_ALS_*. */
 typedef struct { int64_t off1, off2; uint32_t len1, len2; uint8_t fw1, fw2, pad[6]; } bt2gpu_pair_job;
 int bt2gpu_pe_classify_batch(bt2gpu_ctx *ctx, const bt2gpu_pe_policy *pol, const bt2gpu_pair_job *jobs, size_t n,

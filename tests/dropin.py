@@ -36,8 +36,9 @@ def read_fasta(path):
     return names, seqs
 
 
-def build_index(fasta, base):
-    subprocess.check_call([os.path.join(BIN, "bowtie2-build-s"), "-q", fasta, base], stdout=subprocess.DEVNULL)
+def build_index(fasta, base, threads=1):
+    subprocess.check_call([os.path.join(BIN, "bowtie2-build-s"), "-q", "--threads", str(threads), fasta, base],
+                          stdout=subprocess.DEVNULL)
 
 
 def write_fastq(path, reads, quals, prefix, lens=None):

@@ -24,15 +24,15 @@ def work(tmp_path_factory):
     return w
 
 
-def _both(work, tag, server_args, client_args, index="lambda"):
+def _both(work, tag, server_args, client_args, index="lambda", threads=2):
     base = os.path.join(work, index)
-    cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"))
+    cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"), threads=threads)
     stats = os.path.join(work, tag + "_shim_stats.txt")
     gpu, err = D.run(D.GPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_gpu.sam"),
-                     env={"BT2GPU_SHIM_STATS": stats})
+                     env={"BT2GPU_SHIM_STATS": stats}, threads=threads)
     st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
     print(tag, st)
-    for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "frame_calls_on_gpu",
+    for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu",
               "joined_to_text_off_on_gpu", "kernel_launches"):
         assert st.get(k, 0) > 0, "%s: nothing ran on the GPU:\n%s\n%s" % (k, st, err[-2000:])
     return cpu, gpu, st["align_calls_on_gpu"]
@@ -56,7 +56,7 @@ def test_paired_end_to_end_sam_identical(work):
     cpu, gpu, calls = _both(work, "pe", [], ["-1", f1, "-2", f2])
     assert calls > 500
     st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(os.path.join(work, "pe_shim_stats.txt")).read()))
-    assert st["pe_classify_on_gpu"] > 0, st
+    assert st["pe_classify_on_gpu"] > 0 and st["other_mate_on_gpu"] > 0 and st["mate_rect_on_gpu"] > 0, st
     _check(cpu, gpu)
 
 
@@ -178,8 +178,40 @@ def test_config_c2_example_pairs(work):
     f1, f2 = _gunzip(work, "example_reads_1.fq.gz"), _gunzip(work, "example_reads_2.fq.gz")
     cpu, gpu, _ = _both(work, "c2", [], ["-1", f1, "-2", f2])
     st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(os.path.join(work, "c2_shim_stats.txt")).read()))
-    assert st["pe_classify_on_gpu"] > 0, st
+    assert st["pe_classify_on_gpu"] > 0 and st["other_mate_on_gpu"] > 0 and st["mate_rect_on_gpu"] > 0, st
     _check(cpu, gpu)
     # the same pairs in --local mode (the C4 policy on the C2 reads)
     cpu, gpu, _ = _both(work, "c2l", ["--local"], ["-1", f1, "-2", f2])
+    _check(cpu, gpu)
+
+
+def test_config_c3_c4_c5_shapes_on_random_genome(work):
+    """BASELINE.json configs[2..4] at test scale: a 3 Mbp i.i.d. random reference in 10 sequences, 150 bp
+    reads --very-sensitive (C3), 250 bp reads --local (C4), 2x150 pairs -I 0 -X 500 (C5); 4 worker threads, i.e. 4
+    GPU contexts driven concurrently."""
+    rng = np.random.default_rng(20261104)
+    chroms = [synth.random_genome(rng, 300000) for _ in range(10)]
+    fa = os.path.join(work, "rand.fa")
+    with open(fa, "w") as fh:
+        for i, c in enumerate(chroms):
+            fh.write(">chr%d\n" % i)
+            s = "".join("ACGT"[x] for x in c)
+            fh.write("\n".join(s[k:k + 60000] for k in range(0, len(s), 60000)) + "\n")
+    D.build_index(fa, os.path.join(work, "rand"))
+    g = np.concatenate(chroms)          # reads that straddle two sequences exercise the straddle rejection
+    r, q, _, _ = synth.simulate_reads(rng, g, 1500, 150)
+    f = os.path.join(work, "c3.fq")
+    D.write_fastq(f, r, q, "c3r")
+    cpu, gpu, _ = _both(work, "c3", ["--very-sensitive"], ["-U", f], index="rand", threads=4)
+    _check(cpu, gpu)
+    r, q, _, _ = synth.simulate_reads(rng, g, 800, 250)
+    f = os.path.join(work, "c4.fq")
+    D.write_fastq(f, r, q, "c4r")
+    cpu, gpu, _ = _both(work, "c4", ["--local"], ["-U", f], index="rand", threads=4)
+    _check(cpu, gpu)
+    r, q, _, _ = synth.simulate_pairs(rng, g, 800, 150)
+    f1, f2 = os.path.join(work, "c5_1.fq"), os.path.join(work, "c5_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "c5p")
+    D.write_fastq(f2, r[1::2], q[1::2], "c5p")
+    cpu, gpu, _ = _both(work, "c5", ["-I", "0", "-X", "500"], ["-1", f1, "-2", f2], index="rand", threads=4)
     _check(cpu, gpu)

@@ -120,3 +120,35 @@ def test_large_random_batch_matches_oracle():
         assert (int(f["oleft"]), int(f["ofw"]), int(f["ok"])) == (oleft, ofw, ok)
         assert _rect(f["rect"]) == r
     ctx.close()
+
+
+def test_mate_rect_alone_matches_oracle():
+    """bt2gpu_frame_mate_rect_batch (frameFindMateRect for a given otherMate window) against the framing oracle."""
+    rng = np.random.default_rng(77)
+    n = 20000
+    ctx = lib.Context(0)
+    fo = H.FrameOracle()
+    reflen = 100000
+    j = np.zeros(n, dtype=structs.mate_rect_job)
+    ll = rng.integers(-300, reflen + 100, n)
+    j["ll"] = ll
+    j["lr"] = ll + rng.integers(0, 400, n)
+    j["rl"] = j["lr"] + rng.integers(0, 200, n)
+    j["rr"] = j["rl"] + rng.integers(0, 400, n)
+    j["reflen"] = reflen
+    j["maxns"] = rng.integers(0, 40, n)
+    j["rdlen"] = rng.integers(20, 260, n)
+    j["maxrdgap"] = rng.integers(0, 30, n)
+    j["maxrfgap"] = rng.integers(0, 30, n)
+    j["maxhalf"] = 15
+    j["anchor_left"] = rng.integers(0, 2, n)
+    for trim in (0, 1):
+        rects, ok = ctx.frame_mate_rect(trim, j)
+        for k in rng.choice(n, 3000, replace=False):
+            jk = j[k]
+            eok, er = fo.frame_mate(int(jk["anchor_left"]), int(jk["ll"]), int(jk["lr"]), int(jk["rl"]), int(jk["rr"]),
+                                    int(jk["rdlen"]), reflen, int(jk["maxrdgap"]), int(jk["maxrfgap"]), int(jk["maxns"]), 15, trim)
+            assert int(ok[k]) == eok, jk
+            if eok:
+                assert _rect(rects[k]) == er, jk
+    ctx.close()
