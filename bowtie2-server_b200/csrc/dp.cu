@@ -634,13 +634,20 @@ struct BtJob {
 	__device__ __forceinline__ int h_move(int row, int col) const {
 		const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
 		const RowRef rc = mv.rowref(row), ru = mv.rowref(row > 0 ? row - 1 : 0);   // row 0: callers discard the result
-		// all neighbours are fetched up front (independent loads, one round trip)
+		// The diagonal wins whenever it is legal (ee_u8.cpp:1510-1520), and most cells of a walk are diagonal moves:
+		// its two cells are fetched first, the four gap neighbours (each a sector of its own in the wavefront layout)
+		// only when the diagonal fails -- a third of the sectors per walked cell for one more round trip at a gap.
 		const int sc_cur = mv.at(2, rc, col);
-		const int hu = mv.at(2, ru, col), fu = mv.at(1, ru, col);
 		const int cl = col > 0 ? col - 1 : 0;
-		const int hl = mv.at(2, rc, cl), el = mv.at(0, rc, cl), hd = mv.at(2, ru, cl);
+		if(col > 0) {
+			const int hd = mv.at(2, ru, cl);
+			const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
+			if((!local || hd > 0) && sc_cur == hd + sd) return 1;
+		}
 		int mask = 0;
 		if(gapsAllowed) {
+			const int hu = mv.at(2, ru, col), fu = mv.at(1, ru, col);
+			const int hl = mv.at(2, rc, cl), el = mv.at(0, rc, cl);
 			if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) mask |= 1;
 			if((!local || fu > 0) && sc_cur == fu - c_sc.rfe) mask |= 4;
 			if(col > 0) {
@@ -648,12 +655,7 @@ struct BtJob {
 				if((!local || el > 0) && sc_cur == el - c_sc.rde) mask |= 8;
 			}
 		}
-		if(col > 0) {
-			const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
-			if((!local || hd > 0) && sc_cur == hd + sd) mask |= 16;
-		}
-		if(mask & 16) return 1;            // diag > ref open > ref ext > read open > read ext
-		if(mask & 1) return 2;
+		if(mask & 1) return 2;             // (diag >) ref open > ref ext > read open > read ext
 		if(mask & 4) return 5;
 		if(mask & 2) return 3;
 		if(mask & 8) return 4;
