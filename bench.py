@@ -456,17 +456,17 @@ def run_ours(args, rank, world, local_rank):
             rl("k_dp_gather_e2e[mate windows]", 4.0 * cnt["mate_cells"] / RDLEN, kms["mate_dp_gather"] / K),
         ]
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures of this
-    # command at its default batch and genome (profiles/r1p_summary.md for --mode pairs, profiles/r1z_summary.md for
-    # --mode e2e); other workloads: not captured
+    # command at its default batch and genome (profiles/r1q_summary.md for --mode pairs, profiles/r1z_summary.md for
+    # --mode e2e, whose backtrace capture predates the diagonal-first move test: not restated); other workloads: not captured
     if args.batch == 262144 and args.genome_mbp == 1024 and not LOCAL:
         if PAIRED:
             traffic = {"k_exact_sweep": 0.413e9, "k_seed_exact": 0.712e9, "k_extend": 0.532e9, "k_locate": 0.162e9,
-                       "k_dp_fill": 10.627e9, "k_dp_gather_e2e": 0.115e9, "k_dp_backtrace": 9.885e9,
-                       "k_dp_fill[mate windows]": 33.918e9, "k_dp_gather_e2e[mate windows]": 0.304e9,
-                       "k_dp_backtrace[mate windows]": 10.411e9}
+                       "k_dp_fill": 10.624e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 4.885e9,
+                       "k_dp_fill[mate windows]": 33.921e9, "k_dp_gather_e2e[mate windows]": 0.304e9,
+                       "k_dp_backtrace[mate windows]": 5.493e9}
         else:
             traffic = {"k_exact_sweep": 0.409e9, "k_seed_exact": 0.710e9, "k_extend": 0.526e9, "k_locate": 0.159e9,
-                       "k_dp_fill": 10.582e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 9.806e9}
+                       "k_dp_fill": 10.582e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": None}
         for r_ in rls:
             r_["traffic"] = traffic.get(r_["kernel"])
     dominant = max(rls, key=lambda r: r["ms"])
