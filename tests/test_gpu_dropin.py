@@ -215,3 +215,45 @@ def test_config_c3_c4_c5_shapes_on_random_genome(work):
     D.write_fastq(f2, r[1::2], q[1::2], "c5p")
     cpu, gpu, _ = _both(work, "c5", ["-I", "0", "-X", "500"], ["-1", f1, "-2", f2], index="rand", threads=4)
     _check(cpu, gpu)
+
+
+# Cases restated from the reference's own regression table (scripts/test/simple_tests.pl: "Gap penalties 1-7" :3760-3875,
+# "N filtering 1-3" :3877-...): tiny references (16-31 bp, far shorter than the ftab), seeds of length 2, gap budgets
+# that just allow / just forbid one gap.  (reference, read, --policy string, expected offset or None, expected CIGAR)
+_GP = "MMP=C30;SEED=0;SEEDLEN=2;IVAL=C,1,0;%s;MIN=L,-3,-3"
+SIMPLE_CASES = [
+    ("gap1", "TTGTTCGTTTGTTCGT", "TTGTTCTTTGTT", _GP % "RDG=29,10;RFG=25,15", 0, "6M1D6M"),
+    ("gap2", "TTGTTCGTTTGTTCGT", "TTGTTCTTTGTT", _GP % "RDG=30,10;RFG=25,15", None, "*"),
+    ("gap3", "TTGTTCGTTTGTTCGT", "TTGTTCGATTTGTT", _GP % "RDG=25,15;RFG=30,15", 0, "7M1I6M"),
+    ("gap4", "TTGTTCGTTTGTTCGT", "TTGTTCGATTTGTT", _GP % "RDG=25,15;RFG=30,16", None, "*"),
+    ("gap5", "TTGTTCGTTTGTTCGT", "TTGTTCGATTTGTT", _GP % "RDG=25,15;RFG=31,15", None, "*"),
+    ("gap6", "ATTGTTCGTTTGTTCGTA", "ATTGTTGTTTGATTCGTA", _GP % "RDG=19,10;RFG=18,10", 0, "6M1D5M1I6M"),
+    ("gap7", "TTGTTCGTTTGTTCGT", "TTGTTGTTTGATTCGT", _GP % "RDG=16,10;RFG=16,10", None, "*"),
+    ("nfilt1", "GAGACTTTATACGCATCGAACTATCGCTCTA", "ATACGCATCGAAC", "NCEIL=L,0,0", 8, "13M"),
+    ("nfilt2", "GAGACTTTATNCGCATCGAACTATCGCTCTA", "ATACGCATCGAAC", "NCEIL=L,0,0", None, "*"),
+    ("nfilt3", "GAGACTTTATACGCATCGAANTATCGCTCTA", "ATACGCATCGAAC", "NCEIL=L,0,0", None, "*"),
+]
+
+
+@pytest.mark.parametrize("case", SIMPLE_CASES, ids=[c[0] for c in SIMPLE_CASES])
+def test_reference_regression_cases(work, case):
+    name, ref, read, policy, off, cigar = case
+    fa = os.path.join(work, name + ".fa")
+    with open(fa, "w") as fh:
+        fh.write(">0\n%s\n" % ref)
+    D.build_index(fa, os.path.join(work, name))
+    fq = os.path.join(work, name + ".fq")
+    with open(fq, "w") as fh:
+        fh.write("@r0\n%s\n+\n%s\n" % (read, "I" * len(read)))
+    base = os.path.join(work, name)
+    args = ["-a", "--policy", policy]
+    cpu, _ = D.run(D.CPU_SERVER, base, args, ["-U", fq], os.path.join(work, name + "_cpu.sam"), threads=1)
+    gpu, _ = D.run(D.GPU_SERVER, base, args, ["-U", fq], os.path.join(work, name + "_gpu.sam"), threads=1,
+                   env={"BT2GPU_SHIM_STATS": os.path.join(work, name + "_stats.txt")})
+    assert cpu == gpu, (cpu, gpu)
+    f = cpu[0].split("\t")
+    assert f[5] == cigar, cpu[0]
+    if off is None:
+        assert f[2] == "*"
+    else:
+        assert int(f[3]) - 1 == off, cpu[0]
