@@ -100,3 +100,32 @@ def genome_codes(fasta="lambda.fa"):
 
 def lambda_genome():
     return genome_codes("lambda.fa")[0]
+
+
+def write_case_inputs(case, work, tag):
+    """Index + read files of one restated regression case (tests/golden/simple_cases.json).  Like the reference's
+    runner, unpaired reads are given forward and reverse-complemented (unless the case says nofw / norc).
+    Returns (index base, server args, client args)."""
+    base = os.path.join(work, tag)
+    with open(base + ".fa", "w") as fh:
+        for i, r in enumerate(case["ref"]):
+            fh.write(">%d\n%s\n" % (i, r))
+    build_index(base + ".fa", base)
+    comp = str.maketrans("ACGTNacgtn", "TGCANtgcan")
+    args = list(case["args"])
+    if "reads" in case:
+        fq = base + ".fq"
+        with open(fq, "w") as fh:
+            for i, r in enumerate(case["reads"]):
+                q = case["quals"][i] if "quals" in case and i < len(case["quals"]) else "I" * len(r)
+                if not case.get("nofw"):
+                    fh.write("@r%d\n%s\n+\n%s\n" % (i, r, q))
+                if not case.get("norc"):
+                    fh.write("@rc%d\n%s\n+\n%s\n" % (i, r.translate(comp)[::-1], q[::-1]))
+        return base, args, ["-U", fq]
+    f1, f2 = base + "_1.fq", base + "_2.fq"
+    for f, ms in ((f1, case["mate1s"]), (f2, case["mate2s"])):
+        with open(f, "w") as fh:
+            for i, r in enumerate(ms):
+                fh.write("@p%d\n%s\n+\n%s\n" % (i, r, "I" * len(r)))
+    return base, args + [case["orient"]], ["-1", f1, "-2", f2]

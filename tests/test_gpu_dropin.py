@@ -257,3 +257,26 @@ def test_reference_regression_cases(work, case):
         assert f[2] == "*"
     else:
         assert int(f[3]) - 1 == off, cpu[0]
+
+
+# The reference's regression table, restated (scripts/restate_simple_tests.py -> tests/golden/simple_cases.json: every
+# case of scripts/test/simple_tests.pl that gives its reads inline and that the stock server accepts; seeds with
+# mismatches excluded).  The default run takes every fourth case; BT2GPU_ALL_SIMPLE_CASES=1 takes all of them.
+import json
+
+_ALL = json.load(open(os.path.join(D.GOLDEN, "simple_cases.json")))
+_SEL = _ALL if os.environ.get("BT2GPU_ALL_SIMPLE_CASES") else _ALL[::4]
+
+
+@pytest.mark.parametrize("ci", range(len(_SEL)), ids=["%03d" % i for i in range(len(_SEL))])
+def test_restated_regression_table(work, ci):
+    case = _SEL[ci]
+    base, sargs, cargs = D.write_case_inputs(case, work, "sc%03d" % ci)
+    cpu, _ = D.run(D.CPU_SERVER, base, sargs, cargs, base + "_cpu.sam", threads=1)
+    gpu, _ = D.run(D.GPU_SERVER, base, sargs, cargs, base + "_gpu.sam", threads=1)
+    assert cpu == gpu, (case["name"], case["args"], cpu, gpu)
+    if "cigar" in case and "reads" in case and len(case["cigar"]) == len(case["reads"]) and not case.get("nofw"):
+        got = {ln.split("\t")[0].split("/")[0]: ln.split("\t")[5] for ln in cpu}
+        for i, cg in enumerate(case["cigar"]):
+            if "r%d" % i in got and "-k" not in case["args"] and "-a" not in case["args"]:
+                assert got["r%d" % i] == cg, (case["name"], got, case["cigar"])
