@@ -118,6 +118,81 @@ __device__ __forceinline__ void octet_lf(const IndexDev &ix, uint32_t top, uint3
 	topc = h ? oc : c;
 }
 
+// A search that follows one known symbol and has no mirror range to carry (exactSweep) does not need all four
+// ranks (the LT form, which also serves mapBiLFEx's mirror update, measured slower than the four-symbol rank in the
+// seed kernel -- 0.57 -> 0.61 ms -- and is kept for reference only).
+// quad_lf_c: LF(row, c) alone -- one pop-count per word instead of three -- and, when LT, the number of
+// BWT symbols below c before `row` plus their side totals (lt = sum over j < c of occ_side[j] + #j), which is all
+// mapBiLFEx's mirror-range update needs: topb' = topb + sum_{j<c} (b[j] - t[j]), where fchr cancels
+// (bt2_idx.h:2395-2411).  The '$' correction (stored as A, bt2_idx.h:1891-1899) applies to A's count.
+template<bool LT>
+__device__ __forceinline__ void quad_lf_c(const IndexDev &ix, uint32_t row, int c, unsigned gmask, int q,
+                                          uint32_t &val, uint32_t &lt, int &rowc)
+{
+	const uint32_t side = row / 192u;
+	const int co = (int)(row - side * 192u);
+	const uint4 v = __ldg(ix.sides + (size_t)side * 4 + q);
+	uint32_t pk = 0;
+	int myc = 0;
+	if(q < 3) {
+		int m = co - 64 * q;
+		m = m < 0 ? 0 : (m > 64 ? 64 : m);
+		const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+		const uint32_t pat = (uint32_t)c * 0x55555555u;
+		uint32_t nc = 0, nlt = 0;
+#pragma unroll
+		for(int k = 0; k < 4; k++) {
+			int mw = m - 16 * k;
+			mw = mw < 0 ? 0 : mw;
+			const uint32_t pm = pos_mask16(mw);
+			const uint32_t x = ~(w[k] ^ pat);
+			nc += __popc(x & (x >> 1) & pm);
+			if(LT) {
+				const uint32_t lo = w[k], hi = w[k] >> 1;
+				// symbol < c:  c=1: A;  c=2: high bit clear;  c=3: not T
+				const uint32_t ltm = c == 1 ? ~(lo | hi) : (c == 2 ? ~hi : ~(lo & hi));
+				nlt += __popc(ltm & pm);
+			}
+		}
+		if(LT && c == 0) nlt = 0;
+		pk = nc | (nlt << 16);
+		const int ci = co - 64 * q;                               // my slot of the row's own char
+		if(ci >= 0 && ci < 64) myc = (int)((w[ci >> 4] >> (2 * (ci & 15))) & 3u);
+	}
+	pk += __shfl_xor_sync(gmask, pk, 1);
+	pk += __shfl_xor_sync(gmask, pk, 2);
+	// lane 3 of the quad holds occ[A,C,G,T] of the side
+	const uint32_t oc_mine = c == 0 ? v.x : (c == 1 ? v.y : (c == 2 ? v.z : v.w));
+	const uint32_t oc = __shfl_sync(gmask, oc_mine, 3, 4);
+	rowc = __shfl_sync(gmask, myc, co >> 6, 4);
+	const uint32_t fix = (side == ix.zside && (uint32_t)co > ix.zco) ? 1u : 0u;
+	val = ix.fchr[c] + oc + (pk & 0xffffu) - (c == 0 ? fix : 0u);
+	if(LT) {
+		const uint32_t ol_mine = (c > 0 ? v.x : 0u) + (c > 1 ? v.y : 0u) + (c > 2 ? v.z : 0u);
+		const uint32_t ol = __shfl_sync(gmask, ol_mine, 3, 4);
+		lt = ol + (pk >> 16) - (c > 0 ? fix : 0u);
+	} else lt = 0;
+}
+
+// octet_lf_c: lanes 0-3 rank `top`, lanes 4-7 rank `bot` for the one symbol c; every lane gets LF(top,c), LF(bot,c),
+// rowL(top) and, when LT, below = sum_{j<c} (LF(bot,j) - LF(top,j)).
+template<bool LT>
+__device__ __forceinline__ void octet_lf_c(const IndexDev &ix, uint32_t top, uint32_t bot, int c, unsigned gmask, int l8,
+                                           uint32_t &tc, uint32_t &bc, uint32_t &below, int &topc)
+{
+	const int h = l8 >> 2;
+	uint32_t mine, lt; int rc;
+	quad_lf_c<LT>(ix, h ? bot : top, c, gmask, l8 & 3, mine, lt, rc);
+	const uint32_t other = __shfl_xor_sync(gmask, mine, 4);
+	tc = h ? other : mine; bc = h ? mine : other;
+	if(LT) {
+		const uint32_t olt = __shfl_xor_sync(gmask, lt, 4);
+		below = h ? lt - olt : olt - lt;
+	} else below = 0;
+	const int oc = __shfl_xor_sync(gmask, rc, 4);
+	topc = h ? oc : rc;
+}
+
 // v[c] without dynamic register indexing (keeps t[]/b[] out of local memory)
 __device__ __forceinline__ uint32_t pick4(const uint32_t v[4], int c) {
 	return c == 0 ? v[0] : (c == 1 ? v[1] : (c == 2 ? v[2] : v[3]));
@@ -302,14 +377,14 @@ k_exact_sweep(const IndexDev ix, const uint8_t *__restrict__ seq, const bt2gpu_r
 			const int c = s.at(len - dep - 1);
 			if(c > 3) top = bot = 0;
 			else {
-				uint32_t t[4], b[4]; int topc;
+				uint32_t tc, bc, below; int topc;
 				const bool single = (bot - top == 1);
-				octet_lf(ix, top, single ? top : bot, gmask, l8, t, b, topc);
+				octet_lf_c<false>(ix, top, single ? top : bot, c, gmask, l8, tc, bc, below, topc);
 				if(single) {
 					bwops++;
 					if(topc != c || top == ix.zoff) top = bot = 0;
-					else { top = pick4(t, c); bot = top + 1; }
-				} else { bwops += 2; top = pick4(t, c); bot = pick4(b, c); }
+					else { top = tc; bot = top + 1; }
+				} else { bwops += 2; top = tc; bot = bc; }
 			}
 			if(bot <= top) {
 				nedit++;
