@@ -251,7 +251,7 @@ def run_reference(args, rank, world):
                              "sample": "%d reads per step through the unmodified reference (oracle/_ref/ref_seed_dump "
                                        "--bench + ref_dp_dump --bench, %d threads)" % (sample, ncores)},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -506,10 +506,31 @@ def run_ours(args, rank, world, local_rank):
                                               "ref_dp_dump --bench, %d threads)" % (sample, ncores)}
         except Exception as e:   # oracle/_ref missing on this box
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: %r" % (e,)}
-    print(json.dumps(line))
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on the first
+    communicator whatever NCCL_DEBUG level is set above VERSION): from here on file descriptor 1 goes to stderr and the
+    JSON line is written to the original stdout by emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -532,7 +553,7 @@ def main():
         RDLEN, SEED_LEN, IVAL, LOCAL = 250, 20, (1.0, 0.75), True
         args.no_cpu_baseline = True
         if args.impl == "reference":
-            print(json.dumps({"impl": "reference", "unavailable": "the reference arm times the end-to-end workload only"}))
+            emit({"impl": "reference", "unavailable": "the reference arm times the end-to-end workload only"})
             return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
