@@ -377,9 +377,17 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	for(int rix = lane; rix < nrec; rix += 32) {
 		const int l = rix & (GL - 1), t = (rix >> 3) % T, st = (rix >> 3) / T;
 		const uint32_t *rp = mv.base + (size_t)(rix >> 3) * GL * mv.RW;   // whole records, word-addressed (s16 layout: local mode)
-		for(int k = 0; k < S; k++) {
-			const int idx = 2 * S + k;
-			const uint32_t w = __ldcg(rp + ((idx >> 2) * GL + l) * 4 + (idx & 3));
+		// H words 2S..3S-1 of this lane, a 16-byte chunk (four words) per load: the 8 lanes' chunks of one index are
+		// one contiguous 128-byte line, so a warp's load is fully coalesced
+		for(int ch = (2 * S) >> 2; ch <= (3 * S - 1) >> 2; ch++) {
+		const uint4 q4 = __ldcg(reinterpret_cast<const uint4*>(rp + (ch * GL + l) * 4));
+		const uint32_t qw[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+		for(int jw = 0; jw < 4; jw++) {
+			const int idx = 4 * ch + jw;
+			if(idx < 2 * S || idx >= 3 * S) continue;
+			const int k = idx - 2 * S;
+			const uint32_t w = qw[jw];
 #pragma unroll
 			for(int half = 0; half < 2; half++) {
 				const int v = 2 * l + half;
@@ -398,6 +406,7 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 					}
 				}
 			}
+		}
 		}
 	}
 	if(EMIT) return;
