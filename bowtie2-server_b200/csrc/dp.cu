@@ -845,11 +845,11 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 				if(ci < ncand) {
 					const bt2gpu_dp_cand c = cd[ci];
 					keepc = c.score >= jb.minsc && !J.reported((int)c.row, (int)c.col);
+					// |row - dr| <= SQ && |col - dc| <= SQ as two unsigned range tests (x - d + SQ <= 2 SQ)
+					const uint32_t rs = c.row + SQ, cs = c.col + SQ, SQ2 = 2 * SQ;
 					for(uint32_t i = 0; keepc && i < ndone; i++) {
 						const uint32_t dv = done[i];
-						const uint32_t dr = dv >> 16, dc = dv & 0xffff;
-						const uint32_t rh = max(c.row, dr), rl = min(c.row, dr), ch = max(c.col, dc), cl = min(c.col, dc);
-						if(ch - cl <= SQ && rh - rl <= SQ) keepc = false;
+						if(rs - (dv >> 16) <= SQ2 && cs - (dv & 0xffff) <= SQ2) keepc = false;
 					}
 				}
 				const unsigned keep = __ballot_sync(FULL, keepc);
