@@ -456,11 +456,11 @@ def run_ours(args, rank, world, local_rank):
             rl("k_dp_gather_e2e[mate windows]", 4.0 * cnt["mate_cells"] / RDLEN, kms["mate_dp_gather"] / K),
         ]
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures of this
-    # command at its default batch and genome (profiles/r1q_summary.md for --mode pairs, profiles/r1z_summary.md for
+    # command at its default batch and genome (profiles/r1r_summary.md for --mode pairs, profiles/r1z_summary.md for
     # --mode e2e, whose backtrace capture predates the diagonal-first move test: not restated); other workloads: not captured
     if args.batch == 262144 and args.genome_mbp == 1024 and not LOCAL:
         if PAIRED:
-            traffic = {"k_exact_sweep": 0.413e9, "k_seed_exact": 0.712e9, "k_extend": 0.532e9, "k_locate": 0.162e9,
+            traffic = {"k_exact_sweep": 0.453e9, "k_seed_exact": 0.713e9, "k_extend": 0.532e9, "k_locate": 0.162e9,
                        "k_dp_fill": 10.624e9, "k_dp_gather_e2e": 0.112e9, "k_dp_backtrace": 4.885e9,
                        "k_dp_fill[mate windows]": 33.921e9, "k_dp_gather_e2e[mate windows]": 0.304e9,
                        "k_dp_backtrace[mate windows]": 5.493e9}
