@@ -35,39 +35,44 @@ def _key21(codes3, pos):
     return k
 
 
-def _all_keys21(codes3, n1):
-    """_key21 for every position 0..n1-1 by doubling (codes3 is padded with >= 21 sevens)."""
-    k1 = codes3.to(torch.int64)
+def _keys21_range(codes3, lo, hi):
+    """_key21 for the contiguous positions lo..hi-1 by doubling (codes3 is padded with >= 42 sevens)."""
+    m = hi - lo
+    k1 = codes3[lo:hi + 2 * _KCH].to(torch.int64)
     k2 = (k1[:-1] << 3) | k1[1:]
     k4 = (k2[:-2] << 6) | k2[2:]
     del k2
     k8 = (k4[:-4] << 12) | k4[4:]
     k16 = (k8[:-8] << 24) | k8[8:]
     del k8
-    k20 = (k16[:n1 + 1] << 12) | k4[16:16 + n1 + 1]
+    k20 = (k16[:m + 1] << 12) | k4[16:16 + m + 1]
     del k16, k4
-    k21 = (k20[:n1] << 3) | k1[20:20 + n1]
-    return k21
+    return (k20[:m] << 3) | k1[20:20 + m]
 
 
-def suffix_array(s, device):
-    """SA of s (uint8 codes 0..3) with the end of text greater than every base; n+1 rows."""
-    n = int(s.numel())
-    codes3 = torch.cat([s.to(device), torch.full((2 * _KCH + 8,), 7, dtype=torch.uint8, device=device)])
-    keys = _all_keys21(codes3, n + 1)
-    skey, sa = torch.sort(keys)
-    del keys
-    n1 = n + 1
-    # group id = first SA position of the run of equal keys
-    new = torch.ones(n1, dtype=torch.bool, device=device)
+_CHUNK = 1 << 27        # rows per pass of the chunked whole-array operations
+_PFX_BITS = 12          # bucket histogram over the first 4 bases of a key (3 bits each)
+
+
+def _sort_bucket(codes3, pos, keys, n):
+    """Suffix order of the positions `pos` (int64) whose 21-base keys are `keys`: sort by key, then
+    break ties 21 more bases at a time (suffixes of one bucket never tie with another bucket's)."""
+    device = pos.device
+    skey, o = torch.sort(keys)
+    sa = pos[o]
+    del o
+    m = int(sa.numel())
+    new = torch.ones(m, dtype=torch.bool, device=device)
     new[1:] = skey[1:] != skey[:-1]
     del skey
+    if bool(new.all()):
+        return sa
     starts = torch.nonzero(new).squeeze(1)
-    grp = starts[torch.cumsum(new, 0) - 1]            # first SA position of each run
+    grp = starts[torch.cumsum(new, 0) - 1]            # first local position of each run of equal keys
     del starts, new
     depth = _KCH
     while True:
-        tied = torch.zeros(n1, dtype=torch.bool, device=device)
+        tied = torch.zeros(m, dtype=torch.bool, device=device)
         same_next = grp[1:] == grp[:-1]
         tied[1:] |= same_next
         tied[:-1] |= same_next
@@ -90,6 +95,50 @@ def suffix_array(s, device):
     return sa
 
 
+def suffix_array(s, device, bucket_rows=1 << 27):
+    """SA of s (uint8 codes 0..3) with the end of text greater than every base; n+1 rows (int64).
+
+    Memory-lean for human-scale texts (3.1 G rows on one 180 GB device): the 21-base keys of all
+    positions are computed chunk by chunk into one int64 array, the rows are cut into buckets of at
+    most ~bucket_rows suffixes by the first four bases of their key (consecutive key ranges, so the
+    buckets are consecutive SA ranges), and each bucket is sorted and tie-broken on its own."""
+    n = int(s.numel())
+    n1 = n + 1
+    codes3 = torch.cat([s.to(device), torch.full((2 * _KCH + 8,), 7, dtype=torch.uint8, device=device)])
+    keys = torch.empty(n1, dtype=torch.int64, device=device)
+    for lo in range(0, n1, _CHUNK):
+        hi = min(n1, lo + _CHUNK)
+        keys[lo:hi] = _keys21_range(codes3, lo, hi)
+    if n1 <= bucket_rows:
+        return _sort_bucket(codes3, torch.arange(n1, dtype=torch.int64, device=device), keys, n)
+    shift = 3 * _KCH - _PFX_BITS
+    hist = torch.zeros(1 << _PFX_BITS, dtype=torch.int64, device=device)
+    for lo in range(0, n1, _CHUNK):
+        hist += torch.bincount(keys[lo:lo + _CHUNK] >> shift, minlength=1 << _PFX_BITS)
+    hist = hist.cpu().tolist()
+    sa = torch.empty(n1, dtype=torch.int64, device=device)
+    out, b0 = 0, 0
+    while b0 < len(hist):
+        b1, cnt = b0 + 1, hist[b0]
+        while b1 < len(hist) and cnt + hist[b1] <= bucket_rows:
+            cnt += hist[b1]
+            b1 += 1
+        if cnt:
+            klo, khi = b0 << shift, b1 << shift          # khi = 2^63 for the last bucket: no upper bound then
+            parts = []
+            for lo in range(0, n1, _CHUNK):
+                kc = keys[lo:lo + _CHUNK]
+                m = (kc >= klo) & (kc < khi) if b1 < len(hist) else (kc >= klo)
+                parts.append(torch.nonzero(m).squeeze(1) + lo)
+            pos = torch.cat(parts)
+            del parts
+            sa[out:out + cnt] = _sort_bucket(codes3, pos, keys[pos], n)
+            out += cnt
+        b0 = b1
+    assert out == n1
+    return sa
+
+
 def _kmers(s, k, device):
     """Integer of the k bases starting at every i <= n-k (first base most significant)."""
     n = int(s.numel())
@@ -100,7 +149,7 @@ def _kmers(s, k, device):
     return v
 
 
-def build_ebwt(s, fw, off_rate=4, ftab_chars=10, line_rate=6, device=None, want_offs=True):
+def build_ebwt(s, fw, off_rate=4, ftab_chars=10, line_rate=6, device=None, want_offs=True, bucket_rows=1 << 27):
     """One Ebwt over the joined text s (torch uint8 codes 0..3), as Ebwt::buildToDisk writes it."""
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
     e = EbwtData(fw)
@@ -109,50 +158,67 @@ def build_ebwt(s, fw, off_rate=4, ftab_chars=10, line_rate=6, device=None, want_
     e.derive()
     n = e.len
     s = s.to(device)
-    sa = suffix_array(s, device)
+    sa = suffix_array(s, device, bucket_rows=bucket_rows)
     # ---- BWT, zOff, sides ----
-    zrow = torch.nonzero(sa == 0).squeeze(1)
-    e.zoff = int(zrow[0])
-    bwt = s[torch.clamp(sa - 1, min=0)]
-    bwt[e.zoff] = 0
     rows_pad = e.num_sides * e.side_bwt_len
     bp = torch.zeros(rows_pad, dtype=torch.uint8, device=device)
-    bp[:n + 1] = bwt
+    e.zoff = -1
+    for lo in range(0, n + 1, _CHUNK):
+        c = sa[lo:lo + _CHUNK]
+        z = torch.nonzero(c == 0).squeeze(1)
+        if z.numel():
+            e.zoff = lo + int(z[0])
+        bp[lo:lo + c.numel()] = s[torch.clamp(c - 1, min=0)]
+    bp[e.zoff] = 0
     q = bp.view(-1, 4)
     packed = (q[:, 0] | (q[:, 1] << 2) | (q[:, 2] << 4) | (q[:, 3] << 6)).view(e.num_sides, e.side_bwt_sz)
     cnt = torch.stack([(bp.view(e.num_sides, e.side_bwt_len) == c).sum(1) for c in range(4)], 1)   # [sides,4]
+    # the zero padding after row n lies in the last side only and occ[] counts what precedes a side: no correction
     zside = e.zoff // e.side_bwt_len
     cnt[zside, 0] -= 1                                       # the '$' is not an A
     occ = torch.cumsum(cnt, 0) - cnt                         # counted before each side
+    del bp, q
     sides = torch.zeros((e.num_sides, e.side_sz), dtype=torch.uint8, device=device)
     sides[:, :e.side_bwt_sz] = packed
+    del packed
     occ32 = occ.to(torch.int64)
     for c in range(4):
         for b in range(4):
             sides[:, e.side_bwt_sz + 4 * c + b] = ((occ32[:, c] >> (8 * b)) & 0xFF).to(torch.uint8)
     e.ebwt = sides.reshape(-1).cpu().numpy()
+    del sides, occ, occ32, cnt
     # ---- fchr ----
-    tot = torch.bincount(s.to(torch.int64), minlength=4).cpu().numpy().astype(np.int64)
+    tot = np.array([int((s == c).sum()) for c in range(4)], dtype=np.int64)
     e.fchr = np.concatenate([[0], np.cumsum(tot)]).astype(np.uint32)
     # ---- ftab / eftab ----
+    # count[k] = suffixes of at least ftab_chars bases that start with 10-mer k; the (at most ftab_chars + 1)
+    # shorter suffixes are "absorbed" in front of the next long row's 10-mer
     nk = 1 << (2 * ftab_chars)
-    long_mask = (n - sa) >= ftab_chars
-    km = _kmers(s, ftab_chars, device)
-    if km.numel():
-        row_km = km[torch.clamp(sa, max=max(km.numel() - 1, 0))].to(torch.int64)
-        count = torch.bincount(row_km[long_mask], minlength=nk).cpu().numpy().astype(np.int64)
-    else:
-        row_km = torch.zeros(n + 1, dtype=torch.int64, device=device)
-        count = np.zeros(nk, dtype=np.int64)
+    count_t = torch.zeros(nk, dtype=torch.int64, device=device)
+    nlong = max(n - ftab_chars + 1, 0)
+    for lo in range(0, nlong, _CHUNK):
+        hi = min(nlong, lo + _CHUNK)
+        count_t += torch.bincount(_kmers(s[lo:hi + ftab_chars - 1], ftab_chars, device).to(torch.int64), minlength=nk)
+    count = count_t.cpu().numpy().astype(np.int64)
+    del count_t
+
+    def kmer_at(p):
+        v = 0
+        for c in s[p:p + ftab_chars].cpu().tolist():
+            v = (v << 2) | int(c)
+        return v
+    short_rows = []
+    for lo in range(0, n + 1, _CHUNK):
+        z = torch.nonzero(sa[lo:lo + _CHUNK] > n - ftab_chars).squeeze(1)
+        short_rows += [lo + int(x) for x in z.cpu().tolist()]
+    short_set = set(short_rows)
     absorb = np.zeros(nk + 1, dtype=np.int64)
-    short_rows = torch.nonzero(~long_mask).squeeze(1).cpu().numpy()
-    long_cpu = None
-    for r in short_rows:                                     # <= ftab_chars rows
-        r2 = int(r) + 1
-        while r2 <= n and not bool(long_mask[r2]):
+    for r in short_rows:                                     # <= ftab_chars + 1 rows
+        r2 = r + 1
+        while r2 <= n and r2 in short_set:
             r2 += 1
         if r2 <= n:
-            absorb[int(row_km[r2])] += 1
+            absorb[kmer_at(int(sa[r2]))] += 1
         else:
             absorb[nk] += 1
     before = np.concatenate([[0], np.cumsum(count)])         # long rows before 10-mer i
@@ -193,7 +259,7 @@ def fragments(seqs):
     return frags, recs
 
 
-def build_index(seqs, names=None, off_rate=4, ftab_chars=10, device=None):
+def build_index(seqs, names=None, off_rate=4, ftab_chars=10, device=None, bucket_rows=1 << 27):
     """seqs: list of numpy uint8 code arrays (0..3, 4 = N).  Returns (Index, extras) where extras
     holds what the .3/.4.bt2 files need."""
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
@@ -201,8 +267,8 @@ def build_index(seqs, names=None, off_rate=4, ftab_chars=10, device=None):
     frags, recs = fragments(seqs)
     joined = np.concatenate([seqs[si][a:a + ln] for si, a, ln in frags]) if frags else np.zeros(0, np.uint8)
     s = torch.from_numpy(np.ascontiguousarray(joined))
-    fw = build_ebwt(s, True, off_rate, ftab_chars, device=device)
-    bw = build_ebwt(torch.flip(s, [0]), False, off_rate, ftab_chars, device=device)
+    fw = build_ebwt(s, True, off_rate, ftab_chars, device=device, bucket_rows=bucket_rows)
+    bw = build_ebwt(torch.flip(s, [0]), False, off_rate, ftab_chars, device=device, bucket_rows=bucket_rows)
     plen = np.array([len(x) for x in seqs], dtype=np.uint32)
     rs, pos = [], 0
     for si, a, ln in frags:

@@ -24,6 +24,7 @@ SYMBOLS = [
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
     "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch", "bt2gpu_frame_mate_rect_batch",
+    "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
 ]
 
 _lib = None
@@ -278,6 +279,12 @@ class Context:
         self._cand_cap, self._edit_cap = 4096 * max(nj.value, 1), len(out["edits"])
         return out, S.as_dict()
 
+    def hotpath_job_tidx(self, njobs):
+        """Reference sequence of every DP job of the last hotpath_* call (job_start / refoff are offsets inside it)."""
+        t = np.zeros(max(njobs, 1), dtype=np.uint32)
+        _check(self.lib.bt2gpu_hotpath_job_tidx(self._h, _ptr(t)))
+        return t[:njobs]
+
     def hotpath_pairs(self, ref, seq, qual, reads, minsc, nceil, pol, maxhalf=15, seed_len=22, ival=(1.0, 1.15), maxgap=15,
                       max_aln=2, mine_max=2, out=None, cand_per_job=0):
         """bt2gpu_hotpath_pairs_batch: the anchor pass of hotpath_round0 over reads[2i] = mate 1, reads[2i+1] = mate 2,
@@ -411,11 +418,20 @@ class DeviceRef:
     """The joined reference text, 2 bits per base, resident in HBM (bt2gpu_ref_create): the device
     counterpart of BitPairReference (reference.h:180) that SwAligner::initRef reads windows from."""
 
-    def __init__(self, text, device=0):
+    def __init__(self, text, device=0, recs=None):
+        """text: the joined unambiguous text (codes 0..3).  recs: the `.3.bt2` RefRecords [(off, len, first)]
+        (build.build_index's extras["recs"]); None = one gap-free sequence."""
         self.lib = load()
         self.handle = C.c_void_p(0)
         text = np.ascontiguousarray(text, dtype=np.uint8)
-        _check(self.lib.bt2gpu_ref_create(C.c_int(device), _ptr(text), C.c_uint64(len(text)), C.byref(self.handle)))
+        if recs is None:
+            _check(self.lib.bt2gpu_ref_create(C.c_int(device), _ptr(text), C.c_uint64(len(text)), C.byref(self.handle)))
+        else:
+            r = np.zeros(len(recs), dtype=structs.ref_record)
+            for i, (off, ln, first) in enumerate(recs):
+                r[i]["off"], r[i]["len"], r[i]["first"] = off, ln, first
+            _check(self.lib.bt2gpu_ref_create_records(C.c_int(device), _ptr(text), C.c_uint64(len(text)), _ptr(r),
+                                                      C.c_uint64(len(r)), C.byref(self.handle)))
         self.length = len(text)
 
     @property

@@ -66,6 +66,7 @@ mate_frame = np.dtype([("rect", rect), ("oll", "<i8"), ("olr", "<i8"), ("orl", "
                        ("found", "u1"), ("ok", "u1"), ("oleft", "u1"), ("ofw", "u1"), ("pad", "u1", (4,))], align=True)
 mate_info = np.dtype([("anchor_job", "<u4"), ("read", "<u4"), ("cls", "<i4"), ("ofw", "u1"), ("oleft", "u1"), ("pad", "u1", (2,)),
                       ("anchor_refoff", "<i8"), ("anchor_extent", "<u4"), ("mate_extent", "<u4"), ("rect", rect)], align=True)
+ref_record = np.dtype([("off", "<u4"), ("len", "<u4"), ("first", "u1"), ("pad", "u1", (3,))], align=True)
 pair_job = np.dtype([("off1", "<i8"), ("off2", "<i8"), ("len1", "<u4"), ("len2", "<u4"),
                      ("fw1", "u1"), ("fw2", "u1"), ("pad", "u1", (6,))], align=True)
 

@@ -5,6 +5,37 @@ namespace bt2 {
 thread_local std::string g_err;
 void dp_state_free(DpState *d);
 void fm_state_free(FmState *d);
+void hp_state_free(HpState *d);
+}
+
+#include <mutex>
+namespace bt2 {
+// One scoring scheme per device at a time: the kernels read it from __constant__ memory (dp.cu c_sc/c_mmpens/c_npens,
+// fm.cu c_fm_sc/c_fm_mmpens), which all contexts of a device share.  Contexts that set the same scheme share the
+// registration; a different scheme is refused while any other context still holds the current one.
+static std::mutex g_scmu;
+struct ScReg { bt2gpu_scoring sc; int refs; bool uploaded; };
+static ScReg g_screg[64];
+
+int scoring_acquire(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc, bool *upload) {
+	if(ctx->device < 0 || ctx->device >= 64) BT2_FAIL("device ordinal out of range");
+	std::lock_guard<std::mutex> lk(g_scmu);
+	ScReg &r = g_screg[ctx->device];
+	const bool same = r.uploaded && memcmp(&r.sc, sc, sizeof(*sc)) == 0;
+	const int others = r.refs - (ctx->sc_registered ? 1 : 0);
+	if(!same && others > 0)
+		BT2_FAIL("another live context of this device uses a different scoring scheme (one scheme per device at a time: "
+		         "the kernels read it from device-wide constant memory)");
+	if(!ctx->sc_registered) { r.refs++; ctx->sc_registered = true; }
+	*upload = !same;
+	if(!same) { r.sc = *sc; r.uploaded = true; }
+	return 0;
+}
+
+static void scoring_release(bt2gpu_ctx *ctx) {
+	std::lock_guard<std::mutex> lk(g_scmu);
+	if(ctx->sc_registered && ctx->device >= 0 && ctx->device < 64) { g_screg[ctx->device].refs--; ctx->sc_registered = false; }
+}
 }
 using namespace bt2;
 
@@ -45,8 +76,10 @@ extern "C" void bt2gpu_ctx_destroy(bt2gpu_ctx *ctx) {
 	if(!ctx) return;
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
+	scoring_release(ctx);
 	dp_state_free(ctx->dp);
 	fm_state_free(ctx->fm);
+	hp_state_free(ctx->hp);
 	for(int i = 0; i < 2; i++) if(ctx->kev[i]) cudaEventDestroy(ctx->kev[i]);
 	for(int i = 0; i < 2; i++) if(ctx->cev[i]) cudaEventDestroy(ctx->cev[i]);
 	if(ctx->cstream) { cudaStreamSynchronize(ctx->cstream); cudaStreamDestroy(ctx->cstream); }

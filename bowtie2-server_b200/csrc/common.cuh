@@ -62,6 +62,7 @@ struct HostBuf {
 
 struct DpState;   // dp.cu
 struct FmState;   // fm.cu
+struct HpState;   // hotpath.cu
 
 // ---- internal, device-resident plumbing of the chained batch runtime (hotpath.cu) ----
 struct FmReadsDev { const uint8_t *seq, *qual; const bt2gpu_read *reads; };
@@ -78,8 +79,10 @@ struct bt2gpu_ctx {
 	int sm_count = 0;
 	bt2gpu_scoring sc;
 	bool have_sc = false;
+	bool sc_registered = false;           // holds a reference in the per-device scoring registry (api.cu)
 	bt2::DpState *dp = nullptr;
 	bt2::FmState *fm = nullptr;
+	bt2::HpState *hp = nullptr;
 	// device time of the kernels of the last entry point (events on `stream`)
 	cudaEvent_t kev[2] = {nullptr, nullptr};
 	bool kev_valid = false;

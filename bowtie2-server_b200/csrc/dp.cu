@@ -480,7 +480,9 @@ __global__ void k_dp_scan(const uint32_t *__restrict__ counts, uint32_t n, uint3
 		__syncthreads();
 		unsigned long long off = carry + warpsum[threadIdx.x >> 5] + x - v;
 		if(i < n) {
-			if(off + v > cap) { *errflag = 1; off = 0; }
+			// pool overflow: the call fails in bt2gpu_dp_fetch; until then the job must look empty to the emit, sort and
+			// backtrace passes (they index keys/cands/done by cand_off + [0, ncand)), as k_dp_gather_e2e does
+			if(off + v > cap) { *errflag = 1; off = 0; res[job0 + i].ncand = 0; res[job0 + i].aligned = 0; }
 			cand_off[job0 + i] = (uint32_t)off; fillptr[job0 + i] = 0; res[job0 + i].cand_off = (uint32_t)off;
 		}
 		__syncthreads();
@@ -1233,12 +1235,19 @@ int fm_set_scoring(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc);   // fm.cu
 
 using namespace bt2;
 
+namespace bt2 { int scoring_acquire(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc, bool *upload); }   // api.cu
+
 extern "C" int bt2gpu_scoring_set(bt2gpu_ctx *ctx, const bt2gpu_scoring *sc) {
 	if(!ctx || !sc) BT2_FAIL("null argument");
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	if(sc->gapbar < 1) BT2_FAIL("gapbar must be >= 1 (ee_u8.cpp:781)");
 	if(sc->rd_gap_ext > sc->rd_gap_open || sc->rf_gap_ext > sc->rf_gap_open) BT2_FAIL("gap extend > gap open");
+	// The kernels read the scheme from __constant__ symbols, which every context of a device shares: the registry
+	// admits one scheme per device at a time and refuses a second, different one while another context holds the first.
+	bool upload = false;
+	if(scoring_acquire(ctx, sc, &upload)) return 1;
 	ctx->sc = *sc; ctx->have_sc = true;
+	if(!upload) return 0;
 	ScConst c = { sc->match_bonus, sc->rd_gap_open, sc->rd_gap_ext, sc->rf_gap_open, sc->rf_gap_ext, sc->gapbar, sc->monotone };
 	BT2_CUDA(cudaMemcpyToSymbolAsync(c_mmpens, sc->mmpens, sizeof(c_mmpens), 0, cudaMemcpyHostToDevice, ctx->stream));
 	BT2_CUDA(cudaMemcpyToSymbolAsync(c_npens, sc->npens, sizeof(c_npens), 0, cudaMemcpyHostToDevice, ctx->stream));

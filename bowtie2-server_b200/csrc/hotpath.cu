@@ -16,10 +16,16 @@
 
 // 2-bit reference text on the device (BitPairReference::buf_, reference.h:180; `.4.bt2` layout:
 // base i in bits 2*(i&15).. of word i>>4)
+// plus the unambiguous stretches of the `.3.bt2` RefRecords (reference.h:59-103, reference.cpp:122-167): per record the
+// sequence coordinate where its bases start (after its leading Ns), its length and its offset in the joined text; per
+// sequence its record range and its length (Ns included) -- what BitPairReference::getStretch (reference.cpp:425-600)
+// and Ebwt::joinedToTextOff (bt2_idx.cpp:54-124: rstarts triples, plen) work from.
 struct bt2gpu_ref {
 	int device = 0;
 	uint64_t len = 0;
 	bt2::DevBuf packed;
+	uint32_t nrec = 0, nseq = 0, nfrag = 0;
+	bt2::DevBuf rec_start, rec_len, rec_buf, seq_rec0, plen, rstarts;
 };
 
 namespace bt2 {
@@ -28,7 +34,7 @@ typedef unsigned long long u64;
 
 struct HpState {
 	DevBuf cnt, first, spart, tot, hitlist, sjobs, shits, xjobs, xres, pick, val, ppos, pk_read, pk_seed, rows, rdoff, offs, steps,
-	       minsc, nceil, job_read, job_start, job_fw, stats;
+	       minsc, nceil, job_read, job_start, job_fw, job_tidx, stats;
 	HostBuf h_tot, h_stats;
 	cudaEvent_t ev[12] = {};
 	// paired-end pass (bt2gpu_hotpath_pairs_batch): what pass 1 left behind, and the mate-pass scratch
@@ -38,7 +44,53 @@ struct HpState {
 	HostBuf h_mstats;
 	cudaEvent_t mev[6] = {};
 };
-static thread_local HpState tl_st;         // device scratch reused across calls of this host thread
+// device scratch reused across calls; owned by the context (freed by bt2gpu_ctx_destroy), so it lives on the
+// context's device and the paired pass finds what pass 1 left behind whichever host thread drives the context
+static HpState &hp_state(bt2gpu_ctx *ctx) { if(!ctx->hp) ctx->hp = new HpState(); return *ctx->hp; }
+void hp_state_free(HpState *st) {
+	if(!st) return;
+	DevBuf *bufs[] = { &st->cnt, &st->first, &st->spart, &st->tot, &st->hitlist, &st->sjobs, &st->shits, &st->xjobs, &st->xres, &st->pick,
+	                   &st->val, &st->ppos, &st->pk_read, &st->pk_seed, &st->rows, &st->rdoff, &st->offs, &st->steps, &st->minsc, &st->nceil,
+	                   &st->job_read, &st->job_start, &st->job_fw, &st->job_tidx, &st->stats, &st->anc, &st->mtmp, &st->mval, &st->mpos, &st->wval,
+	                   &st->wpos, &st->minfo, &st->mstats };
+	for(DevBuf *b : bufs) b->release();
+	st->h_tot.release(); st->h_stats.release(); st->h_mstats.release();
+	for(int i = 0; i < 12; i++) if(st->ev[i]) cudaEventDestroy(st->ev[i]);
+	for(int i = 0; i < 6; i++) if(st->mev[i]) cudaEventDestroy(st->mev[i]);
+	delete st;
+}
+
+// what the kernels need of a bt2gpu_ref, by value
+struct RefView {
+	const uint32_t *text2; u64 len;
+	const uint32_t *rec_start, *rec_len, *rec_buf, *seq_rec0, *plen, *rstarts;
+	uint32_t nfrag;
+};
+static RefView ref_view(const bt2gpu_ref *r) {
+	RefView v;
+	v.text2 = r->packed.as<uint32_t>(); v.len = r->len;
+	v.rec_start = r->rec_start.as<uint32_t>(); v.rec_len = r->rec_len.as<uint32_t>(); v.rec_buf = r->rec_buf.as<uint32_t>();
+	v.seq_rec0 = r->seq_rec0.as<uint32_t>(); v.plen = r->plen.as<uint32_t>(); v.rstarts = r->rstarts.as<uint32_t>();
+	v.nfrag = r->nfrag;
+	return v;
+}
+
+// BitPairReference::getStretch for one position (reference.cpp:425-600): base 0..3 of sequence `tidx` at offset p, 4 (N)
+// in the gaps between its unambiguous stretches, after the last one and off either end.  Binary search over the
+// sequence's records for the last stretch starting at or before p.
+__device__ __forceinline__ uint32_t ref_code(const RefView &v, uint32_t tidx, long long p) {
+	if(p < 0) return 4u;
+	uint32_t lo = v.seq_rec0[tidx], hi = v.seq_rec0[tidx + 1];
+	if(hi == lo || (u64)p < v.rec_start[lo]) return 4u;
+	while(hi - lo > 1) {
+		const uint32_t mid = lo + ((hi - lo) >> 1);
+		if((u64)v.rec_start[mid] <= (u64)p) lo = mid; else hi = mid;
+	}
+	const u64 d = (u64)p - v.rec_start[lo];
+	if(d >= v.rec_len[lo]) return 4u;
+	const u64 q = (u64)v.rec_buf[lo] + d;
+	return (__ldg(v.text2 + (q >> 4)) >> (2 * (q & 15))) & 3u;
+}
 
 enum { ST_SEED_BWOPS = 0, ST_SEED_SIDES, ST_SEED_HITS, ST_EXT_FMOPS, ST_LOC_STEPS, ST_ALIGNED, ST_SWEEP_BWOPS, ST_N };
 
@@ -156,12 +208,13 @@ k_hp_compact(uint32_t nreads, const uint32_t *__restrict__ pick, const u64 *__re
 // Window bytes are 1 << base, 16 outside the text, plus one pad column (aligner_sw.cpp:155-271).
 __global__ void __launch_bounds__(256)
 k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const bt2gpu_read *__restrict__ reads,
-           const uint32_t *__restrict__ text2, u64 text_len, uint32_t npick, int mg,
+           RefView rv, uint32_t npick, int mg,
            const uint32_t *__restrict__ pk_read, const uint32_t *__restrict__ pk_seed, const uint32_t *__restrict__ rdoff,
            const uint32_t *__restrict__ offs, const uint32_t *__restrict__ steps, const bt2gpu_extend_job *__restrict__ xj,
            const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil,
            uint8_t *__restrict__ dseq, uint8_t *__restrict__ dqual, uint8_t *__restrict__ dwin, bt2gpu_dp_job *__restrict__ dj,
-           uint32_t *__restrict__ job_read, long long *__restrict__ job_start, uint8_t *__restrict__ job_fw, u64 *__restrict__ stats)
+           uint32_t *__restrict__ job_read, long long *__restrict__ job_start, uint8_t *__restrict__ job_fw,
+           uint32_t *__restrict__ job_tidx, u64 *__restrict__ stats)
 {
 	const int lane = threadIdx.x & 31;
 	const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -174,24 +227,24 @@ k_hp_frame(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, co
 	if(x.fw) for(uint32_t i = lane; i < rdlen; i += 32) { os[i] = rd[i]; oq[i] = qu[i]; }
 	else for(uint32_t i = lane; i < rdlen; i += 32) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
 	const long long seedoff = x.fw ? (long long)x.off : (long long)rdlen - x.off - x.len;   // in the oriented read
-	const long long start = (long long)offs[k] - seedoff;
+	// Ebwt::joinedToTextOff of the located seed hit (aligner_sw_driver.cpp:940; seed hits that straddle a fragment end
+	// are kept outside eeMode): sequence, offset inside it, its length
+	uint32_t tidx, toff, tlen; bool straddled;
+	joined_to_text(rv.rstarts, rv.nfrag, rv.plen, (uint32_t)rv.len, true, x.len, offs[k], false, tidx, toff, tlen, straddled);
+	const long long start = (long long)toff - seedoff;
 	bt2gpu_rect rect;         // trimToRef_ = !gReportOverhangs = true (bt2_search.cpp:188); the window holds the located seed, so it is never empty
-	frame_seed_ext(start, rdlen, (long long)text_len, (u64)mg, (u64)mg, nceil[ri], (u64)mg, true, rect);
+	frame_seed_ext(start, rdlen, (long long)tlen, (u64)mg, (u64)mg, nceil[ri], (u64)mg, true, rect);
 	const long long refl = rect.refl;
 	const uint32_t ncol = (uint32_t)(rect.refr - rect.refl + 1);
-	for(uint32_t c = lane; c <= ncol; c += 32) {
-		const long long p = refl + c;
-		uint8_t m = 16;
-		if(p >= 0 && (u64)p < text_len) m = (uint8_t)(1u << ((__ldg(text2 + (p >> 4)) >> (2 * (p & 15))) & 3u));
-		ow[c] = m;
-	}
+	for(uint32_t c = lane; c <= ncol; c += 32)
+		ow[c] = (uint8_t)(1u << ref_code(rv, tidx, refl + c));         // 16 = N: sequence gaps and beyond its ends
 	if(lane == 0) {
 		bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
 		j.rd_off = ro; j.rd_len = rdlen; j.rf_off = wo; j.ncol = ncol;
 		j.minsc = minsc[ri]; j.nceil = nceil[ri]; j.refl = refl; j.triml = (uint32_t)rect.triml;
 		j.corel = (uint32_t)rect.corel; j.corer = (uint32_t)rect.corer; j.fw = x.fw; j.enable8 = 1;
 		dj[k] = j;
-		job_read[k] = ri; job_start[k] = start; job_fw[k] = x.fw;
+		job_read[k] = ri; job_start[k] = start; job_fw[k] = x.fw; job_tidx[k] = tidx;
 		atomicAdd(stats + ST_LOC_STEPS, (u64)steps[k]);
 	}
 }
@@ -228,42 +281,92 @@ k_ref_pack(const uint8_t *__restrict__ bytes, u64 n, uint32_t *__restrict__ out,
 
 using namespace bt2;
 
-extern "C" int bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out) {
-	if(!text || !out) BT2_FAIL("null argument");
+static int ref_create(int device, const uint8_t *text, const uint8_t *bitpairs, uint64_t text_len,
+                      const bt2gpu_ref_record *recs, uint64_t nrec, bt2gpu_ref **out)
+{
+	if((!text && !bitpairs) || !out || !recs) BT2_FAIL("null argument");
 	*out = nullptr;
 	int n = 0;
 	BT2_CUDA(cudaGetDeviceCount(&n));
 	if(n <= 0) BT2_FAIL("no CUDA device: libbt2gpu has no CPU fallback");
 	if(device < 0 || device >= n) BT2_FAIL("bad device ordinal");
 	if(text_len == 0 || text_len > 0xfffffff0ull) BT2_FAIL("reference text length must be in 1..2^32-16 (small index)");
+	if(nrec == 0 || nrec > 0x7fffffffull) BT2_FAIL("bad record count");
+	if(!recs[0].first) BT2_FAIL("first reference record is not marked 'first' (reference.cpp:146-149)");
+	// the tables BitPairReference's constructor derives from the records (reference.cpp:122-167) and the fragment
+	// list Ebwt carries as rstarts/plen (bt2_io.cpp:240-322)
+	std::vector<uint32_t> rstart(nrec), rlen(nrec), rbuf(nrec), seq0, plen, rst;
+	uint64_t cumsz = 0, cumlen = 0;
+	for(uint64_t i = 0; i < nrec; i++) {
+		if(recs[i].first) { if(!seq0.empty()) plen.push_back((uint32_t)cumlen); seq0.push_back((uint32_t)i); cumlen = 0; }
+		cumlen += recs[i].off;
+		if(cumlen + recs[i].len > 0xffffffffull) BT2_FAIL("reference sequence longer than 2^32-1");
+		rstart[i] = (uint32_t)cumlen; rlen[i] = recs[i].len; rbuf[i] = (uint32_t)cumsz;
+		if(recs[i].len) { rst.push_back((uint32_t)cumsz); rst.push_back((uint32_t)seq0.size() - 1); rst.push_back((uint32_t)cumlen); }
+		cumsz += recs[i].len; cumlen += recs[i].len;
+	}
+	plen.push_back((uint32_t)cumlen);
+	seq0.push_back((uint32_t)nrec);
+	if(cumsz != text_len) BT2_FAIL("reference records do not add up to the text length");
 	BT2_CUDA(cudaSetDevice(device));
 	bt2gpu_ref *r = new bt2gpu_ref();
 	r->device = device; r->len = text_len;
+	r->nrec = (uint32_t)nrec; r->nseq = (uint32_t)plen.size(); r->nfrag = (uint32_t)(rst.size() / 3);
 	const uint64_t nwords = (text_len + 15) / 16;
 	DevBuf stage, flag;
 	const uint64_t CH = 64ull << 20;                     // bytes per staged chunk (a multiple of 16)
 	int rc = 0, bad = 0;
-	if(r->packed.reserve(nwords * 4 + 16) || stage.reserve(std::min<uint64_t>(CH, text_len) + 16) || flag.reserve(16)) rc = 1;
-	if(!rc && cudaMemset(flag.p, 0, 4) != cudaSuccess) rc = fail("cudaMemset", __FILE__, __LINE__);
-	for(uint64_t off = 0; !rc && off < text_len; off += CH) {
-		const uint64_t nb = std::min<uint64_t>(CH, text_len - off);
-		if(cudaMemcpy(stage.p, text + off, nb, cudaMemcpyHostToDevice) != cudaSuccess) { rc = fail("cudaMemcpy(reference text)", __FILE__, __LINE__); break; }
-		const uint64_t nw = (nb + 15) / 16;
-		k_ref_pack<<<(unsigned)((nw + 255) / 256), 256>>>(stage.as<uint8_t>(), nb, r->packed.as<uint32_t>() + off / 16, flag.as<int>());
-		if(cudaDeviceSynchronize() != cudaSuccess) { rc = fail("k_ref_pack", __FILE__, __LINE__); break; }
+	auto up = [&](DevBuf &b, const std::vector<uint32_t> &v) {
+		if(b.reserve(v.size() * 4 + 16)) return 1;
+		if(cudaMemcpy(b.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) return fail("cudaMemcpy(reference records)", __FILE__, __LINE__);
+		return 0;
+	};
+	if(up(r->rec_start, rstart) || up(r->rec_len, rlen) || up(r->rec_buf, rbuf) || up(r->seq_rec0, seq0) || up(r->plen, plen) ||
+	   up(r->rstarts, rst)) rc = 1;
+	if(!rc && r->packed.reserve(nwords * 4 + 16)) rc = 1;
+	if(!rc && bitpairs) {                                  // `.4.bt2` bytes: base i at bits 2*(i&3) of byte i>>2 == our words
+		if(cudaMemcpy(r->packed.p, bitpairs, (text_len + 3) / 4, cudaMemcpyHostToDevice) != cudaSuccess)
+			rc = fail("cudaMemcpy(reference bit pairs)", __FILE__, __LINE__);
+	} else if(!rc) {
+		if(stage.reserve(std::min<uint64_t>(CH, text_len) + 16) || flag.reserve(16)) rc = 1;
+		if(!rc && cudaMemset(flag.p, 0, 4) != cudaSuccess) rc = fail("cudaMemset", __FILE__, __LINE__);
+		for(uint64_t off = 0; !rc && off < text_len; off += CH) {
+			const uint64_t nb = std::min<uint64_t>(CH, text_len - off);
+			if(cudaMemcpy(stage.p, text + off, nb, cudaMemcpyHostToDevice) != cudaSuccess) { rc = fail("cudaMemcpy(reference text)", __FILE__, __LINE__); break; }
+			const uint64_t nw = (nb + 15) / 16;
+			k_ref_pack<<<(unsigned)((nw + 255) / 256), 256>>>(stage.as<uint8_t>(), nb, r->packed.as<uint32_t>() + off / 16, flag.as<int>());
+			if(cudaDeviceSynchronize() != cudaSuccess) { rc = fail("k_ref_pack", __FILE__, __LINE__); break; }
+		}
+		if(!rc && cudaMemcpy(&bad, flag.p, 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail("cudaMemcpy", __FILE__, __LINE__);
+		stage.release(); flag.release();
+		if(!rc && bad) rc = fail("reference text holds a byte outside 0..3", __FILE__, __LINE__);
 	}
-	if(!rc && cudaMemcpy(&bad, flag.p, 4, cudaMemcpyDeviceToHost) != cudaSuccess) rc = fail("cudaMemcpy", __FILE__, __LINE__);
-	stage.release(); flag.release();
-	if(!rc && bad) rc = fail("reference text holds a byte outside 0..3", __FILE__, __LINE__);
-	if(rc) { r->packed.release(); delete r; return 1; }
+	if(rc) { bt2gpu_ref_destroy(r); return 1; }
 	*out = r;
 	return 0;
+}
+
+extern "C" int bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out) {
+	bt2gpu_ref_record one; memset(&one, 0, sizeof(one));
+	one.off = 0; one.len = (uint32_t)text_len; one.first = 1;
+	return ref_create(device, text, nullptr, text_len, &one, 1, out);
+}
+
+extern "C" int bt2gpu_ref_create_records(int device, const uint8_t *text, uint64_t text_len,
+                                         const bt2gpu_ref_record *recs, uint64_t nrec, bt2gpu_ref **out) {
+	return ref_create(device, text, nullptr, text_len, recs, nrec, out);
+}
+
+extern "C" int bt2gpu_ref_create_bitpairs(int device, const uint8_t *bitpairs, uint64_t text_len,
+                                          const bt2gpu_ref_record *recs, uint64_t nrec, bt2gpu_ref **out) {
+	return ref_create(device, nullptr, bitpairs, text_len, recs, nrec, out);
 }
 
 extern "C" void bt2gpu_ref_destroy(bt2gpu_ref *r) {
 	if(!r) return;
 	cudaSetDevice(r->device);
 	r->packed.release();
+	r->rec_start.release(); r->rec_len.release(); r->rec_buf.release(); r->seq_rec0.release(); r->plen.release(); r->rstarts.release();
 	delete r;
 }
 
@@ -292,7 +395,7 @@ static int hotpath_round0(
 	*njobs_out = 0; *nedits_out = 0;
 	if(nreads == 0) return 0;
 	BT2_CUDA(cudaSetDevice(ctx->device));
-	HpState &st = tl_st;
+	HpState &st = hp_state(ctx);
 	st.last_npick = 0;
 	cudaStream_t s = ctx->stream;
 	for(int i = 0; i < 12; i++) if(!st.ev[i]) BT2_CUDA(cudaEventCreate(&st.ev[i]));
@@ -373,7 +476,7 @@ static int hotpath_round0(
 		const size_t tot_win = tot_rd + npick * (size_t)(4 * mg + 1);
 		if(st.pk_read.reserve(npick * 4) || st.pk_seed.reserve(npick * 4) || st.rows.reserve(npick * 4) || st.rdoff.reserve(npick * 4) ||
 		   st.offs.reserve(npick * 4) || st.steps.reserve(npick * 4) || st.job_read.reserve(npick * 4) || st.job_start.reserve(npick * 8) ||
-		   st.job_fw.reserve(npick)) return 1;
+		   st.job_fw.reserve(npick) || st.job_tidx.reserve(npick * 4)) return 1;
 		bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>();
 		k_hp_compact<<<nbR, 256, 0, s>>>(n32, st.pick.as<uint32_t>(), st.ppos.as<u64>(), xj, st.pk_read.as<uint32_t>(),
 			st.pk_seed.as<uint32_t>(), st.rows.as<uint32_t>(), st.rdoff.as<uint32_t>());
@@ -384,10 +487,10 @@ static int hotpath_round0(
 		const size_t cpj = P->cand_per_job ? P->cand_per_job : (ctx->sc.monotone ? 256 : 4096);
 		if(dp_dev_begin(ctx, npick, tot_rd, tot_win, max_aln, cpj * npick, edit_cap, &pools)) return 1;
 		BT2_CUDA(cudaStreamWaitEvent(s, ctx->cev[0], 0));
-		k_hp_frame<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(rv.seq, rv.qual, rv.reads, ref->packed.as<uint32_t>(), ref->len,
+		k_hp_frame<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(rv.seq, rv.qual, rv.reads, ref_view(ref),
 			(uint32_t)npick, mg, st.pk_read.as<uint32_t>(), st.pk_seed.as<uint32_t>(), st.rdoff.as<uint32_t>(), st.offs.as<uint32_t>(),
 			st.steps.as<uint32_t>(), xj, st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), pools.seq, pools.qual, pools.win, pools.jobs,
-			st.job_read.as<uint32_t>(), st.job_start.as<long long>(), st.job_fw.as<uint8_t>(), stats);
+			st.job_read.as<uint32_t>(), st.job_start.as<long long>(), st.job_fw.as<uint8_t>(), st.job_tidx.as<uint32_t>(), stats);
 		ctx->launches += 2;
 		BT2_CUDA(cudaGetLastError());
 		if(dp_dev_finish(ctx)) return 1;
@@ -434,6 +537,17 @@ static int hotpath_round0(
 	S->ms_glue = S->ms_total - S->ms_sweep - S->ms_seed - S->ms_extend - S->ms_locate - S->ms_dp;
 	*njobs_out = npick; *nedits_out = ne;
 	st.rv = rv; st.last_npick = npick; st.last_max_aln = max_aln;
+	return 0;
+}
+
+extern "C" int bt2gpu_hotpath_job_tidx(bt2gpu_ctx *ctx, uint32_t *job_tidx) {
+	if(!ctx || !job_tidx) BT2_FAIL("null argument");
+	if(!ctx->hp) BT2_FAIL("no batch has run on this context");
+	const size_t n = ctx->hp->last_npick;
+	if(n == 0) return 0;
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	BT2_CUDA(cudaMemcpyAsync(job_tidx, ctx->hp->job_tidx.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
 	return 0;
 }
 
@@ -486,7 +600,8 @@ __global__ void __launch_bounds__(256)
 k_hp_anchor(const bt2gpu_dp_result *__restrict__ res, const bt2gpu_dp_aln *__restrict__ alns, const bt2gpu_edit *__restrict__ edits,
             uint32_t max_aln, uint32_t njobs, const uint32_t *__restrict__ job_read, const uint8_t *__restrict__ job_fw,
             const bt2gpu_read *__restrict__ reads, const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil,
-            bt2gpu_pe_policy pol, uint32_t maxhalf, long long reflen, int match, int rdo, int rde, int rfo, int rfe,
+            bt2gpu_pe_policy pol, uint32_t maxhalf, const uint32_t *__restrict__ job_tidx, const uint32_t *__restrict__ plen,
+            int match, int rdo, int rde, int rfo, int rfe,
             AnchorSum *__restrict__ anc, bt2gpu_mate_frame *__restrict__ mtmp, u64 *__restrict__ mval, u64 *__restrict__ wval,
             u64 *__restrict__ mstats)
 {
@@ -501,6 +616,7 @@ k_hp_anchor(const bt2gpu_dp_result *__restrict__ res, const bt2gpu_dp_aln *__res
 		AnchorSum s; s.refoff = a.refoff; s.extent = ref_extent(len_a, a, edits); s.score = a.score;
 		anc[k] = s;
 		const long long ominsc = minsc[mate];
+		const long long reflen = (long long)plen[job_tidx[k]];      // the mate is searched in the anchor's sequence
 		const int ordg = max_gaps(ominsc, len_o, match, rdo, rde, false), orfg = max_gaps(ominsc, len_o, match, rfo, rfe, true);
 		bt2gpu_mate_frame f; memset(&f, 0, sizeof(f));
 		MateWin w;
@@ -525,7 +641,7 @@ k_hp_anchor(const bt2gpu_dp_result *__restrict__ res, const bt2gpu_dp_aln *__res
 // (16 outside the text, plus the pad column, aligner_sw.cpp:155-271), write the DP job and its description.
 __global__ void __launch_bounds__(256)
 k_hp_mateframe(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual, const bt2gpu_read *__restrict__ reads,
-               const uint32_t *__restrict__ text2, u64 text_len, uint32_t njobs, const uint32_t *__restrict__ job_read,
+               RefView rv, uint32_t njobs, const uint32_t *__restrict__ job_read, const uint32_t *__restrict__ job_tidx,
                const int32_t *__restrict__ minsc, const int32_t *__restrict__ nceil, const AnchorSum *__restrict__ anc,
                const bt2gpu_mate_frame *__restrict__ mtmp, const u64 *__restrict__ mval, const u64 *__restrict__ mpos,
                const u64 *__restrict__ wpos, uint8_t *__restrict__ dseq, uint8_t *__restrict__ dqual, uint8_t *__restrict__ dwin,
@@ -543,12 +659,9 @@ k_hp_mateframe(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 	else for(uint32_t i = lane; i < rdlen; i += 32) { const uint8_t c = rd[rdlen - 1 - i]; os[i] = c > 3 ? 4 : (uint8_t)(3 - c); oq[i] = qu[rdlen - 1 - i]; }
 	const long long refl = f.rect.refl;
 	const uint32_t ncol = (uint32_t)(f.rect.refr - f.rect.refl + 1);
-	for(uint32_t c = lane; c <= ncol; c += 32) {
-		const long long p = refl + c;
-		uint8_t v = 16;
-		if(p >= 0 && (u64)p < text_len) v = (uint8_t)(1u << ((__ldg(text2 + (p >> 4)) >> (2 * (p & 15))) & 3u));
-		ow[c] = v;
-	}
+	const uint32_t tidx = job_tidx[k];
+	for(uint32_t c = lane; c <= ncol; c += 32)
+		ow[c] = (uint8_t)(1u << ref_code(rv, tidx, refl + c));
 	if(lane == 0) {
 		bt2gpu_dp_job j; memset(&j, 0, sizeof(j));
 		j.rd_off = ro; j.rd_len = rdlen; j.rf_off = wo; j.ncol = ncol;
@@ -596,7 +709,7 @@ static int hotpath_mates(
 	bt2gpu_mate_info *mates, size_t *nmates_out, bt2gpu_dp_result *mresults, bt2gpu_dp_aln *malns, bt2gpu_edit *medits,
 	size_t medit_cap, size_t *nmedits_out, bt2gpu_pairs_stats *S)
 {
-	HpState &st = tl_st;
+	HpState &st = hp_state(ctx);
 	cudaStream_t s = ctx->stream;
 	const size_t npick = st.last_npick;
 	const uint32_t max_aln = st.last_max_aln;
@@ -612,7 +725,7 @@ static int hotpath_mates(
 	const unsigned nbJ = (unsigned)((npick + 255) / 256);
 	k_hp_anchor<<<nbJ, 256, 0, s>>>(dp_dev_results(ctx), dp_dev_alns(ctx), dp_dev_edits(ctx), max_aln, (uint32_t)npick,
 		st.job_read.as<uint32_t>(), st.job_fw.as<uint8_t>(), st.rv.reads, st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), *pol, maxhalf,
-		(long long)ref->len, sc.match_bonus, sc.rd_gap_open, sc.rd_gap_ext, sc.rf_gap_open, sc.rf_gap_ext,
+		st.job_tidx.as<uint32_t>(), ref->plen.as<uint32_t>(), sc.match_bonus, sc.rd_gap_open, sc.rd_gap_ext, sc.rf_gap_open, sc.rf_gap_ext,
 		st.anc.as<AnchorSum>(), st.mtmp.as<bt2gpu_mate_frame>(), st.mval.as<u64>(), st.wval.as<u64>(), mstats);
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
@@ -630,8 +743,8 @@ static int hotpath_mates(
 	DpDevPools pools;
 	const size_t cpj = std::max<size_t>(P->cand_per_job ? P->cand_per_job : (ctx->sc.monotone ? 256 : 4096), ctx->sc.monotone ? 1024 : 4096);
 	if(dp_dev_begin(ctx, nm, tot_rd, tot_win, max_aln, cpj * nm, medit_cap, &pools)) return 1;
-	k_hp_mateframe<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(st.rv.seq, st.rv.qual, st.rv.reads, ref->packed.as<uint32_t>(), ref->len,
-		(uint32_t)npick, st.job_read.as<uint32_t>(), st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), st.anc.as<AnchorSum>(),
+	k_hp_mateframe<<<(unsigned)((npick * 32 + 255) / 256), 256, 0, s>>>(st.rv.seq, st.rv.qual, st.rv.reads, ref_view(ref),
+		(uint32_t)npick, st.job_read.as<uint32_t>(), st.job_tidx.as<uint32_t>(), st.minsc.as<int32_t>(), st.nceil.as<int32_t>(), st.anc.as<AnchorSum>(),
 		st.mtmp.as<bt2gpu_mate_frame>(), st.mval.as<u64>(), st.mpos.as<u64>(), st.wpos.as<u64>(), pools.seq, pools.qual, pools.win, pools.jobs,
 		st.minfo.as<bt2gpu_mate_info>());
 	ctx->launches++;

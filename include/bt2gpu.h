@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BT2GPU_ABI_VERSION 1
+#define BT2GPU_ABI_VERSION 2
 
 typedef struct bt2gpu_ctx   bt2gpu_ctx;
 typedef struct bt2gpu_index bt2gpu_index;   /* one Ebwt (forward or mirror)   */
@@ -429,14 +429,27 @@ typedef struct {
  * (aligner_sw.cpp:155-271).  text = bytes 0..3, host memory, the text the index was built over;
  * uploaded once per device and shared read-only by every context on it. */
 typedef struct bt2gpu_ref bt2gpu_ref;
-int      bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out);
+int      bt2gpu_ref_create(int device, const uint8_t *text, uint64_t text_len, bt2gpu_ref **out);   /* one gap-free sequence */
+/* The same with the `.3.bt2` records: RefRecord{off,len,first} (reference.h:59-103) = `off` ambiguous characters, then
+ * `len` unambiguous ones; `first` starts a new reference sequence.  text = the joined unambiguous stretches
+ * (sum of len bytes, 0..3).  From the records the device derives what BitPairReference's constructor does
+ * (reference.cpp:122-167: per-sequence record ranges, lengths, offsets into the joined text) -- so a window is
+ * fetched per sequence, with N in the gaps and off the ends (BitPairReference::getStretch, reference.cpp:425-600) --
+ * and the fragment list Ebwt::joinedToTextOff searches (rstarts / plen, bt2_idx.cpp:54-124), so a located seed hit
+ * maps to (sequence, offset, sequence length).  _bitpairs takes the text as the `.4.bt2` file holds it
+ * (BitPairReference::buf_: base i at bits 2*(i&3) of byte i>>2). */
+typedef struct { uint32_t off, len; uint8_t first, pad[3]; } bt2gpu_ref_record;
+int      bt2gpu_ref_create_records(int device, const uint8_t *text, uint64_t text_len,
+                                   const bt2gpu_ref_record *recs, uint64_t nrec, bt2gpu_ref **out);
+int      bt2gpu_ref_create_bitpairs(int device, const uint8_t *bitpairs, uint64_t text_len,
+                                    const bt2gpu_ref_record *recs, uint64_t nrec, bt2gpu_ref **out);
 void     bt2gpu_ref_destroy(bt2gpu_ref *ref);
 uint64_t bt2gpu_ref_bytes(const bt2gpu_ref *ref);
 
 /* Per read i: minsc[i], nceil[i].  Inputs are host buffers (pinned memory makes the copies
  * asynchronous); every intermediate stays in HBM.  Outputs (all host, caller-owned):
  * sweep[nreads]; job_read[nreads] = read id of DP job k (first *njobs entries valid);
- * job_start[k] = text offset the oriented read was framed at; results[nreads],
+ * job_start[k] = offset, inside its reference sequence, the oriented read was framed at; results[nreads],
  * alns[nreads*max_aln], edits[edit_cap] indexed by DP job. */
 int bt2gpu_hotpath_round0_batch(
 	bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_ref *ref,
@@ -446,6 +459,10 @@ int bt2gpu_hotpath_round0_batch(
 	bt2gpu_sweep_result *sweep, uint32_t *job_read, int64_t *job_start, uint8_t *job_fw, size_t *njobs,
 	bt2gpu_dp_result *results, bt2gpu_dp_aln *alns, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits,
 	bt2gpu_hotpath_stats *stats);
+
+/* Reference sequence (tidx) of every DP job of the last bt2gpu_hotpath_*_batch call on this context (njobs entries):
+ * job_start[k] and every alignment's refoff are offsets inside sequence job_tidx[k]. */
+int bt2gpu_hotpath_job_tidx(bt2gpu_ctx *ctx, uint32_t *job_tidx);
 
 /* ---- batch runtime, paired-end: anchor pass + mate search ------------------------------- */
 
@@ -457,7 +474,7 @@ int bt2gpu_hotpath_round0_batch(
  * outputs have the same meaning).  Pass 2 takes the FIRST alignment of every anchor DP job, frames
  * the opposite mate's window on the device and runs the DP kernels on those windows; mate job m
  * is described by mates[m] and answered by mresults[m], malns[m*max_aln..], medits.
- * The whole joined text is treated as one reference sequence (tidx 0, reflen = text length). */
+ * The mate is searched in the anchor's reference sequence (reflen = that sequence's length). */
 typedef struct {
 	uint32_t anchor_job;     /* pass-1 DP job this window was framed from                     */
 	uint32_t read;           /* read id of the opposite mate (the one aligned in this window)  */

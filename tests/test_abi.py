@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(l, n), n
     assert sorted(lib.SYMBOLS) == names
-    assert l.bt2gpu_abi_version() == 1
+    assert l.bt2gpu_abi_version() == 2
 
 
 def test_struct_sizes_match_header():

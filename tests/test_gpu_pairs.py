@@ -50,19 +50,22 @@ def _make_pairs(rng, genome, npairs, lens):
     return seqs, quals
 
 
-@pytest.mark.parametrize("flags", [(0, 0, 0, 1, 1, 1), (0, 1, 1, 1, 1, 1), (0, 0, 0, 0, 0, 1)])
-def test_paired_batch_runtime_matches_oracle(flags):
+@pytest.mark.parametrize("flags,nseq", [((0, 0, 0, 1, 1, 1), 1), ((0, 1, 1, 1, 1, 1), 1), ((0, 0, 0, 0, 0, 1), 1), ((0, 0, 0, 1, 1, 1), 3)])
+def test_paired_batch_runtime_matches_oracle(flags, nseq):
     rng = np.random.default_rng(11)
     genome = synth.random_genome(rng, 1 << 18)
-    G = len(genome)
-    ix, _ = build.build_index([genome], ["chr1"])
+    # nseq = 3: the same text cut into three reference sequences (mates are searched in the anchor's sequence,
+    # windows stop at its ends; pairs sampled across a cut do not pair up)
+    cuts = [0, len(genome)] if nseq == 1 else [0, 80000, 180000, len(genome)]
+    refseqs = [genome[cuts[i]:cuts[i + 1]] for i in range(len(cuts) - 1)]
+    ix, extras = build.build_index(refseqs, ["chr%d" % (i + 1) for i in range(len(refseqs))])
     sc = scoring.Scoring(local=False)
     scs = sc.to_struct().reshape(-1)[0]
     ctx = lib.Context(0)
     ctx.set_scoring(sc)
     dix = lib.DeviceIndex(ix, 0)
     ctx.bind_index(dix)
-    dref = lib.DeviceRef(genome)
+    dref = lib.DeviceRef(genome) if nseq == 1 else lib.DeviceRef(extras["joined"], 0, recs=extras["recs"])
     npairs = 400
     lens = rng.integers(60, 180, size=2 * npairs)
     seqs, quals = _make_pairs(rng, genome, npairs, lens)
@@ -81,8 +84,9 @@ def test_paired_batch_runtime_matches_oracle(flags):
 
     out, st, ps = ctx.hotpath_pairs(dref, pool.seq, pool.qual, pool.reads, minsc, nceil, pol, maxhalf=maxhalf, max_aln=max_aln)
     mate_dp = ctx.dp_fetch()                                   # the mate pass is what is still staged
-    want = _oracle_round0(ix, genome, sc, pool, minsc, nceil, max_aln=max_aln)
+    want = _oracle_round0(ix, refseqs, sc, pool, minsc, nceil, max_aln=max_aln)
     nj = out["njobs"]
+    assert np.array_equal(ctx.hotpath_job_tidx(nj), want["tidx"])
     assert nj == want["njobs"] and nj > 500
     assert np.array_equal(out["job_read"][:nj], want["rid"]) and np.array_equal(out["job_fw"][:nj], want["fw"])
     wres, _, walns, wedits = want["dp"]
@@ -100,6 +104,8 @@ def test_paired_batch_runtime_matches_oracle(flags):
         if r["naln"] == 0:
             continue
         a = walns[r["aln_off"]]
+        gseq = refseqs[int(want["tidx"][k])]
+        G = len(gseq)
         ri = int(want["rid"][k]); mate = ri ^ 1
         is1, fw = int(ri % 2 == 0), int(want["fw"][k])
         len_a, len_o = int(rl[ri]), int(rl[mate])
@@ -117,7 +123,7 @@ def test_paired_batch_runtime_matches_oracle(flags):
             rd, qu = COMP[rd[::-1]], qu[::-1]
         refl, ncol = rect[0], rect[1] - rect[0] + 1
         cols = refl + np.arange(ncol + 1)
-        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
+        codes = np.where((cols >= 0) & (cols < G), gseq[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
         b_seq.append(rd); b_qual.append(qu); b_win.append((1 << codes).astype(np.uint8))
         j = np.zeros(1, dtype=structs.dp_job)[0]
         j["rd_off"], j["rd_len"], j["rf_off"], j["ncol"] = ro, len_o, wo, ncol

@@ -73,7 +73,9 @@ def test_hot_path_chain_matches_oracle():
 
 
 def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, max_aln=2):
-    """The batch runtime's chain restated with the CPU oracle stage by stage (ragged reads)."""
+    """The batch runtime's chain restated with the CPU oracle stage by stage (ragged reads).
+    genome: one code array, or the list of reference sequences (codes 0..3, 4 = N) the index was built over."""
+    seqs_ref = genome if isinstance(genome, list) else [genome]
     orc = H.FmOracle(ix, sc.to_struct())
     orc.stage_reads(pool)
     sweep = orc.exact_sweep()
@@ -100,8 +102,7 @@ def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, m
         h = e
     picks = np.array(picks, dtype=np.int64)
     offs, steps = orc.locate(xj["topf"][picks]) if len(picks) else (np.zeros(0, np.uint32), np.zeros(0, np.uint32))
-    b_seq, b_qual, b_win, jobs, rid, starts, fws = [], [], [], np.zeros(len(picks), dtype=structs.dp_job), [], [], []
-    G = len(genome)
+    b_seq, b_qual, b_win, jobs, rid, starts, fws, tidxs = [], [], [], np.zeros(len(picks), dtype=structs.dp_job), [], [], [], []
     fo = H.FrameOracle()
     ro = wo = 0
     comp = np.array([3, 2, 1, 0, 4], np.uint8)
@@ -112,22 +113,29 @@ def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, m
         if not x["fw"]:
             rd, qu = comp[rd[::-1]], qu[::-1]
         seedoff = int(x["off"]) if x["fw"] else rdlen - int(x["off"]) - int(x["len"])
-        start = int(offs[k]) - seedoff
+        # Ebwt::joinedToTextOff of the located hit (straddlers are kept outside eeMode), then the window out of that
+        # sequence with N in its gaps and off its ends (BitPairReference::getStretch)
+        tidx, toff, tlen, _ = fo.joined_to_text_off(ix.fw, int(x["len"]), int(offs[k]), 0)
+        g = seqs_ref[tidx]
+        G = len(g)
+        assert tlen == G
+        start = toff - seedoff
         ok, rect = fo.frame_seed_ext(start, rdlen, G, maxgap, maxgap, int(nceil[ri]), maxgap, 1)   # trimToRef (the reference default)
         assert ok
         refl, ncol = rect[0], rect[1] - rect[0] + 1
         cols = refl + np.arange(ncol + 1)
-        codes = np.where((cols >= 0) & (cols < G), genome[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
+        codes = np.where((cols >= 0) & (cols < G), g[np.clip(cols, 0, G - 1)], 4).astype(np.uint8)
         b_seq.append(rd); b_qual.append(qu); b_win.append((1 << codes).astype(np.uint8))
         j = jobs[k]
         j["rd_off"], j["rd_len"], j["rf_off"], j["ncol"] = ro, rdlen, wo, ncol
         j["minsc"], j["nceil"], j["refl"], j["triml"] = minsc[ri], nceil[ri], refl, rect[4]
         j["corel"], j["corer"], j["fw"], j["enable8"] = rect[6], rect[7], x["fw"], 1
         ro += rdlen; wo += ncol + 1
-        rid.append(ri); starts.append(start); fws.append(int(x["fw"]))
+        rid.append(ri); starts.append(start); fws.append(int(x["fw"])); tidxs.append(tidx)
     cat = lambda a: np.ascontiguousarray(np.concatenate(a)) if a else np.zeros(0, np.uint8)
     ref = H.oracle_dp(sc.to_struct(), cat(b_seq), cat(b_qual), cat(b_win), jobs, max_aln=max_aln) if len(jobs) else None
-    return dict(sweep=sweep, nseeds=len(sj), rid=np.array(rid), start=np.array(starts), fw=np.array(fws), dp=ref, njobs=len(jobs),
+    return dict(sweep=sweep, nseeds=len(sj), rid=np.array(rid), start=np.array(starts), fw=np.array(fws), tidx=np.array(tidxs),
+                dp=ref, njobs=len(jobs),
                 steps=int(steps.sum()) if len(picks) else 0, jobs=jobs)
 
 
@@ -187,4 +195,54 @@ def test_batch_runtime_ragged_reads_match_oracle(local):
     outN, stN = ctx.hotpath_round0(dref, np.full(60, 4, np.uint8), np.full(60, 73, np.uint8), rdN,
                                    np.full(2, -18, np.int32), np.full(2, 1, np.int32))
     assert outN["njobs"] == 0 and stN["seeds"] == 0
+    ctx.close()
+
+
+def test_batch_runtime_multiple_sequences_with_gaps():
+    """IDX-8: the device reference carries the `.3.bt2` records.  Five sequences, two of them with N stretches inside
+    (several fragments each) and one with leading / trailing Ns; reads sampled across fragment and sequence ends:
+    joinedToTextOff, per-sequence framing and the windows (N in the gaps and off the ends) against the oracle chain."""
+    rng = np.random.default_rng(23)
+    seqs = [synth.random_genome(rng, n).astype(np.uint8) for n in (60000, 41000, 90000, 3000, 52000)]
+    seqs[1][15000:15040] = 4; seqs[1][30000:30003] = 4
+    seqs[2][:25] = 4; seqs[2][-60:] = 4; seqs[2][50000:50200] = 4
+    ix, extras = build.build_index(seqs, ["s%d" % i for i in range(len(seqs))])
+    sc = scoring.Scoring(local=False)
+    ctx = lib.Context(0)
+    ctx.set_scoring(sc)
+    dix = lib.DeviceIndex(ix, 0)
+    ctx.bind_index(dix)
+    dref = lib.DeviceRef(extras["joined"], 0, recs=extras["recs"])
+    rs, qs, lens = [], [], []
+    comp = np.array([3, 2, 1, 0, 4], np.uint8)
+    spots = [(1, 14900), (1, 15030), (1, 29950), (2, 0), (2, 30), (2, 89850), (2, 49900), (2, 50150), (3, 0), (3, 2850), (0, 59850), (4, 0)]
+    for i in range(900):
+        L = int(rng.integers(30, 260))
+        if i < 20 * len(spots):
+            t, p = spots[i % len(spots)]
+            p = max(0, min(p + int(rng.integers(-40, 40)), len(seqs[t]) - L))
+        else:
+            t = int(rng.integers(0, len(seqs))); p = int(rng.integers(0, len(seqs[t]) - L))
+        r = seqs[t][p:p + L].copy()
+        mm = rng.random(L) < 0.015
+        r[mm] = rng.integers(0, 4, size=int(mm.sum()))
+        if rng.random() < 0.5:
+            r = comp[r[::-1]]
+        rs.append(r.astype(np.uint8)); qs.append((rng.integers(2, 41, size=L) + 33).astype(np.uint8)); lens.append(L)
+    pool = fmio.ReadPool.__new__(fmio.ReadPool)
+    pool.seq, pool.qual = np.concatenate(rs), np.concatenate(qs)
+    pool.reads = np.zeros(len(lens), dtype=structs.read)
+    pool.reads["rd_len"] = lens
+    pool.reads["rd_off"] = np.concatenate([[0], np.cumsum(lens)[:-1]])
+    minsc = np.array([sc.score_min.f_int(L) for L in lens], dtype=np.int32)
+    nceil = np.array([sc.nceil(L) for L in lens], dtype=np.int32)
+    want = _oracle_round0(ix, seqs, sc, pool, minsc, nceil)
+    out, st = ctx.hotpath_round0(dref, pool.seq, pool.qual, pool.reads, minsc, nceil)
+    nj = out["njobs"]
+    assert nj == want["njobs"] and nj > 500 and len(set(want["tidx"].tolist())) == len(seqs)
+    assert np.array_equal(out["job_read"][:nj], want["rid"]) and np.array_equal(out["job_start"][:nj], want["start"])
+    assert np.array_equal(ctx.hotpath_job_tidx(nj), want["tidx"])
+    got = ctx.dp_fetch()
+    for i in range(nj):
+        assert dpio.results_to_py(*want["dp"], i) == dpio.results_to_py(got[0], got[1], got[2], got[3], i), i
     ctx.close()

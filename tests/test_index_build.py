@@ -62,3 +62,21 @@ def test_random_genome_index_is_self_consistent():
     orc = H.FmOracle(ix, None)
     offs, _ = orc.locate(np.arange(0, e.len + 1, dtype=np.uint32))
     assert sorted(int(x) for x in offs[:-1]) == list(range(e.len)) or sorted(int(x) for x in offs) == list(range(e.len + 1))
+
+
+def test_bucketed_suffix_sort_matches_single_bucket():
+    """The memory-lean path (key-prefix buckets, used for human-scale genomes) gives the same index as the
+    single-sort path: forced with a tiny bucket size on a repetitive text with an N gap and on a random one."""
+    path = os.path.join(H.GOLDEN, "rep.fa")
+    names, seqs = _read_fasta(path)
+    ref = H.load_index_fixture("rep_index.npz")
+    for rows in (64, 1000, 7919):
+        ix, _ = build.build_index(seqs, [n.split()[0] for n in names], device="cpu", bucket_rows=rows)
+        _same(ix.fw, ref.fw)
+        _same(ix.bw, ref.bw)
+    rng = np.random.default_rng(11)
+    s = rng.integers(0, 4, size=30011).astype(np.uint8)
+    a, _ = build.build_index([s[:17000], s[17000:]], device="cpu")
+    b, _ = build.build_index([s[:17000], s[17000:]], device="cpu", bucket_rows=2048)
+    _same(a.fw, b.fw)
+    _same(a.bw, b.bw)
