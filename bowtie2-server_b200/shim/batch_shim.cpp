@@ -1,0 +1,549 @@
+// batch_shim.cpp — the batched binding of gpu_shim.h and the worker scheduler of fiber.h.
+//
+// A call (dpAlign, sweep, seeds, ...) made on a worker's stack appends the problem to the pending batch of the worker's
+// host thread and suspends the worker.  The host thread's scheduler runs every runnable worker once, then hands the
+// pending batch to a free lane; the lane's helper thread executes it -- one bt2gpu_*_batch call per kind of problem,
+// host buffers in, host buffers out -- and marks the batch done; the scheduler then makes the batch's workers runnable
+// again.  Results are written into the callers' own call structs, so a worker finds its answer where the per-call
+// binding would have left it: the shim bodies (sw_aligner_gpu.cpp, seed_aligner_gpu.cpp, ...) are the same code in
+// both builds, and so is everything the reference's driver sees.
+//
+// No CPU path: a lane that cannot create its bt2gpu_ctx, or an ABI call that fails, ends the process with the error.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+#include <sys/mman.h>
+#include <time.h>
+#include <unistd.h>
+#include "bt2_idx.h"
+#include "scoring.h"
+#include "read.h"
+#include "gpu_shim.h"
+#include "fiber.h"
+
+// ---- context switch (x86-64 System V): callee-saved registers on the old stack, stack pointers swapped --------------
+extern "C" void bt2_fiber_switch(void **save_sp, void *load_sp);
+asm(R"(
+	.text
+	.globl bt2_fiber_switch
+	.type bt2_fiber_switch,@function
+bt2_fiber_switch:
+	pushq %rbp
+	pushq %rbx
+	pushq %r12
+	pushq %r13
+	pushq %r14
+	pushq %r15
+	movq %rsp, (%rdi)
+	movq %rsi, %rsp
+	popq %r15
+	popq %r14
+	popq %r13
+	popq %r12
+	popq %rbx
+	popq %rbp
+	ret
+	.size bt2_fiber_switch,.-bt2_fiber_switch
+)");
+
+namespace bt2shim {
+int device();
+namespace {
+
+struct Worker;
+struct Fiber {
+	enum State { RUNNABLE, WAIT_BATCH, WAIT_INPUT, DONE };
+	void *sp = NULL;
+	void *stack = NULL; size_t stackBytes = 0;
+	void (*fn)(void*) = NULL; void *arg = NULL;
+	State state = RUNNABLE;
+	Worker *w = NULL;
+	const char *error = NULL;        // set when the batch that carried this worker's problem failed
+};
+
+// Problems waiting to travel, by kind, and the workers that wait for them.
+struct Batch {
+	std::vector<DpCall*> dps;
+	std::vector<UngapCall*> ungaps;
+	std::vector<SweepCall*> sweeps;
+	std::vector<OneMmCall*> onemms;
+	std::vector<SeedsCall*> seeds;
+	std::vector<ExtendCall*> extends;
+	std::vector<LocateCall*> locates;
+	std::vector<Fiber*> waiters;
+	std::string error;
+	bool empty() const { return waiters.empty(); }
+	void clear() { dps.clear(); ungaps.clear(); sweeps.clear(); onemms.clear(); seeds.clear(); extends.clear(); locates.clear(); waiters.clear(); error.clear(); }
+};
+
+// A submission lane: one bt2gpu_ctx (stream + arenas) and the helper thread that blocks in the ABI calls.
+struct Lane {
+	Worker *w = NULL;
+	bt2gpu_ctx *ctx = NULL;
+	uint64_t launches = 0;
+	bt2gpu_scoring sc; bool haveSc = false;
+	std::thread th;
+	std::mutex mu; std::condition_variable cv;
+	Batch *job = NULL;               // handed over by the scheduler
+	bool busy = false;               // scheduler's view
+	std::atomic<bool> done{false};
+	// host staging, reused
+	std::vector<uint8_t> seq, qual, win;
+	std::vector<bt2gpu_read> reads;
+	std::vector<bt2gpu_dp_job> djobs; std::vector<bt2gpu_dp_result> dres; std::vector<bt2gpu_dp_cand> dcands;
+	std::vector<bt2gpu_dp_aln> dalns; std::vector<bt2gpu_edit> dedits;
+	std::vector<bt2gpu_ungap_job> ujobs; std::vector<bt2gpu_ungap_result> ures;
+	std::vector<bt2gpu_sweep_result> swres;
+	std::vector<bt2gpu_onemm_job> ojobs; std::vector<bt2gpu_onemm_result> ores; std::vector<bt2gpu_ee_hit> ohits;
+	std::vector<bt2gpu_seed_job> sjobs; std::vector<bt2gpu_seed_hit> shits;
+	std::vector<bt2gpu_extend_job> xjobs; std::vector<bt2gpu_extend_result> xres;
+	std::vector<uint32_t> rows, offs, steps;
+	void run();
+	void execute(Batch& b);
+};
+
+struct Worker {
+	int id = 0;
+	std::thread th;
+	std::mutex inboxMu; std::vector<Fiber*> inbox; std::atomic<int> inboxN{0};
+	std::vector<Fiber*> fibers;
+	std::vector<Lane*> lanes;
+	std::vector<Batch*> freeBatches;
+	Batch *pending = NULL;
+	void *schedSp = NULL;
+	Fiber *cur = NULL;
+	std::mutex mu; std::condition_variable cv;     // lane completions
+	bool inputOk = true;             // the last look for input found some
+	bool inputMiss = false;          // a worker looked and found nothing in this pass
+	void loop();
+	void runFiber(Fiber *f);
+};
+
+thread_local Worker *tl_worker = NULL;
+std::mutex g_mu;
+std::vector<Worker*> g_workers;
+size_t g_next = 0;
+std::atomic<bool> g_spawned{false};
+int g_nthreads = 0, g_nlanes = 2;
+size_t g_stackBytes = 1u << 20;
+
+int envInt(const char *name, int dflt, int lo, int hi) {
+	const char *v = getenv(name);
+	if(v == NULL || *v == 0) return dflt;
+	int x = atoi(v);
+	return x < lo ? lo : (x > hi ? hi : x);
+}
+
+[[noreturn]] void die(const char *what, const char *detail) {
+	fprintf(stderr, "bt2gpu shim: %s: %s\n", what, detail ? detail : "");
+	fflush(stderr);
+	_exit(1);
+}
+
+// ---- worker entry ----------------------------------------------------------------------------------------------------
+void fiberMain() {
+	Worker *w = tl_worker;
+	Fiber *f = w->cur;
+	try {
+		f->fn(f->arg);
+	} catch(int e) {
+		die("worker stopped by a fatal error", "see above");       // what bowtie() reports for `throw 1` (bt2_search.cpp:5604-5611)
+	} catch(std::exception& e) {
+		die("worker stopped by an exception", e.what());
+	} catch(...) {
+		die("worker stopped by an exception", "unknown");
+	}
+	f->state = Fiber::DONE;
+	bt2_fiber_switch(&f->sp, w->schedSp);
+	die("finished worker resumed", "");
+}
+
+void prepare(Fiber *f) {
+	const size_t guard = 4096;
+	void *m = mmap(NULL, f->stackBytes + guard, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE | MAP_STACK, -1, 0);
+	if(m == MAP_FAILED) die("mmap of a worker stack failed", "");
+	mprotect(m, guard, PROT_NONE);
+	f->stack = m;
+	uintptr_t top = ((uintptr_t)m + guard + f->stackBytes) & ~(uintptr_t)15;
+	void **s = (void**)top;
+	*--s = NULL;                       // fake return address of fiberMain
+	*--s = (void*)&fiberMain;          // `ret` of the first switch lands here (16-byte aligned slot: ABI-conformant entry)
+	for(int i = 0; i < 6; i++) *--s = NULL;   // rbp rbx r12 r13 r14 r15
+	f->sp = (void*)s;
+}
+
+// suspends the calling worker; returns when the scheduler resumes it
+void yieldTo(Fiber::State st) {
+	Worker *w = tl_worker;
+	Fiber *f = w->cur;
+	f->state = st;
+	bt2_fiber_switch(&f->sp, w->schedSp);
+}
+
+void Worker::runFiber(Fiber *f) {
+	cur = f;
+	bt2_fiber_switch(&schedSp, f->sp);
+	cur = NULL;
+}
+
+void napMicros(long us) { timespec ts = {0, us * 1000}; nanosleep(&ts, NULL); }
+
+void Worker::loop() {
+	tl_worker = this;
+	pending = new Batch();
+	for(int i = 0; i < g_nlanes + 1; i++) freeBatches.push_back(new Batch());
+	for(int i = 0; i < g_nlanes; i++) {
+		Lane *l = new Lane();
+		l->w = this;
+		lanes.push_back(l);
+		l->th = std::thread([l] { l->run(); });
+		l->th.detach();
+	}
+	for(;;) {
+		if(inboxN.load(std::memory_order_acquire) > 0) {
+			std::lock_guard<std::mutex> lk(inboxMu);
+			for(Fiber *f : inbox) { prepare(f); fibers.push_back(f); }
+			inbox.clear(); inboxN.store(0);
+		}
+		bool progress = false, busy = false;
+		// 1. answered batches: their workers may go on
+		for(Lane *l : lanes) {
+			if(!l->busy) continue;
+			if(!l->done.load(std::memory_order_acquire)) { busy = true; continue; }
+			Batch *b = l->job;
+			const char *err = b->error.empty() ? NULL : strdup(b->error.c_str());
+			for(Fiber *f : b->waiters) { f->state = Fiber::RUNNABLE; f->error = err; }
+			b->clear();
+			freeBatches.push_back(b);
+			l->job = NULL; l->busy = false;
+			progress = true;
+		}
+		// 2. every runnable worker runs until its next hot-path call; of the workers that wait for input only one looks
+		//    while the last look found nothing
+		int looks = inputOk ? (int)fibers.size() : 1;
+		inputMiss = false;
+		for(size_t i = 0; i < fibers.size(); i++) {
+			Fiber *f = fibers[i];
+			if(f->state == Fiber::WAIT_INPUT) {
+				if(looks <= 0) continue;
+				looks--;
+			} else if(f->state != Fiber::RUNNABLE) continue;
+			runFiber(f);
+			if(f->state != Fiber::WAIT_INPUT) progress = true;
+			if(inputMiss && looks > 1) looks = 1;
+		}
+		inputOk = !inputMiss;
+		// 3. what they queued travels on a free lane
+		if(!pending->empty()) {
+			Lane *fl = NULL;
+			for(Lane *l : lanes) if(!l->busy) { fl = l; break; }
+			if(fl != NULL) {
+				Batch *b = pending;
+				pending = freeBatches.back(); freeBatches.pop_back();
+				fl->busy = true;
+				fl->done.store(false, std::memory_order_relaxed);
+				{ std::lock_guard<std::mutex> lk(fl->mu); fl->job = b; }
+				fl->cv.notify_one();
+				progress = true; busy = true;
+			}
+		}
+		// 4. nothing to do: wait for a lane, or for input
+		if(!progress) {
+			if(busy) {
+				std::unique_lock<std::mutex> lk(mu);
+				bool any = false;
+				for(Lane *l : lanes) if(l->busy && l->done.load(std::memory_order_acquire)) any = true;
+				if(!any) cv.wait_for(lk, std::chrono::microseconds(500));
+			} else napMicros(fibers.empty() ? 2000 : 300);
+		}
+	}
+}
+
+// ---- lane: executes one batch -------------------------------------------------------------------------------------
+void Lane::run() {
+	for(;;) {
+		Batch *b = NULL;
+		{
+			std::unique_lock<std::mutex> lk(mu);
+			cv.wait(lk, [this] { return job != NULL && !done.load(); });
+			b = job;
+		}
+		try {
+			if(ctx == NULL && bt2gpu_ctx_create(device(), &ctx)) fail("bt2gpu_ctx_create");
+			execute(*b);
+		} catch(int) {
+			die("batched ABI call failed", "the server has no CPU path and stops");
+		}
+		noteLaunches(ctx, launches);
+		{
+			std::lock_guard<std::mutex> lk(w->mu);
+			done.store(true, std::memory_order_release);
+		}
+		w->cv.notify_one();
+	}
+}
+
+void appendRead(Lane& l, const Read& rd) {
+	const size_t len = rd.length();
+	bt2gpu_read r; r.rd_off = (uint32_t)l.seq.size(); r.rd_len = (uint32_t)len;
+	const size_t o = l.seq.size();
+	l.seq.resize(o + len); l.qual.resize(o + len);
+	for(size_t i = 0; i < len; i++) { l.seq[o + i] = (uint8_t)rd.patFw[i]; l.qual[o + i] = (uint8_t)rd.qual[i]; }
+	l.reads.push_back(r);
+}
+
+void stage(Lane& l) {
+	if(bt2gpu_reads_stage(l.ctx, l.seq.data(), l.qual.data(), l.seq.size(), l.reads.data(), l.reads.size())) fail("bt2gpu_reads_stage");
+}
+
+void bind(Lane& l, const Scoring *sc) {
+	bt2gpu_scoring s;
+	toScoring(*sc, s);
+	if(l.haveSc && memcmp(&s, &l.sc, sizeof(s)) == 0) return;
+	if(bt2gpu_scoring_set(l.ctx, &s)) fail("bt2gpu_scoring_set");
+	l.sc = s; l.haveSc = true;
+}
+
+void noteBatch(Counter c, size_t n) { note(c, n); note(C_BATCHES, 1); note(C_BATCH_JOBS, n); }
+
+void Lane::execute(Batch& b) {
+	// ---- exactSweep: reads that share (nofw, norc, mineMax) travel together ----
+	{
+		std::vector<char> taken(b.sweeps.size(), 0);
+		for(size_t i0 = 0; i0 < b.sweeps.size(); i0++) {
+			if(taken[i0]) continue;
+			const SweepCall& k = *b.sweeps[i0];
+			std::vector<size_t> grp;
+			for(size_t i = i0; i < b.sweeps.size(); i++) {
+				const SweepCall& c = *b.sweeps[i];
+				if(!taken[i] && c.fw == k.fw && c.nofw == k.nofw && c.norc == k.norc && c.mineMax == k.mineMax) { taken[i] = 1; grp.push_back(i); }
+			}
+			bind(*this, k.sc);
+			seq.clear(); qual.clear(); reads.clear();
+			for(size_t i : grp) appendRead(*this, *b.sweeps[i]->rd);
+			stage(*this);
+			swres.resize(grp.size());
+			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
+			for(size_t j = 0; j < grp.size(); j++) b.sweeps[grp[j]]->res = swres[j];
+			noteBatch(C_SWEEP, grp.size());
+		}
+	}
+	// ---- oneMmSearch: by (local, repex, rep1mm) ----
+	{
+		std::vector<char> taken(b.onemms.size(), 0);
+		for(size_t i0 = 0; i0 < b.onemms.size(); i0++) {
+			if(taken[i0]) continue;
+			const OneMmCall& k = *b.onemms[i0];
+			std::vector<size_t> grp;
+			for(size_t i = i0; i < b.onemms.size(); i++) {
+				const OneMmCall& c = *b.onemms[i];
+				if(!taken[i] && c.fw == k.fw && c.bw == k.bw && c.local == k.local && c.repex == k.repex && c.rep1mm == k.rep1mm) { taken[i] = 1; grp.push_back(i); }
+			}
+			bind(*this, k.sc);
+			seq.clear(); qual.clear(); reads.clear(); ojobs.clear();
+			size_t cap = 0;
+			for(size_t i : grp) { appendRead(*this, *b.onemms[i]->rd); ojobs.push_back(b.onemms[i]->job); cap += 8 * b.onemms[i]->rd->length() + 64; }
+			stage(*this);
+			ores.resize(grp.size()); ohits.resize(cap);
+			size_t n = 0;
+			if(bt2gpu_onemm_batch(ctx, index(*k.fw), index(*k.bw), ojobs.data(), k.local ? 1 : 0, k.repex ? 1 : 0, k.rep1mm ? 1 : 0,
+			                      ores.data(), ohits.data(), cap, &n)) fail("bt2gpu_onemm_batch");
+			for(size_t j = 0; j < grp.size(); j++) {
+				OneMmCall& c = *b.onemms[grp[j]];
+				c.res = ores[j];
+				c.hits.assign(ohits.begin() + ores[j].hit_off, ohits.begin() + ores[j].hit_off + ores[j].nhits);
+				c.res.hit_off = 0;
+			}
+			noteBatch(C_ONEMM, grp.size());
+		}
+	}
+	// ---- exact seeds and seed-hit extensions share one staged read pool ----
+	if(!b.seeds.empty() || !b.extends.empty()) {
+		const Ebwt *fw = !b.seeds.empty() ? b.seeds[0]->fw : b.extends[0]->fw, *bw = !b.seeds.empty() ? b.seeds[0]->bw : b.extends[0]->bw;
+		if(!b.seeds.empty()) bind(*this, b.seeds[0]->sc);
+		seq.clear(); qual.clear(); reads.clear(); sjobs.clear(); xjobs.clear();
+		for(SeedsCall *c : b.seeds) {
+			if(c->fw != fw || c->bw != bw) { fprintf(stderr, "bt2gpu shim: workers of one server use different indexes\n"); throw 1; }
+			const uint32_t ri = (uint32_t)reads.size();
+			appendRead(*this, *c->rd);
+			for(bt2gpu_seed_job j : c->jobs) { j.read = ri; sjobs.push_back(j); }
+		}
+		for(ExtendCall *c : b.extends) {
+			if(c->fw != fw || c->bw != bw) { fprintf(stderr, "bt2gpu shim: workers of one server use different indexes\n"); throw 1; }
+			bt2gpu_extend_job j = c->job;
+			j.read = (uint32_t)reads.size();
+			appendRead(*this, *c->rd);
+			xjobs.push_back(j);
+		}
+		stage(*this);
+		if(!sjobs.empty()) {
+			shits.resize(sjobs.size());
+			if(bt2gpu_seed_exact_batch(ctx, index(*fw), index(*bw), sjobs.data(), sjobs.size(), shits.data())) fail("bt2gpu_seed_exact_batch");
+			size_t o = 0;
+			for(SeedsCall *c : b.seeds) { c->out.assign(shits.begin() + o, shits.begin() + o + c->jobs.size()); o += c->jobs.size(); }
+			noteBatch(C_SEEDS, sjobs.size());
+		} else for(SeedsCall *c : b.seeds) c->out.clear();
+		if(!xjobs.empty()) {
+			xres.resize(xjobs.size());
+			if(bt2gpu_extend_batch(ctx, index(*fw), index(*bw), xjobs.data(), xjobs.size(), xres.data())) fail("bt2gpu_extend_batch");
+			for(size_t j = 0; j < xjobs.size(); j++) b.extends[j]->res = xres[j];
+			noteBatch(C_EXTEND, xjobs.size());
+		}
+	}
+	// ---- BW rows to text offsets ----
+	if(!b.locates.empty()) {
+		const size_t n = b.locates.size();
+		rows.resize(n); offs.resize(n); steps.resize(n);
+		for(size_t j = 0; j < n; j++) rows[j] = b.locates[j]->row;
+		if(bt2gpu_locate_batch(ctx, index(*b.locates[0]->fw), rows.data(), n, offs.data(), steps.data())) fail("bt2gpu_locate_batch");
+		for(size_t j = 0; j < n; j++) { b.locates[j]->off = offs[j]; b.locates[j]->steps = steps[j]; }
+		noteBatch(C_LOCATE, n);
+	}
+	// ---- ungapped diagonals ----
+	if(!b.ungaps.empty()) {
+		const size_t n = b.ungaps.size();
+		bind(*this, b.ungaps[0]->sc);
+		seq.clear(); qual.clear(); win.clear(); ujobs.clear();
+		size_t cap = 0;
+		for(UngapCall *c : b.ungaps) {
+			bt2gpu_ungap_job j = c->job;
+			j.rd_off = (uint32_t)seq.size(); j.rf_off = (uint32_t)win.size();
+			seq.insert(seq.end(), c->seq, c->seq + j.rd_len); qual.insert(qual.end(), c->qual, c->qual + j.rd_len);
+			win.insert(win.end(), c->win, c->win + j.rd_len);
+			ujobs.push_back(j);
+			cap += j.rd_len + 1;
+		}
+		ures.resize(n); dedits.resize(cap);
+		size_t ne = 0;
+		if(bt2gpu_ungapped_batch(ctx, seq.data(), qual.data(), seq.size(), win.data(), win.size(), ujobs.data(), n, ures.data(),
+		                         dedits.data(), cap, &ne)) fail("bt2gpu_ungapped_batch");
+		for(size_t j = 0; j < n; j++) {
+			UngapCall& c = *b.ungaps[j];
+			c.res = ures[j];
+			c.edits.assign(dedits.begin() + ures[j].edit_off, dedits.begin() + ures[j].edit_off + (ures[j].ret == 1 ? ures[j].nedits : 0));
+			c.res.edit_off = 0;
+		}
+		noteBatch(C_UNGAPPED, n);
+	}
+	// ---- DP windows: by the bound on the nextAlignment loop (the first ask is short, the rare re-ask is complete) ----
+	{
+		std::vector<char> taken(b.dps.size(), 0);
+		for(size_t i0 = 0; i0 < b.dps.size(); i0++) {
+			if(taken[i0]) continue;
+			const DpCall& k = *b.dps[i0];
+			std::vector<size_t> grp;
+			for(size_t i = i0; i < b.dps.size(); i++) if(!taken[i] && b.dps[i]->max_aln == k.max_aln && b.dps[i]->sc == k.sc) { taken[i] = 1; grp.push_back(i); }
+			bind(*this, k.sc);
+			const size_t n = grp.size();
+			seq.clear(); qual.clear(); win.clear(); djobs.clear();
+			size_t ccap = 0, ecap = 1024;
+			for(size_t i : grp) {
+				DpCall& c = *b.dps[i];
+				c.job.rd_off = (uint32_t)seq.size(); c.job.rf_off = (uint32_t)win.size();
+				seq.insert(seq.end(), c.seq, c.seq + c.job.rd_len); qual.insert(qual.end(), c.qual, c.qual + c.job.rd_len);
+				win.insert(win.end(), c.win, c.win + c.job.ncol + 1);
+				djobs.push_back(c.job);
+				ccap += k.sc->monotone ? (size_t)c.job.ncol + 64 : (size_t)c.job.rd_len * c.job.ncol + 64;
+				ecap += (size_t)(c.job.rd_len + 64) * (k.max_aln < 4 ? k.max_aln : 4);
+			}
+			dres.resize(n); dalns.resize(n * (size_t)k.max_aln);
+			for(int attempt = 0; ; attempt++) {
+				dcands.resize(ccap); dedits.resize(ecap);
+				if(bt2gpu_dp_align_batch(ctx, seq.data(), qual.data(), seq.size(), win.data(), win.size(), djobs.data(), n, k.max_aln,
+				                         dres.data(), dcands.data(), ccap, dalns.data(), dedits.data(), ecap) == 0) break;
+				const char *e = bt2gpu_last_error();
+				if(attempt < 6 && strstr(e, "edit pool overflow")) { ecap *= 4; continue; }
+				fail("bt2gpu_dp_align_batch");
+			}
+			for(size_t j = 0; j < n; j++) {
+				DpCall& c = *b.dps[grp[j]];
+				const bt2gpu_dp_result& r = dres[j];
+				c.res = r;
+				c.cands.assign(dcands.begin() + r.cand_off, dcands.begin() + r.cand_off + r.ncand);
+				c.alns.assign(dalns.begin() + r.aln_off, dalns.begin() + r.aln_off + r.naln);
+				c.edits.clear();
+				for(bt2gpu_dp_aln& a : c.alns) {
+					const uint32_t o = (uint32_t)c.edits.size();
+					c.edits.insert(c.edits.end(), dedits.begin() + a.edit_off, dedits.begin() + a.edit_off + a.nedits);
+					a.edit_off = o;
+				}
+				c.res.cand_off = 0; c.res.aln_off = 0;
+			}
+			noteBatch(C_ALIGN, n);
+		}
+	}
+}
+
+// ---- the binding: queue, suspend, resume with the answer ---------------------------------------------------------------
+template<typename T> void travel(std::vector<T*> Batch::*list, T& c) {
+	Worker *w = tl_worker;
+	if(w == NULL || w->cur == NULL) { fprintf(stderr, "bt2gpu shim: hot-path call outside a worker (batched binding)\n"); throw 1; }
+	Fiber *f = w->cur;
+	(w->pending->*list).push_back(&c);
+	w->pending->waiters.push_back(f);
+	yieldTo(Fiber::WAIT_BATCH);
+	if(f->error != NULL) { fprintf(stderr, "bt2gpu shim: %s\n", f->error); throw 1; }
+}
+
+} // namespace
+
+bt2gpu_ctx *ctx() { fprintf(stderr, "bt2gpu shim: per-thread context requested in the batched binding\n"); throw 1; }
+
+void dpAlign(DpCall& c)   { travel(&Batch::dps, c); }
+void ungapped(UngapCall& c) { travel(&Batch::ungaps, c); }
+void sweep(SweepCall& c)  { travel(&Batch::sweeps, c); }
+void oneMm(OneMmCall& c)  { travel(&Batch::onemms, c); }
+void seeds(SeedsCall& c)  { c.out.clear(); if(c.jobs.empty()) return; travel(&Batch::seeds, c); }
+void extend(ExtendCall& c) { travel(&Batch::extends, c); }
+void locate(LocateCall& c) { travel(&Batch::locates, c); }
+
+// ---- fiber.h ------------------------------------------------------------------------------------------------------
+bool inWorker() { return tl_worker != NULL && tl_worker->cur != NULL; }
+
+void waitInput() {
+	Worker *w = tl_worker;
+	if(w == NULL || w->cur == NULL) { napMicros(200); return; }
+	w->inputMiss = true;
+	yieldTo(Fiber::WAIT_INPUT);
+}
+
+void sleepMs(int ms) {
+	if(g_spawned.exchange(false)) return;
+	timespec ts = {ms / 1000, (long)(ms % 1000) * 1000000L};
+	nanosleep(&ts, NULL);
+}
+
+void spawnWorker(void (*fn)(void*), void *arg) {
+	std::lock_guard<std::mutex> lk(g_mu);
+	if(g_nthreads == 0) {
+		int hw = (int)std::thread::hardware_concurrency();
+		if(hw < 1) hw = 1;
+		g_nthreads = envInt("BT2GPU_THREADS", hw > 16 ? 16 : hw, 1, 1024);
+		g_nlanes = envInt("BT2GPU_LANES", 2, 1, 8);
+		g_stackBytes = (size_t)envInt("BT2GPU_STACK_KB", 1024, 64, 1 << 20) * 1024;
+	}
+	Worker *w = NULL;
+	if((int)g_workers.size() < g_nthreads) {
+		w = new Worker();
+		w->id = (int)g_workers.size();
+		g_workers.push_back(w);
+		w->th = std::thread([w] { w->loop(); });
+		w->th.detach();
+	} else w = g_workers[g_next++ % g_workers.size()];
+	Fiber *f = new Fiber();
+	f->fn = fn; f->arg = arg; f->w = w; f->stackBytes = g_stackBytes;
+	{
+		std::lock_guard<std::mutex> lk2(w->inboxMu);
+		w->inbox.push_back(f);
+		w->inboxN.fetch_add(1, std::memory_order_release);
+	}
+	g_spawned.store(true);
+}
+
+} // namespace bt2shim

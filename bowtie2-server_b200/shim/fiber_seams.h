@@ -1,0 +1,100 @@
+// fiber_seams.h — FORCE-INCLUDED (-include, with -DBT2SHIM_SEAMS_SEARCH) when the unmodified bt2_search.cpp is compiled
+// for the batched GPU-bound server (oracle/Makefile, target gpub).  It stands for the three `#ifdef BT2_GPU` edits a
+// maintainer would make in that file; nothing else of the reference changes:
+//
+//   1. worker start-up (bt2_search.cpp:4913-4925): `new std::thread(multiseedSearchWorker, &tps[i])` starts a worker
+//      FIBER (fiber.h) instead of an OS thread -- `-p N` is then the number of reads in flight, spread over
+//      BT2GPU_THREADS host threads -- and the 10 ms pause after each start is skipped;
+//   2. input (bt2_search.cpp:3201): `PSFactory::ReadAhead psrah(factory)` blocks the calling thread on the server's
+//      ready queue (pat.h:1885-1911, :1987-1994); a fiber must not block its host thread, so the batched build takes
+//      the next filled read buffer if there is one and otherwise lets the other workers of the thread run;
+//   3. GroupWalk2S -> the locate call of the binding (group_walk_gpu.h, as in the per-call build).
+//
+// All reference headers bt2_search.cpp uses are included FIRST, so the renames below touch that one file only.
+#ifndef BT2GPU_FIBER_SEAMS_H_
+#define BT2GPU_FIBER_SEAMS_H_
+
+#include "group_walk_gpu.h"
+
+#ifdef BT2SHIM_SEAMS_SEARCH
+#include <thread>
+#include <mutex>
+#include <condition_variable>
+#include <queue>
+#include "alphabet.h"
+#include "assert_helpers.h"
+#include "endian_swap.h"
+#include "bt2_idx.h"
+#include "formats.h"
+#include "sequence_io.h"
+#include "tokenize.h"
+#include "aln_sink.h"
+#include "pat.h"
+#include "threading.h"
+#include "ds.h"
+#include "aligner_metrics.h"
+#include "sam.h"
+#include "aligner_seed.h"
+#include "aligner_seed_policy.h"
+#include "aligner_driver.h"
+#include "aligner_sw.h"
+#include "aligner_sw_driver.h"
+#include "aligner_cache.h"
+#include "util.h"
+#include "pe.h"
+#include "simple_func.h"
+#include "presets.h"
+#include "opts.h"
+#include "outq.h"
+#include "aligner_seed2.h"
+#include "fiber.h"
+
+namespace bt2shim {
+
+// PatternSourceServiceFactory::ReadAhead (pat.h:1885-1911) with a non-blocking first step: same members, same
+// protocol (the element goes back to the connection's idle queue when the holder is destroyed).
+// Compiled with -fno-access-control: the ready queue and its lock are private members of the factory.
+class FiberReadAhead {
+public:
+	typedef PatternSourceServiceFactory::ReadElement ReadElement;
+	FiberReadAhead(PatternSourceServiceFactory& fact) : fact_(fact), re_(take(fact)), first_(true) {}
+	~FiberReadAhead() { fact_.returnUnready(re_); }
+	const std::pair<bool, bool>& nextReadResult() {
+		if(first_) first_ = false;       // nextReadPair was already called by the connection's thread (pat.cpp:2064-2079)
+		else re_.nextReadPair();
+		return re_.readResult;
+	}
+	PatternSourcePerThread* ptr() { return re_.ps; }
+private:
+	static ReadElement take(PatternSourceServiceFactory& fact) {
+		for(;;) {
+			{
+				std::unique_lock<std::mutex> lk(fact.psq_ready_.m_);
+				if(!fact.psq_ready_.q_.empty()) {
+					ReadElement r(fact.psq_ready_.q_.front());
+					fact.psq_ready_.q_.pop();
+					return r;
+				}
+			}
+			waitInput();
+		}
+	}
+	PatternSourceServiceFactory& fact_;
+	ReadElement re_;
+	bool first_;
+};
+
+} // namespace bt2shim
+
+namespace std { typedef ::bt2shim::FiberThread bt2shim_fiber_thread; }
+
+// 1. std::thread -> worker fibers (the only uses of the token in bt2_search.cpp are `std::thread`)
+#define thread bt2shim_fiber_thread
+// 2. `PSFactory::ReadAhead psrah(f);` -> `PSFactory::ReadElement *bt2shim_unused_ = 0; bt2shim::FiberReadAhead psrah(f);`
+#define ReadAhead ReadElement *bt2shim_unused_ = 0; ::bt2shim::FiberReadAhead
+// the pause after each worker start (threading.h:44-51)
+#undef SLEEP
+#define SLEEP(x) ::bt2shim::sleepMs(x)
+#endif  // BT2SHIM_SEAMS_SEARCH
+
+#endif

@@ -1,23 +1,21 @@
-// gpu_shim.cpp — see gpu_shim.h.  Our code, compiled against the reference's headers.
+// gpu_shim.cpp — the per-call binding of gpu_shim.h: every problem is one ABI call (a batch of one) on the calling
+// worker thread's own context, as the reference calls its SeedAligner / SwAligner once per read / seed hit / window
+// ("one SeedAligner/SwAligner per thread", bt2_search.cpp:3128-3130).  The batched binding is batch_shim.cpp.
 #include <cstdio>
-#include <cstdlib>
-#include <atomic>
-#include <mutex>
-#include <unordered_map>
-#include <fcntl.h>
-#include <unistd.h>
+#include <cstring>
+#include <vector>
 #include "bt2_idx.h"
 #include "scoring.h"
 #include "read.h"
-#include <vector>
 #include "gpu_shim.h"
 
 namespace bt2shim {
+int device();
 namespace {
 
 struct Thread {
 	bt2gpu_ctx *ctx = NULL;
-	const Scoring *sc = NULL;
+	bt2gpu_scoring sc; bool haveSc = false;
 	uint64_t launches = 0;
 	std::vector<uint8_t> seq, qual;           // the staged read
 	const Read *rd = NULL; uint64_t rdid = 0; int mate = 0;
@@ -25,35 +23,15 @@ struct Thread {
 };
 thread_local Thread g_t;
 
-std::mutex g_ixmu;
-std::unordered_map<const Ebwt*, bt2gpu_index*> g_ix;
-std::atomic<uint64_t> g_cnt[C_NCOUNTERS], g_launches(0);
-
-int device() { const char *d = getenv("BT2GPU_DEVICE"); return d ? atoi(d) : 0; }
-
-} // namespace
-
-void fail(const char *what) {
-	fprintf(stderr, "bt2gpu shim: %s: %s\n", what, bt2gpu_last_error());
-	throw 1;
-}
-
-bt2gpu_ctx *ctx() {
-	if(g_t.ctx == NULL && bt2gpu_ctx_create(device(), &g_t.ctx)) fail("bt2gpu_ctx_create");
-	return g_t.ctx;
-}
-
+// bt2gpu_scoring_set once per (thread, scheme): compared by content, so a Scoring rebuilt at the same address with
+// other penalties is uploaded again
 void bindScoring(const Scoring& sc) {
 	bt2gpu_ctx *c = ctx();
-	if(g_t.sc == &sc) return;
 	bt2gpu_scoring s;
-	for(int q = 0; q < 256; q++) { s.mmpens[q] = sc.mmpens[q]; s.npens[q] = sc.npens[q]; }
-	s.match_bonus = (int32_t)sc.match(30);
-	s.rd_gap_open = sc.readGapOpen();  s.rd_gap_ext = sc.readGapExtend();
-	s.rf_gap_open = sc.refGapOpen();   s.rf_gap_ext = sc.refGapExtend();
-	s.gapbar = sc.gapbar;              s.monotone = sc.monotone ? 1 : 0;
+	toScoring(sc, s);
+	if(g_t.haveSc && memcmp(&s, &g_t.sc, sizeof(s)) == 0) return;
 	if(bt2gpu_scoring_set(c, &s)) fail("bt2gpu_scoring_set");
-	g_t.sc = &sc;
+	g_t.sc = s; g_t.haveSc = true;
 }
 
 // Read::patFw (codes 0..4) + Read::qual (Phred+33) -> the context's read pool.  The reference hands the same Read to
@@ -74,42 +52,79 @@ void stageRead(const Read& rd) {
 	t.rd = &rd; t.rdid = (uint64_t)rd.rdid; t.mate = rd.mate;
 }
 
-// Ebwt as loaded by Ebwt::readIntoMemory (bt2_io.cpp:131-614) -> bt2gpu_index_desc, field for field
-bt2gpu_index *index(const Ebwt& e) {
-	std::lock_guard<std::mutex> lk(g_ixmu);
-	auto it = g_ix.find(&e);
-	if(it != g_ix.end()) return it->second;
-	bt2gpu_index_desc d;
-	d.ebwt = e.ebwt();             d.ebwt_bytes = e.eh().ebwtTotLen();
-	d.offs = e.offs();             d.n_offs = e.offs() ? e.eh().offsLen() : 0;
-	d.ftab = e.ftab();             d.eftab = e.eftab();
-	for(int i = 0; i < 5; i++) d.fchr[i] = e.fchr()[i];
-	d.zoff = e.zOff();             d.len = e.eh().len();
-	d.off_rate = e.eh().offRate(); d.ftab_chars = e.eh().ftabChars();
-	d.is_fw = e.fw() ? 1 : 0;
-	bt2gpu_index *h = NULL;
-	if(bt2gpu_index_create(device(), &d, &h)) fail("bt2gpu_index_create");
-	g_ix[&e] = h;
-	return h;
+void noted(Counter c, uint64_t n) { noteLaunches(g_t.ctx, g_t.launches); note(c, n); }
+
+} // namespace
+
+bt2gpu_ctx *ctx() {
+	if(g_t.ctx == NULL && bt2gpu_ctx_create(device(), &g_t.ctx)) fail("bt2gpu_ctx_create");
+	return g_t.ctx;
 }
 
-void note(Counter c, uint64_t n) {
-	static const char *path = getenv("BT2GPU_SHIM_STATS");
-	static int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
-	g_cnt[c] += n;
-	if(g_t.ctx != NULL) {
-		uint64_t l = bt2gpu_ctx_launches(g_t.ctx);
-		g_launches += l - g_t.launches; g_t.launches = l;
-	}
-	if(fd < 0) return;
-	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapped_calls_on_gpu", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
-	                                          "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu", "other_mate_on_gpu", "mate_rect_on_gpu", "pe_classify_on_gpu",
-	                                          "joined_to_text_off_on_gpu" };
-	char buf[1024]; int n2 = 0;
-	for(int i = 0; i < C_NCOUNTERS; i++)
-		n2 += snprintf(buf + n2, sizeof buf - n2, "%s %12llu ", names[i], (unsigned long long)g_cnt[i].load());
-	n2 += snprintf(buf + n2, sizeof buf - n2, "kernel_launches %12llu\n", (unsigned long long)g_launches.load());
-	if(pwrite(fd, buf, (size_t)n2, 0) < 0) { /* evidence only */ }
+void dpAlign(DpCall& c) {
+	bindScoring(*c.sc);
+	const size_t cc = c.sc->monotone ? (size_t)c.job.ncol + 64 : (size_t)c.job.rd_len * c.job.ncol + 64;
+	const size_t ec = (size_t)1 << 18;
+	c.job.rd_off = 0; c.job.rf_off = 0;
+	c.cands.resize(cc); c.alns.resize(c.max_aln); c.edits.resize(ec);
+	if(bt2gpu_dp_align_batch(ctx(), c.seq, c.qual, c.job.rd_len, c.win, (size_t)c.job.ncol + 1, &c.job, 1, c.max_aln,
+	                         &c.res, c.cands.data(), cc, c.alns.data(), c.edits.data(), ec))
+		fail("bt2gpu_dp_align_batch");
+	noted(C_ALIGN, 1);
+}
+
+void ungapped(UngapCall& c) {
+	bindScoring(*c.sc);
+	const size_t len = c.job.rd_len;
+	c.job.rd_off = 0; c.job.rf_off = 0;
+	c.edits.resize(len + 1);
+	size_t ne = 0;
+	if(bt2gpu_ungapped_batch(ctx(), c.seq, c.qual, len, c.win, len, &c.job, 1, &c.res, c.edits.data(), len + 1, &ne))
+		fail("bt2gpu_ungapped_batch");
+	noted(C_UNGAPPED, 1);
+}
+
+void sweep(SweepCall& c) {
+	bindScoring(*c.sc);
+	stageRead(*c.rd);
+	if(bt2gpu_exact_sweep_batch(ctx(), index(*c.fw), c.nofw ? 1 : 0, c.norc ? 1 : 0, c.mineMax, &c.res))
+		fail("bt2gpu_exact_sweep_batch");
+	noted(C_SWEEP, 1);
+}
+
+void oneMm(OneMmCall& c) {
+	bindScoring(*c.sc);
+	stageRead(*c.rd);
+	const size_t cap = 8 * c.rd->length() + 64;
+	size_t n = 0;
+	c.hits.resize(cap);
+	if(bt2gpu_onemm_batch(ctx(), index(*c.fw), index(*c.bw), &c.job, c.local ? 1 : 0, c.repex ? 1 : 0, c.rep1mm ? 1 : 0,
+	                      &c.res, c.hits.data(), cap, &n))
+		fail("bt2gpu_onemm_batch");
+	noted(C_ONEMM, 1);
+}
+
+void seeds(SeedsCall& c) {
+	c.out.resize(c.jobs.size());
+	if(c.jobs.empty()) return;
+	bindScoring(*c.sc);
+	stageRead(*c.rd);
+	for(size_t i = 0; i < c.jobs.size(); i++) c.jobs[i].read = 0;
+	if(bt2gpu_seed_exact_batch(ctx(), index(*c.fw), index(*c.bw), c.jobs.data(), c.jobs.size(), c.out.data()))
+		fail("bt2gpu_seed_exact_batch");
+	noted(C_SEEDS, c.jobs.size());
+}
+
+void extend(ExtendCall& c) {
+	stageRead(*c.rd);
+	c.job.read = 0;
+	if(bt2gpu_extend_batch(ctx(), index(*c.fw), index(*c.bw), &c.job, 1, &c.res)) fail("bt2gpu_extend_batch");
+	noted(C_EXTEND, 1);
+}
+
+void locate(LocateCall& c) {
+	if(bt2gpu_locate_batch(ctx(), index(*c.fw), &c.row, 1, &c.off, &c.steps)) fail("bt2gpu_locate_batch");
+	noted(C_LOCATE, 1);
 }
 
 } // namespace bt2shim

@@ -30,12 +30,11 @@ public:
 	                    GroupWalkState& gws, WalkResult& res, WalkMetrics& met, PerReadMetrics& prm)
 	{
 		if(sa.offs[elt] == OFF_MASK) {
-			uint32_t row = (uint32_t)(sa.topf + elt), off = 0, steps = 0;
-			if(bt2gpu_locate_batch(bt2shim::ctx(), bt2shim::index(ebwtFw), &row, 1, &off, &steps))
-				bt2shim::fail("bt2gpu_locate_batch");
-			bt2shim::note(bt2shim::C_LOCATE, 1);
-			sa.offs[elt] = (TIndexOffU)off;
-			met.bwops += steps; prm.nExFmops += steps;
+			bt2shim::LocateCall lc;
+			lc.fw = &ebwtFw; lc.row = (uint32_t)(sa.topf + elt); lc.off = 0; lc.steps = 0;
+			bt2shim::locate(lc);
+			sa.offs[elt] = (TIndexOffU)lc.off;
+			met.bwops += lc.steps; prm.nExFmops += lc.steps;
 			met.resolves++;
 		}
 		met.reports++;

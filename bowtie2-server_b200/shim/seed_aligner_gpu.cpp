@@ -11,17 +11,6 @@
 #include "aligner_seed.h"
 #include "gpu_shim.h"
 
-namespace {
-
-struct SeedThread {
-	std::vector<bt2gpu_seed_job> jobs;
-	std::vector<bt2gpu_seed_hit> out;
-	std::vector<bt2gpu_ee_hit> ee;
-};
-thread_local SeedThread g_s;
-
-} // namespace
-
 /**
  * SeedAligner::exactSweep (aligner_seed.cpp:854-968): same contract — returns the number of BW elements of the exact
  * end-to-end hits, sets mineFw/mineRc as exactSweepStep / the final loop do, installs the exact hits in `hits`.
@@ -30,12 +19,10 @@ size_t SeedAligner::exactSweep(
 	const Ebwt& ebwt, const Read& read, const Scoring& sc, bool nofw, bool norc, size_t mineMax,
 	size_t& mineFw, size_t& mineRc, bool repex, SeedResults& hits, SeedSearchMetrics& met)
 {
-	bt2shim::bindScoring(sc);
-	bt2shim::stageRead(read);
-	bt2gpu_sweep_result r;
-	if(bt2gpu_exact_sweep_batch(bt2shim::ctx(), bt2shim::index(ebwt), nofw ? 1 : 0, norc ? 1 : 0, (uint32_t)mineMax, &r))
-		bt2shim::fail("bt2gpu_exact_sweep_batch");
-	bt2shim::note(bt2shim::C_SWEEP, 1);
+	bt2shim::SweepCall sw;
+	sw.fw = &ebwt; sw.sc = &sc; sw.rd = &read; sw.nofw = nofw; sw.norc = norc; sw.mineMax = (uint32_t)mineMax;
+	bt2shim::sweep(sw);
+	const bt2gpu_sweep_result& r = sw.res;
 	bwops_ += r.bwops;
 	const size_t len = read.length();
 	size_t nelt = 0;
@@ -73,22 +60,16 @@ bool SeedAligner::oneMmSearch(
 	if(ns > 1) return false;                 // :990-997
 	else if(ns == 1 && !rep1mm) return false;
 	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: oneMmSearch needs the mirror index\n"); throw 1; }
-	bt2shim::bindScoring(sc);
-	bt2shim::stageRead(read);
-	bt2gpu_onemm_job job;
-	job.minsc = (int32_t)minsc; job.nceil = sc.nCeil.f<int>((double)len);
-	job.nofw = nofw ? 1 : 0; job.norc = norc ? 1 : 0; job.pad[0] = job.pad[1] = 0;
-	bt2gpu_onemm_result res;
-	SeedThread& t = g_s;
-	size_t cap = 8 * len + 64, n = 0;
-	t.ee.resize(cap);
-	if(bt2gpu_onemm_batch(bt2shim::ctx(), bt2shim::index(*ebwtFw), bt2shim::index(*ebwtBw), &job, local ? 1 : 0,
-	                      repex ? 1 : 0, rep1mm ? 1 : 0, &res, t.ee.data(), cap, &n))
-		bt2shim::fail("bt2gpu_onemm_batch");
-	bt2shim::note(bt2shim::C_ONEMM, 1);
+	bt2shim::OneMmCall om;
+	om.fw = ebwtFw; om.bw = ebwtBw; om.sc = &sc; om.rd = &read;
+	om.job.minsc = (int32_t)minsc; om.job.nceil = sc.nCeil.f<int>((double)len);
+	om.job.nofw = nofw ? 1 : 0; om.job.norc = norc ? 1 : 0; om.job.pad[0] = om.job.pad[1] = 0;
+	om.local = local; om.repex = repex; om.rep1mm = rep1mm;
+	bt2shim::oneMm(om);
+	const bt2gpu_onemm_result& res = om.res;
 	bwops_ += res.bwops;
 	for(uint32_t k = 0; k < res.nhits; k++) {
-		const bt2gpu_ee_hit& h = t.ee[res.hit_off + k];
+		const bt2gpu_ee_hit& h = om.hits[res.hit_off + k];
 		const bool fw = h.fw != 0;
 		if(h.pos == 0xffff) {
 			int64_t score = len * sc.match();
@@ -118,8 +99,8 @@ void SeedAligner::searchAllSeeds(
 	bwops_ = bwedits_ = 0;
 	uint64_t possearches = 0, seedsearches = 0, ooms = 0;
 	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: searchAllSeeds needs the mirror index\n"); throw 1; }
-	SeedThread& t = g_s;
-	t.jobs.clear();
+	bt2shim::SeedsCall sd;
+	sd.fw = ebwtFw; sd.bw = ebwtBw; sd.sc = &pens; sd.rd = &read;
 	for(int fwi = 0; fwi < 2; fwi++) {
 		const bool fw = (fwi == 0);
 		for(size_t i = 0; i < sr.numOffs(); i++) {
@@ -133,24 +114,16 @@ void SeedAligner::searchAllSeeds(
 			seedsearches++;
 			bt2gpu_seed_job j;
 			j.read = 0; j.off = (uint16_t)iss[0].seedoff; j.len = (uint8_t)sr.seqs(fw)[i].length(); j.fw = fw ? 1 : 0;
-			t.jobs.push_back(j);
+			sd.jobs.push_back(j);
 		}
 	}
-	t.out.resize(t.jobs.size());
-	if(!t.jobs.empty()) {
-		bt2shim::bindScoring(pens);
-		bt2shim::stageRead(read);
-		if(bt2gpu_seed_exact_batch(bt2shim::ctx(), bt2shim::index(*ebwtFw), bt2shim::index(*ebwtBw),
-		                           t.jobs.data(), t.jobs.size(), t.out.data()))
-			bt2shim::fail("bt2gpu_seed_exact_batch");
-		bt2shim::note(bt2shim::C_SEEDS, t.jobs.size());
-	}
+	bt2shim::seeds(sd);
 	size_t k = 0;
 	for(int fwi = 0; fwi < 2; fwi++) {
 		const bool fw = (fwi == 0);
 		for(size_t i = 0; i < sr.numOffs(); i++) {
 			if(sr.instantiatedSeeds(fw, i).empty()) continue;
-			const bt2gpu_seed_hit& h = t.out[k++];
+			const bt2gpu_seed_hit& h = sd.out[k++];
 			bwops_ += h.bwops;
 			const BTDnaString& seq = sr.seqs(fw)[i];
 			SeedSearchCache srcache(seq, sr.quals(fw)[i]);

@@ -23,34 +23,26 @@
 #include "reference.h"
 #include "gpu_shim.h"
 
+#ifndef BT2SHIM_BATCHED
+#define BT2SHIM_BATCHED 0      /* 1: compiled for the batched binding (batch_shim.cpp) */
+#endif
+
 namespace {
 
 struct ShimState {               // what align() got back for one SwAligner instance
-	bt2gpu_dp_result res;
-	std::vector<bt2gpu_dp_aln> alns;
-	std::vector<bt2gpu_edit> edits;
+	bt2shim::DpCall call;        // the problem (kept for the raised-minsc replay of nextAlignment()) and its results
+	std::vector<uint8_t> seq, qual, win;
 	uint32_t next = 0;           // next alignment to hand out
 	TAlScore minsc = 0;          // initRef's minsc_
-	bt2gpu_dp_job job;           // the problem, kept for the raised-minsc replay of nextAlignment()
-	std::vector<uint8_t> seq, qual, win;
 };
 
-struct ShimThread {
-	std::unordered_map<const SwAligner*, ShimState> st;
-	std::vector<bt2gpu_dp_cand> cands;
-	std::vector<bt2gpu_dp_aln> alns2;
-	std::vector<bt2gpu_edit> edits2;
-	std::vector<uint8_t> useq, uqual, uwin;   // ungappedAlign
-	std::vector<bt2gpu_edit> uedits;
-};
-thread_local ShimThread g_t;
+// One state per SwAligner instance.  Instances belong to one worker (thread or fiber) and workers never migrate
+// between host threads, so the map is per host thread; std::unordered_map keeps references to its elements valid when
+// another worker of the same thread inserts, and nothing here is held across a call into the binding except `st`.
+thread_local std::unordered_map<const SwAligner*, ShimState> g_st;
 
-const uint32_t kMaxAln = 1024;
-const size_t kEditCap = (size_t)1 << 18;
-
-size_t candCap(const bt2gpu_dp_job& j, bool monotone) {
-	return monotone ? (size_t)j.ncol + 64 : (size_t)j.rd_len * j.ncol + 64;
-}
+const uint32_t kMaxAln = 1024;   // per-call binding: the whole nextAlignment loop in one call
+const uint32_t kFirstAln = 16;   // batched binding: first ask; a window with more alignments is asked again in full
 
 } // namespace
 
@@ -74,40 +66,38 @@ bool SwAligner::align(TAlScore& best) {
 		fprintf(stderr, "bt2gpu shim: checkpointed DP (read of %zu rows >= %zu) is not on the CUDA path\n", rdlen, cperMinlen_);
 		throw 1;
 	}
-	bt2shim::bindScoring(*sc_);
-	ShimThread& t = g_t;
-	ShimState& st = t.st[this];
+	ShimState& st = g_st[this];
 	// the oriented read, rows rdi_..rdf_-1 (bytes 0..4 + Phred+33), and the window incl. the extra column of initRef
 	st.seq.resize(rdlen); st.qual.resize(rdlen); st.win.resize(ncol + 1);
 	for(size_t i = 0; i < rdlen; i++) { st.seq[i] = (uint8_t)(*rd_)[rdi_ + i]; st.qual[i] = (uint8_t)(*qu_)[rdi_ + i]; }
 	for(size_t i = 0; i <= ncol; i++) st.win[i] = (uint8_t)rf_[rfi_ + i];
-	bt2gpu_dp_job& job = st.job;
+	bt2shim::DpCall& c = st.call;
+	c.sc = sc_; c.seq = st.seq.data(); c.qual = st.qual.data(); c.win = st.win.data();
+	bt2gpu_dp_job& job = c.job;
 	job.rd_off = 0; job.rd_len = (uint32_t)rdlen; job.rf_off = 0; job.ncol = (uint32_t)ncol;
 	job.minsc = (int32_t)minsc_; job.nceil = nceil_;
 	job.refl = rect_->refl; job.triml = (uint32_t)rect_->triml;
 	job.corel = (uint32_t)rect_->corel; job.corer = (uint32_t)rect_->corer;
 	job.fw = fw_ ? 1 : 0; job.enable8 = (enable8_ && !readSse16_) ? 1 : 0;
 	job.reserved[0] = job.reserved[1] = 0;
-	const size_t cc = candCap(job, sc_->monotone);
-	t.cands.resize(cc); st.alns.resize(kMaxAln); st.edits.resize(kEditCap);
-	if(bt2gpu_dp_align_batch(bt2shim::ctx(), st.seq.data(), st.qual.data(), rdlen, st.win.data(), ncol + 1, &job, 1, kMaxAln,
-	                         &st.res, t.cands.data(), cc, st.alns.data(), st.edits.data(), kEditCap))
-		bt2shim::fail("bt2gpu_dp_align_batch");
-	if(st.res.naln >= kMaxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", kMaxAln); throw 1; }
-	bt2shim::note(bt2shim::C_ALIGN, 1);
+	c.max_aln = BT2SHIM_BATCHED ? kFirstAln : kMaxAln;
+	bt2shim::dpAlign(c);
+	if(c.res.naln >= c.max_aln && c.max_aln < kMaxAln) { c.max_aln = kMaxAln; bt2shim::dpAlign(c); }
+	if(c.res.naln >= kMaxAln) { fprintf(stderr, "bt2gpu shim: more than %u alignments in one window\n", kMaxAln); throw 1; }
+	const bt2gpu_dp_result& r = c.res;
 	st.next = 0; st.minsc = minsc_;
-	sse8succ_ = st.res.width == 8; sse16succ_ = st.res.width == 16;
-	best = st.res.best;                      // INT64_MIN == MIN_I64
+	sse8succ_ = r.width == 8; sse16succ_ = r.width == 16;
+	best = r.best;                           // INT64_MIN == MIN_I64
 	if(best == MIN_I64 || best < minsc_) {   // aligner_sw.cpp:681-686
 		if(dpLog_ != NULL) (*dpLog_) << ",0,0";
 		return false;
 	}
 	if(dpLog_ != NULL) (*dpLog_) << ",1," << best;
-	for(uint32_t i = 0; i < st.res.ncand; i++) {
-		const bt2gpu_dp_cand& c = t.cands[st.res.cand_off + i];
-		btncand_.push_back(DpBtCandidate(c.row, c.col, c.score));
+	for(uint32_t i = 0; i < r.ncand; i++) {
+		const bt2gpu_dp_cand& k = c.cands[i];
+		btncand_.push_back(DpBtCandidate(k.row, k.col, k.score));
 	}
-	return st.res.aligned != 0;
+	return r.aligned != 0;
 }
 
 /**
@@ -117,10 +107,11 @@ bool SwAligner::align(TAlScore& best) {
 bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) {
 	assert(initedRead() && initedRef());
 	if(done()) { res.reset(); return false; }
-	ShimState& st = g_t.st[this];
+	ShimState& st = g_st[this];
+	const bt2gpu_dp_result& r0 = st.call.res;
 	if(minsc < st.minsc) { fprintf(stderr, "bt2gpu shim: nextAlignment minsc below initRef's\n"); throw 1; }
-	const bt2gpu_dp_aln *a = (st.next < st.res.naln) ? &st.alns[st.res.aln_off + st.next] : NULL;
-	uint32_t tries = a ? a->tries : st.res.tail_tries;
+	const bt2gpu_dp_aln *a = (st.next < r0.naln) ? &st.call.alns[st.next] : NULL;
+	uint32_t tries = a ? a->tries : r0.tail_tries;
 	if(minsc > st.minsc) {
 		// The driver tightened minsc after reporting an alignment (aligner_sw_driver.cpp:1255-1284).  nextAlignment only
 		// uses its minsc argument to drop candidates (aligner_sw.cpp:762); btncand_ is sorted by score, so from the
@@ -130,17 +121,14 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 			// The GPU loop's next success (or its tail) lies beyond that point: the backtraces attempted before it are
 			// those of the same problem with minsc raised from the start (candidates >= the new minsc come first and
 			// see the same history) -- replay it and take its tail count.
-			ShimThread& t = g_t;
-			bt2gpu_dp_job j2 = st.job; bt2gpu_dp_result r2;
-			j2.minsc = (int32_t)minsc; j2.enable8 = sse8succ_ ? 1 : 0;
-			const size_t cc = candCap(j2, sc_->monotone);
-			t.cands.resize(cc); t.alns2.resize(kMaxAln); t.edits2.resize(kEditCap);
-			bt2shim::bindScoring(*sc_);
-			if(bt2gpu_dp_align_batch(bt2shim::ctx(), st.seq.data(), st.qual.data(), j2.rd_len, st.win.data(), j2.ncol + 1, &j2, 1,
-			                         kMaxAln, &r2, t.cands.data(), cc, t.alns2.data(), t.edits2.data(), kEditCap))
-				bt2shim::fail("bt2gpu_dp_align_batch (raised minsc)");
-			bt2shim::note(bt2shim::C_ALIGN, 1);
-			if(r2.naln != st.next || (r2.width != 0 && r2.width != st.res.width)) {
+			bt2shim::DpCall c2;
+			c2.sc = sc_; c2.seq = st.seq.data(); c2.qual = st.qual.data(); c2.win = st.win.data();
+			c2.job = st.call.job;
+			c2.job.minsc = (int32_t)minsc; c2.job.enable8 = sse8succ_ ? 1 : 0;
+			c2.max_aln = st.next + 1 < kFirstAln ? kFirstAln : kMaxAln;     // the replay stops after st.next alignments
+			bt2shim::dpAlign(c2);
+			const bt2gpu_dp_result& r2 = c2.res;
+			if(r2.naln != st.next || (r2.width != 0 && r2.width != r0.width)) {
 				fprintf(stderr, "bt2gpu shim: raised-minsc replay diverged (%u alignments, expected %u)\n", r2.naln, st.next);
 				throw 1;
 			}
@@ -157,7 +145,7 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 	const size_t trimBeg = fw_ ? a->trim5 : a->trim3;
 	EList<Edit>& ned = res.alres.ned();
 	for(uint32_t i = 0; i < a->nedits; i++) {
-		const bt2gpu_edit& e = st.edits[a->edit_off + i];
+		const bt2gpu_edit& e = st.call.edits[a->edit_off + i];
 		ned.push_back(Edit(e.pos, (int)e.chr, (int)e.qchr, (int)e.type));
 	}
 	// back to the backtrace's frame (w.r.t. the upstream end, before AlnRes::setShape's trim shift), so that
@@ -188,27 +176,22 @@ int SwAligner::ungappedAlign(
 	const Scoring& sc, bool ohang, TAlScore minsc, SwResult& res)
 {
 	const size_t len = rd.length();
-	bt2shim::bindScoring(sc);
-	ShimThread& t = g_t;
-	std::vector<uint8_t>& seq = t.useq; std::vector<uint8_t>& qual = t.uqual; std::vector<uint8_t>& win = t.uwin;
-	seq.resize(len); qual.resize(len); win.resize(len);
+	std::vector<uint8_t> seq(len), qual(len), win(len);
 	const TRefOff rfi = coord.off();
 	for(size_t i = 0; i < len; i++) {
 		seq[i] = (uint8_t)rd[i]; qual[i] = (uint8_t)qu[i];
 		const TRefOff p = rfi + (TRefOff)i;
 		win[i] = (p < 0 || (size_t)p >= reflen) ? 4 : (uint8_t)refs.getBase(coord.ref(), (size_t)p);
 	}
-	bt2gpu_ungap_job j;
+	bt2shim::UngapCall uc;
+	uc.sc = &sc; uc.seq = seq.data(); uc.qual = qual.data(); uc.win = win.data();
+	bt2gpu_ungap_job& j = uc.job;
 	j.rd_off = 0; j.rd_len = (uint32_t)len; j.rf_off = 0; j.minsc = (int32_t)minsc;
 	j.nceil = sc.nCeil.f<int>((double)len);
 	j.fw = coord.fw() ? 1 : 0; j.ohang = ohang ? 1 : 0; j.pad[0] = j.pad[1] = 0;
 	j.off = rfi; j.reflen = (int64_t)reflen;
-	bt2gpu_ungap_result r; size_t ne = 0;
-	t.uedits.resize(len + 1);
-	if(bt2gpu_ungapped_batch(bt2shim::ctx(), seq.data(), qual.data(), len, win.data(), len, &j, 1, &r, t.uedits.data(),
-	                         len + 1, &ne))
-		bt2shim::fail("bt2gpu_ungapped_batch");
-	bt2shim::note(bt2shim::C_UNGAPPED, 1);
+	bt2shim::ungapped(uc);
+	const bt2gpu_ungap_result& r = uc.res;
 	if(r.ret != 1) {
 		// the reference has reset res.alres by the time it scores (:386); before that it returns with res untouched
 		bool early = false;
@@ -224,7 +207,7 @@ int SwAligner::ungappedAlign(
 	const size_t rowi = fw ? r.trim5 : r.trim3, trimEnd = fw ? r.trim3 : r.trim5;
 	EList<Edit>& ned = res.alres.ned();
 	for(uint32_t i = 0; i < r.nedits; i++) {
-		const bt2gpu_edit& e = t.uedits[r.edit_off + i];
+		const bt2gpu_edit& e = uc.edits[r.edit_off + i];
 		ned.push_back(Edit(e.pos, (int)e.chr, (int)e.qchr, (int)e.type));
 	}
 	// back to row coordinates so that setShape / invertEdits below run as in the reference (:456-490)

@@ -10,14 +10,13 @@ void SwDriver::extend(
 	TIndexOffU botb, bool fw, size_t off, size_t len, PerReadMetrics& prm, size_t& nlex, size_t& nrex)
 {
 	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: SwDriver::extend needs the mirror index\n"); throw 1; }
-	bt2shim::stageRead(rd);
-	bt2gpu_extend_job j;
+	bt2shim::ExtendCall x;
+	x.fw = &ebwtFw; x.bw = ebwtBw; x.rd = &rd;
+	bt2gpu_extend_job& j = x.job;
 	j.read = 0; j.topf = topf; j.botf = botf; j.topb = topb; j.botb = botb;
 	j.off = (uint16_t)off; j.len = (uint8_t)len; j.fw = fw ? 1 : 0;
-	bt2gpu_extend_result r;
-	if(bt2gpu_extend_batch(bt2shim::ctx(), bt2shim::index(ebwtFw), bt2shim::index(*ebwtBw), &j, 1, &r))
-		bt2shim::fail("bt2gpu_extend_batch");
-	bt2shim::note(bt2shim::C_EXTEND, 1);
+	bt2shim::extend(x);
+	const bt2gpu_extend_result& r = x.res;
 	prm.nSdFmops += r.fmops;      // :362,386,427,451
 	nlex = r.nlex; nrex = r.nrex;
 }

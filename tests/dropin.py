@@ -15,7 +15,9 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 sys.path.insert(0, os.path.join(ROOT, "bowtie2-server_b200"))
 
 CPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s")
-GPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s-gpu")
+GPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s-gpu")      # per-call binding (shim/gpu_shim.cpp)
+GPUB_SERVER = os.path.join(BIN, "bowtie2-align-server-s-gpub")    # batched binding: worker fibers (shim/batch_shim.cpp)
+EMUL_SERVER = os.path.join(BIN, "bowtie2-align-server-s-emul")    # test double: batched binding over the CPU oracle (oracle/emul_abi.c)
 CLIENT = os.path.join(BIN, "bowtie2-align-l")
 
 

@@ -1,0 +1,119 @@
+"""CPU: the batched binding's host logic -- worker fibers, batch assembly, scatter of results (shim/batch_shim.cpp,
+shim/fiber_seams.h) -- against the stock reference server.  There is no GPU here, so the server under test is the TEST
+DOUBLE oracle/_ref/bowtie2-align-server-s-emul: the unmodified reference + the shim + the scheduler, linked against
+oracle/emul_abi.c (the C ABI's names answered by the pinned CPU oracle).  Scheduling must not change a byte of SAM:
+same records as bowtie2-align-server-s for paired / unpaired / local / near-exact / repeat-genome reads, with few and
+with many workers per host thread.  The product binary (…-gpub, libbt2gpu.so) is compared the same way on the GPU
+(tests/test_gpu_dropin.py)."""
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import dropin as D
+from bt2gpu import synth
+
+
+@pytest.fixture(scope="module")
+def work(tmp_path_factory):
+    if not (D.have_binaries() and os.path.exists(D.EMUL_SERVER)):
+        pytest.skip("oracle/_ref binaries missing: run __graft_entry__.build() where /root/reference is mounted")
+    w = str(tmp_path_factory.mktemp("emul"))
+    D.build_index(os.path.join(D.GOLDEN, "lambda.fa"), os.path.join(w, "lambda"))
+    return w
+
+
+def _both(work, tag, server_args, client_args, index="lambda", workers=48, host_threads=2, lanes=2):
+    base = os.path.join(work, index)
+    cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"), threads=2)
+    stats = os.path.join(work, tag + "_stats.txt")
+    em, err = D.run(D.EMUL_SERVER, base, server_args, client_args, os.path.join(work, tag + "_emul.sam"), threads=workers,
+                    env={"BT2GPU_SHIM_STATS": stats, "BT2GPU_THREADS": str(host_threads), "BT2GPU_LANES": str(lanes)})
+    st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
+    assert len(cpu) == len(em)
+    bad = [(a, b) for a, b in zip(cpu, em) if a != b]
+    assert not bad, "%d of %d SAM records differ, first:\n%s%s" % (len(bad), len(cpu), bad[0][0], bad[0][1])
+    assert st["abi_batches"] > 0 and st["abi_batch_jobs"] >= st["abi_batches"]
+    return cpu, st
+
+
+def test_paired_end_to_end(work):
+    rng = np.random.default_rng(11)
+    r, q, _, _ = synth.simulate_pairs(rng, D.lambda_genome(), 1200, 100)
+    f1, f2 = os.path.join(work, "pe_1.fq"), os.path.join(work, "pe_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "pair")
+    D.write_fastq(f2, r[1::2], q[1::2], "pair")
+    cpu, st = _both(work, "pe", [], ["-1", f1, "-2", f2], workers=64, host_threads=3)
+    assert st["align_calls_on_gpu"] > 500 and st["abi_batch_jobs"] > 4 * st["abi_batches"]     # problems do travel together
+    # one worker per host thread and a single lane: the degenerate schedule gives the same records
+    _both(work, "pe1", [], ["-1", f1, "-2", f2], workers=2, host_threads=2, lanes=1)
+    # more workers than read buffers can keep busy
+    _both(work, "pe256", [], ["-1", f1, "-2", f2], workers=256, host_threads=4)
+
+
+def test_unpaired_ragged_and_local(work):
+    rng = np.random.default_rng(12)
+    L = 500
+    r, q, _, _ = synth.simulate_reads(rng, D.lambda_genome(), 300, L)
+    lens = rng.integers(30, L + 1, size=300)
+    f = os.path.join(work, "long.fq")
+    D.write_fastq(f, r, q, "long", lens)
+    _both(work, "long", ["--sensitive"], ["-U", f])
+    r, q, _, _ = synth.simulate_reads(rng, D.lambda_genome(), 300, 200)
+    f = os.path.join(work, "loc.fq")
+    D.write_fastq(f, r, q, "loc")
+    _both(work, "loc", ["--local"], ["-U", f])
+
+
+def test_near_exact_one_mismatch_and_ungapped(work):
+    rng = np.random.default_rng(15)
+    g = D.lambda_genome()
+    n, L = 600, 80
+    pos = rng.integers(0, len(g) - L, size=n)
+    r = g[pos[:, None] + np.arange(L)[None, :]].copy()
+    nsub = rng.choice([0, 1, 1, 3], size=n)
+    for i in range(n):
+        for p in rng.choice(L, size=int(nsub[i]), replace=False):
+            r[i, p] = (r[i, p] + rng.integers(1, 4)) % 4
+    rc = rng.random(n) < 0.5
+    r[rc] = np.array([3, 2, 1, 0, 4], dtype=np.uint8)[r[rc, ::-1]]
+    q = np.full((n, L), ord("I"), dtype=np.uint8)
+    f = os.path.join(work, "near.fq")
+    D.write_fastq(f, r, q, "near")
+    for tag, args in (("near", []), ("nearung", ["--score-min", "L,0,-0.2", "--rdg", "20,3", "--rfg", "20,3"]),
+                      ("nearungloc", ["--local", "--score-min", "L,0,1.95"])):
+        _, st = _both(work, tag, args, ["-U", f])
+        assert st["onemm_calls_on_gpu"] > 0 and st["sweep_calls_on_gpu"] > 0
+        if "ung" in tag:
+            assert st["ungapped_calls_on_gpu"] > 0
+
+
+def test_repeat_genome_k5(work):
+    """Wide BW ranges: RowSampler draws, many locate calls and nextAlignment candidates per read, -k 5."""
+    D.build_index(os.path.join(D.GOLDEN, "rep.fa"), os.path.join(work, "rep"))
+    rng = np.random.default_rng(16)
+    rs, qs = [], []
+    for c in D.genome_codes("rep.fa"):
+        r, q, _, _ = synth.simulate_pairs(rng, c, 150, 120)
+        rs.append(r); qs.append(q)
+    r, q = np.concatenate(rs), np.concatenate(qs)
+    f1, f2 = os.path.join(work, "rep_1.fq"), os.path.join(work, "rep_2.fq")
+    D.write_fastq(f1, r[0::2], q[0::2], "rep")
+    D.write_fastq(f2, r[1::2], q[1::2], "rep")
+    _both(work, "rep", ["-k", "5"], ["-1", f1, "-2", f2], index="rep")
+    _both(work, "repl", ["--local", "--very-sensitive-local"], ["-U", f1 + "," + f2], index="rep")
+
+
+_ALL = json.load(open(os.path.join(D.GOLDEN, "simple_cases.json")))
+_SEL = _ALL[3::16]
+
+
+@pytest.mark.parametrize("ci", range(len(_SEL)), ids=["%03d" % i for i in range(len(_SEL))])
+def test_restated_regression_table(work, ci):
+    case = _SEL[ci]
+    base, sargs, cargs = D.write_case_inputs(case, work, "sc%03d" % ci)
+    cpu, _ = D.run(D.CPU_SERVER, base, sargs, cargs, base + "_cpu.sam", threads=1)
+    em, _ = D.run(D.EMUL_SERVER, base, sargs, cargs, base + "_emul.sam", threads=8, env={"BT2GPU_THREADS": "2"})
+    assert cpu == em, (case["name"], case["args"], cpu, em)
