@@ -49,6 +49,16 @@ extern "C" int bt2gpu_device_count(int *n) {
 	return 0;
 }
 
+extern "C" int bt2gpu_device_blocking_sync(int device, int on) {
+	int n = 0;
+	BT2_CUDA(cudaGetDeviceCount(&n));
+	if(n <= 0) BT2_FAIL("no CUDA device: libbt2gpu has no CPU fallback");
+	if(device < 0 || device >= n) BT2_FAIL("bad device ordinal");
+	BT2_CUDA(cudaSetDevice(device));
+	BT2_CUDA(cudaSetDeviceFlags(on ? cudaDeviceScheduleBlockingSync : cudaDeviceScheduleAuto));
+	return 0;
+}
+
 extern "C" int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
 	if(!out) BT2_FAIL("null argument");
 	*out = nullptr;

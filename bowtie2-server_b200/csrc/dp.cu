@@ -1272,13 +1272,13 @@ extern "C" int bt2gpu_dp_stage(
 	if(njobs == 0) return 0;
 	if(njobs > 0x7fffffffu / d->max_aln) BT2_FAIL("too many jobs");
 	const bool local = !ctx->sc.monotone;
-	size_t freeB = 0, totalB = 0;
-	BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
-	const uint64_t mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
+	// cudaMemGetInfo is slow (and serialises the device's contexts): the arena budget is only asked for when the batch
+	// does not fit the arena this context already holds (first pass with no limit, second with the real one)
+	uint64_t mat_budget_words = ~0ull;
 	std::vector<DpAux> aux(njobs);
 	std::vector<uint32_t> order(njobs);
 	std::vector<uint8_t> cls(njobs);
-	DpChunk ch; memset(&ch, 0, sizeof(ch)); ch.job0 = 0;
+	DpChunk ch;
 	std::vector<std::pair<uint64_t, uint32_t>> tmp;
 	auto close_chunk = [&](uint32_t end) {
 		ch.njobs = end - ch.job0;
@@ -1295,6 +1295,9 @@ extern "C" int bt2gpu_dp_stage(
 		ch.cls_off[kNClasses] = pos;
 		d->chunks.push_back(ch);
 	};
+	for(int pass = 0; pass < 2; pass++) {
+	d->chunks.clear(); d->cells = 0; d->maxcol_all = 0;
+	memset(&ch, 0, sizeof(ch)); ch.job0 = 0;
 	for(size_t i = 0; i < njobs; i++) {
 		const bt2gpu_dp_job &j = jobs[i];
 		if(j.rd_len == 0 || j.ncol == 0) BT2_FAIL("empty DP problem");
@@ -1325,6 +1328,14 @@ extern "C" int bt2gpu_dp_stage(
 		if((int)j.ncol > ch.maxcol) ch.maxcol = (int)j.ncol;
 		aux[i] = a;
 		d->cells += (uint64_t)j.rd_len * j.ncol;
+	}
+	if(pass == 0 && d->chunks.empty() && ch.mat_words * 4 <= d->mat.cap) break;       // fits what is already there
+	if(pass == 0) {
+		size_t freeB = 0, totalB = 0;
+		BT2_CUDA(cudaMemGetInfo(&freeB, &totalB));
+		mat_budget_words = (uint64_t)((freeB + d->mat.cap) * 0.55) / 4;
+		if(d->chunks.empty() && ch.mat_words <= mat_budget_words) break;               // one chunk, and it may grow
+	}
 	}
 	close_chunk((uint32_t)njobs);
 	uint64_t maxMat = 0, maxRep = 0; uint32_t maxBound = 0, maxEscr = 0;

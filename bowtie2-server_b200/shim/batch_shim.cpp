@@ -221,7 +221,8 @@ void Worker::loop() {
 			for(Fiber *f : b->waiters) { f->state = Fiber::RUNNABLE; f->error = err; }
 			b->clear();
 			freeBatches.push_back(b);
-			l->job = NULL; l->busy = false;
+			{ std::lock_guard<std::mutex> lk(l->mu); l->job = NULL; }    // `job` and `done` only change under the lane's lock
+			l->busy = false;
 			progress = true;
 		}
 		// 2. every runnable worker runs until its next hot-path call; of the workers that wait for input only one looks
@@ -247,8 +248,7 @@ void Worker::loop() {
 				Batch *b = pending;
 				pending = freeBatches.back(); freeBatches.pop_back();
 				fl->busy = true;
-				fl->done.store(false, std::memory_order_relaxed);
-				{ std::lock_guard<std::mutex> lk(fl->mu); fl->job = b; }
+				{ std::lock_guard<std::mutex> lk(fl->mu); fl->done.store(false, std::memory_order_relaxed); fl->job = b; }
 				fl->cv.notify_one();
 				progress = true; busy = true;
 			}
@@ -275,6 +275,9 @@ void Lane::run() {
 			b = job;
 		}
 		try {
+			// the helper threads of all lanes wait in the ABI calls: they must sleep there, not spin
+			static std::once_flag once;
+			std::call_once(once, [] { if(getenv("BT2GPU_SPIN") == NULL && bt2gpu_device_blocking_sync(device(), 1)) fail("bt2gpu_device_blocking_sync"); });
 			if(ctx == NULL && bt2gpu_ctx_create(device(), &ctx)) fail("bt2gpu_ctx_create");
 			execute(*b);
 		} catch(int) {

@@ -11,6 +11,10 @@
  * error (message via bt2gpu_last_error()).  There is NO CPU fallback: every
  * compute entry point fails if no CUDA device is usable.
  *
+ * Scoring: the kernels read the scheme from device-wide constant memory, so a device holds ONE
+ * scheme at a time: contexts that set the same scheme share it; bt2gpu_scoring_set fails for a
+ * different scheme while another live context of the device holds the current one.
+ *
  * Threading: a bt2gpu_ctx owns one CUDA stream and its scratch arenas; use
  * one ctx per host thread (mirrors "one SwAligner/SeedAligner per worker
  * thread", bt2_search.cpp:3128-3130).  Index/reference handles are immutable
@@ -36,6 +40,9 @@ typedef struct bt2gpu_ref   bt2gpu_ref;     /* BitPairReference (.3/.4.bt2)    *
 int         bt2gpu_abi_version(void);
 const char *bt2gpu_last_error(void);
 int         bt2gpu_device_count(int *n);
+/* Host threads waiting for this device sleep (cudaDeviceScheduleBlockingSync) instead of spinning: for callers that
+ * drive more contexts than they have cores to burn (the batched server binding: one helper thread per lane). */
+int         bt2gpu_device_blocking_sync(int device, int on);
 int         bt2gpu_ctx_create(int device, bt2gpu_ctx **ctx);
 void        bt2gpu_ctx_destroy(bt2gpu_ctx *ctx);
 /* Block until everything enqueued on the context's stream has finished. */
