@@ -144,3 +144,18 @@ class Index:
 
 def exists(base):
     return all(os.path.exists(base + s) for s in (".1.bt2", ".2.bt2", ".rev.1.bt2"))
+
+
+def read_ref_records(base):
+    """RefRecords of <base>.3.bt2 (reference.cpp:100-167): [(off, len, first)]."""
+    raw = np.fromfile(base + ".3.bt2", dtype=np.uint8)
+    if int(raw[0:4].view("<u4")[0]) != 1:
+        raise ValueError("bad .3.bt2")
+    n = int(raw[4:8].view("<u4")[0])
+    recs = []
+    p = 8
+    for _ in range(n):
+        off, ln = (int(x) for x in raw[p:p + 8].view("<u4"))
+        recs.append((off, ln, int(raw[p + 8])))
+        p += 9
+    return recs

@@ -264,7 +264,7 @@ class Context:
                        job_start=np.zeros(n, dtype=np.int64), job_fw=np.zeros(n, dtype=np.uint8),
                        results=np.zeros(n, dtype=structs.dp_result), alns=np.zeros(n * max_aln, dtype=structs.dp_aln),
                        edits=np.zeros(64 * n + 1024, dtype=structs.edit))
-        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, nthreads, cand_per_job)
+        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, 0, cand_per_job)
         S = structs.HotpathStats()
         nj, ne = C.c_size_t(0), C.c_size_t(0)
         _check(self.lib.bt2gpu_hotpath_round0_batch(
@@ -298,7 +298,8 @@ class Context:
                        edits=np.zeros(64 * n + 1024, dtype=structs.edit),
                        mates=np.zeros(n, dtype=structs.mate_info), mresults=np.zeros(n, dtype=structs.dp_result),
                        malns=np.zeros(n * max_aln, dtype=structs.dp_aln), medits=np.zeros(64 * n + 1024, dtype=structs.edit))
-        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, 0, cand_per_job)
+        # both mates are searched: the seed interval gets the reference's 20 % paired boost (bt2_search.cpp:3392-3395)
+        P = structs.HotpathParams(seed_len, ival[0], ival[1], maxgap, max_aln, mine_max, 1, cand_per_job)
         S, PS = structs.HotpathStats(), structs.PairsStats()
         nj, ne, nm, nme = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
         _check(self.lib.bt2gpu_hotpath_pairs_batch(
@@ -448,3 +449,18 @@ class DeviceRef:
             self.close()
         except Exception:
             pass
+
+
+# ---- what the current kernels do per DP cell (bench.py's roofline inputs) ----
+def dpx_per_pair():
+    """DPX instructions k_dp_fill issues per packed pair of cells."""
+    return 5.0
+
+
+def fill_bytes_per_cell(local):
+    """bytes k_dp_fill stores per cell (E, F, H): byte records on the u8 end-to-end path, s16 records otherwise."""
+    return 6.0 if local else 3.0
+
+
+def backtrace_bytes_per_cell(local):
+    return 6.0 if local else 3.0

@@ -112,7 +112,7 @@ _HP_F32 = ("ms_sweep", "ms_seed", "ms_extend", "ms_locate", "ms_dp", "ms_dp_fill
 class HotpathParams(_ct.Structure):
     """bt2gpu_hotpath_params"""
     _fields_ = [("seed_len", _ct.c_int32), ("ival_const", _ct.c_double), ("ival_coeff", _ct.c_double),
-                ("maxgap", _ct.c_int32), ("max_aln", _ct.c_uint32), ("mine_max", _ct.c_uint32), ("nthreads", _ct.c_int32),
+                ("maxgap", _ct.c_int32), ("max_aln", _ct.c_uint32), ("mine_max", _ct.c_uint32), ("pair_boost", _ct.c_int32),
                 ("cand_per_job", _ct.c_uint32)]
 
 

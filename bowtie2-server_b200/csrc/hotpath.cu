@@ -96,23 +96,25 @@ enum { ST_SEED_BWOPS = 0, ST_SEED_SIDES, ST_SEED_HITS, ST_EXT_FMOPS, ST_LOC_STEP
 
 // msIval.f<int>(len) for SIMPLE_FUNC_SQRT (simple_func.h:89-112), then max(.,1) (bt2_search.cpp:3396);
 // explicit round-to-nearest steps so that the product is not contracted into an fma
-__device__ __forceinline__ int seed_interval(double c, double l, uint32_t rdlen) {
+// boost: both mates of a pair are searched -> (int)(interval * 1.2 + 0.5) (bt2_search.cpp:3392-3395)
+__device__ __forceinline__ int seed_interval(double c, double l, uint32_t rdlen, int boost) {
 	double v = __dadd_rn(c, __dmul_rn(l, sqrt((double)rdlen)));
 	if(v < 0.0) v = 0.0;
-	const int iv = (int)v;
+	int iv = (int)v;
+	if(boost) iv = (int)__dadd_rn(__dmul_rn((double)iv, 1.2), 0.5);
 	return iv < 1 ? 1 : iv;
 }
 
 // ---- seed instantiation: count, then emit (fw seeds of a read, then its rc seeds) ----------
 template<bool EMIT> __global__ void __launch_bounds__(256)
-k_hp_seeds(const uint8_t *__restrict__ seq, const bt2gpu_read *__restrict__ reads, uint32_t nreads, int L, double ic, double il,
+k_hp_seeds(const uint8_t *__restrict__ seq, const bt2gpu_read *__restrict__ reads, uint32_t nreads, int L, double ic, double il, int boost,
            uint32_t *__restrict__ cnt, const uint32_t *__restrict__ first, bt2gpu_seed_job *__restrict__ out)
 {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i >= nreads) return;
 	const uint32_t rdlen = reads[i].rd_len;
 	const uint8_t *rd = seq + reads[i].rd_off;
-	const int per = seed_interval(ic, il, rdlen);
+	const int per = seed_interval(ic, il, rdlen, boost);
 	const int sl = (int)min((uint32_t)L, rdlen);
 	int nseeds = 1;
 	if((int)rdlen > L) nseeds += ((int)rdlen - L) / per;
@@ -429,7 +431,7 @@ static int hotpath_round0(
 	if(fm_hp_sweep(ctx, fw, P->mine_max ? P->mine_max : 2, &dsweep)) return 1;
 	BT2_CUDA(cudaEventRecord(st.ev[1], s));
 	uint32_t *cnt = st.cnt.as<uint32_t>(), *first = st.first.as<uint32_t>();
-	k_hp_seeds<false><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, cnt, nullptr, nullptr);
+	k_hp_seeds<false><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, P->pair_boost, cnt, nullptr, nullptr);
 	ctx->launches++;
 	if(dev_exclusive_scan<uint32_t>(ctx, cnt, first, st.spart.as<uint32_t>(), st.tot.as<uint32_t>(), nreads)) return 1;
 	BT2_CUDA(cudaMemcpyAsync(st.h_tot.p, st.tot.p, 4, cudaMemcpyDeviceToHost, s));
@@ -450,7 +452,7 @@ static int hotpath_round0(
 		BT2_CUDA(cudaMemsetAsync(st.tot.as<uint32_t>() + 8, 0, 4, s));
 		bt2gpu_seed_job *sj = st.sjobs.as<bt2gpu_seed_job>(); bt2gpu_seed_hit *sh = st.shits.as<bt2gpu_seed_hit>();
 		bt2gpu_extend_job *xj = st.xjobs.as<bt2gpu_extend_job>(); bt2gpu_extend_result *xr = st.xres.as<bt2gpu_extend_result>();
-		k_hp_seeds<true><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, cnt, first, sj);
+		k_hp_seeds<true><<<nbR, 256, 0, s>>>(rv.seq, rv.reads, n32, P->seed_len, P->ival_const, P->ival_coeff, P->pair_boost, cnt, first, sj);
 		BT2_CUDA(cudaEventRecord(st.ev[2], s));
 		if(fm_hp_seed(ctx, fw, bw, sj, nseed, sh)) return 1;
 		BT2_CUDA(cudaEventRecord(st.ev[3], s));

@@ -313,7 +313,8 @@ void bind(Lane& l, const Scoring *sc) {
 	l.sc = s; l.haveSc = true;
 }
 
-void noteBatch(Counter c, size_t n) { note(c, n); note(C_BATCHES, 1); note(C_BATCH_JOBS, n); }
+// evidence: problems per ABI call, and the bytes of the host buffers that went in and came back
+void noteBatch(Counter c, size_t n, size_t in_bytes, size_t out_bytes) { note(c, n); note(C_BATCHES, 1); note(C_BATCH_JOBS, n); note(C_H2D, in_bytes); note(C_D2H, out_bytes); }
 
 void Lane::execute(Batch& b) {
 	// ---- exactSweep: reads that share (nofw, norc, mineMax) travel together ----
@@ -334,7 +335,7 @@ void Lane::execute(Batch& b) {
 			swres.resize(grp.size());
 			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
 			for(size_t j = 0; j < grp.size(); j++) b.sweeps[grp[j]]->res = swres[j];
-			noteBatch(C_SWEEP, grp.size());
+			noteBatch(C_SWEEP, grp.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read), grp.size() * sizeof(bt2gpu_sweep_result));
 		}
 	}
 	// ---- oneMmSearch: by (local, repex, rep1mm) ----
@@ -363,7 +364,7 @@ void Lane::execute(Batch& b) {
 				c.hits.assign(ohits.begin() + ores[j].hit_off, ohits.begin() + ores[j].hit_off + ores[j].nhits);
 				c.res.hit_off = 0;
 			}
-			noteBatch(C_ONEMM, grp.size());
+			noteBatch(C_ONEMM, grp.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read) + ojobs.size() * sizeof(bt2gpu_onemm_job), grp.size() * sizeof(bt2gpu_onemm_result) + n * sizeof(bt2gpu_ee_hit));
 		}
 	}
 	// ---- exact seeds and seed-hit extensions share one staged read pool ----
@@ -390,13 +391,13 @@ void Lane::execute(Batch& b) {
 			if(bt2gpu_seed_exact_batch(ctx, index(*fw), index(*bw), sjobs.data(), sjobs.size(), shits.data())) fail("bt2gpu_seed_exact_batch");
 			size_t o = 0;
 			for(SeedsCall *c : b.seeds) { c->out.assign(shits.begin() + o, shits.begin() + o + c->jobs.size()); o += c->jobs.size(); }
-			noteBatch(C_SEEDS, sjobs.size());
+			noteBatch(C_SEEDS, sjobs.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read) + sjobs.size() * sizeof(bt2gpu_seed_job), sjobs.size() * sizeof(bt2gpu_seed_hit));
 		} else for(SeedsCall *c : b.seeds) c->out.clear();
 		if(!xjobs.empty()) {
 			xres.resize(xjobs.size());
 			if(bt2gpu_extend_batch(ctx, index(*fw), index(*bw), xjobs.data(), xjobs.size(), xres.data())) fail("bt2gpu_extend_batch");
 			for(size_t j = 0; j < xjobs.size(); j++) b.extends[j]->res = xres[j];
-			noteBatch(C_EXTEND, xjobs.size());
+			noteBatch(C_EXTEND, xjobs.size(), xjobs.size() * sizeof(bt2gpu_extend_job), xjobs.size() * sizeof(bt2gpu_extend_result));
 		}
 	}
 	// ---- BW rows to text offsets ----
@@ -406,7 +407,7 @@ void Lane::execute(Batch& b) {
 		for(size_t j = 0; j < n; j++) rows[j] = b.locates[j]->row;
 		if(bt2gpu_locate_batch(ctx, index(*b.locates[0]->fw), rows.data(), n, offs.data(), steps.data())) fail("bt2gpu_locate_batch");
 		for(size_t j = 0; j < n; j++) { b.locates[j]->off = offs[j]; b.locates[j]->steps = steps[j]; }
-		noteBatch(C_LOCATE, n);
+		noteBatch(C_LOCATE, n, n * 4, n * 8);
 	}
 	// ---- ungapped diagonals ----
 	if(!b.ungaps.empty()) {
@@ -432,7 +433,7 @@ void Lane::execute(Batch& b) {
 			c.edits.assign(dedits.begin() + ures[j].edit_off, dedits.begin() + ures[j].edit_off + (ures[j].ret == 1 ? ures[j].nedits : 0));
 			c.res.edit_off = 0;
 		}
-		noteBatch(C_UNGAPPED, n);
+		noteBatch(C_UNGAPPED, n, 2 * seq.size() + win.size() + n * sizeof(bt2gpu_ungap_job), n * sizeof(bt2gpu_ungap_result) + ne * sizeof(bt2gpu_edit));
 	}
 	// ---- DP windows: by the bound on the nextAlignment loop (the first ask is short, the rare re-ask is complete) ----
 	{
@@ -478,7 +479,10 @@ void Lane::execute(Batch& b) {
 				}
 				c.res.cand_off = 0; c.res.aln_off = 0;
 			}
-			noteBatch(C_ALIGN, n);
+			size_t nc = 0, ne = 0;
+			for(size_t j = 0; j < n; j++) { nc += dres[j].ncand; ne += b.dps[grp[j]]->edits.size(); }
+			noteBatch(C_ALIGN, n, 2 * seq.size() + win.size() + n * sizeof(bt2gpu_dp_job),
+			          n * (sizeof(bt2gpu_dp_result) + k.max_aln * sizeof(bt2gpu_dp_aln)) + nc * sizeof(bt2gpu_dp_cand) + ne * sizeof(bt2gpu_edit));
 		}
 	}
 }

@@ -22,7 +22,7 @@ struct Read;
 namespace bt2shim {
 
 enum Counter { C_ALIGN = 0, C_ALN, C_UNGAPPED, C_SWEEP, C_ONEMM, C_SEEDS, C_EXTEND, C_LOCATE, C_FRAME, C_OTHERMATE, C_MATERECT, C_PECLASS, C_JOINED,
-               C_BATCHES, C_BATCH_JOBS, C_NCOUNTERS };
+               C_BATCHES, C_BATCH_JOBS, C_H2D, C_D2H, C_NCOUNTERS };
 
 // SwAligner::initRef + align + the nextAlignment loop of one window (bt2gpu_dp_align_batch)
 struct DpCall {

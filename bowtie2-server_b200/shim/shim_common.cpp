@@ -75,8 +75,8 @@ void note(Counter c, uint64_t n) {
 	if(fd < 0) return;
 	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapped_calls_on_gpu", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
 	                                          "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu", "other_mate_on_gpu", "mate_rect_on_gpu", "pe_classify_on_gpu",
-	                                          "joined_to_text_off_on_gpu", "abi_batches", "abi_batch_jobs" };
-	char buf[1280]; int n2 = 0;
+	                                          "joined_to_text_off_on_gpu", "abi_batches", "abi_batch_jobs", "h2d_bytes", "d2h_bytes" };
+	char buf[1536]; int n2 = 0;
 	for(int i = 0; i < C_NCOUNTERS; i++)
 		n2 += snprintf(buf + n2, sizeof buf - n2, "%s %12llu ", names[i], (unsigned long long)g_cnt[i].load());
 	n2 += snprintf(buf + n2, sizeof buf - n2, "kernel_launches %12llu\n", (unsigned long long)g_launches.load());

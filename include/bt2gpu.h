@@ -415,7 +415,7 @@ typedef struct {
 	int32_t  maxgap;            /* DPRect::maxgap = min(max(rdgaps, rfgaps), maxhalf)      */
 	uint32_t max_aln;           /* nextAlignment() calls per window                        */
 	uint32_t mine_max;          /* exactSweep mineMax                                      */
-	int32_t  nthreads;          /* unused since the glue moved to the device (kept for layout) */
+	int32_t  pair_boost;        /* 1: both mates of a pair are searched: interval = (int)(interval * 1.2 + 0.5) (bt2_search.cpp:3392-3395) */
 	uint32_t cand_per_job;      /* candidate pool = this many cells per DP window (0: 256 end-to-end, 4096 local) */
 } bt2gpu_hotpath_params;
 

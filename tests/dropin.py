@@ -22,7 +22,7 @@ CLIENT = os.path.join(BIN, "bowtie2-align-l")
 
 
 def have_binaries():
-    return all(os.path.exists(p) for p in (CPU_SERVER, GPU_SERVER, CLIENT, os.path.join(BIN, "bowtie2-build-s")))
+    return all(os.path.exists(p) for p in (CPU_SERVER, GPU_SERVER, GPUB_SERVER, CLIENT, os.path.join(BIN, "bowtie2-build-s")))
 
 
 def read_fasta(path):

@@ -118,3 +118,37 @@ def test_non_default_scoring(ctx):
     got = ctx.dp_align_batch(seq, qual, win, jobs, max_aln=8)
     for i in range(len(jobs)):
         assert dpio.results_to_py(*ref, i) == dpio.results_to_py(*got, i), i
+
+
+def test_one_scoring_scheme_per_device():
+    """The kernels read the scheme from device-wide constant memory: a second, different scheme is refused while another
+    live context holds the first (instead of silently overwriting it under that context's kernels)."""
+    a, b = lib.Context(0), lib.Context(0)
+    try:
+        a.set_scoring(scoring.Scoring(local=False))
+        b.set_scoring(scoring.Scoring(local=False))            # the same scheme is shared
+        with pytest.raises(lib.Bt2GpuError, match="different scoring scheme"):
+            b.set_scoring(scoring.Scoring(local=True))
+        a.close()
+        b.set_scoring(scoring.Scoring(local=True))             # the only holder may change it
+        probs = list(dpio.parse_dump(os.path.join(H.GOLDEN, "dp_c2loc_ext.txt"), limit=40))
+        sc = scoring.Scoring(local=True)
+        seq, qual, win, jobs = dpio.batch_from_problems(probs, sc)
+        res = b.dp_align_batch(seq, qual, win, jobs, max_aln=8, cand_cap=4_000_000, edit_cap=200_000)
+        assert H.compare_with_dump(probs, *res) == len(probs)
+    finally:
+        a.close(); b.close()
+
+
+def test_candidate_pool_overflow_is_an_error_not_a_scribble(ctx):
+    """Local mode with a candidate pool far too small: the call fails cleanly (no out-of-bounds emit / sort / backtrace
+    on the jobs that did not fit) and the context is usable afterwards."""
+    sc = scoring.Scoring(local=True)
+    ctx.set_scoring(sc)
+    probs = list(dpio.parse_dump(os.path.join(H.GOLDEN, "dp_c2loc_ext.txt"), limit=200))
+    seq, qual, win, jobs = dpio.batch_from_problems(probs, sc)
+    for cap in (16, 700, 5000):
+        with pytest.raises(lib.Bt2GpuError, match="candidate pool overflow"):
+            ctx.dp_align_batch(seq, qual, win, jobs, max_aln=8, cand_cap=cap, edit_cap=200_000)
+    res = ctx.dp_align_batch(seq, qual, win, jobs, max_aln=8, cand_cap=8_000_000, edit_cap=400_000)
+    assert H.compare_with_dump(probs, *res) == len(probs)

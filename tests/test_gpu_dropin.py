@@ -1,8 +1,10 @@
 """GPU: the drop-in statement.  The unmodified reference (oracle/_ref/bowtie2-align-server-s + client) and the same
 reference with SeedAligner::exactSweep / oneMmSearch / searchAllSeeds and SwAligner::align / nextAlignment bound
-to libbt2gpu.so through bowtie2-server_b200/shim/
-(bowtie2-align-server-s-gpu) must print byte-identical SAM records for the same reads, --seed 0.
-SwDriver, AlnSinkWrap and the SAM writer are the reference's in both runs (SURVEY §8b, §8d parity gate)."""
+to libbt2gpu.so through bowtie2-server_b200/shim/ must print byte-identical SAM records for the same reads, --seed 0:
+  bowtie2-align-server-s-gpu    per-call binding (one problem per ABI call; also binds the framer / paired-end geometry),
+  bowtie2-align-server-s-gpub   batched binding (worker fibers: the problems of all reads in flight per ABI call) -- the
+                                path bench.py times as `e2e`.
+SwDriver, AlnSinkWrap and the SAM writer are the reference's in all runs (SURVEY §8b, §8d parity gate)."""
 import os
 import re
 
@@ -37,15 +39,28 @@ def _both(work, tag, server_args, client_args, index="lambda", threads=2):
     for k in ("align_calls_on_gpu", "sweep_calls_on_gpu", "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu",
               "joined_to_text_off_on_gpu", "kernel_launches"):
         assert st.get(k, 0) > 0, "%s: nothing ran on the GPU:\n%s\n%s" % (k, st, err[-2000:])
+    _batched(work, tag, cpu, base, server_args, client_args)
     return cpu, gpu, st["align_calls_on_gpu"]
 
 
-def _check(cpu, gpu):
+def _batched(work, tag, cpu, base, server_args, client_args, workers=96, host_threads=3):
+    """The same reads through the batched binding: identical records, and the problems did travel together."""
+    stats = os.path.join(work, tag + "_batched_stats.txt")
+    got, err = D.run(D.GPUB_SERVER, base, server_args, client_args, os.path.join(work, tag + "_gpub.sam"), threads=workers,
+                     env={"BT2GPU_SHIM_STATS": stats, "BT2GPU_THREADS": str(host_threads)})
+    st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
+    print(tag, "batched", st)
+    assert st.get("kernel_launches", 0) > 0 and st.get("abi_batches", 0) > 0, (st, err[-2000:])
+    _check(cpu, got, need_aligned=False)
+    return st
+
+
+def _check(cpu, gpu, need_aligned=True):
     assert len(cpu) == len(gpu)
     bad = [(a, b) for a, b in zip(cpu, gpu) if a != b]
     assert not bad, "%d of %d SAM records differ, first:\n%s%s" % (len(bad), len(cpu), bad[0][0], bad[0][1])
     aligned = sum(1 for ln in cpu if ln.split("\t")[2] != "*")
-    assert aligned > len(cpu) // 4
+    assert aligned > len(cpu) // 4 or not need_aligned
 
 
 def test_paired_end_to_end_sam_identical(work):
@@ -128,6 +143,8 @@ def test_near_exact_reads_one_mismatch_path(work):
         if "ung" in tag:
             assert st.get("ungapped_calls_on_gpu", 0) > 0, st
         _check(cpu, gpu)
+        bst = _batched(work, tag, cpu, base, args, ["-U", f])
+        assert bst.get("onemm_calls_on_gpu", 0) > 0 and ("ung" not in tag or bst.get("ungapped_calls_on_gpu", 0) > 0), bst
 
 
 def test_repeat_genome_three_chromosomes(work):
@@ -253,6 +270,8 @@ def test_reference_regression_cases(work, case):
     gpu, _ = D.run(D.GPU_SERVER, base, args, ["-U", fq], os.path.join(work, name + "_gpu.sam"), threads=1,
                    env={"BT2GPU_SHIM_STATS": os.path.join(work, name + "_stats.txt")})
     assert cpu == gpu, (cpu, gpu)
+    gpub, _ = D.run(D.GPUB_SERVER, base, args, ["-U", fq], os.path.join(work, name + "_gpub.sam"), threads=4, env={"BT2GPU_THREADS": "2"})
+    assert cpu == gpub, (cpu, gpub)
     f = cpu[0].split("\t")
     assert f[5] == cigar, cpu[0]
     if off is None:
@@ -263,20 +282,23 @@ def test_reference_regression_cases(work, case):
 
 # The reference's regression table, restated (scripts/restate_simple_tests.py -> tests/golden/simple_cases.json: every
 # case of scripts/test/simple_tests.pl that gives its reads inline and that the stock server accepts; seeds with
-# mismatches excluded).  The default run takes every fourth case; BT2GPU_ALL_SIMPLE_CASES=1 takes all of them.
+# mismatches excluded).  EVERY case runs through the batched binding (the path bench.py times); the per-call binding takes
+# every fourth case (BT2GPU_ALL_SIMPLE_CASES=1: all of them).
 import json
 
 _ALL = json.load(open(os.path.join(D.GOLDEN, "simple_cases.json")))
-_SEL = _ALL if os.environ.get("BT2GPU_ALL_SIMPLE_CASES") else _ALL[::4]
 
 
-@pytest.mark.parametrize("ci", range(len(_SEL)), ids=["%03d" % i for i in range(len(_SEL))])
+@pytest.mark.parametrize("ci", range(len(_ALL)), ids=["%03d" % i for i in range(len(_ALL))])
 def test_restated_regression_table(work, ci):
-    case = _SEL[ci]
+    case = _ALL[ci]
     base, sargs, cargs = D.write_case_inputs(case, work, "sc%03d" % ci)
     cpu, _ = D.run(D.CPU_SERVER, base, sargs, cargs, base + "_cpu.sam", threads=1)
-    gpu, _ = D.run(D.GPU_SERVER, base, sargs, cargs, base + "_gpu.sam", threads=1)
-    assert cpu == gpu, (case["name"], case["args"], cpu, gpu)
+    gpub, _ = D.run(D.GPUB_SERVER, base, sargs, cargs, base + "_gpub.sam", threads=4, env={"BT2GPU_THREADS": "2"})
+    assert cpu == gpub, (case["name"], case["args"], cpu, gpub)
+    if ci % 4 == 0 or os.environ.get("BT2GPU_ALL_SIMPLE_CASES"):
+        gpu, _ = D.run(D.GPU_SERVER, base, sargs, cargs, base + "_gpu.sam", threads=1)
+        assert cpu == gpu, (case["name"], case["args"], cpu, gpu)
     if "cigar" in case and "reads" in case and len(case["cigar"]) == len(case["reads"]) and not case.get("nofw"):
         got = {ln.split("\t")[0].split("/")[0]: ln.split("\t")[5] for ln in cpu}
         for i, cg in enumerate(case["cigar"]):

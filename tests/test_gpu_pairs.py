@@ -84,7 +84,7 @@ def test_paired_batch_runtime_matches_oracle(flags, nseq):
 
     out, st, ps = ctx.hotpath_pairs(dref, pool.seq, pool.qual, pool.reads, minsc, nceil, pol, maxhalf=maxhalf, max_aln=max_aln)
     mate_dp = ctx.dp_fetch()                                   # the mate pass is what is still staged
-    want = _oracle_round0(ix, refseqs, sc, pool, minsc, nceil, max_aln=max_aln)
+    want = _oracle_round0(ix, refseqs, sc, pool, minsc, nceil, max_aln=max_aln, pair_boost=True)
     nj = out["njobs"]
     assert np.array_equal(ctx.hotpath_job_tidx(nj), want["tidx"])
     assert nj == want["njobs"] and nj > 500

@@ -72,14 +72,16 @@ def test_hot_path_chain_matches_oracle():
     ctx.close()
 
 
-def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, max_aln=2):
+def _oracle_round0(ix, genome, sc, pool, minsc, nceil, seed_len=22, maxgap=15, max_aln=2, pair_boost=False):
     """The batch runtime's chain restated with the CPU oracle stage by stage (ragged reads).
     genome: one code array, or the list of reference sequences (codes 0..3, 4 = N) the index was built over."""
     seqs_ref = genome if isinstance(genome, list) else [genome]
     orc = H.FmOracle(ix, sc.to_struct())
     orc.stage_reads(pool)
     sweep = orc.exact_sweep()
-    sj, _ = fmio.instantiate_exact_seeds(pool, seed_len)
+    # paired driver: interval boosted by 20 % (bt2_search.cpp:3392-3395)
+    ival = (lambda L: max(int(fmio.seed_interval(L) * 1.2 + 0.5), 1)) if pair_boost else fmio.seed_interval
+    sj, _ = fmio.instantiate_exact_seeds(pool, seed_len, interval_fn=ival)
     sh = orc.seed_exact(sj) if len(sj) else np.zeros(0, dtype=structs.seed_hit)
     hit = np.nonzero(sh["botf"] > sh["topf"])[0]
     xj = np.zeros(len(hit), dtype=structs.extend_job)
