@@ -331,10 +331,11 @@ def run_ours(args, rank, world, local_rank):
         return ctx.hotpath_round0(dref, io["seq"], io["qual"], io["rd"], io["minsc"], io["nceil"], seed_len=SEED_LEN,
                                   ival=IVAL, maxgap=MAXGAP, max_aln=max_aln, mine_max=2, nthreads=0, out=io["out"])
 
-    def barrier():
+    def barrier(with_ctx=True):
         if world > 1:
             dist.barrier()
-        ctx.sync()
+        if with_ctx:
+            ctx.sync()
         torch.cuda.synchronize()
 
     # ---- (1) `value`: the device-resident stage chain ----
@@ -377,7 +378,7 @@ def run_ours(args, rank, world, local_rank):
     if have:
         shards = write_shards(td, "r%d" % rank, reads, quals, nclients)
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
-        barrier()
+        barrier(False)
         e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
                                                           args.warmup, args.steps)
     sampler.stop_flag = True

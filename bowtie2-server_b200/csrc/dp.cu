@@ -12,8 +12,10 @@
 //    F/H dependency never crosses the two halves of a register in the same step.  All
 //    recurrences are DPX: VIADDMNMX.S16x2 (add + clamp-at-floor) and VIMNMX3.S16x2.  The
 //    gap barrier (--gbar) is folded into per-row gap constants, the query profile lives in
-//    shared memory, E/F/H of every cell are streamed to HBM as 16-byte stores in wavefront
-//    order for the backtrace.
+//    shared memory.  Only H of every cell is streamed to HBM (8-byte stores in wavefront order: one byte
+//    per cell on the u8 end-to-end path, a halfword otherwise): the backtrace never needs the VALUE of
+//    an E or F cell, only whether it EQUALS a number it already knows, and that follows from H alone
+//    (BtJob::e_is / f_is below).
 //  * k_dp_gather_*: candidate cells + best/flag/width with the exact u8/i16 decision rules
 //    of aligner_sw.cpp:516-621 (including the stripe-padding rows that leak into the local
 //    column maxima), two passes + device scan, then a per-job bitonic sort in the order of
@@ -52,7 +54,7 @@ struct DpAux {
 	uint32_t S;           // packed registers per lane (stripe = 16*S rows)
 	uint32_t nstripes;
 	uint32_t T;           // steps per stripe = ncol + 16
-	uint32_t RW;          // words per lane-step record = roundup4(3*S)
+	uint32_t RW;          // words per lane-step record (H only): roundup2(S), or roundup2(ceil(S/2)) for byte records
 	int32_t  fl;          // floor of the score domain
 	uint32_t pad;
 };
@@ -104,7 +106,7 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
           uint32_t *__restrict__ mat, uint32_t *__restrict__ bound)
 {
 	constexpr int SP = (S + 3) & ~3;          // profile row stride (words)
-	constexpr int RW = (3 * S + 3) & ~3;      // record words
+	constexpr int RW = (S + 1) & ~1;          // record words (s16 H values)
 	extern __shared__ uint32_t smem[];
 	const int lane  = threadIdx.x & 31;
 	const int l     = lane & (GL - 1);
@@ -170,7 +172,7 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 			// byte identifies it (0 -> 0, b -> b - 256); halves the matrix stream of the headline path
 			const bool rec8 = (fl == -255);
 			const int rwj = (int)ax.RW;
-			uint32_t *rec_base = mat + ax.mat_off + (size_t)st * T * GL * rwj + l * 4;
+			uint32_t *rec_base = mat + ax.mat_off + (size_t)st * T * GL * rwj + l * 2;
 			for(int t = 0; t < T; t++) {
 				const int col_lo = t - 2 * l;
 				int c = 5;
@@ -202,7 +204,6 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 				const uint32_t Ftop = __byte_perm(recv, Fbot, 0x5432);
 				uint32_t hdiag = HtopPrev; HtopPrev = Htop;
 				uint32_t Hup = Htop, Fup = Ftop;
-				uint32_t rec[RW];
 #pragma unroll
 				for(int k = 0; k < S; k++) {
 					const uint32_t sck = __byte_perm(P[k], Pprev[k], 0x7610);
@@ -211,7 +212,6 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 					const uint32_t d = __viaddmax_s16x2(hdiag, sck, FLv);
 					const uint32_t e = E[k];
 					const uint32_t H = __vimax3_s16x2(d, e, F);
-					rec[k] = e; rec[S + k] = F; rec[2 * S + k] = H;
 					E[k] = __viaddmax_s16x2(e, nrde, __viaddmax_s16x2(H, nrdo[k], FLv));
 					hdiag = Hprev[k]; Hprev[k] = H; Hup = H; Fup = F;
 				}
@@ -219,37 +219,33 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 				if(ownLast) {
 					const int cl = t - vlast;
 					if(cl >= 0 && cl < ncol) {
-						const uint32_t hw = pick_reg<S>(rec + 2 * S, klast);
+						const uint32_t hw = pick_reg<S>(Hprev, klast);
 						bout[cl] = (uint32_t)((vlast & 1) ? hi16(hw) : lo16(hw));
 					}
 				}
+				// H of this step (now in Hprev[]) goes to the matrix stream, 8 bytes per store: chunk q of the 8 lanes
+				// is one contiguous 64-byte run (two full sectors)
 				if(rec8) {
-					// byte records: word m * SH + k / 2 holds the low bytes of [lo(k), hi(k), lo(k+1), hi(k+1)] of
-					// matrix m (one PRMT per word; a cell-major order costs three and did not pay off downstream)
+					// byte records: word k / 2 holds the low bytes of [lo(k), hi(k), lo(k+1), hi(k+1)] (one PRMT per word)
 					constexpr int SH = (S + 1) / 2;
-					constexpr int RW8 = (3 * SH + 3) & ~3;
+					constexpr int RW8 = (SH + 1) & ~1;
 					uint32_t r8[RW8];
 #pragma unroll
-					for(int m = 0; m < 3; m++)
+					for(int kp = 0; kp < SH; kp++) {
+						const uint32_t a = Hprev[2 * kp];
+						const uint32_t b = (2 * kp + 1 < S) ? Hprev[2 * kp + 1] : 0u;
+						r8[kp] = __byte_perm(a, b, 0x6420);
+					}
 #pragma unroll
-						for(int kp = 0; kp < SH; kp++) {
-							const uint32_t a = rec[m * S + 2 * kp];
-							const uint32_t b = (2 * kp + 1 < S) ? rec[m * S + 2 * kp + 1] : 0u;
-							r8[m * SH + kp] = __byte_perm(a, b, 0x6420);
-						}
+					for(int k = SH; k < RW8; k++) r8[k] = 0;
+					uint2 *dst = reinterpret_cast<uint2*>(rec_base + (size_t)t * GL * RW8);
 #pragma unroll
-					for(int k = 3 * SH; k < RW8; k++) r8[k] = 0;
-					uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW8);
-#pragma unroll
-					for(int q = 0; q < RW8 / 4; q++)
-						dst[q * GL] = make_uint4(r8[4 * q], r8[4 * q + 1], r8[4 * q + 2], r8[4 * q + 3]);
+					for(int q = 0; q < RW8 / 2; q++) dst[q * GL] = make_uint2(r8[2 * q], r8[2 * q + 1]);
 				} else {
+					uint2 *dst = reinterpret_cast<uint2*>(rec_base + (size_t)t * GL * RW);
 #pragma unroll
-					for(int k = 3 * S; k < RW; k++) rec[k] = 0;
-					uint4 *dst = reinterpret_cast<uint4*>(rec_base + (size_t)t * GL * RW);
-#pragma unroll
-					for(int q = 0; q < RW / 4; q++)      // chunk q of the 8 lanes is one contiguous 128-byte line
-						dst[q * GL] = make_uint4(rec[4 * q], rec[4 * q + 1], rec[4 * q + 2], rec[4 * q + 3]);
+					for(int q = 0; q < RW / 2; q++)
+						dst[q * GL] = make_uint2(Hprev[2 * q], (2 * q + 1 < S) ? Hprev[2 * q + 1] : 0u);
 				}
 			}
 			if(!lastStripe) __threadfence();   // boundary row visible to lane 0 of the next stripe
@@ -258,18 +254,18 @@ k_dp_fill(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 }
 
 // ---------------------------------------------------------------------------------------
-// Matrix access for gather / backtrace: cell (row, col) of matrix m (0=E, 1=F, 2=H).
+// Matrix access for gather / backtrace: H(row, col).
 // ---------------------------------------------------------------------------------------
 // A DP row resolved once: its step offset (stripe * T + virtual lane) and the byte offset of its
-// E, F and H elements inside a lane-step record chunk; a cell is then one byte/halfword load at
-// base + (tv + col) * record bytes + off[m].
-struct RowRef { int tv; int off[3]; };
+// H element inside a lane-step record; a cell is then one byte/halfword load at
+// base + (tv + col) * record bytes + off.
+struct RowRef { int tv; int off; };
 struct MatView {
-	const uint32_t *base; int S, T, RW, SH;
+	const uint32_t *base; int S, T, RW;
 	uint32_t invS, invRS; int stride;     // ceil(2^32 / S), ceil(2^32 / (16 S)), record bytes of one step (GL * RW * 4)
 	bool rec8;                            // byte records (u8 end-to-end path)
 	__device__ __forceinline__ void init(const uint32_t *b, int S_, int T_, int RW_, bool rec8_) {
-		base = b; S = S_; T = T_; RW = RW_; rec8 = rec8_; SH = (S_ + 1) >> 1;
+		base = b; S = S_; T = T_; RW = RW_; rec8 = rec8_;
 		invS = 0xffffffffu / (uint32_t)S + 1u; invRS = 0xffffffffu / (uint32_t)(VL * S) + 1u;
 		stride = GL * RW * 4;
 	}
@@ -278,30 +274,20 @@ struct MatView {
 		const int st = (int)__umulhi((uint32_t)row, invRS), r = row - st * (VL * S);
 		const int v = (int)__umulhi((uint32_t)r, invS), k = r - v * S;
 		RowRef rr; rr.tv = st * T + v;
-		const int lane_b = (v >> 1) * 16;
-		if(rec8) {       // byte records: word m * SH + k / 2, byte (k & 1) * 2 + (v & 1)
-			const int sub = ((k & 1) << 1) | (v & 1);
-#pragma unroll
-			for(int m = 0; m < 3; m++) {
-				const int idx = m * SH + (k >> 1);
-				rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + sub;
-			}
-			return rr;
-		}
-#pragma unroll
-		for(int m = 0; m < 3; m++) {
-			const int idx = m * S + k;
-			rr.off[m] = (idx >> 2) * (GL * 16) + lane_b + (idx & 3) * 4 + ((v & 1) << 1);
-		}
+		// word idx of the lane's record, in 8-byte chunks interleaved over the 8 lanes
+		const int idx = rec8 ? (k >> 1) : k;
+		const int sub = rec8 ? (((k & 1) << 1) | (v & 1)) : ((v & 1) << 1);
+		rr.off = (idx >> 1) * (GL * 8) + (v >> 1) * 8 + (idx & 1) * 4 + sub;
 		return rr;
 	}
-	__device__ __forceinline__ int at(int m, const RowRef &rr, int col) const {
+	// H(row, col)
+	__device__ __forceinline__ int at(const RowRef &rr, int col) const {
 		// a job's matrix is far below 4 GiB (dp_stage bounds rows and columns): 32-bit offset, one IMAD
-		const unsigned char *p = reinterpret_cast<const unsigned char*>(base) + (uint32_t)((rr.tv + col) * stride + rr.off[m]);
+		const unsigned char *p = reinterpret_cast<const unsigned char*>(base) + (uint32_t)((rr.tv + col) * stride + rr.off);
 		if(rec8) { const int b = (int)__ldcg(p); return b ? b - 256 : 0; }
 		return (int)__ldcg(reinterpret_cast<const short*>(p));
 	}
-	__device__ __forceinline__ int get(int m, int row, int col) const { return at(m, rowref(row), col); }
+	__device__ __forceinline__ int get(int row, int col) const { return at(rowref(row), col); }
 };
 
 __device__ __forceinline__ uint64_t cand_key(int score, int row, int col) {
@@ -340,7 +326,7 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 		// gatherCellsNucleotidesEnd2EndSse* (ee_u8.cpp:1176-1208): last row, score >= minsc
 		int best = INT32_MIN, cnt = 0;
 		for(int j = lane; j < ncol; j += 32) {
-			int h = mv.get(2, nrow - 1, j);
+			int h = mv.get(nrow - 1, j);
 			best = max(best, h);
 			if(h >= minsc) {
 				if(EMIT) { uint32_t p = atomicAdd(fillptr + ji, 1u); keys[coff + p] = cand_key(h, nrow - 1, j); }
@@ -377,36 +363,35 @@ k_dp_gather(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual,
 	for(int rix = lane; rix < nrec; rix += 32) {
 		const int l = rix & (GL - 1), t = (rix >> 3) % T, st = (rix >> 3) / T;
 		const uint32_t *rp = mv.base + (size_t)(rix >> 3) * GL * mv.RW;   // whole records, word-addressed (s16 layout: local mode)
-		// H words 2S..3S-1 of this lane, a 16-byte chunk (four words) per load: the 8 lanes' chunks of one index are
-		// one contiguous 128-byte line, so a warp's load is fully coalesced
-		for(int ch = (2 * S) >> 2; ch <= (3 * S - 1) >> 2; ch++) {
-		const uint4 q4 = __ldcg(reinterpret_cast<const uint4*>(rp + (ch * GL + l) * 4));
-		const uint32_t qw[4] = {q4.x, q4.y, q4.z, q4.w};
+		// the lane's H words 0..S-1, an 8-byte chunk (two words) per load: the 8 lanes' chunks of one index are one
+		// contiguous 64-byte run
+		for(int ch = 0; ch < (S + 1) >> 1; ch++) {
+			const uint2 q2 = __ldcg(reinterpret_cast<const uint2*>(rp + (ch * GL + l) * 2));
+			const uint32_t qw[2] = {q2.x, q2.y};
 #pragma unroll
-		for(int jw = 0; jw < 4; jw++) {
-			const int idx = 4 * ch + jw;
-			if(idx < 2 * S || idx >= 3 * S) continue;
-			const int k = idx - 2 * S;
-			const uint32_t w = qw[jw];
+			for(int jw = 0; jw < 2; jw++) {
+				const int k = 2 * ch + jw;
+				if(k >= S) continue;
+				const uint32_t w = qw[jw];
 #pragma unroll
-			for(int half = 0; half < 2; half++) {
-				const int v = 2 * l + half;
-				const int row = st * RS + v * S + k, col = t - v;
-				if(col < 0 || col >= ncol || row >= P16) continue;
-				const int h = half ? hi16(w) : lo16(w);
-				if(!EMIT) { if(h > 0) atomicMax(row < P8 ? &cmA[col] : &cmB[col], h); }
-				if(row < nrow && h >= minsc && (uint64_t)row >= minrow64) {
-					const int readc = rd[row], refc = rf[col];
-					const bool match = (refc & (1 << readc)) != 0;
-					bool matchSucc = false;
-					if(row < nrow - 1) matchSucc = ((int)rf[col + 1] & (1 << (int)rd[row + 1])) != 0;
-					if(match && !matchSucc) {
-						if(EMIT) { uint32_t p = atomicAdd(fillptr + ji, 1u); keys[coff + p] = cand_key(h, row, col); }
-						cnt++;
+				for(int half = 0; half < 2; half++) {
+					const int v = 2 * l + half;
+					const int row = st * RS + v * S + k, col = t - v;
+					if(col < 0 || col >= ncol || row >= P16) continue;
+					const int h = half ? hi16(w) : lo16(w);
+					if(!EMIT) { if(h > 0) atomicMax(row < P8 ? &cmA[col] : &cmB[col], h); }
+					if(row < nrow && h >= minsc && (uint64_t)row >= minrow64) {
+						const int readc = rd[row], refc = rf[col];
+						const bool match = (refc & (1 << readc)) != 0;
+						bool matchSucc = false;
+						if(row < nrow - 1) matchSucc = ((int)rf[col + 1] & (1 << (int)rd[row + 1])) != 0;
+						if(match && !matchSucc) {
+							if(EMIT) { uint32_t p = atomicAdd(fillptr + ji, 1u); keys[coff + p] = cand_key(h, row, col); }
+							cnt++;
+						}
 					}
 				}
 			}
-		}
 		}
 	}
 	if(EMIT) return;
@@ -641,65 +626,79 @@ struct BtJob {
 		const long long d = (long long)col - row + triml;
 		return d >= 0 && (unsigned long long)d >= corel && (unsigned long long)d <= corer;
 	}
-	// move out of an H cell: 0 = none (empty mask), 1 diag, 2 ref-open, 5 ref-ext, 3 read-open, 4 read-ext
-	__device__ __forceinline__ int h_move(int row, int col) const {
-		const bool gapsAllowed = !(row < gapbar || (nrow - row - 1) < gapbar);
+	__device__ __forceinline__ bool in_barrier(int row) const { return row < gapbar || (nrow - row - 1) < gapbar; }
+	// E(row, col) == T ?  The matrix stream holds H only.  The fill computes, along a row,
+	//   E(r,c) = max(floor, E(r,c-1) - rde, H(r,c-1) - rdo)     (E(r,0) = floor; no read gap opens inside the gap barrier)
+	// so E(r,c) = T (T above the floor) iff the chain "E(r,c) extends E(r,c-1) extends ..." reaches a column c' where
+	// H(r,c'-1) - rdo equals what E(r,c') has to be.  The chain stops as soon as the required value exceeds what the
+	// cell can hold: E(r,c') <= H(r,c') always (H is the maximum of its three sources), and H(r,c'-1) - rdo <= E(r,c').
+	// One H load per link; a gap of length g costs g loads, and nearly every test ends at the first.
+	__device__ __forceinline__ bool e_is(int row, int col, int T) const {
+		if(in_barrier(row)) return false;
+		const RowRef rr = mv.rowref(row);
+		int need = T;
+		for(int c = col; c > 0; c--) {
+			const int h = mv.at(rr, c - 1);
+			const int o = h - c_sc.rdo;
+			if(o == need) return true;
+			if(o > need) return false;         // E(row,c) >= o: it cannot be `need`
+			need += c_sc.rde;                  // then E(row,c) extends E(row,c-1), which has to be need + rde ...
+			if(need > h) return false;         // ... and cannot exceed H(row,c-1)
+		}
+		return false;
+	}
+	// F(row, col) == T ?  Down a column: F(r,c) = max(floor, F(r-1,c) - rfe, H(r-1,c) - rfo), no reference gap inside the
+	// gap barrier (F is the floor there, and in row 0).
+	__device__ __forceinline__ bool f_is(int row, int col, int T) const {
+		int need = T;
+		for(int r = row; r > 0; r--) {
+			if(in_barrier(r)) return false;
+			const int h = mv.get(r - 1, col);
+			const int o = h - c_sc.rfo;
+			if(o == need) return true;
+			if(o > need) return false;
+			need += c_sc.rfe;
+			if(need > h) return false;
+		}
+		return false;
+	}
+	// move out of an H cell: 0 = none (empty mask), 1 diag, 2 ref-open, 5 ref-ext, 3 read-open, 4 read-ext.
+	// sc_cur = H(row, col): the value of the gap cell the walk enters on move 4 (E(row,col-1) = sc_cur + rde) or 5
+	// (F(row-1,col) = sc_cur + rfe) follows from it.
+	__device__ __forceinline__ int h_move(int row, int col, int &sc_cur) const {
+		const bool gapsAllowed = !in_barrier(row);
 		const RowRef rc = mv.rowref(row), ru = mv.rowref(row > 0 ? row - 1 : 0);   // row 0: callers discard the result
 		// The diagonal wins whenever it is legal (ee_u8.cpp:1510-1520), and most cells of a walk are diagonal moves:
-		// its two cells are fetched first, the four gap neighbours (each a sector of its own in the wavefront layout)
-		// only when the diagonal fails -- a third of the sectors per walked cell for one more round trip at a gap.
-		const int sc_cur = mv.at(2, rc, col);
+		// its two cells are fetched first, the gap neighbours only when the diagonal fails.
+		sc_cur = mv.at(rc, col);
 		const int cl = col > 0 ? col - 1 : 0;
 		if(col > 0) {
-			const int hd = mv.at(2, ru, cl);
+			const int hd = mv.at(ru, cl);
 			const int sd = dev_score_mask(rd[row], rf[col], (int)qu[row] - 33);
 			if((!local || hd > 0) && sc_cur == hd + sd) return 1;
 		}
-		int mask = 0;
-		if(gapsAllowed) {
-			const int hu = mv.at(2, ru, col), fu = mv.at(1, ru, col);
-			const int hl = mv.at(2, rc, cl), el = mv.at(0, rc, cl);
-			if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) mask |= 1;
-			if((!local || fu > 0) && sc_cur == fu - c_sc.rfe) mask |= 4;
-			if(col > 0) {
-				if((!local || hl > 0) && sc_cur == hl - c_sc.rdo) mask |= 2;
-				if((!local || el > 0) && sc_cur == el - c_sc.rde) mask |= 8;
-			}
+		if(!gapsAllowed) return 0;
+		// (diag >) ref open > ref ext > read open > read ext; "x > 0" of the local rules is a test on the value the
+		// neighbour would have to hold
+		const int hu = mv.at(ru, col);
+		if((!local || hu > 0) && sc_cur == hu - c_sc.rfo) return 2;
+		if((!local || sc_cur + c_sc.rfe > 0) && f_is(row - 1, col, sc_cur + c_sc.rfe)) return 5;
+		if(col > 0) {
+			const int hl = mv.at(rc, cl);
+			if((!local || hl > 0) && sc_cur == hl - c_sc.rdo) return 3;
+			if((!local || sc_cur + c_sc.rde > 0) && e_is(row, cl, sc_cur + c_sc.rde)) return 4;
 		}
-		if(mask & 1) return 2;             // (diag >) ref open > ref ext > read open > read ext
-		if(mask & 4) return 5;
-		if(mask & 2) return 3;
-		if(mask & 8) return 4;
 		return 0;
 	}
-	// E (ct 0) or F (ct 1) cell in one code path: 3/2 open, 4/5 extend, 0 none
-	__device__ __forceinline__ int g_move(int ct, int row, int col) const {
-		const int pr = max(row - ct, 0), pc = max(col - (1 - ct), 0);      // clamped: callers discard row 0 / col 0 results
-		const int sc_cur = mv.get(ct, row, col);
-		const int hp = mv.get(2, pr, pc), gp = mv.get(ct, pr, pc);
+	// move out of the E (ct 0) or F (ct 1) cell (row, col) whose value is gv: 3/2 open, 4/5 extend, 0 none
+	__device__ __forceinline__ int g_move(int ct, int row, int col, int gv) const {
+		if(ct == 0 && col == 0) return 0;
+		const int pr = max(row - ct, 0), pc = max(col - (1 - ct), 0);      // callers discard row 0 results
+		const int hp = mv.get(pr, pc);
 		const int open = ct ? c_sc.rfo : c_sc.rdo, ext = ct ? c_sc.rfe : c_sc.rde;
-		int mask = 0;
-		if((!local || hp > 0) && hp - open == sc_cur) mask |= 1;
-		if((!local || gp > 0) && gp - ext == sc_cur) mask |= 2;
-		if(mask & 1) return ct ? 2 : 3;
-		return mask == 2 ? (ct ? 5 : 4) : 0;
-	}
-	// move out of an E cell (read gap): 3 open, 4 extend, 0 none;  out of an F cell (ref gap): 2 open, 5 extend
-	__device__ __forceinline__ int e_move(int row, int col) const {
-		const int sc_cur = mv.get(0, row, col);
-		const int hl = mv.get(2, row, col - 1), el = mv.get(0, row, col - 1);
-		int mask = 0;
-		if((!local || hl > 0) && hl - c_sc.rdo == sc_cur) mask |= 1;
-		if((!local || el > 0) && el - c_sc.rde == sc_cur) mask |= 2;
-		return (mask & 1) ? 3 : (mask == 2 ? 4 : 0);
-	}
-	__device__ __forceinline__ int f_move(int row, int col) const {
-		const int sc_cur = mv.get(1, row, col);
-		const int hu = mv.get(2, row - 1, col), fu = mv.get(1, row - 1, col);
-		int mask = 0;
-		if((!local || hu > 0) && hu - c_sc.rfo == sc_cur) mask |= 1;
-		if((!local || fu > 0) && fu - c_sc.rfe == sc_cur) mask |= 2;
-		return (mask & 1) ? 2 : (mask == 2 ? 5 : 0);
+		if((!local || hp > 0) && hp - open == gv) return ct ? 2 : 3;
+		if((!local || gv + ext > 0) && (ct ? f_is(pr, pc, gv + ext) : e_is(pr, pc, gv + ext))) return ct ? 5 : 4;
+		return 0;
 	}
 };
 
@@ -767,7 +766,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 				// ---- trial group: lanes = candidates cural .. cural+31 ----
 				const uint32_t ci = cural + lane;
 				enum { T_RUN = 0, T_INACTIVE, T_SKIP, T_BLOCKED, T_END, T_HORIZON };
-				int status = T_INACTIVE, row = 0, col = 0, ct = 2, len = 0;
+				int status = T_INACTIVE, row = 0, col = 0, ct = 2, len = 0, gv = 0;
 				int cmin = INT32_MAX, cmax = -1;
 				if(ci < ncand) {
 					const bt2gpu_dp_cand c = cd[ci];
@@ -787,18 +786,20 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 						if(!__any_sync(FULL, status == T_RUN)) break;
 						if(status == T_RUN) {
 							const bool rep = J.reported(row, col);
-							int m = 0;
-							if(!rep && row > 0) m = ct == 2 ? J.h_move(row, col) : J.g_move(ct, row, col);
+							int m = 0, hv = 0;
+							if(!rep && row > 0) m = ct == 2 ? J.h_move(row, col, hv) : J.g_move(ct, row, col, gv);
 							tcells[t * 32 + lane] = (uint16_t)(((nrow - 1 - row) << 8) | (col - wbase));
 							len = t + 1;
 							if(rep) status = t == 0 ? T_SKIP : T_BLOCKED;
 							else if(row == 0 || m == 0) status = T_END;
 							else {
+								// the value of the gap cell entered by an extension: one extension above the cell left
+								const int from = ct == 2 ? hv : gv;
 								if(m == 1) { row--; col--; ct = 2; }
 								else if(m == 2) { row--; ct = 2; }
-								else if(m == 5) { row--; ct = 1; }
+								else if(m == 5) { row--; ct = 1; gv = from + c_sc.rfe; }
 								else if(m == 3) { col--; ct = 2; }
-								else { col--; ct = 0; }
+								else { col--; ct = 0; gv = from + c_sc.rde; }
 							}
 						}
 					}
@@ -874,6 +875,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 			bool fresh = true, skipped = false;
 			// ---- walk ----
 			int score = 0, ns = 0, gaps = 0, ned = 0, ct = 2;
+			int gval = 0;                          // value of the E / F cell the walk is in (ct 0 / 1)
 			const int origCol = col;
 			const int trimEnd = nrow - row - 1;
 			int trimBeg = 0;
@@ -883,10 +885,10 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					// ---- speculative diagonal batch: lane i looks at (row-i, col-i) in the H state ----
 					const int ri = row - lane, ci = col - lane;
 					const bool valid = ri >= 0 && ci >= 0;
-					bool rep_i = false; int mv_i = 0;
+					bool rep_i = false; int mv_i = 0, hv_i = 0;
 					if(valid) {
 						rep_i = J.reported(ri, ci);
-						if(!rep_i && ri > 0) mv_i = J.h_move(ri, ci);
+						if(!rep_i && ri > 0) mv_i = J.h_move(ri, ci, hv_i);
 					}
 					const bool plain = valid && !rep_i && ri > 0 && mv_i == 1;
 					const unsigned pb = __ballot_sync(FULL, plain);
@@ -939,7 +941,7 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 						blocked = true; break;
 					}
 					const bool e_rep = __shfl_sync(FULL, (int)rep_i, nk) != 0;
-					const int e_mv = __shfl_sync(FULL, mv_i, nk);
+					const int e_mv = __shfl_sync(FULL, mv_i, nk), e_hv = __shfl_sync(FULL, hv_i, nk);
 					J.mark(row, col); btcells++;
 					if(e_rep) { blocked = true; break; }
 					if(J.on_core(row, col)) overlapped = true;
@@ -949,13 +951,13 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 						e.pos = (uint32_t)row; e.chr = '-'; e.qchr = (uint8_t)"ACGTN"[rd[row]]; e.type = BT2GPU_EDIT_REF_GAP;
 						if(lane == 0) ed[ned] = e;
 						ned++; row--;
-						if(e_mv == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; }
+						if(e_mv == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; gval = e_hv + c_sc.rfe; }
 						gaps++;
 					} else {
 						e.pos = (uint32_t)row + 1; e.chr = dev_mask2dna(rf[col]); e.qchr = '-'; e.type = BT2GPU_EDIT_READ_GAP;
 						if(lane == 0) ed[ned] = e;
 						ned++; col--;
-						if(e_mv == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; }
+						if(e_mv == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; gval = e_hv + c_sc.rde; }
 						gaps++;
 					}
 					continue;
@@ -965,21 +967,8 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 				bool empty = false;
 				int cur = 0;
 				if(!reported && row > 0) {
-					if(ct == 0) {
-						const int sc_cur = J.mv.get(0, row, col);
-						const int hl = J.mv.get(2, row, col - 1), el = J.mv.get(0, row, col - 1);
-						int mask = 0;
-						if((!local || hl > 0) && hl - c_sc.rdo == sc_cur) mask |= 1;
-						if((!local || el > 0) && el - c_sc.rde == sc_cur) mask |= 2;
-						if(mask & 1) cur = 3; else if(mask == 2) cur = 4; else empty = true;
-					} else {
-						const int sc_cur = J.mv.get(1, row, col);
-						const int hu = J.mv.get(2, row - 1, col), fu = J.mv.get(1, row - 1, col);
-						int mask = 0;
-						if((!local || hu > 0) && hu - c_sc.rfo == sc_cur) mask |= 1;
-						if((!local || fu > 0) && fu - c_sc.rfe == sc_cur) mask |= 2;
-						if(mask & 1) cur = 2; else if(mask == 2) cur = 5; else empty = true;
-					}
+					cur = J.g_move(ct, row, col, gval);          // 3 / 2 open (back to the H state), 4 / 5 extend
+					empty = cur == 0;
 				}
 				__syncwarp();
 				J.mark(row, col); btcells++;
@@ -991,13 +980,13 @@ k_dp_backtrace(const uint8_t *__restrict__ seq, const uint8_t *__restrict__ qual
 					e.pos = (uint32_t)row; e.chr = '-'; e.qchr = (uint8_t)"ACGTN"[rd[row]]; e.type = BT2GPU_EDIT_REF_GAP;
 					if(lane == 0) ed[ned] = e;
 					ned++; row--;
-					if(cur == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; }
+					if(cur == 2) { ct = 2; score -= c_sc.rfo; } else { ct = 1; score -= c_sc.rfe; gval += c_sc.rfe; }
 					gaps++;
 				} else {
 					e.pos = (uint32_t)row + 1; e.chr = dev_mask2dna(rf[col]); e.qchr = '-'; e.type = BT2GPU_EDIT_READ_GAP;
 					if(lane == 0) ed[ned] = e;
 					ned++; col--;
-					if(cur == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; }
+					if(cur == 3) { ct = 2; score -= c_sc.rdo; } else { ct = 0; score -= c_sc.rde; gval += c_sc.rde; }
 					gaps++;
 				}
 			}
@@ -1163,7 +1152,7 @@ k_dp_aux(const bt2gpu_dp_job *__restrict__ jobs, uint32_t njobs, unsigned long l
 		if(local) a.fl = 0;
 		else if(j.enable8 && j.minsc >= -254) a.fl = -255;
 		else { a.fl = FL_I16; if(j.minsc < -15000) err = 6; }
-		a.RW = (a.fl == -255) ? ((3 * ((a.S + 1) / 2) + 3) & ~3u) : ((3 * a.S + 3) & ~3u);
+		a.RW = (a.fl == -255) ? ((((a.S + 1) / 2) + 1) & ~1u) : ((a.S + 1) & ~1u);
 		DpSizes z;
 		z.mat = (unsigned long long)a.nstripes * a.T * GL * a.RW;
 		z.rep = (((unsigned long long)j.rd_len * j.ncol + 31) / 32) * 4;
@@ -1314,7 +1303,7 @@ extern "C" int bt2gpu_dp_stage(
 		if(local) a.fl = 0;
 		else if(j.enable8 && j.minsc >= -254) a.fl = -255;            // aligner_sw.cpp:518
 		else { a.fl = FL_I16; if(j.minsc < -15000) BT2_FAIL("minsc below the 16-bit end-to-end domain"); }
-		a.RW = (a.fl == -255) ? ((3 * ((a.S + 1) / 2) + 3) & ~3u) : ((3 * a.S + 3) & ~3u);   // byte records on the u8 path
+		a.RW = (a.fl == -255) ? ((((a.S + 1) / 2) + 1) & ~1u) : ((a.S + 1) & ~1u);   // H only; byte records on the u8 path
 		const uint64_t mw = (uint64_t)a.nstripes * a.T * GL * a.RW;
 		if(mw > mat_budget_words) BT2_FAIL("single DP problem exceeds the matrix arena");
 		if(ch.mat_words + mw > mat_budget_words || ch.bound_words > 0x70000000u || ch.escr_edits > 0x70000000u) {

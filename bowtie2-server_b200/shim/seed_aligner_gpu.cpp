@@ -107,7 +107,9 @@ void SeedAligner::searchAllSeeds(
 			EList<InstantiatedSeed>& iss = sr.instantiatedSeeds(fw, i);
 			if(iss.empty()) continue;              // seed window with an N, or a cross-read cache hit
 			possearches++;
-			if(iss.size() != 1 || seeds[iss[0].seedtypeidx].type != SEED_TYPE_EXACT) {
+			// one seed type per offset, and it is the exact one (iss[j] was instantiated from seeds[j],
+			// aligner_seed.cpp:560-583; InstantiatedSeed::seedtypeidx is never assigned by the reference)
+			if(iss.size() != 1 || seeds.size() != 1 || seeds[0].type != SEED_TYPE_EXACT) {
 				fprintf(stderr, "bt2gpu shim: only exact seeds (-N 0) are on the CUDA path\n");
 				throw 1;
 			}

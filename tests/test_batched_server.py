@@ -117,3 +117,32 @@ def test_restated_regression_table(work, ci):
     cpu, _ = D.run(D.CPU_SERVER, base, sargs, cargs, base + "_cpu.sam", threads=1)
     em, _ = D.run(D.EMUL_SERVER, base, sargs, cargs, base + "_emul.sam", threads=8, env={"BT2GPU_THREADS": "2"})
     assert cpu == em, (case["name"], case["args"], cpu, em)
+
+
+def test_server_survives_many_connections(work):
+    """A server is long-lived: three rounds of two concurrent clients through ONE batched server, every round's SAM equal
+    to the stock server's (workers go idle between rounds, read buffers and per-read state are reused)."""
+    from bt2gpu import serverbench as SB
+    rng = np.random.default_rng(31)
+    r, q, _, _ = synth.simulate_pairs(rng, D.lambda_genome(), 800, 120)
+    shards = []
+    for k in range(2):
+        f1, f2 = os.path.join(work, "mc%d_1.fq" % k), os.path.join(work, "mc%d_2.fq" % k)
+        SB.write_fastq(f1, r[800 * k:800 * (k + 1):2], q[800 * k:800 * (k + 1):2], 400 * k, "/1")
+        SB.write_fastq(f2, r[800 * k + 1:800 * (k + 1):2], q[800 * k + 1:800 * (k + 1):2], 400 * k, "/2")
+        shards.append(["-1", f1, "-2", f2])
+    base = os.path.join(work, "lambda")
+    stock = SB.Server(SB.CPU_SERVER, base, 2, log=os.path.join(work, "mc_stock.err"))
+    try:
+        _, sams = stock.align(shards, os.path.join(work, "mc_stock"))
+        want = SB.sam_records(sams)
+    finally:
+        stock.close()
+    assert len(want) == 1600 and sum(1 for ln in want if ln.split("\t")[2] != "*") > 400
+    srv = SB.Server(D.EMUL_SERVER, base, 96, env={"BT2GPU_THREADS": "3"}, log=os.path.join(work, "mc_emul.err"))
+    try:
+        for rnd in range(3):
+            _, sams = srv.align(shards, os.path.join(work, "mc_emul%d" % rnd))
+            assert SB.count_differing(want, SB.sam_records(sams)) == 0, rnd
+    finally:
+        srv.close()

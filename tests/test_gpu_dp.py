@@ -120,9 +120,10 @@ def test_non_default_scoring(ctx):
         assert dpio.results_to_py(*ref, i) == dpio.results_to_py(*got, i), i
 
 
-def test_one_scoring_scheme_per_device():
+def test_one_scoring_scheme_per_device(ctx):
     """The kernels read the scheme from device-wide constant memory: a second, different scheme is refused while another
     live context holds the first (instead of silently overwriting it under that context's kernels)."""
+    ctx.set_scoring(scoring.Scoring(local=False))      # the module's context is alive too: all three share one scheme
     a, b = lib.Context(0), lib.Context(0)
     try:
         a.set_scoring(scoring.Scoring(local=False))
@@ -130,7 +131,12 @@ def test_one_scoring_scheme_per_device():
         with pytest.raises(lib.Bt2GpuError, match="different scoring scheme"):
             b.set_scoring(scoring.Scoring(local=True))
         a.close()
-        b.set_scoring(scoring.Scoring(local=True))             # the only holder may change it
+        with pytest.raises(lib.Bt2GpuError, match="different scoring scheme"):
+            b.set_scoring(scoring.Scoring(local=True))         # the module's context still holds the end-to-end scheme
+        b.close()
+        b = lib.Context(0)
+        ctx.set_scoring(scoring.Scoring(local=True))           # a scheme nobody else holds may be replaced
+        b.set_scoring(scoring.Scoring(local=True))
         probs = list(dpio.parse_dump(os.path.join(H.GOLDEN, "dp_c2loc_ext.txt"), limit=40))
         sc = scoring.Scoring(local=True)
         seq, qual, win, jobs = dpio.batch_from_problems(probs, sc)
