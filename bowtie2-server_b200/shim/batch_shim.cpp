@@ -85,6 +85,7 @@ struct Batch {
 // A submission lane: one bt2gpu_ctx (stream + arenas) and the helper thread that blocks in the ABI calls.
 struct Lane {
 	Worker *w = NULL;
+	int dev = 0;                     // the device this lane's context lives on
 	bt2gpu_ctx *ctx = NULL;
 	uint64_t launches = 0;
 	bt2gpu_scoring sc; bool haveSc = false;
@@ -131,6 +132,7 @@ std::vector<Worker*> g_workers;
 size_t g_next = 0;
 std::atomic<bool> g_spawned{false};
 int g_nthreads = 0, g_nlanes = 2;
+std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
 
 int envInt(const char *name, int dflt, int lo, int hi) {
@@ -201,6 +203,7 @@ void Worker::loop() {
 	for(int i = 0; i < g_nlanes; i++) {
 		Lane *l = new Lane();
 		l->w = this;
+		l->dev = g_devices[(size_t)id % g_devices.size()];
 		lanes.push_back(l);
 		l->th = std::thread([l] { l->run(); });
 		l->th.detach();
@@ -277,8 +280,11 @@ void Lane::run() {
 		try {
 			// the helper threads of all lanes wait in the ABI calls: they must sleep there, not spin
 			static std::once_flag once;
-			std::call_once(once, [] { if(getenv("BT2GPU_SPIN") == NULL && bt2gpu_device_blocking_sync(device(), 1)) fail("bt2gpu_device_blocking_sync"); });
-			if(ctx == NULL && bt2gpu_ctx_create(device(), &ctx)) fail("bt2gpu_ctx_create");
+			std::call_once(once, [] {
+				if(getenv("BT2GPU_SPIN") != NULL) return;
+				for(int d : g_devices) if(bt2gpu_device_blocking_sync(d, 1)) fail("bt2gpu_device_blocking_sync");
+			});
+			if(ctx == NULL && bt2gpu_ctx_create(dev, &ctx)) fail("bt2gpu_ctx_create");
 			execute(*b);
 		} catch(int) {
 			die("batched ABI call failed", "the server has no CPU path and stops");
@@ -333,7 +339,7 @@ void Lane::execute(Batch& b) {
 			for(size_t i : grp) appendRead(*this, *b.sweeps[i]->rd);
 			stage(*this);
 			swres.resize(grp.size());
-			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
+			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw, dev), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
 			for(size_t j = 0; j < grp.size(); j++) b.sweeps[grp[j]]->res = swres[j];
 			noteBatch(C_SWEEP, grp.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read), grp.size() * sizeof(bt2gpu_sweep_result));
 		}
@@ -356,7 +362,7 @@ void Lane::execute(Batch& b) {
 			stage(*this);
 			ores.resize(grp.size()); ohits.resize(cap);
 			size_t n = 0;
-			if(bt2gpu_onemm_batch(ctx, index(*k.fw), index(*k.bw), ojobs.data(), k.local ? 1 : 0, k.repex ? 1 : 0, k.rep1mm ? 1 : 0,
+			if(bt2gpu_onemm_batch(ctx, index(*k.fw, dev), index(*k.bw, dev), ojobs.data(), k.local ? 1 : 0, k.repex ? 1 : 0, k.rep1mm ? 1 : 0,
 			                      ores.data(), ohits.data(), cap, &n)) fail("bt2gpu_onemm_batch");
 			for(size_t j = 0; j < grp.size(); j++) {
 				OneMmCall& c = *b.onemms[grp[j]];
@@ -388,14 +394,14 @@ void Lane::execute(Batch& b) {
 		stage(*this);
 		if(!sjobs.empty()) {
 			shits.resize(sjobs.size());
-			if(bt2gpu_seed_exact_batch(ctx, index(*fw), index(*bw), sjobs.data(), sjobs.size(), shits.data())) fail("bt2gpu_seed_exact_batch");
+			if(bt2gpu_seed_exact_batch(ctx, index(*fw, dev), index(*bw, dev), sjobs.data(), sjobs.size(), shits.data())) fail("bt2gpu_seed_exact_batch");
 			size_t o = 0;
 			for(SeedsCall *c : b.seeds) { c->out.assign(shits.begin() + o, shits.begin() + o + c->jobs.size()); o += c->jobs.size(); }
 			noteBatch(C_SEEDS, sjobs.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read) + sjobs.size() * sizeof(bt2gpu_seed_job), sjobs.size() * sizeof(bt2gpu_seed_hit));
 		} else for(SeedsCall *c : b.seeds) c->out.clear();
 		if(!xjobs.empty()) {
 			xres.resize(xjobs.size());
-			if(bt2gpu_extend_batch(ctx, index(*fw), index(*bw), xjobs.data(), xjobs.size(), xres.data())) fail("bt2gpu_extend_batch");
+			if(bt2gpu_extend_batch(ctx, index(*fw, dev), index(*bw, dev), xjobs.data(), xjobs.size(), xres.data())) fail("bt2gpu_extend_batch");
 			for(size_t j = 0; j < xjobs.size(); j++) b.extends[j]->res = xres[j];
 			noteBatch(C_EXTEND, xjobs.size(), xjobs.size() * sizeof(bt2gpu_extend_job), xjobs.size() * sizeof(bt2gpu_extend_result));
 		}
@@ -405,7 +411,7 @@ void Lane::execute(Batch& b) {
 		const size_t n = b.locates.size();
 		rows.resize(n); offs.resize(n); steps.resize(n);
 		for(size_t j = 0; j < n; j++) rows[j] = b.locates[j]->row;
-		if(bt2gpu_locate_batch(ctx, index(*b.locates[0]->fw), rows.data(), n, offs.data(), steps.data())) fail("bt2gpu_locate_batch");
+		if(bt2gpu_locate_batch(ctx, index(*b.locates[0]->fw, dev), rows.data(), n, offs.data(), steps.data())) fail("bt2gpu_locate_batch");
 		for(size_t j = 0; j < n; j++) { b.locates[j]->off = offs[j]; b.locates[j]->steps = steps[j]; }
 		noteBatch(C_LOCATE, n, n * 4, n * 8);
 	}
@@ -534,6 +540,16 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 		g_nthreads = envInt("BT2GPU_THREADS", hw > 16 ? 16 : hw, 1, 1024);
 		g_nlanes = envInt("BT2GPU_LANES", 2, 1, 8);
 		g_stackBytes = (size_t)envInt("BT2GPU_STACK_KB", 1024, 64, 1 << 20) * 1024;
+		if(const char *dv = getenv("BT2GPU_DEVICES")) {
+			for(const char *p = dv; *p; ) {
+				char *e = NULL;
+				long d = strtol(p, &e, 10);
+				if(e == p) break;
+				g_devices.push_back((int)d);
+				p = (*e == ',') ? e + 1 : e;
+			}
+		}
+		if(g_devices.empty()) g_devices.push_back(device());
 	}
 	Worker *w = NULL;
 	if((int)g_workers.size() < g_nthreads) {

@@ -78,7 +78,7 @@ void locate(LocateCall& c);
 
 // ---- shared by the bindings and the geometry shims (frame_gpu.cpp) ----
 bt2gpu_ctx   *ctx();                         // the calling thread's context (created on first use; throws 1 on failure)
-bt2gpu_index *index(const Ebwt& e);          // uploaded once per process (and device), shared read-only by all contexts
+bt2gpu_index *index(const Ebwt& e, int dev = -1);   // uploaded once per process and device (-1: BT2GPU_DEVICE), shared read-only by its contexts
 void          toScoring(const Scoring& sc, bt2gpu_scoring& out);
 void          fail(const char *what);        // prints bt2gpu_last_error() and throws 1 (bt2_search.cpp:5604-5611)
 void          note(Counter c, uint64_t n);   // with BT2GPU_SHIM_STATS=<file>: totals rewritten in place

@@ -42,8 +42,8 @@ void toScoring(const Scoring& sc, bt2gpu_scoring& s) {
 }
 
 // Ebwt as loaded by Ebwt::readIntoMemory (bt2_io.cpp:131-614) -> bt2gpu_index_desc, field for field
-bt2gpu_index *index(const Ebwt& e) {
-	const int dev = device();
+bt2gpu_index *index(const Ebwt& e, int dev) {
+	if(dev < 0) dev = device();
 	const IxKey key(&e, e.ebwt(), (uint32_t)e.eh().len(), (uint32_t)e.zOff(), dev);
 	std::lock_guard<std::mutex> lk(g_ixmu);
 	auto it = g_ix.find(key);
