@@ -374,7 +374,7 @@ def run_ours(args, rank, world, local_rank):
     e2e_s, srv_start, rss, shim, sams, parity = None, None, None, None, [], None
     td_obj = tempfile.TemporaryDirectory()
     td = td_obj.name
-    have = SB.have_binaries()
+    have = SB.have_binaries() and not args.chain_only
     if have:
         shards = write_shards(td, "r%d" % rank, reads, quals, nclients)
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
@@ -553,6 +553,7 @@ def main():
     ap.add_argument("--clients", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads of the batch the CPU server sees (0 = the whole batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chain-only", action="store_true", help="device stage chain only (for ncu: no server processes)")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()
     global RDLEN, SEED_LEN, IVAL, LOCAL, PAIRED, SERVER_ARGS

@@ -128,7 +128,15 @@ def main():
             continue
         ref, reads = listval(b, "ref"), listval(b, "reads")
         m1, m2 = listval(b, "mate1s"), listval(b, "mate2s")
-        if not ref or (not reads and not (m1 and m2)) or re.search(r"\b(should_abort|idx_map|color)\s*=>", b):
+        # reads given as the CONTENT of a read file (the table's parser cases): kept as content + format
+        files = None
+        for fmt, flag in (("fastq", "-q"), ("tabbed", "--tab5"), ("fasta", "-f"), ("qseq", "--qseq"), ("raw", "-r")):
+            one, f1, f2 = scalar(b, fmt), scalar(b, fmt + "1"), scalar(b, fmt + "2")
+            if one is not None and not one.isdigit():
+                files = {"flag": flag, "file": one}
+            elif f1 is not None and f2 is not None:
+                files = {"flag": flag, "file1": f1, "file2": f2}
+        if not ref or (not reads and not (m1 and m2) and not files) or re.search(r"\b(should_abort|idx_map|color)\s*=>", b):
             skipped += 1
             continue
         args = (scalar(b, "args") or "") + " " + (scalar(b, "report") or "")
@@ -143,6 +151,8 @@ def main():
             q = listval(b, "quals")
             if q:
                 c["quals"] = q
+        elif files and not (m1 and m2):
+            c["files"] = files
         else:
             c["mate1s"], c["mate2s"] = m1, m2
             f1, f2 = scalar(b, "mate1fw"), scalar(b, "mate2fw")

@@ -125,6 +125,15 @@ def write_case_inputs(case, work, tag):
                 if not case.get("norc"):
                     fh.write("@rc%d\n%s\n+\n%s\n" % (i, r.translate(comp)[::-1], q[::-1]))
         return base, args, ["-U", fq]
+    if "files" in case:          # the table's read-file cases: content and format flag as the Perl runner passes them
+        fl = case["files"]
+        if "file" in fl:
+            f = base + ".reads"
+            open(f, "w").write(fl["file"])
+            return base, args, [fl["flag"], f] if fl["flag"] == "--tab5" else [fl["flag"], "-U", f]
+        f1, f2 = base + "_1.reads", base + "_2.reads"
+        open(f1, "w").write(fl["file1"]); open(f2, "w").write(fl["file2"])
+        return base, args, [fl["flag"], "-1", f1, "-2", f2]
     f1, f2 = base + "_1.fq", base + "_2.fq"
     for f, ms in ((f1, case["mate1s"]), (f2, case["mate2s"])):
         with open(f, "w") as fh:
