@@ -217,6 +217,27 @@ def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, kee
     return t, srv.start_s, rss, sams, cnt
 
 
+def stock_server_steps(base, ncores, shards, td, tag, warmup, steps):
+    """The unmodified reference server in both of its builds (SSE2 default, SSE_AVX2=1): the faster one counts
+    (SURVEY 8d).  Returns (seconds, start_s, rss, sams, build name, {build: seconds})."""
+    from bt2gpu import serverbench as SB
+    best, times = None, {}
+    for name, binary in (("sse2", SB.CPU_SERVER), ("avx2", SB.CPU_SERVER_AVX2)):
+        if not os.path.exists(binary):
+            continue
+        try:
+            t, start_s, rss, sams, _ = server_steps(binary, base, ncores, None, shards, td, "%s_%s" % (tag, name), warmup, steps)
+        except Exception as e:      # e.g. a host CPU without AVX2
+            sys.stderr.write("bench: stock server build %s failed: %s\n" % (name, str(e).splitlines()[0][:200]))
+            continue
+        times[name] = t
+        if best is None or t < best[0]:
+            best = (t, start_s, rss, sams, name)
+    if best is None:
+        raise RuntimeError("no stock reference server could be run")
+    return best + (times,)
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -231,17 +252,18 @@ def run_reference(args, rank, world):
     nclients = args.clients or max(2, min(8, ncores // 4))
     with tempfile.TemporaryDirectory() as td:
         shards = write_shards(td, "ref", reads, quals, nclients)
-        t, start_s, rss, _, _ = server_steps(SB.CPU_SERVER, base, ncores, None, shards, td, "ref", args.warmup, args.steps)
+        t, start_s, rss, _, build, times = stock_server_steps(base, ncores, shards, td, "ref", args.warmup, args.steps)
     val = len(reads) * args.steps / t
-    sample = ("%d reads per step through the unmodified reference server (oracle/_ref/bowtie2-align-server-s -p %d, SSE2 build) "
-              "and %d bowtie2-align-l clients; wall time from the first client's start to the last client's exit"
-              % (len(reads), ncores, nclients))
+    sample = ("%d reads per step through the unmodified reference server (bowtie2-align-server-s -p %d, the faster of its "
+              "SSE2 and SSE_AVX2=1 builds: %s) and %d bowtie2-align-l clients; wall time from the first client's start to the "
+              "last client's exit" % (len(reads), ncores, build, nclients))
     emit({"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
           "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
           "vs_baseline": None, "dtype": "u8/i16/u32", "data": "synthetic",
           "config": {"workload": workload_name(args.batch, args.genome_mbp, args.nseq), "reads_per_step": len(reads),
                      "server_threads": ncores, "clients": nclients, "server_args": SERVER_ARGS, "server_start_s": start_s,
-                     "server_rss_mb": rss},
+                     "server_rss_mb": rss, "server_build": build,
+                     "seconds_by_build": times},
           "cpu_baseline": {"value": val, "unit": UNIT, "cores": ncores, "kind": "reference", "sample": sample},
           "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
@@ -400,10 +422,12 @@ def run_ours(args, rank, world, local_rank):
         m = min(n, args.cpu_sample) if args.cpu_sample else n
         m -= m % 2
         cshards = shards if m == n else write_shards(td, "cpu", reads[:m], quals[:m], nclients)
-        t_cpu, cstart, crss, csams, _ = server_steps(SB.CPU_SERVER, base, ncores, None, cshards, td, "cpu", 1, 1)
-        cpu_line = {"value": m / t_cpu, "unit": UNIT, "cores": ncores, "kind": "reference",
-                    "sample": "%d reads through the unmodified reference server (oracle/_ref/bowtie2-align-server-s -p %d, SSE2 "
-                              "build) and %d bowtie2-align-l clients, one pass after one warm-up pass" % (m, ncores, nclients)}
+        t_cpu, cstart, crss, csams, cbuild, ctimes = stock_server_steps(base, ncores, cshards, td, "cpu", 1, 1)
+        cpu_line = {"value": m / t_cpu, "unit": UNIT, "cores": ncores, "kind": "reference", "build": cbuild,
+                    "reads_per_s_by_build": {k: m / v for k, v in ctimes.items()},
+                    "sample": "%d reads through the unmodified reference server (bowtie2-align-server-s -p %d, the faster of its SSE2 "
+                              "and SSE_AVX2=1 builds: %s) and %d bowtie2-align-l clients, one pass after one warm-up pass"
+                              % (m, ncores, cbuild, nclients)}
         if m == n:
             a, b = SB.sam_records(csams), SB.sam_records(sams)
         else:

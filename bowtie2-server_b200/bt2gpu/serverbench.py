@@ -19,7 +19,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 BIN = os.path.join(ROOT, "oracle", "_ref")
-CPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s")
+CPU_SERVER = os.path.join(BIN, "bowtie2-align-server-s")                  # the reference's default build (-msse2)
+CPU_SERVER_AVX2 = os.path.join(BIN, "avx2", "bowtie2-align-server-s")     # its SSE_AVX2=1 build (Makefile:79-83)
 GPUB_SERVER = os.path.join(BIN, "bowtie2-align-server-s-gpub")
 CLIENT = os.path.join(BIN, "bowtie2-align-l")
 
