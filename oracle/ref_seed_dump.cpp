@@ -65,6 +65,7 @@ int main(int argc, char** argv) {
 	size_t limit = (size_t)-1, maxloc = 16;
 	int seedLen = 22, nthreads = 1, reps = 1;
 	double ivC = 1.0, ivL = 1.15;     // default end-to-end interval S,1,1.15 (--sensitive)
+	int seedMms = 0;
 	bool local = false, bench = false;
 	for(int i = 1; i < argc; i++) {
 		string a = argv[i];
@@ -79,6 +80,7 @@ int main(int argc, char** argv) {
 		else if(a == "--threads") nthreads = atoi(argv[++i]);
 		else if(a == "--reps") reps = atoi(argv[++i]);
 		else if(a == "--hits-out") hitsOut = argv[++i];
+		else if(a == "--seedmms") seedMms = atoi(argv[++i]);      // -N: 1 / 2 = multi-zone seeds (Seed::oneMmSeeds / twoMmSeeds)
 		else { cerr << "unknown arg " << a << endl; return 2; }
 	}
 	Ebwt* ebwtFw = loadEbwt(idx, true);
@@ -208,7 +210,7 @@ int main(int argc, char** argv) {
 		if(interval < 1) interval = 1;
 		ca.nextRead(); shs.clearSeeds();
 		seeds.clear();
-		Seed::mmSeeds(0, seedLen, seeds, gc);
+		Seed::mmSeeds(seedMms, seedLen, seeds, gc);
 		pair<int,int> instFw, instRc;
 		pair<int,int> inst = al.instantiateSeeds(seeds, 0, interval, rd, sc, false, false, ca, shs, sdm, instFw, instRc);
 		if(inst.first + inst.second == 0) { cout << "SD " << seedLen << ' ' << interval << " 0 0\n"; continue; }
@@ -230,6 +232,13 @@ int main(int argc, char** argv) {
 					cout << ' ' << satups[k].topf << ' ' << satups[k].topf + sz << ' ' << satups[k].topb << ' ' << satups[k].topb + sz;
 				}
 				cout << '\n';
+				if(seedMms > 0) {
+					// the reference strings the ranges stand for (SAKey: 2 bits per base, first base most significant):
+					// the seed with its mismatches applied, in the cache's order = the order of the reportHit calls
+					cout << "K " << (fw ? 1 : 0) << ' ' << i << ' ' << satups.size();
+					for(size_t k = 0; k < satups.size(); k++) cout << ' ' << satups[k].key.seq << ' ' << satups[k].key.len;
+					cout << '\n';
+				}
 				for(size_t k = 0; k < satups.size(); k++) {
 					TIndexOffU sz = (TIndexOffU)satups[k].offs.size();
 					size_t nlex = 0, nrex = 0;
