@@ -518,6 +518,7 @@ void locate(LocateCall& c) { travel(&Batch::locates, c); }
 
 // ---- fiber.h ------------------------------------------------------------------------------------------------------
 bool inWorker() { return tl_worker != NULL && tl_worker->cur != NULL; }
+void *currentWorkerArg() { return inWorker() ? tl_worker->cur->arg : NULL; }
 
 void waitInput() {
 	Worker *w = tl_worker;

@@ -8,6 +8,13 @@
 //   2. input (bt2_search.cpp:3201): `PSFactory::ReadAhead psrah(factory)` blocks the calling thread on the server's
 //      ready queue (pat.h:1885-1911, :1987-1994); a fiber must not block its host thread, so the batched build takes
 //      the next filled read buffer if there is one and otherwise lets the other workers of the thread run;
+//      When a worker hands a read buffer back it also writes out the results it has buffered for that connection.
+//      The reference's OutputQueue keeps the last readsPerBatch (16) results of every worker per connection until that
+//      worker's 17th arrives (outq.cpp:84-96) -- 256 read pairs with 16 threads, but 32768 with 2048 workers, more than
+//      the 20000 pairs a client may have in flight (PatternSourceWebClient::LockedOrigBufMap, pat.h:2464-2550: two
+//      halves of 10000, a half is reused only when ALL its results are back).  Held-back results then starve the
+//      input and, with few clients, deadlock client and server.  Same records, same per-connection stream; only
+//      when a worker's records are written changes (their order was thread-dependent already).
 //   3. GroupWalk2S -> the locate call of the binding (group_walk_gpu.h, as in the per-call build).
 //
 // All reference headers bt2_search.cpp uses are included FIRST, so the renames below touch that one file only.
@@ -58,7 +65,10 @@ class FiberReadAhead {
 public:
 	typedef PatternSourceServiceFactory::ReadElement ReadElement;
 	FiberReadAhead(PatternSourceServiceFactory& fact) : fact_(fact), re_(take(fact)), first_(true) {}
-	~FiberReadAhead() { fact_.returnUnready(re_); }
+	~FiberReadAhead() {
+		if(re_.ps != NULL) flushWorker(re_.ps->msink().outq());      // before returnUnready: it may delete ps
+		fact_.returnUnready(re_);
+	}
 	const std::pair<bool, bool>& nextReadResult() {
 		if(first_) first_ = false;       // nextReadPair was already called by the connection's thread (pat.cpp:2064-2079)
 		else re_.nextReadPair();
@@ -66,6 +76,20 @@ public:
 	}
 	PatternSourcePerThread* ptr() { return re_.ps; }
 private:
+	// OutputQueue::flushImpl (outq.cpp:101-115) for the calling worker's buffer only
+	static void flushWorker(OutputQueue& oq) {
+		thread_tracking_pair *tp = (thread_tracking_pair*)currentWorkerArg();
+		if(tp == NULL || oq.reorder_ || oq.perThreadCounter == NULL) return;
+		const size_t tid = (size_t)tp->tid;
+		if(tid >= oq.nthreads_ || oq.perThreadCounter[tid] == 0) return;
+		ThreadSafe ts(oq.mutex_m);
+		for(int j = 0; j < oq.perThreadCounter[tid]; j++) {
+			oq.obuf_.writeString(oq.perThreadBuf[tid][j]);
+			oq.nfinished_++;
+			oq.nflushed_++;
+		}
+		oq.perThreadCounter[tid] = 0;
+	}
 	static ReadElement take(PatternSourceServiceFactory& fact) {
 		for(;;) {
 			{
