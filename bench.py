@@ -191,7 +191,7 @@ def host_cores():
 # ---------------------------------------------------------------------------------------------
 # server runs (both arms)
 # ---------------------------------------------------------------------------------------------
-def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, keep_sam=False):
+def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, keep_sam=False, pass_timeout=600):
     """Start one server, run warmup + steps passes of the shard set through it.  Returns (seconds of the timed steps,
     server start seconds, RSS MB, sam paths of the last step, shim counters or None)."""
     from bt2gpu import serverbench as SB
@@ -202,10 +202,10 @@ def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, kee
     srv = SB.Server(binary, base, workers, SERVER_ARGS, env=e, log=os.path.join(td, tag + "_server.err"))
     try:
         for w in range(warmup):
-            srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)))
+            srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)), timeout=pass_timeout)
         t, sams = 0.0, []
         for s in range(steps):
-            dt, sams = srv.align(shards, os.path.join(td, "%s_s%d" % (tag, s)))
+            dt, sams = srv.align(shards, os.path.join(td, "%s_s%d" % (tag, s)), timeout=pass_timeout)
             t += dt
         rss = srv.rss_mb()
     finally:
@@ -402,7 +402,7 @@ def run_ours(args, rank, world, local_rank):
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
         barrier(False)
         e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
-                                                          args.warmup, args.steps)
+                                                          args.warmup, args.steps, pass_timeout=args.pass_timeout)
     sampler.stop_flag = True
     sampler.join()
     t = torch.tensor([dev_ms, e2e_s or 0.0], dtype=torch.float64, device="cuda")
@@ -577,6 +577,7 @@ def main():
     ap.add_argument("--clients", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads of the batch the CPU server sees (0 = the whole batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pass-timeout", type=int, default=300, help="seconds one pass of a batch through a server may take")
     ap.add_argument("--chain-only", action="store_true", help="device stage chain only (for ncu: no server processes)")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()

@@ -82,11 +82,17 @@ class Server:
             sams.append(sam)
             procs.append(subprocess.Popen([CLIENT, "--server-port", str(self.port), "-x", self.base] + list(cargs) + ["-S", sam],
                                           stdout=subprocess.DEVNULL, stderr=open(sam + ".err", "w")))
-        for p, sam in zip(procs, sams):
-            rc = p.wait(timeout=timeout)
-            if rc != 0 or self.proc.poll() is not None:
-                raise RuntimeError("client exit %s; client stderr:\n%s\nserver stderr:\n%s"
-                                   % (rc, open(sam + ".err").read()[-1500:], open(self.log).read()[-3000:]))
+        deadline = time.time() + timeout          # one deadline for the whole pass, not one per client
+        try:
+            for p, sam in zip(procs, sams):
+                rc = p.wait(timeout=max(0.1, deadline - time.time()))
+                if rc != 0 or self.proc.poll() is not None:
+                    raise RuntimeError("client exit %s; client stderr:\n%s\nserver stderr:\n%s"
+                                       % (rc, open(sam + ".err").read()[-1500:], open(self.log).read()[-3000:]))
+        finally:
+            for p in procs:                       # a pass that failed or timed out leaves no client behind
+                if p.poll() is None:
+                    p.kill()
         return time.perf_counter() - t0, sams
 
     def rss_mb(self):

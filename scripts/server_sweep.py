@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--points", default="16:128:2:8")
     ap.add_argument("--stock", action="store_true", help="also time the stock server (-p all cores) per client count")
     ap.add_argument("--passes", type=int, default=2)
+    ap.add_argument("--pass-timeout", type=int, default=90, help="seconds a single pass may take before the point is abandoned")
     a = ap.parse_args()
     if a.mode == "pairs":
         bench.PAIRED = True
@@ -42,11 +43,16 @@ def main():
             shards = bench.write_shards(td, "c%d" % ncl, reads, quals, ncl)
             if a.stock and ncl not in done_stock:
                 done_stock.add(ncl)
-                t, st, rss, _, _ = bench.server_steps(SB.CPU_SERVER, base, cores, None, shards, td, "stock%d" % ncl, 1, a.passes)
+                t, st, rss, _, _ = bench.server_steps(SB.CPU_SERVER, base, cores, None, shards, td, "stock%d" % ncl, 1, a.passes, pass_timeout=a.pass_timeout)
                 print(json.dumps({"server": "stock", "threads": cores, "clients": ncl, "reads_per_s": len(reads) * a.passes / t,
                                   "start_s": st, "rss_mb": rss}), flush=True)
             env = {"BT2GPU_THREADS": str(th), "BT2GPU_LANES": str(lanes)}
-            t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_%s" % pt.replace(":", "_"), 1, a.passes)
+            try:
+                t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_%s" % pt.replace(":", "_"), 1, a.passes,
+                                                        pass_timeout=a.pass_timeout)
+            except Exception as e:      # a point that hangs or fails must not take the rest of the sweep (and the GPU lease) with it
+                print(json.dumps({"server": "gpub", "point": pt, "failed": str(e).splitlines()[0][:200]}), flush=True)
+                continue
             jobs = (cnt or {}).get("abi_batch_jobs", 0) / max((cnt or {}).get("abi_batches", 1), 1)
             print(json.dumps({"server": "gpub", "host_threads": th, "workers": th * wpt, "lanes": lanes, "clients": ncl,
                               "reads_per_s": len(reads) * a.passes / t, "start_s": st, "rss_mb": rss, "jobs_per_abi_call": jobs,
