@@ -527,6 +527,11 @@ void waitInput() {
 	yieldTo(Fiber::WAIT_INPUT);
 }
 
+void yieldNow() {
+	if(tl_worker == NULL || tl_worker->cur == NULL) { napMicros(50); return; }
+	yieldTo(Fiber::RUNNABLE);
+}
+
 void sleepMs(int ms) {
 	if(g_spawned.exchange(false)) return;
 	timespec ts = {ms / 1000, (long)(ms % 1000) * 1000000L};

@@ -32,6 +32,7 @@ public:
 bool inWorker();        // true on a worker's stack
 void *currentWorkerArg(); // the `arg` the running worker was started with (NULL outside a worker)
 void waitInput();       // a worker found nothing to read: suspend until the scheduler lets it look again
+void yieldNow();        // let the other workers of this host thread run; the caller stays runnable
 void sleepMs(int ms);   // SLEEP(): skipped right after a spawn (10 ms per worker x thousands of workers otherwise)
 
 } // namespace bt2shim

@@ -13,7 +13,8 @@
 //      worker's 17th arrives (outq.cpp:84-96) -- 256 read pairs with 16 threads, but 32768 with 2048 workers, more than
 //      the 20000 pairs a client may have in flight (PatternSourceWebClient::LockedOrigBufMap, pat.h:2464-2550: two
 //      halves of 10000, a half is reused only when ALL its results are back).  Held-back results then starve the
-//      input and, with few clients, deadlock client and server.  Same records, same per-connection stream; only
+//      input and, with few clients, deadlock client and server; for the same reason the connection's OutFileBuf is
+//      handed to its writer then, instead of waiting for 16 KB of further output.  Same records, same stream; only
 //      when a worker's records are written changes (their order was thread-dependent already).
 //   3. GroupWalk2S -> the locate call of the binding (group_walk_gpu.h, as in the per-call build).
 //
@@ -82,13 +83,27 @@ private:
 		if(tp == NULL || oq.reorder_ || oq.perThreadCounter == NULL) return;
 		const size_t tid = (size_t)tp->tid;
 		if(tid >= oq.nthreads_ || oq.perThreadCounter[tid] == 0) return;
-		ThreadSafe ts(oq.mutex_m);
-		for(int j = 0; j < oq.perThreadCounter[tid]; j++) {
-			oq.obuf_.writeString(oq.perThreadBuf[tid][j]);
-			oq.nfinished_++;
-			oq.nflushed_++;
+		{
+			ThreadSafe ts(oq.mutex_m);
+			for(int j = 0; j < oq.perThreadCounter[tid]; j++) {
+				oq.obuf_.writeString(oq.perThreadBuf[tid][j]);
+				oq.nfinished_++;
+				oq.nflushed_++;
+			}
+			oq.perThreadCounter[tid] = 0;
 		}
-		oq.perThreadCounter[tid] = 0;
+		// ... and on to the socket: OutFileBuf keeps up to 16 KB (16 MB while its writer is busy, filebuf.h:999-1000,
+		// :757-773) until more output pushes it out.  With a thousand workers finishing in any order the records left
+		// there can be ones the client's window is waiting for, and then nothing more is ever written.  flush() waits
+		// for the connection's writer thread: while that one is busy this worker lets the others run instead.
+		for(;;) {
+			{
+				ThreadSafe ts(oq.mutex_m);
+				if(oq.obuf_.cur_ == 0) break;
+				if(!oq.obuf_.flushBlocking()) { oq.obuf_.flush(); break; }
+			}
+			yieldNow();
+		}
 	}
 	static ReadElement take(PatternSourceServiceFactory& fact) {
 		for(;;) {
