@@ -24,7 +24,7 @@ SYMBOLS = [
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
     "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch", "bt2gpu_frame_mate_rect_batch",
-    "bt2gpu_device_blocking_sync", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
+    "bt2gpu_device_blocking_sync", "bt2gpu_noalloc_scratch_bytes", "bt2gpu_ungapped_batch_noalloc", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
 ]
 
 _lib = None
@@ -47,6 +47,7 @@ def load():
         lib.bt2gpu_dp_walked_cells.restype = C.c_uint64
         lib.bt2gpu_index_bytes.restype = C.c_uint64
         lib.bt2gpu_ref_bytes.restype = C.c_uint64
+        lib.bt2gpu_noalloc_scratch_bytes.restype = C.c_uint64
         lib.bt2gpu_ref_destroy.restype = None
         lib.bt2gpu_index_bytes.argtypes = [C.c_void_p]
         lib.bt2gpu_index_destroy.argtypes = [C.c_void_p]
@@ -175,6 +176,19 @@ class Context:
         return res, edits[: ne.value]
 
     # ---- FM index (seed side) ---------------------------------------------------------------
+    def ungapped_batch_noalloc(self, seq, qual, win, jobs, edit_cap=None):
+        """bt2gpu_ungapped_batch_noalloc: the same call with its device scratch in the library's static array (no
+        cudaMalloc); fails for batches beyond BT2GPU_NOALLOC_SCRATCH_BYTES."""
+        n = len(jobs)
+        edit_cap = edit_cap if edit_cap is not None else int(jobs["rd_len"].sum()) + 16
+        res = np.zeros(n, dtype=structs.ungap_result)
+        edits = np.zeros(edit_cap, dtype=structs.edit)
+        ne = C.c_size_t(0)
+        _check(self.lib.bt2gpu_ungapped_batch_noalloc(self._h, _ptr(seq), _ptr(qual), C.c_size_t(len(seq)), _ptr(win),
+                                                      C.c_size_t(len(win)), _ptr(jobs), C.c_size_t(n), _ptr(res), _ptr(edits),
+                                                      C.c_size_t(edit_cap), C.byref(ne)))
+        return res, edits[: ne.value]
+
     def stage_reads(self, pool):
         """bt2gpu_reads_stage: pool = fmio.ReadPool (replaces the per-call `const Read&`)."""
         self._pool_n = len(pool)

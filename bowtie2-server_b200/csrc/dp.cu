@@ -1753,3 +1753,101 @@ extern "C" int bt2gpu_ungapped_batch(
 	buf.release();
 	return rc;
 }
+
+// ---------------------------------------------------------------------------------------
+// bt2gpu_ungapped_batch_noalloc: the same kernel and the same host-buffer signature as bt2gpu_ungapped_batch, for callers
+// that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.
+//
+// bt2gpu_ungapped_batch cudaMallocs its scratch arena per call (staged pools, job table, results, edit pool, and the
+// counter block the kernel reserves edit ranges from) and frees it afterwards.  Here the arena is a file-scope device
+// array of BT2GPU_NOALLOC_SCRATCH_BYTES; every GPU that loads the library holds it until the process exits.  The call
+// makes no cudaMalloc / cudaFree and no allocating library call; a batch whose arena does not fit is rejected.
+//
+// In HOST code the array's name is only a host-side stand-in for the symbol, not a device address: its device address
+// is asked for once per device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel
+// and the copies get.  All calls on a device share the array and it keeps the previous call's contents: the counter block
+// is cleared on the stream before every launch (everything else is overwritten before it is read), and two calls that
+// overlap on the GPU (different contexts / streams of one device) RACE -- serialise them.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BT2GPU_NOALLOC_SCRATCH_BYTES];
+
+namespace bt2 {
+static std::mutex g_noalloc_mu;
+static unsigned char *g_noalloc_ptr[64];     // device address of g_noalloc_scratch, per device ordinal
+
+// set-up, once per device, with that device current
+static int noalloc_scratch(int device, unsigned char **out) {
+	if(device < 0 || device >= 64) BT2_FAIL("device ordinal out of range");
+	std::lock_guard<std::mutex> lk(g_noalloc_mu);
+	if(!g_noalloc_ptr[device]) {
+		BT2_CUDA(cudaSetDevice(device));
+		void *p = nullptr;
+		BT2_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+		if(!p) BT2_FAIL("cudaGetSymbolAddress returned a null scratch address");
+		g_noalloc_ptr[device] = static_cast<unsigned char*>(p);
+	}
+	*out = g_noalloc_ptr[device];
+	return 0;
+}
+}
+
+extern "C" uint64_t bt2gpu_noalloc_scratch_bytes(void) { return BT2GPU_NOALLOC_SCRATCH_BYTES; }
+
+extern "C" int bt2gpu_ungapped_batch_noalloc(
+	bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len, const bt2gpu_ungap_job *jobs, size_t njobs,
+	bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits)
+{
+	using namespace bt2;
+	if(!ctx) BT2_FAIL("null context");
+	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set has not been called");
+	if(nedits) *nedits = 0;
+	if(njobs == 0) return 0;
+	if(!seq_pool || !qual_pool || !win_pool || !jobs || !results || (!edits && edit_cap)) BT2_FAIL("null argument");
+	if(njobs > 0x7fffffffu) BT2_FAIL("too many jobs");
+	for(size_t i = 0; i < njobs; i++) {
+		const bt2gpu_ungap_job& j = jobs[i];
+		if(j.rd_len == 0) BT2_FAIL("empty read");
+		if((size_t)j.rd_off + j.rd_len > pool_len || (size_t)j.rf_off + j.rd_len > win_len) BT2_FAIL("job outside its pool");
+	}
+	// the arena of bt2gpu_ungapped_batch, laid out in the static array: the counter block first
+	auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+	const size_t cap = BT2GPU_NOALLOC_SCRATCH_BYTES;
+	if(pool_len > cap || win_len > cap || njobs > cap / sizeof(bt2gpu_ungap_job) || edit_cap > cap / sizeof(bt2gpu_edit))
+		BT2_FAIL("batch exceeds the no-allocation scratch (BT2GPU_NOALLOC_SCRATCH_BYTES): split it or use bt2gpu_ungapped_batch");
+	const size_t o_scal = 0, o_seq = 256, o_qual = o_seq + al(pool_len), o_win = o_qual + al(pool_len), o_jobs = o_win + al(win_len),
+	             o_res = o_jobs + al(njobs * sizeof(bt2gpu_ungap_job)), o_ed = o_res + al(njobs * sizeof(bt2gpu_ungap_result)),
+	             total = o_ed + al(edit_cap * sizeof(bt2gpu_edit));
+	if(total > cap)
+		BT2_FAIL("batch exceeds the no-allocation scratch (BT2GPU_NOALLOC_SCRATCH_BYTES): split it or use bt2gpu_ungapped_batch");
+	unsigned char *b = nullptr;
+	if(noalloc_scratch(ctx->device, &b)) return 1;
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	cudaStream_t s = ctx->stream;
+	BT2_CUDA(cudaMemsetAsync(b + o_scal, 0, 256, s));          // edit counter + error flag must start at zero
+	BT2_CUDA(cudaMemcpyAsync(b + o_seq, seq_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(b + o_qual, qual_pool, pool_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(b + o_win, win_pool, win_len, cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemcpyAsync(b + o_jobs, jobs, njobs * sizeof(bt2gpu_ungap_job), cudaMemcpyHostToDevice, s));
+	const unsigned wpb = 4;
+	k_ungapped<<<(unsigned)((njobs + wpb - 1) / wpb), wpb * 32, 0, s>>>(
+		b + o_seq, b + o_qual, b + o_win, reinterpret_cast<const bt2gpu_ungap_job*>(b + o_jobs), (uint32_t)njobs,
+		reinterpret_cast<bt2gpu_ungap_result*>(b + o_res), reinterpret_cast<bt2gpu_edit*>(b + o_ed),
+		reinterpret_cast<unsigned long long*>(b + o_scal), (unsigned long long)edit_cap,
+		reinterpret_cast<int*>(b + o_scal + 8));
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	unsigned long long scal[2] = {0, 0};
+	BT2_CUDA(cudaMemcpyAsync(results, b + o_res, njobs * sizeof(bt2gpu_ungap_result), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaMemcpyAsync(scal, b + o_scal, sizeof scal, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaStreamSynchronize(s));
+	if((int)(scal[1] & 0xffffffffu) == 2 || scal[0] > edit_cap) BT2_FAIL("edit pool overflow (raise edit_cap)");
+	if(scal[0]) {
+		BT2_CUDA(cudaMemcpyAsync(edits, b + o_ed, (size_t)scal[0] * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, s));
+		BT2_CUDA(cudaStreamSynchronize(s));
+	}
+	if(nedits) *nedits = (size_t)scal[0];
+	return 0;
+}

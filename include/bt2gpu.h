@@ -199,6 +199,25 @@ int bt2gpu_ungapped_batch(
 	const bt2gpu_ungap_job *jobs, size_t njobs,
 	bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits);
 
+/* bt2gpu_ungapped_batch without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results as bt2gpu_ungapped_batch; the device scratch that call
+ * allocates per call (staged pools, job table, results, edit pool, counter block) lives in a static device array of
+ * BT2GPU_NOALLOC_SCRATCH_BYTES instead, held by every GPU that loads the library until the process exits.
+ * Limit: 512 bytes + 2*pool_len + win_len + njobs*80 + edit_cap*8 (each term rounded up to 256) must not exceed
+ * BT2GPU_NOALLOC_SCRATCH_BYTES, else the call fails with an error naming the limit (split the batch, or use
+ * bt2gpu_ungapped_batch).  The call makes no cudaMalloc / cudaFree / allocating library call.  All calls on a device share
+ * the array: it keeps the previous call's contents (what must start at zero is cleared per call), and calls that overlap
+ * on the GPU -- two contexts of one device running this entry point at the same time -- RACE: serialise them. */
+#define BT2GPU_NOALLOC_SCRATCH_BYTES (4u << 20)
+uint64_t bt2gpu_noalloc_scratch_bytes(void);
+int bt2gpu_ungapped_batch_noalloc(
+	bt2gpu_ctx *ctx,
+	const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
+	const uint8_t *win_pool, size_t win_len,
+	const bt2gpu_ungap_job *jobs, size_t njobs,
+	bt2gpu_ungap_result *results, bt2gpu_edit *edits, size_t edit_cap, size_t *nedits);
+
 /* ======================================================================== */
 /* ---- FM index (replaces Ebwt's search-side state, bt2_idx.h:2530-2570) --- */
 
