@@ -181,6 +181,15 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons)}
 
 
+_T0 = time.time()
+
+
+def progress(msg):
+    """One time-stamped line on stderr per stage: a run that is cut off shows where it was."""
+    sys.stderr.write("bench [%6.1f s] %s\n" % (time.time() - _T0, msg))
+    sys.stderr.flush()
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -199,13 +208,16 @@ def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, kee
     e = dict(env or {})
     if binary == SB.GPUB_SERVER:
         e["BT2GPU_SHIM_STATS"] = stats
-    srv = SB.Server(binary, base, workers, SERVER_ARGS, env=e, log=os.path.join(td, tag + "_server.err"))
+    srv = SB.Server(binary, base, workers, SERVER_ARGS, env=e, log=os.path.join(td, tag + "_server.err"), start_timeout=300)
+    progress("%s: server up in %.1f s (-p %d)" % (tag, srv.start_s, workers))
     try:
         for w in range(warmup):
-            srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)), timeout=pass_timeout)
+            dt, _ = srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)), timeout=pass_timeout)
+            progress("%s: warm-up pass %d %.1f s" % (tag, w, dt))
         t, sams = 0.0, []
         for s in range(steps):
             dt, sams = srv.align(shards, os.path.join(td, "%s_s%d" % (tag, s)), timeout=pass_timeout)
+            progress("%s: timed pass %d %.1f s" % (tag, s, dt))
             t += dt
         rss = srv.rss_mb()
     finally:
@@ -298,8 +310,10 @@ def run_ours(args, rank, world, local_rank):
     base, seqs, ix = get_index(args)
     if world > 1 and rank == 0:
         dist.barrier()
+    progress("index files ready")
     if ix is None:
         ix = index.Index.load(base)
+    progress("index in host memory")
     torch.cuda.empty_cache()
     sc = scoring.Scoring(local=LOCAL)
     dix = lib.DeviceIndex(ix, local_rank)
@@ -309,8 +323,10 @@ def run_ours(args, rank, world, local_rank):
     ctx = lib.Context(local_rank)
     ctx.set_scoring(sc)
     ctx.bind_index(dix)
+    progress("index and reference in HBM")
     reads, quals = make_reads(args.seed + 7 + 1000 * rank, seqs, args.batch)   # each rank its own shard of the read stream
     n = len(reads)
+    progress("%d reads made" % n)
 
     keep = []
 
@@ -364,6 +380,7 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.warmup):
         chain()
     barrier()
+    progress("chain: %d warm-up steps done" % args.warmup)
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = ctx.launches
@@ -379,11 +396,13 @@ def run_ours(args, rank, world, local_rank):
                 kms["mate_" + k] = kms.get("mate_" + k, 0.0) + cnt["mate_ms_" + k]
     barrier()
     chain_launches = ctx.launches - l0
+    progress("chain: %d timed steps done, %.1f ms on the device" % (args.steps, dev_ms))
     cnt = {k: (int(v) if not k.startswith(("ms_", "wall_", "mate_ms_")) else float(v)) for k, v in cnt.items()}
     probe_ix = ctx.gather_probe("fw", 1 << 27)                # random sides of the index itself (L2 helps when it fits)
     probe = ctx.probe_random_gather(8 << 30, 1 << 27)         # random 64-B gathers over 8 GiB: the HBM random-access ceiling
     dpx_peak = ctx.probe_dpx()                                # G thread-instr/s of packed s16x2 DPX
     index_bytes = dix.nbytes + dref.nbytes
+    progress("probes done")
     ctx.close(); dref.close(); dix.close()
     del keep[:]
     torch.cuda.empty_cache()
@@ -399,6 +418,7 @@ def run_ours(args, rank, world, local_rank):
     have = SB.have_binaries() and not args.chain_only
     if have:
         shards = write_shards(td, "r%d" % rank, reads, quals, nclients)
+        progress("FASTQ shards for %d clients written" % nclients)
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
         barrier(False)
         e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
@@ -428,6 +448,7 @@ def run_ours(args, rank, world, local_rank):
                     "sample": "%d reads through the unmodified reference server (bowtie2-align-server-s -p %d, the faster of its SSE2 "
                               "and SSE_AVX2=1 builds: %s) and %d bowtie2-align-l clients, one pass after one warm-up pass"
                               % (m, ncores, cbuild, nclients)}
+        progress("stock server done")
         if m == n:
             a, b = SB.sam_records(csams), SB.sam_records(sams)
         else:
@@ -435,6 +456,7 @@ def run_ours(args, rank, world, local_rank):
             a, b = SB.sam_records(csams), SB.sam_records(gsams)
         parity = {"sam_records": len(a), "differing_records": SB.count_differing(a, b),
                   "aligned_records": sum(1 for ln in a if ln.split("\t")[2] != "*")}
+    progress("parity compared")
     td_obj.cleanup()
 
     peaks = {}

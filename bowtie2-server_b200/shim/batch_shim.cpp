@@ -18,6 +18,8 @@
 #include <string>
 #include <thread>
 #include <vector>
+#include <malloc.h>
+#include <pthread.h>
 #include <sys/mman.h>
 #include <time.h>
 #include <unistd.h>
@@ -135,6 +137,21 @@ int g_nthreads = 0, g_nlanes = 2;
 std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
 
+// glibc's allocator, as the reference uses it, gives memory back to the kernel whenever the top of a thread's arena
+// is free (madvise / mprotect) and asks for it again page by page -- with thousands of workers' buffers per host thread,
+// and connection threads that build 4 * (-p) + 1 read buffers each, a profile of the batched server showed more time in
+// those two system calls than in the reference's own code.  Keep freed memory, grow in large steps.  Process set-up of
+// the batched binding only; BT2GPU_MALLOC_TUNING=0 leaves the allocator alone.
+struct MallocTuning {
+	MallocTuning() {
+		const char *v = getenv("BT2GPU_MALLOC_TUNING");
+		if(v != NULL && atoi(v) == 0) return;
+		mallopt(M_TRIM_THRESHOLD, 1 << 30);
+		mallopt(M_TOP_PAD, 16 << 20);
+		mallopt(M_MMAP_THRESHOLD, 32 << 20);
+	}
+} g_mallocTuning;
+
 int envInt(const char *name, int dflt, int lo, int hi) {
 	const char *v = getenv(name);
 	if(v == NULL || *v == 0) return dflt;
@@ -196,8 +213,24 @@ void Worker::runFiber(Fiber *f) {
 
 void napMicros(long us) { timespec ts = {0, us * 1000}; nanosleep(&ts, NULL); }
 
+inline uint64_t cpuUs() { timespec ts; clock_gettime(CLOCK_THREAD_CPUTIME_ID, &ts); return (uint64_t)ts.tv_sec * 1000000u + (uint64_t)ts.tv_nsec / 1000u; }
+inline uint64_t nowUs() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (uint64_t)ts.tv_sec * 1000000u + (uint64_t)ts.tv_nsec / 1000u; }
+// adds the time a scope took to one of the us_* counters
+struct Timed {
+	Counter c; uint64_t t0;
+	explicit Timed(Counter c_) : c(c_), t0(nowUs()) {}
+	~Timed() { note(c, nowUs() - t0); }
+};
+
+void nameThread(const char *kind, int a, int b) {      // readable in top -H / a sampling profiler
+	char nm[16];
+	snprintf(nm, sizeof nm, b < 0 ? "bt2-%s-%d" : "bt2-%s-%d.%d", kind, a, b);
+	pthread_setname_np(pthread_self(), nm);
+}
+
 void Worker::loop() {
 	tl_worker = this;
+	nameThread("host", id, -1);
 	pending = new Batch();
 	for(int i = 0; i < g_nlanes + 1; i++) freeBatches.push_back(new Batch());
 	for(int i = 0; i < g_nlanes; i++) {
@@ -205,7 +238,7 @@ void Worker::loop() {
 		l->w = this;
 		l->dev = g_devices[(size_t)id % g_devices.size()];
 		lanes.push_back(l);
-		l->th = std::thread([l] { l->run(); });
+		l->th = std::thread([l, i] { nameThread("lane", l->w->id, i); l->run(); });
 		l->th.detach();
 	}
 	for(;;) {
@@ -232,6 +265,7 @@ void Worker::loop() {
 		//    while the last look found nothing
 		int looks = inputOk ? (int)fibers.size() : 1;
 		inputMiss = false;
+		const uint64_t tRun = nowUs(), cRun = cpuUs();
 		for(size_t i = 0; i < fibers.size(); i++) {
 			Fiber *f = fibers[i];
 			if(f->state == Fiber::WAIT_INPUT) {
@@ -243,6 +277,7 @@ void Worker::loop() {
 			if(inputMiss && looks > 1) looks = 1;
 		}
 		inputOk = !inputMiss;
+		if(progress) { note(C_US_WORKERS, nowUs() - tRun); note(C_US_WORKERS_CPU, cpuUs() - cRun); }
 		// 3. what they queued travels on a free lane
 		if(!pending->empty()) {
 			Lane *fl = NULL;
@@ -258,6 +293,7 @@ void Worker::loop() {
 		}
 		// 4. nothing to do: wait for a lane, or for input
 		if(!progress) {
+			Timed tw(C_US_WAIT);
 			if(busy) {
 				std::unique_lock<std::mutex> lk(mu);
 				bool any = false;
@@ -285,7 +321,10 @@ void Lane::run() {
 				for(int d : g_devices) if(bt2gpu_device_blocking_sync(d, 1)) fail("bt2gpu_device_blocking_sync");
 			});
 			if(ctx == NULL && bt2gpu_ctx_create(dev, &ctx)) fail("bt2gpu_ctx_create");
+			Timed tl(C_US_LANES);
+			const uint64_t c0 = cpuUs();
 			execute(*b);
+			note(C_US_LANES_CPU, cpuUs() - c0);
 		} catch(int) {
 			die("batched ABI call failed", "the server has no CPU path and stops");
 		}
@@ -303,11 +342,12 @@ void appendRead(Lane& l, const Read& rd) {
 	bt2gpu_read r; r.rd_off = (uint32_t)l.seq.size(); r.rd_len = (uint32_t)len;
 	const size_t o = l.seq.size();
 	l.seq.resize(o + len); l.qual.resize(o + len);
-	for(size_t i = 0; i < len; i++) { l.seq[o + i] = (uint8_t)rd.patFw[i]; l.qual[o + i] = (uint8_t)rd.qual[i]; }
+	if(len > 0) { memcpy(&l.seq[o], rd.patFw.buf(), len); memcpy(&l.qual[o], rd.qual.buf(), len); }   // codes 0..4, Phred+33
 	l.reads.push_back(r);
 }
 
 void stage(Lane& l) {
+	Timed t(C_US_ABI_STAGE);
 	if(bt2gpu_reads_stage(l.ctx, l.seq.data(), l.qual.data(), l.seq.size(), l.reads.data(), l.reads.size())) fail("bt2gpu_reads_stage");
 }
 
@@ -339,7 +379,9 @@ void Lane::execute(Batch& b) {
 			for(size_t i : grp) appendRead(*this, *b.sweeps[i]->rd);
 			stage(*this);
 			swres.resize(grp.size());
+			const uint64_t t_sweep = nowUs();
 			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw, dev), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
+			note(C_US_ABI_SWEEP, nowUs() - t_sweep);
 			for(size_t j = 0; j < grp.size(); j++) b.sweeps[grp[j]]->res = swres[j];
 			noteBatch(C_SWEEP, grp.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read), grp.size() * sizeof(bt2gpu_sweep_result));
 		}
@@ -362,8 +404,10 @@ void Lane::execute(Batch& b) {
 			stage(*this);
 			ores.resize(grp.size()); ohits.resize(cap);
 			size_t n = 0;
+			const uint64_t t_onemm = nowUs();
 			if(bt2gpu_onemm_batch(ctx, index(*k.fw, dev), index(*k.bw, dev), ojobs.data(), k.local ? 1 : 0, k.repex ? 1 : 0, k.rep1mm ? 1 : 0,
 			                      ores.data(), ohits.data(), cap, &n)) fail("bt2gpu_onemm_batch");
+			note(C_US_ABI_ONEMM, nowUs() - t_onemm);
 			for(size_t j = 0; j < grp.size(); j++) {
 				OneMmCall& c = *b.onemms[grp[j]];
 				c.res = ores[j];
@@ -394,14 +438,18 @@ void Lane::execute(Batch& b) {
 		stage(*this);
 		if(!sjobs.empty()) {
 			shits.resize(sjobs.size());
+			const uint64_t t_seeds = nowUs();
 			if(bt2gpu_seed_exact_batch(ctx, index(*fw, dev), index(*bw, dev), sjobs.data(), sjobs.size(), shits.data())) fail("bt2gpu_seed_exact_batch");
+			note(C_US_ABI_SEEDS, nowUs() - t_seeds);
 			size_t o = 0;
 			for(SeedsCall *c : b.seeds) { c->out.assign(shits.begin() + o, shits.begin() + o + c->jobs.size()); o += c->jobs.size(); }
 			noteBatch(C_SEEDS, sjobs.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read) + sjobs.size() * sizeof(bt2gpu_seed_job), sjobs.size() * sizeof(bt2gpu_seed_hit));
 		} else for(SeedsCall *c : b.seeds) c->out.clear();
 		if(!xjobs.empty()) {
 			xres.resize(xjobs.size());
+			const uint64_t t_extend = nowUs();
 			if(bt2gpu_extend_batch(ctx, index(*fw, dev), index(*bw, dev), xjobs.data(), xjobs.size(), xres.data())) fail("bt2gpu_extend_batch");
+			note(C_US_ABI_EXTEND, nowUs() - t_extend);
 			for(size_t j = 0; j < xjobs.size(); j++) b.extends[j]->res = xres[j];
 			noteBatch(C_EXTEND, xjobs.size(), xjobs.size() * sizeof(bt2gpu_extend_job), xjobs.size() * sizeof(bt2gpu_extend_result));
 		}
@@ -411,7 +459,9 @@ void Lane::execute(Batch& b) {
 		const size_t n = b.locates.size();
 		rows.resize(n); offs.resize(n); steps.resize(n);
 		for(size_t j = 0; j < n; j++) rows[j] = b.locates[j]->row;
+		const uint64_t t_locate = nowUs();
 		if(bt2gpu_locate_batch(ctx, index(*b.locates[0]->fw, dev), rows.data(), n, offs.data(), steps.data())) fail("bt2gpu_locate_batch");
+		note(C_US_ABI_LOCATE, nowUs() - t_locate);
 		for(size_t j = 0; j < n; j++) { b.locates[j]->off = offs[j]; b.locates[j]->steps = steps[j]; }
 		noteBatch(C_LOCATE, n, n * 4, n * 8);
 	}
@@ -431,8 +481,10 @@ void Lane::execute(Batch& b) {
 		}
 		ures.resize(n); dedits.resize(cap);
 		size_t ne = 0;
+		const uint64_t t_ungapped = nowUs();
 		if(bt2gpu_ungapped_batch(ctx, seq.data(), qual.data(), seq.size(), win.data(), win.size(), ujobs.data(), n, ures.data(),
 		                         dedits.data(), cap, &ne)) fail("bt2gpu_ungapped_batch");
+		note(C_US_ABI_UNGAPPED, nowUs() - t_ungapped);
 		for(size_t j = 0; j < n; j++) {
 			UngapCall& c = *b.ungaps[j];
 			c.res = ures[j];
@@ -465,8 +517,11 @@ void Lane::execute(Batch& b) {
 			dres.resize(n); dalns.resize(n * (size_t)k.max_aln);
 			for(int attempt = 0; ; attempt++) {
 				dcands.resize(ccap); dedits.resize(ecap);
-				if(bt2gpu_dp_align_batch(ctx, seq.data(), qual.data(), seq.size(), win.data(), win.size(), djobs.data(), n, k.max_aln,
-				                         dres.data(), dcands.data(), ccap, dalns.data(), dedits.data(), ecap) == 0) break;
+				const uint64_t t_align = nowUs();
+				const int rc = bt2gpu_dp_align_batch(ctx, seq.data(), qual.data(), seq.size(), win.data(), win.size(), djobs.data(), n, k.max_aln,
+				                                     dres.data(), dcands.data(), ccap, dalns.data(), dedits.data(), ecap);
+				note(C_US_ABI_ALIGN, nowUs() - t_align);
+				if(rc == 0) break;
 				const char *e = bt2gpu_last_error();
 				if(attempt < 6 && strstr(e, "edit pool overflow")) { ecap *= 4; continue; }
 				fail("bt2gpu_dp_align_batch");

@@ -22,7 +22,11 @@ struct Read;
 namespace bt2shim {
 
 enum Counter { C_ALIGN = 0, C_ALN, C_UNGAPPED, C_SWEEP, C_ONEMM, C_SEEDS, C_EXTEND, C_LOCATE, C_FRAME, C_OTHERMATE, C_MATERECT, C_PECLASS, C_JOINED,
-               C_BATCHES, C_BATCH_JOBS, C_H2D, C_D2H, C_NCOUNTERS };
+               C_BATCHES, C_BATCH_JOBS, C_H2D, C_D2H,
+               // batched binding only, microseconds summed over threads: host threads running workers (wall, CPU) / waiting;
+               // lanes executing batches (wall, CPU); and of that, inside the ABI calls of each kind
+               C_US_WORKERS, C_US_WORKERS_CPU, C_US_WAIT, C_US_LANES, C_US_LANES_CPU, C_US_ABI_STAGE, C_US_ABI_SWEEP, C_US_ABI_ONEMM, C_US_ABI_SEEDS, C_US_ABI_EXTEND,
+               C_US_ABI_LOCATE, C_US_ABI_UNGAPPED, C_US_ABI_ALIGN, C_NCOUNTERS };
 
 // SwAligner::initRef + align + the nextAlignment loop of one window (bt2gpu_dp_align_batch)
 struct DpCall {
@@ -81,7 +85,7 @@ bt2gpu_ctx   *ctx();                         // the calling thread's context (cr
 bt2gpu_index *index(const Ebwt& e, int dev = -1);   // uploaded once per process and device (-1: BT2GPU_DEVICE), shared read-only by its contexts
 void          toScoring(const Scoring& sc, bt2gpu_scoring& out);
 void          fail(const char *what);        // prints bt2gpu_last_error() and throws 1 (bt2_search.cpp:5604-5611)
-void          note(Counter c, uint64_t n);   // with BT2GPU_SHIM_STATS=<file>: totals rewritten in place
+void          note(Counter c, uint64_t n);   // with BT2GPU_SHIM_STATS=<file>: totals rewritten in place (by a writer thread, every 20 ms while they change)
 void          noteLaunches(bt2gpu_ctx *c, uint64_t& seen);
 
 } // namespace bt2shim

@@ -5,6 +5,8 @@
 #include <cstring>
 #include <atomic>
 #include <mutex>
+#include <thread>
+#include <time.h>
 #include <map>
 #include <tuple>
 #include <fcntl.h>
@@ -22,6 +24,7 @@ std::mutex g_ixmu;
 typedef std::tuple<const Ebwt*, const uint8_t*, uint32_t, uint32_t, int> IxKey;
 std::map<IxKey, bt2gpu_index*> g_ix;
 std::atomic<uint64_t> g_cnt[C_NCOUNTERS], g_launches(0);
+std::atomic<bool> g_dirty(false);
 
 } // namespace
 
@@ -65,22 +68,41 @@ bt2gpu_index *index(const Ebwt& e, int dev) {
 void noteLaunches(bt2gpu_ctx *c, uint64_t& seen) {
 	if(c == NULL) return;
 	const uint64_t l = bt2gpu_ctx_launches(c);
-	g_launches += l - seen; seen = l;
+	if(l != seen) { g_launches += l - seen; seen = l; g_dirty.store(true, std::memory_order_relaxed); }
 }
 
+namespace {
+const char *g_names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapped_calls_on_gpu", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
+                                     "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu", "other_mate_on_gpu", "mate_rect_on_gpu", "pe_classify_on_gpu",
+                                     "joined_to_text_off_on_gpu", "abi_batches", "abi_batch_jobs", "h2d_bytes", "d2h_bytes",
+                                     "us_workers", "us_workers_cpu", "us_wait", "us_lanes", "us_lanes_cpu", "us_abi_stage", "us_abi_sweep", "us_abi_onemm", "us_abi_seeds", "us_abi_extend",
+                                     "us_abi_locate", "us_abi_ungapped", "us_abi_align" };
+// The totals are rewritten in place by this thread, not by the callers: note() is on the per-alignment path of every
+// worker (a formatted pwrite there cost more than the alignment, and serialised the host threads on the file's lock).
+void statsWriter(int fd) {
+	for(;;) {
+		timespec ts = {0, 20 * 1000000L};
+		nanosleep(&ts, NULL);
+		if(!g_dirty.exchange(false)) continue;
+		char buf[4096]; int n2 = 0;
+		for(int i = 0; i < C_NCOUNTERS; i++)
+			n2 += snprintf(buf + n2, sizeof buf - n2, "%s %12llu ", g_names[i], (unsigned long long)g_cnt[i].load());
+		n2 += snprintf(buf + n2, sizeof buf - n2, "kernel_launches %12llu\n", (unsigned long long)g_launches.load());
+		if(pwrite(fd, buf, (size_t)n2, 0) < 0) { /* evidence only */ }
+	}
+}
+int statsStart() {
+	const char *path = getenv("BT2GPU_SHIM_STATS");
+	const int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
+	if(fd >= 0) std::thread(statsWriter, fd).detach();
+	return fd;
+}
+} // namespace
+
 void note(Counter c, uint64_t n) {
-	static const char *path = getenv("BT2GPU_SHIM_STATS");
-	static int fd = path ? open(path, O_CREAT | O_WRONLY | O_TRUNC, 0644) : -1;
-	g_cnt[c] += n;
-	if(fd < 0) return;
-	static const char *names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapped_calls_on_gpu", "sweep_calls_on_gpu", "onemm_calls_on_gpu",
-	                                          "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu", "other_mate_on_gpu", "mate_rect_on_gpu", "pe_classify_on_gpu",
-	                                          "joined_to_text_off_on_gpu", "abi_batches", "abi_batch_jobs", "h2d_bytes", "d2h_bytes" };
-	char buf[1536]; int n2 = 0;
-	for(int i = 0; i < C_NCOUNTERS; i++)
-		n2 += snprintf(buf + n2, sizeof buf - n2, "%s %12llu ", names[i], (unsigned long long)g_cnt[i].load());
-	n2 += snprintf(buf + n2, sizeof buf - n2, "kernel_launches %12llu\n", (unsigned long long)g_launches.load());
-	if(pwrite(fd, buf, (size_t)n2, 0) < 0) { /* evidence only */ }
+	static const int fd = statsStart();
+	g_cnt[c].fetch_add(n, std::memory_order_relaxed);
+	if(fd >= 0 && !g_dirty.load(std::memory_order_relaxed)) g_dirty.store(true, std::memory_order_relaxed);
 }
 
 } // namespace bt2shim
