@@ -59,6 +59,24 @@ extern "C" int bt2gpu_device_blocking_sync(int device, int on) {
 	return 0;
 }
 
+extern "C" int bt2gpu_device_sync_mode(int device, int mode) {
+	int n = 0;
+	BT2_CUDA(cudaGetDeviceCount(&n));
+	if(n <= 0) BT2_FAIL("no CUDA device: libbt2gpu has no CPU fallback");
+	if(device < 0 || device >= n) BT2_FAIL("bad device ordinal");
+	unsigned int f = 0;
+	switch(mode) {
+		case BT2GPU_SYNC_AUTO:  f = cudaDeviceScheduleAuto; break;
+		case BT2GPU_SYNC_SPIN:  f = cudaDeviceScheduleSpin; break;
+		case BT2GPU_SYNC_YIELD: f = cudaDeviceScheduleYield; break;
+		case BT2GPU_SYNC_BLOCK: f = cudaDeviceScheduleBlockingSync; break;
+		default: BT2_FAIL("bad sync mode");
+	}
+	BT2_CUDA(cudaSetDevice(device));
+	BT2_CUDA(cudaSetDeviceFlags(f));
+	return 0;
+}
+
 extern "C" int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
 	if(!out) BT2_FAIL("null argument");
 	*out = nullptr;

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <mutex>
@@ -59,6 +60,7 @@ int device();
 namespace {
 
 struct Worker;
+struct Lane;
 struct Fiber {
 	enum State { RUNNABLE, WAIT_BATCH, WAIT_INPUT, DONE };
 	void *sp = NULL;
@@ -66,8 +68,10 @@ struct Fiber {
 	void (*fn)(void*) = NULL; void *arg = NULL;
 	State state = RUNNABLE;
 	Worker *w = NULL;
-	const char *error = NULL;        // set when the batch that carried this worker's problem failed
+	bool queued = false;             // on its host thread's run queue
 };
+
+enum Kind { K_DP = 0, K_UNGAP, K_SWEEP, K_ONEMM, K_SEEDS, K_EXTEND, K_LOCATE, K_NKINDS };
 
 // Problems waiting to travel, by kind, and the workers that wait for them.
 struct Batch {
@@ -79,23 +83,26 @@ struct Batch {
 	std::vector<ExtendCall*> extends;
 	std::vector<LocateCall*> locates;
 	std::vector<Fiber*> waiters;
-	std::string error;
 	bool empty() const { return waiters.empty(); }
-	void clear() { dps.clear(); ungaps.clear(); sweeps.clear(); onemms.clear(); seeds.clear(); extends.clear(); locates.clear(); waiters.clear(); error.clear(); }
+	void clear() { dps.clear(); ungaps.clear(); sweeps.clear(); onemms.clear(); seeds.clear(); extends.clear(); locates.clear(); waiters.clear(); }
+	template<typename T> static void cat(std::vector<T>& d, std::vector<T>& s) { d.insert(d.end(), s.begin(), s.end()); s.clear(); }
 };
 
-// A submission lane: one bt2gpu_ctx (stream + arenas) and the helper thread that blocks in the ABI calls.
+// A submission lane: one bt2gpu_ctx (stream + arenas) of one device and the thread that blocks in its ABI calls.  A
+// lane serves a fixed set of problem kinds for ALL host threads that drive its device: whatever they have queued when
+// the lane is free travels in one bt2gpu_*_batch call per kind, so the batch grows with the load (thousands of problems
+// per call when the GPU is the slower side, a handful when the workers are), and the kinds run side by side on their
+// own streams.
 struct Lane {
-	Worker *w = NULL;
-	int dev = 0;                     // the device this lane's context lives on
+	int dev = 0, id = 0;
 	bt2gpu_ctx *ctx = NULL;
 	uint64_t launches = 0;
 	bt2gpu_scoring sc; bool haveSc = false;
 	std::thread th;
 	std::mutex mu; std::condition_variable cv;
-	Batch *job = NULL;               // handed over by the scheduler
-	bool busy = false;               // scheduler's view
-	std::atomic<bool> done{false};
+	Batch inbox;                     // filled by the host threads (under mu)
+	std::atomic<int> load{0};        // problems queued or being executed: the host threads pick the lighter lane of a kind
+	Batch work;                      // the lane's own
 	// host staging, reused
 	std::vector<uint8_t> seq, qual, win;
 	std::vector<bt2gpu_read> reads;
@@ -111,31 +118,44 @@ struct Lane {
 	void execute(Batch& b);
 };
 
+// The lanes of one device.
+struct Hub {
+	int dev = 0;
+	std::vector<Lane*> lanes;
+	std::vector<Lane*> of[K_NKINDS];   // the lanes that serve a kind
+};
+
 struct Worker {
 	int id = 0;
+	Hub *hub = NULL;
 	std::thread th;
 	std::mutex inboxMu; std::vector<Fiber*> inbox; std::atomic<int> inboxN{0};
 	std::vector<Fiber*> fibers;
-	std::vector<Lane*> lanes;
-	std::vector<Batch*> freeBatches;
-	Batch *pending = NULL;
+	std::vector<Fiber*> runq, nextq;
+	Batch pending;                   // queued by this thread's workers since the last hand-over
+	std::vector<Fiber*> pw[K_NKINDS];// ... and who waits for each kind
+	size_t npending = 0;
 	void *schedSp = NULL;
 	Fiber *cur = NULL;
-	std::mutex mu; std::condition_variable cv;     // lane completions
+	std::mutex mu; std::condition_variable cv;     // answered workers, handed back by the lanes
+	std::vector<Fiber*> ready; std::atomic<int> readyN{0};
 	bool inputOk = true;             // the last look for input found some
 	bool inputMiss = false;          // a worker looked and found nothing in this pass
 	void loop();
 	void runFiber(Fiber *f);
+	void publish();
 };
 
 thread_local Worker *tl_worker = NULL;
 std::mutex g_mu;
 std::vector<Worker*> g_workers;
+std::vector<Hub*> g_hubs;
 size_t g_next = 0;
 std::atomic<bool> g_spawned{false};
 int g_nthreads = 0, g_nlanes = 2;
 std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
+size_t g_publishAt = 32;           // BT2GPU_PUBLISH: a host thread hands its queued problems over at the latest after this many
 
 // glibc's allocator, as the reference uses it, gives memory back to the kernel whenever the top of a thread's arena
 // is free (madvise / mprotect) and asks for it again page by page -- with thousands of workers' buffers per host thread,
@@ -228,112 +248,128 @@ void nameThread(const char *kind, int a, int b) {      // readable in top -H / a
 	pthread_setname_np(pthread_self(), nm);
 }
 
+// hands what this thread's workers have queued to the lanes of their kinds (the lighter one where a kind has several)
+void Worker::publish() {
+	if(npending == 0) return;
+	auto to = [&](Kind k, auto Batch::*list) {
+		std::vector<Fiber*>& who = pw[k];
+		if(who.empty()) return;
+		const std::vector<Lane*>& ls = hub->of[k];
+		Lane *l = ls[0];
+		for(size_t i = 1; i < ls.size(); i++) if(ls[i]->load.load(std::memory_order_relaxed) < l->load.load(std::memory_order_relaxed)) l = ls[i];
+		l->load.fetch_add((int)who.size(), std::memory_order_relaxed);
+		bool wasEmpty;
+		{
+			std::lock_guard<std::mutex> lk(l->mu);
+			wasEmpty = l->inbox.empty();
+			Batch::cat(l->inbox.*list, pending.*list);
+			Batch::cat(l->inbox.waiters, who);
+		}
+		if(wasEmpty) l->cv.notify_one();
+	};
+	to(K_SWEEP, &Batch::sweeps); to(K_ONEMM, &Batch::onemms); to(K_SEEDS, &Batch::seeds); to(K_EXTEND, &Batch::extends);
+	to(K_LOCATE, &Batch::locates); to(K_UNGAP, &Batch::ungaps); to(K_DP, &Batch::dps);
+	npending = 0;
+}
+
 void Worker::loop() {
 	tl_worker = this;
 	nameThread("host", id, -1);
-	pending = new Batch();
-	for(int i = 0; i < g_nlanes + 1; i++) freeBatches.push_back(new Batch());
-	for(int i = 0; i < g_nlanes; i++) {
-		Lane *l = new Lane();
-		l->w = this;
-		l->dev = g_devices[(size_t)id % g_devices.size()];
-		lanes.push_back(l);
-		l->th = std::thread([l, i] { nameThread("lane", l->w->id, i); l->run(); });
-		l->th.detach();
-	}
 	for(;;) {
 		if(inboxN.load(std::memory_order_acquire) > 0) {
 			std::lock_guard<std::mutex> lk(inboxMu);
-			for(Fiber *f : inbox) { prepare(f); fibers.push_back(f); }
+			for(Fiber *f : inbox) { prepare(f); fibers.push_back(f); f->queued = true; runq.push_back(f); }
 			inbox.clear(); inboxN.store(0);
 		}
-		bool progress = false, busy = false;
-		// 1. answered batches: their workers may go on
-		for(Lane *l : lanes) {
-			if(!l->busy) continue;
-			if(!l->done.load(std::memory_order_acquire)) { busy = true; continue; }
-			Batch *b = l->job;
-			const char *err = b->error.empty() ? NULL : strdup(b->error.c_str());
-			for(Fiber *f : b->waiters) { f->state = Fiber::RUNNABLE; f->error = err; }
-			b->clear();
-			freeBatches.push_back(b);
-			{ std::lock_guard<std::mutex> lk(l->mu); l->job = NULL; }    // `job` and `done` only change under the lane's lock
-			l->busy = false;
-			progress = true;
+		// 1. answered workers may go on
+		if(readyN.load(std::memory_order_acquire) > 0) {
+			std::lock_guard<std::mutex> lk(mu);
+			for(Fiber *f : ready) { f->state = Fiber::RUNNABLE; f->queued = true; runq.push_back(f); }
+			ready.clear(); readyN.store(0, std::memory_order_relaxed);
 		}
-		// 2. every runnable worker runs until its next hot-path call; of the workers that wait for input only one looks
-		//    while the last look found nothing
-		int looks = inputOk ? (int)fibers.size() : 1;
-		inputMiss = false;
-		const uint64_t tRun = nowUs(), cRun = cpuUs();
-		for(size_t i = 0; i < fibers.size(); i++) {
-			Fiber *f = fibers[i];
-			if(f->state == Fiber::WAIT_INPUT) {
-				if(looks <= 0) continue;
-				looks--;
-			} else if(f->state != Fiber::RUNNABLE) continue;
-			runFiber(f);
-			if(f->state != Fiber::WAIT_INPUT) progress = true;
-			if(inputMiss && looks > 1) looks = 1;
-		}
-		inputOk = !inputMiss;
-		if(progress) { note(C_US_WORKERS, nowUs() - tRun); note(C_US_WORKERS_CPU, cpuUs() - cRun); }
-		// 3. what they queued travels on a free lane
-		if(!pending->empty()) {
-			Lane *fl = NULL;
-			for(Lane *l : lanes) if(!l->busy) { fl = l; break; }
-			if(fl != NULL) {
-				Batch *b = pending;
-				pending = freeBatches.back(); freeBatches.pop_back();
-				fl->busy = true;
-				{ std::lock_guard<std::mutex> lk(fl->mu); fl->done.store(false, std::memory_order_relaxed); fl->job = b; }
-				fl->cv.notify_one();
-				progress = true; busy = true;
+		// of the workers that wait for input only one looks while the last look found nothing
+		{
+			int looks = inputOk ? (int)fibers.size() : 1;
+			for(size_t i = 0; i < fibers.size() && looks > 0; i++) {
+				Fiber *f = fibers[i];
+				if(f->state == Fiber::WAIT_INPUT && !f->queued) { f->queued = true; runq.push_back(f); looks--; }
 			}
 		}
-		// 4. nothing to do: wait for a lane, or for input
-		if(!progress) {
+		// 2. every runnable worker runs until its next hot-path call
+		bool progress = false;
+		inputMiss = false;
+		const uint64_t tRun = nowUs(), cRun = cpuUs();
+		for(size_t i = 0; i < runq.size(); i++) {
+			Fiber *f = runq[i];
+			f->queued = false;
+			if(f->state == Fiber::WAIT_INPUT && inputMiss) continue;     // an earlier look of this pass found nothing
+			runFiber(f);
+			if(f->state != Fiber::WAIT_INPUT) progress = true;
+			if(f->state == Fiber::RUNNABLE) { f->queued = true; nextq.push_back(f); }    // yieldNow()
+			// 3. what they queue travels while the rest of the pass runs
+			if(npending >= g_publishAt) publish();
+		}
+		runq.clear(); runq.swap(nextq);
+		inputOk = !inputMiss;
+		publish();
+		if(progress) { note(C_US_WORKERS, nowUs() - tRun); note(C_US_WORKERS_CPU, cpuUs() - cRun); }
+		// 4. nothing to do: wait for an answer, or for input
+		if(!progress && runq.empty()) {
 			Timed tw(C_US_WAIT);
-			if(busy) {
-				std::unique_lock<std::mutex> lk(mu);
-				bool any = false;
-				for(Lane *l : lanes) if(l->busy && l->done.load(std::memory_order_acquire)) any = true;
-				if(!any) cv.wait_for(lk, std::chrono::microseconds(500));
-			} else napMicros(fibers.empty() ? 2000 : 300);
+			std::unique_lock<std::mutex> lk(mu);
+			if(ready.empty()) cv.wait_for(lk, std::chrono::microseconds(fibers.empty() ? 2000 : 300));
 		}
 	}
 }
 
-// ---- lane: executes one batch -------------------------------------------------------------------------------------
+// ---- lane: executes what the host threads have queued for its kinds ----------------------------------------------------
 void Lane::run() {
+	nameThread("lane", dev, id);
+	std::vector<std::pair<Worker*, Fiber*> > back;
 	for(;;) {
-		Batch *b = NULL;
 		{
 			std::unique_lock<std::mutex> lk(mu);
-			cv.wait(lk, [this] { return job != NULL && !done.load(); });
-			b = job;
+			cv.wait(lk, [this] { return !inbox.empty(); });
+			std::swap(inbox, work);
 		}
+		const int n = (int)work.waiters.size();
 		try {
-			// the helper threads of all lanes wait in the ABI calls: they must sleep there, not spin
+			// The lane threads wait in the ABI calls.  They are few (one per kind), their calls are short and every
+			// worker waits for them: they poll and give the core away between polls (a blocked waiter wakes 0.15-0.2 ms
+			// late, several times per call).  BT2GPU_SYNC=block|spin|auto for other machines.
 			static std::once_flag once;
 			std::call_once(once, [] {
-				if(getenv("BT2GPU_SPIN") != NULL) return;
-				for(int d : g_devices) if(bt2gpu_device_blocking_sync(d, 1)) fail("bt2gpu_device_blocking_sync");
+				const char *m = getenv("BT2GPU_SYNC");
+				int mode = BT2GPU_SYNC_YIELD;
+				if(m != NULL) mode = !strcmp(m, "block") ? BT2GPU_SYNC_BLOCK : !strcmp(m, "spin") ? BT2GPU_SYNC_SPIN : !strcmp(m, "auto") ? BT2GPU_SYNC_AUTO : BT2GPU_SYNC_YIELD;
+				for(int d : g_devices) if(bt2gpu_device_sync_mode(d, mode)) fail("bt2gpu_device_sync_mode");
 			});
 			if(ctx == NULL && bt2gpu_ctx_create(dev, &ctx)) fail("bt2gpu_ctx_create");
 			Timed tl(C_US_LANES);
 			const uint64_t c0 = cpuUs();
-			execute(*b);
+			execute(work);
 			note(C_US_LANES_CPU, cpuUs() - c0);
 		} catch(int) {
 			die("batched ABI call failed", "the server has no CPU path and stops");
 		}
 		noteLaunches(ctx, launches);
-		{
-			std::lock_guard<std::mutex> lk(w->mu);
-			done.store(true, std::memory_order_release);
+		// the answers are in the callers' own call structs: hand the workers back to their host threads
+		back.clear();
+		for(Fiber *f : work.waiters) back.push_back(std::make_pair(f->w, f));
+		std::sort(back.begin(), back.end());
+		for(size_t i = 0; i < back.size(); ) {
+			Worker *w = back[i].first;
+			size_t j = i;
+			{
+				std::lock_guard<std::mutex> lk(w->mu);
+				for(; j < back.size() && back[j].first == w; j++) w->ready.push_back(back[j].second);
+				w->readyN.store((int)w->ready.size(), std::memory_order_release);
+			}
+			w->cv.notify_one();
+			i = j;
 		}
-		w->cv.notify_one();
+		work.clear();
+		load.fetch_sub(n, std::memory_order_relaxed);
 	}
 }
 
@@ -549,27 +585,26 @@ void Lane::execute(Batch& b) {
 }
 
 // ---- the binding: queue, suspend, resume with the answer ---------------------------------------------------------------
-template<typename T> void travel(std::vector<T*> Batch::*list, T& c) {
+template<typename T> void travel(Kind k, std::vector<T*> Batch::*list, T& c) {
 	Worker *w = tl_worker;
 	if(w == NULL || w->cur == NULL) { fprintf(stderr, "bt2gpu shim: hot-path call outside a worker (batched binding)\n"); throw 1; }
-	Fiber *f = w->cur;
-	(w->pending->*list).push_back(&c);
-	w->pending->waiters.push_back(f);
+	(w->pending.*list).push_back(&c);
+	w->pw[k].push_back(w->cur);
+	w->npending++;
 	yieldTo(Fiber::WAIT_BATCH);
-	if(f->error != NULL) { fprintf(stderr, "bt2gpu shim: %s\n", f->error); throw 1; }
 }
 
 } // namespace
 
 bt2gpu_ctx *ctx() { fprintf(stderr, "bt2gpu shim: per-thread context requested in the batched binding\n"); throw 1; }
 
-void dpAlign(DpCall& c)   { travel(&Batch::dps, c); }
-void ungapped(UngapCall& c) { travel(&Batch::ungaps, c); }
-void sweep(SweepCall& c)  { travel(&Batch::sweeps, c); }
-void oneMm(OneMmCall& c)  { travel(&Batch::onemms, c); }
-void seeds(SeedsCall& c)  { c.out.clear(); if(c.jobs.empty()) return; travel(&Batch::seeds, c); }
-void extend(ExtendCall& c) { travel(&Batch::extends, c); }
-void locate(LocateCall& c) { travel(&Batch::locates, c); }
+void dpAlign(DpCall& c)   { travel(K_DP, &Batch::dps, c); }
+void ungapped(UngapCall& c) { travel(K_UNGAP, &Batch::ungaps, c); }
+void sweep(SweepCall& c)  { travel(K_SWEEP, &Batch::sweeps, c); }
+void oneMm(OneMmCall& c)  { travel(K_ONEMM, &Batch::onemms, c); }
+void seeds(SeedsCall& c)  { c.out.clear(); if(c.jobs.empty()) return; travel(K_SEEDS, &Batch::seeds, c); }
+void extend(ExtendCall& c) { travel(K_EXTEND, &Batch::extends, c); }
+void locate(LocateCall& c) { travel(K_LOCATE, &Batch::locates, c); }
 
 // ---- fiber.h ------------------------------------------------------------------------------------------------------
 bool inWorker() { return tl_worker != NULL && tl_worker->cur != NULL; }
@@ -611,11 +646,30 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 			}
 		}
 		if(g_devices.empty()) g_devices.push_back(device());
+		g_publishAt = (size_t)envInt("BT2GPU_PUBLISH", 32, 1, 1 << 20);
+		// per device: BT2GPU_FM_LANES x { exactSweep + oneMmSearch + ungapped | seeds + extend | locate } and
+		// BT2GPU_LANES x { DP windows }
+		const int fmLanes = envInt("BT2GPU_FM_LANES", 1, 1, 8);
+		for(int d : g_devices) {
+			Hub *h = new Hub();
+			h->dev = d;
+			auto add = [&](std::initializer_list<Kind> kinds) {
+				Lane *l = new Lane();
+				l->dev = d; l->id = (int)h->lanes.size();
+				h->lanes.push_back(l);
+				for(Kind k : kinds) h->of[k].push_back(l);
+			};
+			for(int i = 0; i < fmLanes; i++) { add({K_SWEEP, K_ONEMM, K_UNGAP}); add({K_SEEDS, K_EXTEND}); add({K_LOCATE}); }
+			for(int i = 0; i < g_nlanes; i++) add({K_DP});
+			for(Lane *l : h->lanes) { l->th = std::thread([l] { l->run(); }); l->th.detach(); }
+			g_hubs.push_back(h);
+		}
 	}
 	Worker *w = NULL;
 	if((int)g_workers.size() < g_nthreads) {
 		w = new Worker();
 		w->id = (int)g_workers.size();
+		w->hub = g_hubs[(size_t)w->id % g_hubs.size()];
 		g_workers.push_back(w);
 		w->th = std::thread([w] { w->loop(); });
 		w->th.detach();

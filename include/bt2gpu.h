@@ -43,6 +43,15 @@ int         bt2gpu_device_count(int *n);
 /* Host threads waiting for this device sleep (cudaDeviceScheduleBlockingSync) instead of spinning: for callers that
  * drive more contexts than they have cores to burn (the batched server binding: one helper thread per lane). */
 int         bt2gpu_device_blocking_sync(int device, int on);
+/* How host threads wait for this device (no counterpart in the reference: its hot path never waits for anything):
+ * BT2GPU_SYNC_AUTO the driver's choice, BT2GPU_SYNC_SPIN poll, BT2GPU_SYNC_YIELD poll and give the core away between
+ * polls (a few threads that wait for short calls next to busy worker threads: the batched server's lanes; a blocked
+ * waiter costs 0.15-0.2 ms per wake-up, measured: profiles/r2_abi_latency.md), BT2GPU_SYNC_BLOCK sleep. */
+#define BT2GPU_SYNC_AUTO  0
+#define BT2GPU_SYNC_SPIN  1
+#define BT2GPU_SYNC_YIELD 2
+#define BT2GPU_SYNC_BLOCK 3
+int         bt2gpu_device_sync_mode(int device, int mode);
 int         bt2gpu_ctx_create(int device, bt2gpu_ctx **ctx);
 void        bt2gpu_ctx_destroy(bt2gpu_ctx *ctx);
 /* Block until everything enqueued on the context's stream has finished. */

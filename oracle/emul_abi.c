@@ -46,6 +46,7 @@ static int fail(const char *m) { g_err = m; return 1; }
 int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
 const char *bt2gpu_last_error(void) { return g_err; }
 int bt2gpu_device_blocking_sync(int device, int on) { (void)device; (void)on; return 0; }
+int bt2gpu_device_sync_mode(int device, int mode) { (void)device; (void)mode; return 0; }
 int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
 	(void)device;
 	if(getenv("BT2GPU_EMUL_NO_DEVICE")) return fail("no CUDA device (emulated)");

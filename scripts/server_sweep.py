@@ -39,7 +39,9 @@ def main():
     done_stock = set()
     with tempfile.TemporaryDirectory() as td:
         for pt in a.points.split(","):
-            th, wpt, lanes, ncl = (int(x) for x in pt.split(":"))
+            f = pt.split(":")                      # th:wpt:lanes:clients[:KEY=VALUE[:KEY=VALUE...]] (extra environment of the server)
+            th, wpt, lanes, ncl = (int(x) for x in f[:4])
+            extra = dict(x.split("=", 1) for x in f[4:])
             shards = bench.write_shards(td, "c%d" % ncl, reads, quals, ncl)
             if a.stock and ncl not in done_stock:
                 done_stock.add(ncl)
@@ -47,14 +49,15 @@ def main():
                 print(json.dumps({"server": "stock", "threads": cores, "clients": ncl, "reads_per_s": len(reads) * a.passes / t,
                                   "start_s": st, "rss_mb": rss}), flush=True)
             env = {"BT2GPU_THREADS": str(th), "BT2GPU_LANES": str(lanes)}
+            env.update(extra)
             try:
-                t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_%s" % pt.replace(":", "_"), 1, a.passes,
+                t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_%s" % pt.replace(":", "_").replace("=", "-"), 1, a.passes,
                                                         pass_timeout=a.pass_timeout)
             except Exception as e:      # a point that hangs or fails must not take the rest of the sweep (and the GPU lease) with it
                 print(json.dumps({"server": "gpub", "point": pt, "failed": str(e).splitlines()[0][:200]}), flush=True)
                 continue
             jobs = (cnt or {}).get("abi_batch_jobs", 0) / max((cnt or {}).get("abi_batches", 1), 1)
-            print(json.dumps({"server": "gpub", "host_threads": th, "workers": th * wpt, "lanes": lanes, "clients": ncl,
+            print(json.dumps({"server": "gpub", "host_threads": th, "workers": th * wpt, "lanes": lanes, "clients": ncl, "env": extra,
                               "reads_per_s": len(reads) * a.passes / t, "start_s": st, "rss_mb": rss, "jobs_per_abi_call": jobs,
                               "counters": cnt}), flush=True)
 
