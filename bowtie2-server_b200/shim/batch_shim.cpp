@@ -167,7 +167,7 @@ struct MallocTuning {
 		const char *v = getenv("BT2GPU_MALLOC_TUNING");
 		if(v != NULL && atoi(v) == 0) return;
 		mallopt(M_TRIM_THRESHOLD, 1 << 30);
-		mallopt(M_TOP_PAD, 16 << 20);
+		mallopt(M_TOP_PAD, 64 << 20);      // a thread arena's heap (64 MB) is made accessible at once, not page by page (one mprotect, under the process's mmap lock, per page otherwise)
 		mallopt(M_MMAP_THRESHOLD, 32 << 20);
 	}
 } g_mallocTuning;

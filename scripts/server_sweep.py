@@ -4,6 +4,7 @@ host threads x worker fibers per thread x lanes x clients -> reads/s, one JSON l
 import argparse
 import json
 import os
+import re
 import sys
 import tempfile
 
@@ -51,7 +52,7 @@ def main():
             env = {"BT2GPU_THREADS": str(th), "BT2GPU_LANES": str(lanes)}
             env.update(extra)
             try:
-                t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_%s" % pt.replace(":", "_").replace("=", "-"), 1, a.passes,
+                t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_" + re.sub(r"[^A-Za-z0-9]+", "_", pt), 1, a.passes,
                                                         pass_timeout=a.pass_timeout)
             except Exception as e:      # a point that hangs or fails must not take the rest of the sweep (and the GPU lease) with it
                 print(json.dumps({"server": "gpub", "point": pt, "failed": str(e).splitlines()[0][:200]}), flush=True)
