@@ -190,6 +190,14 @@ def progress(msg):
     sys.stderr.flush()
 
 
+def default_clients(nreads):
+    """Client processes per server: enough that no client sends more than 16384 read pairs (or reads) per pass -- the
+    reference client keeps at most 20000 in flight (pat.h:2464-2550) and its flow control can stall beyond that, with the
+    stock server too -- and at least 2, at most 16."""
+    units = nreads // 2 if PAIRED else nreads
+    return max(2, min(16, -(-units // 16384)))
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -200,28 +208,38 @@ def host_cores():
 # ---------------------------------------------------------------------------------------------
 # server runs (both arms)
 # ---------------------------------------------------------------------------------------------
-def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, keep_sam=False, pass_timeout=600):
+def server_steps(binary, base, workers, env, shards, td, tag, warmup, steps, keep_sam=False, pass_timeout=600, retries=1):
     """Start one server, run warmup + steps passes of the shard set through it.  Returns (seconds of the timed steps,
-    server start seconds, RSS MB, sam paths of the last step, shim counters or None)."""
+    server start seconds, RSS MB, sam paths of the last step, shim counters or None).
+    A pass that does not end within pass_timeout abandons that server (its clients are killed) and the whole series is
+    run again on a fresh one, `retries` times: the reference's client / server pair can stall on its own flow control
+    (PatternSourceWebClient's window of 20000 pairs against results the server has not flushed yet), the stock server
+    included, and one stalled pass must not cost the run its JSON line."""
     from bt2gpu import serverbench as SB
     stats = os.path.join(td, tag + "_shim_stats.txt")
     e = dict(env or {})
     if binary == SB.GPUB_SERVER:
         e["BT2GPU_SHIM_STATS"] = stats
-    srv = SB.Server(binary, base, workers, SERVER_ARGS, env=e, log=os.path.join(td, tag + "_server.err"), start_timeout=300)
-    progress("%s: server up in %.1f s (-p %d)" % (tag, srv.start_s, workers))
-    try:
-        for w in range(warmup):
-            dt, _ = srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)), timeout=pass_timeout)
-            progress("%s: warm-up pass %d %.1f s" % (tag, w, dt))
-        t, sams = 0.0, []
-        for s in range(steps):
-            dt, sams = srv.align(shards, os.path.join(td, "%s_s%d" % (tag, s)), timeout=pass_timeout)
-            progress("%s: timed pass %d %.1f s" % (tag, s, dt))
-            t += dt
-        rss = srv.rss_mb()
-    finally:
-        srv.close()
+    for attempt in range(retries + 1):
+        srv = SB.Server(binary, base, workers, SERVER_ARGS, env=e, log=os.path.join(td, "%s_server%d.err" % (tag, attempt)), start_timeout=300)
+        progress("%s: server up in %.1f s (-p %d)" % (tag, srv.start_s, workers))
+        try:
+            for w in range(warmup):
+                dt, _ = srv.align(shards, os.path.join(td, "%s_w%d" % (tag, w)), timeout=pass_timeout)
+                progress("%s: warm-up pass %d %.1f s" % (tag, w, dt))
+            t, sams = 0.0, []
+            for s in range(steps):
+                dt, sams = srv.align(shards, os.path.join(td, "%s_s%d" % (tag, s)), timeout=pass_timeout)
+                progress("%s: timed pass %d %.1f s" % (tag, s, dt))
+                t += dt
+            rss = srv.rss_mb()
+            break
+        except Exception as ex:
+            progress("%s: attempt %d failed: %s" % (tag, attempt, str(ex).splitlines()[0][:200]))
+            if attempt == retries:
+                raise
+        finally:
+            srv.close()
     cnt = None
     if os.path.exists(stats):
         import re
@@ -238,7 +256,7 @@ def stock_server_steps(base, ncores, shards, td, tag, warmup, steps):
         if not os.path.exists(binary):
             continue
         try:
-            t, start_s, rss, sams, _ = server_steps(binary, base, ncores, None, shards, td, "%s_%s" % (tag, name), warmup, steps)
+            t, start_s, rss, sams, _ = server_steps(binary, base, ncores, None, shards, td, "%s_%s" % (tag, name), warmup, steps, pass_timeout=120)
         except Exception as e:      # e.g. a host CPU without AVX2
             sys.stderr.write("bench: stock server build %s failed: %s\n" % (name, str(e).splitlines()[0][:200]))
             continue
@@ -261,7 +279,7 @@ def run_reference(args, rank, world):
     base, seqs, _ = get_index(args)
     n = min(args.batch, args.cpu_sample) if args.cpu_sample else args.batch
     reads, quals = make_reads(args.seed + 7, seqs, n)
-    nclients = args.clients or max(2, min(8, ncores // 4))
+    nclients = args.clients or default_clients(len(reads))
     with tempfile.TemporaryDirectory() as td:
         shards = write_shards(td, "ref", reads, quals, nclients)
         t, start_s, rss, _, build, times = stock_server_steps(base, ncores, shards, td, "ref", args.warmup, args.steps)
@@ -411,8 +429,9 @@ def run_ours(args, rank, world, local_rank):
     ncores = host_cores()
     threads = args.host_threads or max(1, min(16, ncores // world))
     workers = args.workers or threads * args.workers_per_thread
-    nclients = args.clients or max(2, min(8, ncores // (4 * world)))
+    nclients = args.clients or default_clients(n)
     e2e_s, srv_start, rss, shim, sams, parity = None, None, None, None, [], None
+    e2e_error = None
     td_obj = tempfile.TemporaryDirectory()
     td = td_obj.name
     have = SB.have_binaries() and not args.chain_only
@@ -421,8 +440,12 @@ def run_ours(args, rank, world, local_rank):
         progress("FASTQ shards for %d clients written" % nclients)
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
         barrier(False)
-        e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
-                                                          args.warmup, args.steps, pass_timeout=args.pass_timeout)
+        try:
+            e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
+                                                              args.warmup, args.steps, pass_timeout=args.pass_timeout)
+        except Exception as ex:      # reported in the line (e2e null, e2e_error), not a crash without a line
+            e2e_error = str(ex).splitlines()[0][:300]
+            progress("e2e failed: " + e2e_error)
     sampler.stop_flag = True
     sampler.join()
     t = torch.tensor([dev_ms, e2e_s or 0.0], dtype=torch.float64, device="cuda")
@@ -438,7 +461,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- CPU baseline + parity on rank 0 at N=1: the stock server on the same reads (bounded sample) ----
     cpu_line = None
-    if world == 1 and have and not args.no_cpu_baseline:
+    if world == 1 and have and not args.no_cpu_baseline and e2e_error is None:
         m = min(n, args.cpu_sample) if args.cpu_sample else n
         m -= m % 2
         cshards = shards if m == n else write_shards(td, "cpu", reads[:m], quals[:m], nclients)
@@ -542,9 +565,9 @@ def run_ours(args, rank, world, local_rank):
                          % (index_bytes / 1e6, n, 2.0 * n * RDLEN / 1e6),
                    "index_bytes": index_bytes, "counters": cnt,
                    "e2e_path": {"server": "oracle/_ref/bowtie2-align-server-s-gpub", "workers": workers, "host_threads": threads,
-                                "lanes_per_thread": args.lanes, "clients": nclients, "server_args": SERVER_ARGS,
+                                "dp_lanes": args.lanes, "clients": nclients, "server_args": SERVER_ARGS,
                                 "server_start_s": srv_start, "server_rss_mb": rss, "seconds_per_step": (e2e_s / args.steps) if e2e_s else None,
-                                "shim_counters": shim, "host_cores": ncores},
+                                "shim_counters": shim, "host_cores": ncores, "error": e2e_error},
                    "peak_source": "measured" if peaks else "fallback", "traffic_source": traffic_src},
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": per_step(h2d), "d2h_bytes_per_step": per_step(d2h)},
         "gpu_launches": launches,
@@ -555,7 +578,7 @@ def run_ours(args, rank, world, local_rank):
     if cpu_line is not None:
         line["cpu_baseline"] = cpu_line
     elif world == 1:
-        line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: oracle/_ref binaries missing"}
+        line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "unavailable: " + (e2e_error or "oracle/_ref binaries missing, or --no-cpu-baseline / --chain-only")}
     emit(line)
 
 
@@ -595,11 +618,11 @@ def main():
     ap.add_argument("--workers-per-thread", type=int, default=128, help="worker fibers (reads in flight) per host thread of the GPU-bound server")
     ap.add_argument("--workers", type=int, default=0)
     ap.add_argument("--host-threads", type=int, default=0)
-    ap.add_argument("--lanes", type=int, default=2)
+    ap.add_argument("--lanes", type=int, default=1, help="DP lanes per device of the GPU-bound server (BT2GPU_LANES)")
     ap.add_argument("--clients", type=int, default=0)
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads of the batch the CPU server sees (0 = the whole batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--pass-timeout", type=int, default=300, help="seconds one pass of a batch through a server may take")
+    ap.add_argument("--pass-timeout", type=int, default=120, help="seconds one pass of a batch through a server may take")
     ap.add_argument("--chain-only", action="store_true", help="device stage chain only (for ncu: no server processes)")
     ap.add_argument("--seed", type=int, default=20261104)
     args = ap.parse_args()

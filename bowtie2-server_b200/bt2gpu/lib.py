@@ -24,7 +24,7 @@ SYMBOLS = [
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
     "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch", "bt2gpu_frame_mate_rect_batch",
-    "bt2gpu_device_blocking_sync", "bt2gpu_device_sync_mode", "bt2gpu_noalloc_scratch_bytes", "bt2gpu_ungapped_batch_noalloc", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
+    "bt2gpu_device_blocking_sync", "bt2gpu_device_sync_mode", "bt2gpu_ctx_set_wait", "bt2gpu_ctx_set_timing", "bt2gpu_noalloc_scratch_bytes", "bt2gpu_ungapped_batch_noalloc", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
 ]
 
 _lib = None

@@ -59,6 +59,19 @@ extern "C" int bt2gpu_device_blocking_sync(int device, int on) {
 	return 0;
 }
 
+extern "C" int bt2gpu_ctx_set_wait(bt2gpu_ctx *ctx, uint32_t poll_ns) {
+	if(!ctx) BT2_FAIL("null ctx");
+	if(poll_ns > 100000000u) BT2_FAIL("poll interval above 100 ms");
+	ctx->poll_ns = poll_ns;
+	return 0;
+}
+
+extern "C" int bt2gpu_ctx_set_timing(bt2gpu_ctx *ctx, int on) {
+	if(!ctx) BT2_FAIL("null ctx");
+	ctx->timing = on != 0;
+	return 0;
+}
+
 extern "C" int bt2gpu_device_sync_mode(int device, int mode) {
 	int n = 0;
 	BT2_CUDA(cudaGetDeviceCount(&n));

@@ -2,6 +2,7 @@
 // libbt2gpu.so (C ABI in include/bt2gpu.h).  sm_100a only; no CPU fallback anywhere.
 #pragma once
 #include <cuda_runtime.h>
+#include <time.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -83,16 +84,23 @@ struct bt2gpu_ctx {
 	bt2::DpState *dp = nullptr;
 	bt2::FmState *fm = nullptr;
 	bt2::HpState *hp = nullptr;
+	// how the batch entry points wait for the stream: 0 = cudaStreamSynchronize (the device's sync mode); > 0 = poll
+	// cudaStreamQuery and sleep this many nanoseconds between polls (bt2gpu_ctx_set_wait)
+	uint32_t poll_ns = 0;
+	bool timing = true;                   // record the kernel-time events of every entry point (bt2gpu_ctx_set_timing)
+	bool in_batch = false;                // inside a *_batch entry point: its stage step need not wait for its copies
 	// device time of the kernels of the last entry point (events on `stream`)
 	cudaEvent_t kev[2] = {nullptr, nullptr};
 	bool kev_valid = false;
 	int kstart() {
+		if(!timing) { kev_valid = false; return 0; }
 		for(int i = 0; i < 2; i++) if(!kev[i]) BT2_CUDA(cudaEventCreate(&kev[i]));
 		kev_valid = false;
 		BT2_CUDA(cudaEventRecord(kev[0], stream));
 		return 0;
 	}
 	int kend() {
+		if(!timing) return 0;
 		BT2_CUDA(cudaEventRecord(kev[1], stream));
 		kev_valid = true;
 		return 0;
@@ -100,6 +108,19 @@ struct bt2gpu_ctx {
 };
 
 namespace bt2 {
+// Wait until everything enqueued on `s` has finished, the way the context was told to (bt2gpu_ctx_set_wait).
+inline cudaError_t wait_stream(const bt2gpu_ctx *ctx, cudaStream_t s) {
+	if(ctx->poll_ns == 0) return cudaStreamSynchronize(s);
+	for(;;) {
+		cudaError_t e = cudaStreamQuery(s);
+		if(e != cudaErrorNotReady) return e;
+		timespec ts = {0, (long)ctx->poll_ns};
+		nanosleep(&ts, nullptr);
+	}
+}
+// Before a device-to-host copy into pageable memory (which waits for the stream inside the driver, in the device's sync
+// mode): with polling asked for, do the waiting here, so that the copy finds the stream idle.
+inline cudaError_t settle(const bt2gpu_ctx *ctx, cudaStream_t s) { return ctx->poll_ns ? wait_stream(ctx, s) : cudaSuccess; }
 // fm.cu: same kernels as the C-ABI entry points, device pointers in and out, no synchronisation
 int fm_hp_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len,
                       const bt2gpu_read *reads, size_t nreads, FmReadsDev *view, cudaStream_t qual_stream);

@@ -1349,7 +1349,10 @@ extern "C" int bt2gpu_dp_stage(
 	BT2_CUDA(cudaMemcpyAsync(d->jobs.p, jobs, njobs * sizeof(bt2gpu_dp_job), cudaMemcpyHostToDevice, s));
 	BT2_CUDA(cudaMemcpyAsync(d->aux.p, aux.data(), njobs * sizeof(DpAux), cudaMemcpyHostToDevice, s));
 	BT2_CUDA(cudaMemcpyAsync(d->order.p, order.data(), njobs * 4, cudaMemcpyHostToDevice, s));
-	BT2_CUDA(cudaStreamSynchronize(s));   // aux/order are stack-owned host vectors
+	// aux/order are stack-owned host vectors.  Pageable sources have been copied out by the driver when cudaMemcpyAsync
+	// returns; the caller's pools, if pinned, must outlive the copies: inside bt2gpu_dp_align_batch they do (it returns after
+	// its fetch), a separate bt2gpu_dp_stage waits here
+	if(!ctx->in_batch) BT2_CUDA(bt2::wait_stream(ctx, s));
 	return 0;
 }
 
@@ -1365,7 +1368,7 @@ extern "C" int bt2gpu_dp_run(bt2gpu_ctx *ctx, uint32_t phases) {
 	unsigned long long *scal = d->scal.as<unsigned long long>();
 	int *errflag = reinterpret_cast<int*>(scal + 2);
 	const bool local = !ctx->sc.monotone;
-	const bool timed = d->chunks.size() == 1;
+	const bool timed = d->chunks.size() == 1 && ctx->timing;
 	if(timed) {
 		for(int i = 0; i < 4; i++) if(!d->ev[i]) BT2_CUDA(cudaEventCreate(&d->ev[i]));
 		d->ev_phases = phases;
@@ -1450,17 +1453,18 @@ extern "C" int bt2gpu_dp_fetch(
 	if(ncands) *ncands = 0;
 	if(nedits) *nedits = 0;
 	if(d->njobs == 0) return 0;
+	BT2_CUDA(bt2::settle(ctx, s));
 	BT2_CUDA(cudaMemcpyAsync(d->h_scal.p, d->scal.p, 64, cudaMemcpyDeviceToHost, s));
 	if(results) BT2_CUDA(cudaMemcpyAsync(results, d->res.p, d->njobs * sizeof(bt2gpu_dp_result), cudaMemcpyDeviceToHost, s));
 	if(alns) BT2_CUDA(cudaMemcpyAsync(alns, d->alns.p, d->njobs * d->max_aln * sizeof(bt2gpu_dp_aln), cudaMemcpyDeviceToHost, s));
-	BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
 	const unsigned long long *hs = d->h_scal.as<unsigned long long>();
 	const int err = *reinterpret_cast<const int*>(hs + 2);
 	if(err == 1) BT2_FAIL("candidate pool overflow (raise cand_cap)");
 	if(err == 2) BT2_FAIL("edit pool overflow (raise edit_cap)");
 	if(cands && hs[0]) BT2_CUDA(cudaMemcpyAsync(cands, d->cands.p, hs[0] * sizeof(bt2gpu_dp_cand), cudaMemcpyDeviceToHost, s));
 	if(edits && hs[1]) BT2_CUDA(cudaMemcpyAsync(edits, d->edits.p, hs[1] * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, s));
-	BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
 	if(ncands) *ncands = (size_t)hs[0];
 	if(nedits) *nedits = (size_t)hs[1];
 	return 0;
@@ -1476,7 +1480,11 @@ extern "C" int bt2gpu_dp_align_batch(
 	bt2gpu_dp_result *results, bt2gpu_dp_cand *cands, size_t cand_cap, bt2gpu_dp_aln *alns,
 	bt2gpu_edit *edits, size_t edit_cap)
 {
-	if(bt2gpu_dp_stage(ctx, seq_pool, qual_pool, pool_len, win_pool, win_len, jobs, njobs, max_aln, cand_cap, edit_cap)) return 1;
+	if(!ctx) BT2_FAIL("null ctx");
+	ctx->in_batch = true;
+	int rc = bt2gpu_dp_stage(ctx, seq_pool, qual_pool, pool_len, win_pool, win_len, jobs, njobs, max_aln, cand_cap, edit_cap);
+	ctx->in_batch = false;
+	if(rc) return 1;
 	if(bt2gpu_dp_run(ctx, 7)) return 1;
 	return bt2gpu_dp_fetch(ctx, results, cands, alns, edits, nullptr, nullptr);
 }

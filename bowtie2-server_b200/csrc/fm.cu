@@ -805,7 +805,7 @@ extern "C" int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, cons
 		if(qual_pool) BT2_CUDA(cudaMemcpyAsync(f->qual.p, qual_pool, pool_len, cudaMemcpyHostToDevice, s));
 	}
 	if(nreads) BT2_CUDA(cudaMemcpyAsync(f->reads.p, reads, nreads * sizeof(bt2gpu_read), cudaMemcpyHostToDevice, s));
-	BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
 	f->nreads = nreads; f->pool_len = pool_len;
 	f->rdlen.resize(nreads);
 	for(size_t i = 0; i < nreads; i++) f->rdlen[i] = reads[i].rd_len;
@@ -919,7 +919,7 @@ extern "C" int bt2gpu_seed_exact_stage(bt2gpu_ctx *ctx, const bt2gpu_seed_job *j
 	}
 	if(f->sjobs.reserve(njobs * sizeof(bt2gpu_seed_job) + 16) || f->sout.reserve(njobs * sizeof(bt2gpu_seed_hit) + 16)) return 1;
 	if(njobs) BT2_CUDA(cudaMemcpyAsync(f->sjobs.p, jobs, njobs * sizeof(bt2gpu_seed_job), cudaMemcpyHostToDevice, ctx->stream));
-	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	if(!ctx->in_batch) BT2_CUDA(bt2::wait_stream(ctx, ctx->stream));   // inside bt2gpu_seed_exact_batch the fetch waits
 	f->n_seed_jobs = njobs;
 	return 0;
 }
@@ -954,15 +954,20 @@ extern "C" int bt2gpu_seed_exact_fetch(bt2gpu_ctx *ctx, bt2gpu_seed_hit *out) {
 	if(!ctx || !ctx->fm) BT2_FAIL("nothing staged");
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	FmState *f = ctx->fm;
+	BT2_CUDA(bt2::settle(ctx, ctx->stream));
 	if(f->n_seed_jobs && out)
 		BT2_CUDA(cudaMemcpyAsync(out, f->sout.p, f->n_seed_jobs * sizeof(bt2gpu_seed_hit), cudaMemcpyDeviceToHost, ctx->stream));
-	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	BT2_CUDA(bt2::wait_stream(ctx, ctx->stream));
 	return 0;
 }
 
 extern "C" int bt2gpu_seed_exact_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
                                        const bt2gpu_seed_job *jobs, size_t njobs, bt2gpu_seed_hit *out) {
-	if(bt2gpu_seed_exact_stage(ctx, jobs, njobs)) return 1;
+	if(!ctx) BT2_FAIL("null ctx");
+	ctx->in_batch = true;
+	const int rc = bt2gpu_seed_exact_stage(ctx, jobs, njobs);
+	ctx->in_batch = false;
+	if(rc) return 1;
 	if(bt2gpu_seed_exact_run(ctx, fw, bw)) return 1;
 	return bt2gpu_seed_exact_fetch(ctx, out);
 }
@@ -986,8 +991,9 @@ extern "C" int bt2gpu_exact_sweep_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw,
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
 	if(ctx->kend()) return 1;
+	BT2_CUDA(bt2::settle(ctx, s));
 	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, n * sizeof(bt2gpu_sweep_result), cudaMemcpyDeviceToHost, s));
-	BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
 	return 0;
 }
 
@@ -1070,8 +1076,9 @@ extern "C" int bt2gpu_extend_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, cons
 	ctx->launches++;
 	BT2_CUDA(cudaGetLastError());
 	if(ctx->kend()) return 1;
+	BT2_CUDA(bt2::settle(ctx, s));
 	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, njobs * sizeof(bt2gpu_extend_result), cudaMemcpyDeviceToHost, s));
-	BT2_CUDA(cudaStreamSynchronize(s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
 	return 0;
 }
 
@@ -1084,7 +1091,7 @@ extern "C" int bt2gpu_locate_stage(bt2gpu_ctx *ctx, const uint32_t *rows, size_t
 	if(n > 0x3ffffff0u) BT2_FAIL("too many rows");
 	if(f->lrows.reserve(n * 4 + 16) || f->loffs.reserve(n * 4 + 16) || f->lsteps.reserve(n * 4 + 16)) return 1;
 	if(n) BT2_CUDA(cudaMemcpyAsync(f->lrows.p, rows, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	if(!ctx->in_batch) BT2_CUDA(bt2::wait_stream(ctx, ctx->stream));   // inside bt2gpu_locate_batch the fetch waits
 	f->n_rows = n;
 	return 0;
 }
@@ -1109,16 +1116,21 @@ extern "C" int bt2gpu_locate_fetch(bt2gpu_ctx *ctx, uint32_t *offs_out, uint32_t
 	BT2_CUDA(cudaSetDevice(ctx->device));
 	FmState *f = ctx->fm;
 	if(f->n_rows) {
+		BT2_CUDA(bt2::settle(ctx, ctx->stream));
 		if(offs_out) BT2_CUDA(cudaMemcpyAsync(offs_out, f->loffs.p, f->n_rows * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		if(steps_out) BT2_CUDA(cudaMemcpyAsync(steps_out, f->lsteps.p, f->n_rows * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	}
-	BT2_CUDA(cudaStreamSynchronize(ctx->stream));
+	BT2_CUDA(bt2::wait_stream(ctx, ctx->stream));
 	return 0;
 }
 
 extern "C" int bt2gpu_locate_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const uint32_t *rows, size_t n,
                                    uint32_t *offs_out, uint32_t *steps_out) {
-	if(bt2gpu_locate_stage(ctx, rows, n)) return 1;
+	if(!ctx) BT2_FAIL("null ctx");
+	ctx->in_batch = true;
+	const int rc = bt2gpu_locate_stage(ctx, rows, n);
+	ctx->in_batch = false;
+	if(rc) return 1;
 	if(bt2gpu_locate_run(ctx, fw)) return 1;
 	return bt2gpu_locate_fetch(ctx, offs_out, steps_out);
 }

@@ -22,6 +22,7 @@
 #include <malloc.h>
 #include <pthread.h>
 #include <sys/mman.h>
+#include <sys/prctl.h>
 #include <time.h>
 #include <unistd.h>
 #include "bt2_idx.h"
@@ -315,6 +316,11 @@ void Worker::loop() {
 		if(progress) { note(C_US_WORKERS, nowUs() - tRun); note(C_US_WORKERS_CPU, cpuUs() - cRun); }
 		// 4. nothing to do: wait for an answer, or for input
 		if(!progress && runq.empty()) {
+			if(!fibers.empty()) {
+				size_t ni = 0;
+				for(Fiber *f : fibers) if(f->state == Fiber::WAIT_INPUT) ni++;
+				note(C_IDLE_WAITS, 1); note(C_IDLE_WORKERS, fibers.size()); note(C_IDLE_WORKERS_INPUT, ni);
+			}
 			Timed tw(C_US_WAIT);
 			std::unique_lock<std::mutex> lk(mu);
 			if(ready.empty()) cv.wait_for(lk, std::chrono::microseconds(fibers.empty() ? 2000 : 300));
@@ -344,7 +350,18 @@ void Lane::run() {
 				if(m != NULL) mode = !strcmp(m, "block") ? BT2GPU_SYNC_BLOCK : !strcmp(m, "spin") ? BT2GPU_SYNC_SPIN : !strcmp(m, "auto") ? BT2GPU_SYNC_AUTO : BT2GPU_SYNC_YIELD;
 				for(int d : g_devices) if(bt2gpu_device_sync_mode(d, mode)) fail("bt2gpu_device_sync_mode");
 			});
-			if(ctx == NULL && bt2gpu_ctx_create(dev, &ctx)) fail("bt2gpu_ctx_create");
+			if(ctx == NULL) {
+				if(bt2gpu_ctx_create(dev, &ctx)) fail("bt2gpu_ctx_create");
+				// BT2GPU_POLL_US (default 20): this lane sleeps between polls of its stream instead of waiting in the
+				// driver -- on a machine whose cores are all busy with workers a waiter that spins or yields gets the
+				// core back a time slice later, a sleeper that wakes gets it at once; 0 = wait in the driver
+				const int us = envInt("BT2GPU_POLL_US", 20, 0, 10000);
+				if(us > 0) {
+					prctl(PR_SET_TIMERSLACK, 1000UL, 0, 0, 0);        // this thread's sleeps end within 1 us of their time
+					if(bt2gpu_ctx_set_wait(ctx, (uint32_t)us * 1000u)) fail("bt2gpu_ctx_set_wait");
+				}
+				if(bt2gpu_ctx_set_timing(ctx, 0)) fail("bt2gpu_ctx_set_timing");   // nobody asks a lane for kernel times
+			}
 			Timed tl(C_US_LANES);
 			const uint64_t c0 = cpuUs();
 			execute(work);
@@ -382,9 +399,10 @@ void appendRead(Lane& l, const Read& rd) {
 	l.reads.push_back(r);
 }
 
-void stage(Lane& l) {
+// `quals`: only oneMmSearch reads the qualities of the staged reads (N penalties); the other FM calls skip their copy
+void stage(Lane& l, bool quals) {
 	Timed t(C_US_ABI_STAGE);
-	if(bt2gpu_reads_stage(l.ctx, l.seq.data(), l.qual.data(), l.seq.size(), l.reads.data(), l.reads.size())) fail("bt2gpu_reads_stage");
+	if(bt2gpu_reads_stage(l.ctx, l.seq.data(), quals ? l.qual.data() : NULL, l.seq.size(), l.reads.data(), l.reads.size())) fail("bt2gpu_reads_stage");
 }
 
 void bind(Lane& l, const Scoring *sc) {
@@ -413,7 +431,7 @@ void Lane::execute(Batch& b) {
 			bind(*this, k.sc);
 			seq.clear(); qual.clear(); reads.clear();
 			for(size_t i : grp) appendRead(*this, *b.sweeps[i]->rd);
-			stage(*this);
+			stage(*this, false);
 			swres.resize(grp.size());
 			const uint64_t t_sweep = nowUs();
 			if(bt2gpu_exact_sweep_batch(ctx, index(*k.fw, dev), k.nofw ? 1 : 0, k.norc ? 1 : 0, k.mineMax, swres.data())) fail("bt2gpu_exact_sweep_batch");
@@ -437,7 +455,7 @@ void Lane::execute(Batch& b) {
 			seq.clear(); qual.clear(); reads.clear(); ojobs.clear();
 			size_t cap = 0;
 			for(size_t i : grp) { appendRead(*this, *b.onemms[i]->rd); ojobs.push_back(b.onemms[i]->job); cap += 8 * b.onemms[i]->rd->length() + 64; }
-			stage(*this);
+			stage(*this, true);
 			ores.resize(grp.size()); ohits.resize(cap);
 			size_t n = 0;
 			const uint64_t t_onemm = nowUs();
@@ -471,7 +489,7 @@ void Lane::execute(Batch& b) {
 			appendRead(*this, *c->rd);
 			xjobs.push_back(j);
 		}
-		stage(*this);
+		stage(*this, false);
 		if(!sjobs.empty()) {
 			shits.resize(sjobs.size());
 			const uint64_t t_seeds = nowUs();

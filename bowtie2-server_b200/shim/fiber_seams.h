@@ -17,6 +17,10 @@
 //      handed to its writer then, instead of waiting for 16 KB of further output.  Same records, same stream; only
 //      when a worker's records are written changes (their order was thread-dependent already).
 //   3. GroupWalk2S -> the locate call of the binding (group_walk_gpu.h, as in the per-call build).
+//   4. read buffers per connection (bt2_search.cpp:4859 asks for 4 * nthreads + 1, pat.cpp:2045-2050 builds them for every
+//      connection): with `-p` in the thousands that is 8193+ PatternSourcePerThread of 32 Reads each, built and torn
+//      down per connection, of which the reference's client can never have more than 20000 / 16 = 1250 in flight (its
+//      window, above).  The batched build caps the count at BT2GPU_READ_BUFFERS (default 1280).
 //
 // All reference headers bt2_search.cpp uses are included FIRST, so the renames below touch that one file only.
 #ifndef BT2GPU_FIBER_SEAMS_H_
@@ -123,6 +127,20 @@ private:
 	bool first_;
 };
 
+// 4. the factory with the number of read buffers per connection capped
+class BatchedServiceFactory : public PatternSourceServiceFactory {
+public:
+	BatchedServiceFactory(int server_port, PatternComposer& composer, const PatternParams& pp, size_t n_readahead,
+	                      AlnSinkSam& msink, const Config& config)
+		: PatternSourceServiceFactory(server_port, composer, pp, readBuffers(n_readahead), msink, config) {}
+private:
+	static size_t readBuffers(size_t asked) {
+		const char *v = getenv("BT2GPU_READ_BUFFERS");
+		size_t cap = (v != NULL && atol(v) > 0) ? (size_t)atol(v) : 1280;
+		return asked < cap ? asked : cap;
+	}
+};
+
 } // namespace bt2shim
 
 namespace std { typedef ::bt2shim::FiberThread bt2shim_fiber_thread; }
@@ -131,6 +149,8 @@ namespace std { typedef ::bt2shim::FiberThread bt2shim_fiber_thread; }
 #define thread bt2shim_fiber_thread
 // 2. `PSFactory::ReadAhead psrah(f);` -> `PSFactory::ReadElement *bt2shim_unused_ = 0; bt2shim::FiberReadAhead psrah(f);`
 #define ReadAhead ReadElement *bt2shim_unused_ = 0; ::bt2shim::FiberReadAhead
+// 4. `PatternSourceServiceFactory readahead_factory(port, patsrc, pp, 4*nthreads+1, ...)` -> the capped factory
+#define PatternSourceServiceFactory ::bt2shim::BatchedServiceFactory
 // the pause after each worker start (threading.h:44-51)
 #undef SLEEP
 #define SLEEP(x) ::bt2shim::sleepMs(x)

@@ -26,7 +26,9 @@ enum Counter { C_ALIGN = 0, C_ALN, C_UNGAPPED, C_SWEEP, C_ONEMM, C_SEEDS, C_EXTE
                // batched binding only, microseconds summed over threads: host threads running workers (wall, CPU) / waiting;
                // lanes executing batches (wall, CPU); and of that, inside the ABI calls of each kind
                C_US_WORKERS, C_US_WORKERS_CPU, C_US_WAIT, C_US_LANES, C_US_LANES_CPU, C_US_ABI_STAGE, C_US_ABI_SWEEP, C_US_ABI_ONEMM, C_US_ABI_SEEDS, C_US_ABI_EXTEND,
-               C_US_ABI_LOCATE, C_US_ABI_UNGAPPED, C_US_ABI_ALIGN, C_NCOUNTERS };
+               C_US_ABI_LOCATE, C_US_ABI_UNGAPPED, C_US_ABI_ALIGN,
+               // times a host thread found nothing to run, and how many of its workers were then waiting for input (the rest: for the GPU)
+               C_IDLE_WAITS, C_IDLE_WORKERS, C_IDLE_WORKERS_INPUT, C_NCOUNTERS };
 
 // SwAligner::initRef + align + the nextAlignment loop of one window (bt2gpu_dp_align_batch)
 struct DpCall {

@@ -84,6 +84,48 @@ bool SeedAligner::oneMmSearch(
 }
 
 /**
+ * SeedAligner::instantiateSeeds (aligner_seed.cpp:498-587): same contract -- the seed offsets, SeedResults::reset, the
+ * seed sequences / qualities of both strands (instantiateSeq: the alignment cache keys on them), one entry per seed
+ * that Seed::instantiate accepts (Ns), the same counts and metrics.
+ * The steps / zones / constraints Seed::instantiate lays out are read by searchSeedBi only, which the GPU replaces:
+ * they are computed into one scratch object per host thread instead of into the read's SeedResults (whose buffers,
+ * with thousands of workers per process, are never in cache: the stores were a third of a host thread's time).  The
+ * SeedResults entry keeps what searchAllSeeds below reads (offset, index, strand) and maxjump.
+ */
+pair<int, int> SeedAligner::instantiateSeeds(
+	const EList<Seed>& seeds, size_t off, int per, const Read& read, const Scoring& pens, bool nofw, bool norc,
+	AlignmentCacheIface& cache, SeedResults& sr, SeedSearchMetrics& met, pair<int, int>& instFw, pair<int, int>& instRc)
+{
+	offIdx2off_.clear();
+	const int len = seeds[0].len;
+	int nseeds = 1;
+	if((int)read.length() - (int)off > len) nseeds += ((int)read.length() - (int)off - len) / per;
+	for(int i = 0; i < nseeds; i++) offIdx2off_.push_back(per * i + (int)off);
+	pair<int, int> ret(0, 0);
+	sr.reset(read, offIdx2off_, nseeds);
+	static thread_local InstantiatedSeed scratch;
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		if((fw && nofw) || (!fw && norc)) continue;
+		for(int i = 0; i < nseeds; i++) {
+			const int depth = i * per + (int)off;
+			instantiateSeq(read, sr.seqs(fw)[i], sr.quals(fw)[i], std::min<int>(len, (int)read.length()), depth, fw);
+			EList<InstantiatedSeed>& iss = sr.instantiatedSeeds(fw, i);
+			for(int j = 0; j < (int)seeds.size(); j++) {
+				if(seeds[j].instantiate(read, sr.seqs(fw)[i], sr.quals(fw)[i], pens, depth, i, j, fw, scratch)) {
+					iss.expand();
+					InstantiatedSeed& is = iss.back();
+					is.seedoff = scratch.seedoff; is.seedoffidx = scratch.seedoffidx; is.fw = scratch.fw; is.maxjump = scratch.maxjump;
+					ret.first++;
+					if(fwi == 0) instFw.first++; else instRc.first++;
+				} else met.filteredseed++;
+			}
+		}
+	}
+	return ret;
+}
+
+/**
  * SeedAligner::searchAllSeeds (aligner_seed.cpp:597-718) for exact seeds (-N 0): every instantiated seed of the read
  * goes to the GPU in one bt2gpu_seed_exact_batch call (ftab jump + mapBiLFEx / mapLF1 steps, startSearchSeedBi :1633,
  * searchSeedBi :1854); the hits then go through the reference's own cache protocol (reportHit :1575 -> addOnTheFly,

@@ -76,7 +76,7 @@ const char *g_names[C_NCOUNTERS] = { "align_calls_on_gpu", "alignments", "ungapp
                                      "seeds_on_gpu", "extend_calls_on_gpu", "locate_rows_on_gpu", "frame_calls_on_gpu", "other_mate_on_gpu", "mate_rect_on_gpu", "pe_classify_on_gpu",
                                      "joined_to_text_off_on_gpu", "abi_batches", "abi_batch_jobs", "h2d_bytes", "d2h_bytes",
                                      "us_workers", "us_workers_cpu", "us_wait", "us_lanes", "us_lanes_cpu", "us_abi_stage", "us_abi_sweep", "us_abi_onemm", "us_abi_seeds", "us_abi_extend",
-                                     "us_abi_locate", "us_abi_ungapped", "us_abi_align" };
+                                     "us_abi_locate", "us_abi_ungapped", "us_abi_align", "idle_waits", "idle_workers", "idle_workers_wait_input" };
 // The totals are rewritten in place by this thread, not by the callers: note() is on the per-alignment path of every
 // worker (a formatted pwrite there cost more than the alignment, and serialised the host threads on the file's lock).
 void statsWriter(int fd) {

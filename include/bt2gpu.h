@@ -53,6 +53,15 @@ int         bt2gpu_device_blocking_sync(int device, int on);
 #define BT2GPU_SYNC_BLOCK 3
 int         bt2gpu_device_sync_mode(int device, int mode);
 int         bt2gpu_ctx_create(int device, bt2gpu_ctx **ctx);
+/* How the batch entry points of THIS context wait for its stream (no counterpart in the reference): poll_ns = 0 (the
+ * default) waits in the driver, in the device's sync mode; poll_ns > 0 polls the stream and sleeps that many nanoseconds
+ * between polls.  For a thread that shares its cores with busy worker threads (the batched server's lanes): a sleeper
+ * that wakes is scheduled at once, a spinning or yielding waiter queues behind the workers' time slices. */
+int         bt2gpu_ctx_set_wait(bt2gpu_ctx *ctx, uint32_t poll_ns);
+/* on = 0: the entry points of this context stop recording the CUDA events behind bt2gpu_ctx_kernel_ms /
+ * bt2gpu_dp_phase_ms (two to six driver calls per entry point; a caller that makes thousands of small calls per second
+ * and never asks for the times).  Default: on. */
+int         bt2gpu_ctx_set_timing(bt2gpu_ctx *ctx, int on);
 void        bt2gpu_ctx_destroy(bt2gpu_ctx *ctx);
 /* Block until everything enqueued on the context's stream has finished. */
 int         bt2gpu_ctx_sync(bt2gpu_ctx *ctx);
@@ -266,7 +275,9 @@ int bt2gpu_probe_dpx(bt2gpu_ctx *ctx, double *ginstr_per_s);
 typedef struct { uint32_t rd_off; uint32_t rd_len; } bt2gpu_read;
 
 /* Stage a batch of reads on the device for the seed-side calls below (replaces the
- * per-read `const Read&` argument of the SeedAligner entry points). */
+ * per-read `const Read&` argument of the SeedAligner entry points).  qual_pool may be NULL when only
+ * calls that never look at qualities follow (exact sweep, exact seeds, extend, locate); bt2gpu_onemm_batch
+ * needs them (N penalties). */
 int bt2gpu_reads_stage(bt2gpu_ctx *ctx, const uint8_t *seq_pool, const uint8_t *qual_pool,
                        size_t pool_len, const bt2gpu_read *reads, size_t nreads);
 

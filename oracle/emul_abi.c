@@ -47,6 +47,8 @@ int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
 const char *bt2gpu_last_error(void) { return g_err; }
 int bt2gpu_device_blocking_sync(int device, int on) { (void)device; (void)on; return 0; }
 int bt2gpu_device_sync_mode(int device, int mode) { (void)device; (void)mode; return 0; }
+int bt2gpu_ctx_set_wait(bt2gpu_ctx *ctx, uint32_t poll_ns) { (void)ctx; (void)poll_ns; return 0; }
+int bt2gpu_ctx_set_timing(bt2gpu_ctx *ctx, int on) { (void)ctx; (void)on; return 0; }
 int bt2gpu_ctx_create(int device, bt2gpu_ctx **out) {
 	(void)device;
 	if(getenv("BT2GPU_EMUL_NO_DEVICE")) return fail("no CUDA device (emulated)");
@@ -71,7 +73,8 @@ int bt2gpu_reads_stage(bt2gpu_ctx *c, const uint8_t *seq_pool, const uint8_t *qu
 	free(c->seq); free(c->qual); free(c->reads);
 	c->seq = (uint8_t*)malloc(pool_len + 1); c->qual = (uint8_t*)malloc(pool_len + 1);
 	c->reads = (bt2gpu_read*)malloc((nreads + 1) * sizeof(bt2gpu_read));
-	memcpy(c->seq, seq_pool, pool_len); memcpy(c->qual, qual_pool, pool_len);
+	memcpy(c->seq, seq_pool, pool_len);
+	if(qual_pool) memcpy(c->qual, qual_pool, pool_len); else memset(c->qual, 0xff, pool_len);   /* poison: a call that reads them shows */
 	memcpy(c->reads, reads, nreads * sizeof(bt2gpu_read));
 	c->nreads = nreads;
 	return 0;

@@ -1,0 +1,15 @@
+#!/bin/bash
+# GPU job 12: lanes that sleep between polls of their stream (bt2gpu_ctx_set_wait) against yield / spin.
+mkdir -p gpurun_out
+O=gpurun_out/j12
+timeout 400 python scripts/server_sweep.py --passes 2 --pass-timeout 60 \
+  --points 16:128:1:8,16:128:1:8:BT2GPU_POLL_US=0,16:128:1:8:BT2GPU_POLL_US=50,16:128:1:8:BT2GPU_POLL_US=5,16:64:1:8,16:128:2:8:BT2GPU_FM_LANES=2 \
+  > ${O}_sweep.jsonl 2> ${O}_sweep.err; echo "sweep rc=$?" > ${O}_box.txt
+cat ${O}_box.txt; python - <<'PY'
+import json
+for ln in open("gpurun_out/j12_sweep.jsonl"):
+    d = json.loads(ln); c = d.pop("counters", None) or {}
+    print({k: (round(v, 1) if isinstance(v, float) else v) for k, v in d.items()})
+    if c: print("   ", {k: round(v / 1e6, 1) for k, v in c.items() if k.startswith("us_")}, "calls", c.get("abi_batches"))
+PY
+grep -h "failed" ${O}_sweep.err | cut -c1-200
