@@ -38,7 +38,7 @@ paired = a.mode == "pairs"
 names = {"k_seed_exact": "k_seed_exact", "k_exact_sweep": "k_exact_sweep", "k_extend": "k_extend", "k_locate": "k_locate"}
 out = {}
 for k, ms in launches.items():
-    base = k.split("::")[-1]
+    base = k.split("::")[-1].replace("void ", "").strip()
     if base in names:
         out[names[base]] = dram(ms[-1])
     elif base.startswith("k_dp_fill") or base.startswith("k_dp_backtrace") or base.startswith("k_dp_gather"):
