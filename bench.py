@@ -615,7 +615,7 @@ def main():
     ap.add_argument("--mode", default="pairs", choices=["pairs", "e2e", "local"],
                     help="pairs: 2x150 --fr pairs, -I 0 -X 500 (C5, the metric's shape); e2e: unpaired 150 bp reads, --very-sensitive (C3); "
                          "local: 250 bp reads, --local (C4)")
-    ap.add_argument("--workers-per-thread", type=int, default=128, help="worker fibers (reads in flight) per host thread of the GPU-bound server")
+    ap.add_argument("--workers-per-thread", type=int, default=64, help="worker fibers (reads in flight) per host thread of the GPU-bound server")
     ap.add_argument("--workers", type=int, default=0)
     ap.add_argument("--host-threads", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=1, help="DP lanes per device of the GPU-bound server (BT2GPU_LANES)")

@@ -109,6 +109,14 @@ class Context:
         _check(self.lib.bt2gpu_ctx_kernel_ms(self._h, C.byref(ms)))
         return float(ms.value)
 
+    def set_wait(self, poll_ns):
+        """bt2gpu_ctx_set_wait: 0 = wait in the driver, > 0 = poll the stream and sleep poll_ns between polls."""
+        _check(self.lib.bt2gpu_ctx_set_wait(self._h, C.c_uint32(poll_ns)))
+
+    def set_timing(self, on):
+        """bt2gpu_ctx_set_timing: whether the entry points record the events behind kernel_ms / dp_phase_ms."""
+        _check(self.lib.bt2gpu_ctx_set_timing(self._h, C.c_int(1 if on else 0)))
+
     def set_scoring(self, sc):
         s = sc.to_struct() if hasattr(sc, "to_struct") else sc
         _check(self.lib.bt2gpu_scoring_set(self._h, _ptr(s)))
@@ -163,6 +171,21 @@ class Context:
         r = self.dp_fetch()
         return r[0], r[1], r[2], r[3]
 
+    def dp_align_batch_abi(self, seq, qual, win, jobs, max_aln=8, cand_cap=None, edit_cap=None):
+        """The same through the single entry point bt2gpu_dp_align_batch (what the server shim calls); pools are
+        returned whole: results[i].cand_off / aln_off and alns[k].edit_off index them."""
+        n = len(jobs)
+        cand_cap = cand_cap if cand_cap is not None else 512 * max(n, 1)
+        edit_cap = edit_cap if edit_cap is not None else 256 * max(n, 1)
+        results = np.zeros(n, dtype=structs.dp_result)
+        cands = np.zeros(cand_cap, dtype=structs.dp_cand)
+        alns = np.zeros(n * max_aln, dtype=structs.dp_aln)
+        edits = np.zeros(edit_cap, dtype=structs.edit)
+        _check(self.lib.bt2gpu_dp_align_batch(
+            self._h, _ptr(seq), _ptr(qual), C.c_size_t(len(seq)), _ptr(win), C.c_size_t(len(win)), _ptr(jobs), C.c_size_t(n),
+            C.c_uint32(max_aln), _ptr(results), _ptr(cands), C.c_size_t(cand_cap), _ptr(alns), _ptr(edits), C.c_size_t(edit_cap)))
+        return results, cands, alns, edits
+
     def ungapped_batch(self, seq, qual, win, jobs, edit_cap=None):
         """bt2gpu_ungapped_batch: SwAligner::ungappedAlign for a batch -> (results, edits)."""
         n = len(jobs)
@@ -189,10 +212,11 @@ class Context:
                                                       C.c_size_t(edit_cap), C.byref(ne)))
         return res, edits[: ne.value]
 
-    def stage_reads(self, pool):
-        """bt2gpu_reads_stage: pool = fmio.ReadPool (replaces the per-call `const Read&`)."""
+    def stage_reads(self, pool, quals=True):
+        """bt2gpu_reads_stage: pool = fmio.ReadPool (replaces the per-call `const Read&`); quals=False stages no
+        qualities (NULL qual_pool: enough for every call but one_mm)."""
         self._pool_n = len(pool)
-        _check(self.lib.bt2gpu_reads_stage(self._h, _ptr(pool.seq), _ptr(pool.qual), C.c_size_t(len(pool.seq)),
+        _check(self.lib.bt2gpu_reads_stage(self._h, _ptr(pool.seq), _ptr(pool.qual) if quals else None, C.c_size_t(len(pool.seq)),
                                            _ptr(pool.reads), C.c_size_t(len(pool))))
 
     def bind_index(self, dev_index):

@@ -23,6 +23,9 @@
 #include <pthread.h>
 #include <sys/mman.h>
 #include <sys/prctl.h>
+#include <sys/resource.h>
+#include <sys/syscall.h>
+#include <sched.h>
 #include <time.h>
 #include <unistd.h>
 #include "bt2_idx.h"
@@ -307,8 +310,14 @@ void Worker::loop() {
 			runFiber(f);
 			if(f->state != Fiber::WAIT_INPUT) progress = true;
 			if(f->state == Fiber::RUNNABLE) { f->queued = true; nextq.push_back(f); }    // yieldNow()
-			// 3. what they queue travels while the rest of the pass runs
-			if(npending >= g_publishAt) publish();
+			// 3. what they queue travels while the rest of the pass runs (at the latest every 16 workers), and workers
+			//    whose answers arrive meanwhile join this pass (a bounded one: input is looked for between passes)
+			if(npending >= g_publishAt || (npending > 0 && (i & 15) == 15)) publish();
+			if(i < 4096 && readyN.load(std::memory_order_acquire) > 0) {
+				std::lock_guard<std::mutex> lk(mu);
+				for(Fiber *r : ready) { r->state = Fiber::RUNNABLE; r->queued = true; runq.push_back(r); }
+				ready.clear(); readyN.store(0, std::memory_order_relaxed);
+			}
 		}
 		runq.clear(); runq.swap(nextq);
 		inputOk = !inputMiss;
@@ -331,6 +340,16 @@ void Worker::loop() {
 // ---- lane: executes what the host threads have queued for its kinds ----------------------------------------------------
 void Lane::run() {
 	nameThread("lane", dev, id);
+	// A lane runs for microseconds at a time (assemble, a few driver calls, sleep until the next poll) and every worker
+	// waits for it: it should get a core the moment it wakes, ahead of the host threads' time slices.  Real-time
+	// round-robin at the lowest priority where the process may ask for it (CAP_SYS_NICE), a negative nice value where it
+	// may ask for that; BT2GPU_LANE_PRIORITY=0 leaves the lanes as they are.
+	if(envInt("BT2GPU_LANE_PRIORITY", 1, 0, 1)) {
+		sched_param sp; memset(&sp, 0, sizeof sp); sp.sched_priority = 1;
+		if(pthread_setschedparam(pthread_self(), SCHED_RR, &sp) != 0) {
+			if(setpriority(PRIO_PROCESS, (id_t)syscall(SYS_gettid), -10) != 0) { /* unprivileged: stay as we are */ }
+		}
+	}
 	std::vector<std::pair<Worker*, Fiber*> > back;
 	for(;;) {
 		{
