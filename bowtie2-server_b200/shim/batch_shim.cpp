@@ -156,7 +156,7 @@ std::vector<Worker*> g_workers;
 std::vector<Hub*> g_hubs;
 size_t g_next = 0;
 std::atomic<bool> g_spawned{false};
-int g_nthreads = 0, g_nlanes = 2;
+int g_nthreads = 0, g_nlanes = 1;
 std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
 size_t g_publishAt = 32;           // BT2GPU_PUBLISH: a host thread hands its queued problems over at the latest after this many
@@ -671,7 +671,7 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 		int hw = (int)std::thread::hardware_concurrency();
 		if(hw < 1) hw = 1;
 		g_nthreads = envInt("BT2GPU_THREADS", hw > 16 ? 16 : hw, 1, 1024);
-		g_nlanes = envInt("BT2GPU_LANES", 2, 1, 8);
+		g_nlanes = envInt("BT2GPU_LANES", 1, 1, 8);
 		g_stackBytes = (size_t)envInt("BT2GPU_STACK_KB", 1024, 64, 1 << 20) * 1024;
 		if(const char *dv = getenv("BT2GPU_DEVICES")) {
 			for(const char *p = dv; *p; ) {

@@ -6,10 +6,11 @@
 // which problems exist at all -- every worker the reference starts (`-p N`) becomes a fiber: a worker with its own
 // stack that runs the reference's unmodified per-read code until it reaches a hot-path call, queues the problem, and
 // switches (in user space, ~20 ns) to the next worker of the same host thread.  When every worker of the thread is
-// waiting, the queued problems travel in one bt2gpu_*_batch call per kind; each worker resumes with its own answer.
-// N workers are spread over BT2GPU_THREADS host threads (default: the machine's cores, at most 16); each host thread
-// has BT2GPU_LANES (default 2) submission lanes (a bt2gpu_ctx with its own stream and arenas, driven by a helper
-// thread), so one batch is on the GPU while the workers that are not part of it build the next.
+// waiting (and at the latest every 16 workers), the queued problems are handed to the lanes of their kinds, which make
+// one bt2gpu_*_batch call per kind; each worker resumes with its own answer.
+// N workers are spread over BT2GPU_THREADS host threads (default: the machine's cores, at most 16).  Each device has one
+// submission lane per kind of problem (a bt2gpu_ctx with its own stream and arenas, driven by its own thread), shared by
+// all host threads: whatever is queued for a kind when its lane is free travels together, and the kinds overlap.
 //
 // Nothing here computes an alignment: it only decides when problems travel.  x86-64 System V only.
 #ifndef BT2GPU_FIBER_H_

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--stock", action="store_true", help="also time the stock server (-p all cores) per client count")
     ap.add_argument("--passes", type=int, default=2)
     ap.add_argument("--pass-timeout", type=int, default=90, help="seconds a single pass may take before the point is abandoned")
+    ap.add_argument("--devices", default="", help="BT2GPU_DEVICES of every point (one server process driving several GPUs), e.g. 0,1")
     a = ap.parse_args()
     if a.mode == "pairs":
         bench.PAIRED = True
@@ -50,6 +51,8 @@ def main():
                 print(json.dumps({"server": "stock", "threads": cores, "clients": ncl, "reads_per_s": len(reads) * a.passes / t,
                                   "start_s": st, "rss_mb": rss}), flush=True)
             env = {"BT2GPU_THREADS": str(th), "BT2GPU_LANES": str(lanes)}
+            if a.devices:
+                env["BT2GPU_DEVICES"] = a.devices
             env.update(extra)
             try:
                 t, st, rss, _, cnt = bench.server_steps(SB.GPUB_SERVER, base, th * wpt, env, shards, td, "g_" + re.sub(r"[^A-Za-z0-9]+", "_", pt), 1, a.passes,
@@ -58,7 +61,7 @@ def main():
                 print(json.dumps({"server": "gpub", "point": pt, "failed": str(e).splitlines()[0][:200]}), flush=True)
                 continue
             jobs = (cnt or {}).get("abi_batch_jobs", 0) / max((cnt or {}).get("abi_batches", 1), 1)
-            print(json.dumps({"server": "gpub", "host_threads": th, "workers": th * wpt, "lanes": lanes, "clients": ncl, "env": extra,
+            print(json.dumps({"server": "gpub", "host_threads": th, "workers": th * wpt, "lanes": lanes, "clients": ncl, "env": extra, "devices": a.devices or "0",
                               "reads_per_s": len(reads) * a.passes / t, "start_s": st, "rss_mb": rss, "jobs_per_abi_call": jobs,
                               "counters": cnt}), flush=True)
 
