@@ -159,6 +159,7 @@ std::atomic<bool> g_spawned{false};
 int g_nthreads = 0, g_nlanes = 1;
 std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
+size_t g_batchMin = 0, g_batchWaitUs = 50;
 size_t g_publishAt = 32;           // BT2GPU_PUBLISH: a host thread hands its queued problems over at the latest after this many
 
 // glibc's allocator, as the reference uses it, gives memory back to the kernel whenever the top of a thread's arena
@@ -355,6 +356,13 @@ void Lane::run() {
 		{
 			std::unique_lock<std::mutex> lk(mu);
 			cv.wait(lk, [this] { return !inbox.empty(); });
+			// BT2GPU_BATCH_MIN / BT2GPU_BATCH_WAIT_US: a lane that finds fewer problems than that waits once, that long, for
+			// more (fewer, fuller calls: less lane CPU per problem, more latency per worker); off by default
+			if(g_batchMin > 0 && inbox.waiters.size() < g_batchMin) {
+				lk.unlock();
+				napMicros((long)g_batchWaitUs);
+				lk.lock();
+			}
 			std::swap(inbox, work);
 		}
 		const int n = (int)work.waiters.size();
@@ -577,14 +585,18 @@ void Lane::execute(Batch& b) {
 			bind(*this, k.sc);
 			const size_t n = grp.size();
 			seq.clear(); qual.clear(); win.clear(); djobs.clear();
-			size_t ccap = 0, ecap = 1024;
+			size_t ccap = 0, cfull = 0, ecap = 1024;
 			for(size_t i : grp) {
 				DpCall& c = *b.dps[i];
 				c.job.rd_off = (uint32_t)seq.size(); c.job.rf_off = (uint32_t)win.size();
 				seq.insert(seq.end(), c.seq, c.seq + c.job.rd_len); qual.insert(qual.end(), c.qual, c.qual + c.job.rd_len);
 				win.insert(win.end(), c.win, c.win + c.job.ncol + 1);
 				djobs.push_back(c.job);
-				ccap += k.sc->monotone ? (size_t)c.job.ncol + 64 : (size_t)c.job.rd_len * c.job.ncol + 64;
+				// candidates: end-to-end, at most one per column; local, any cell can be one (rd_len x ncol) but a window has
+				// a few thousand -- ask for 8192 per window and come back with more if the pool overflows
+				const size_t cells = (size_t)c.job.rd_len * c.job.ncol;
+				ccap += k.sc->monotone ? (size_t)c.job.ncol + 64 : (cells < 8192 ? cells : 8192) + 64;
+				cfull += k.sc->monotone ? (size_t)c.job.ncol + 64 : cells + 64;
 				ecap += (size_t)(c.job.rd_len + 64) * (k.max_aln < 4 ? k.max_aln : 4);
 			}
 			dres.resize(n); dalns.resize(n * (size_t)k.max_aln);
@@ -597,6 +609,7 @@ void Lane::execute(Batch& b) {
 				if(rc == 0) break;
 				const char *e = bt2gpu_last_error();
 				if(attempt < 6 && strstr(e, "edit pool overflow")) { ecap *= 4; continue; }
+				if(ccap < cfull && strstr(e, "candidate pool overflow")) { ccap = ccap * 4 < cfull ? ccap * 4 : cfull; continue; }
 				fail("bt2gpu_dp_align_batch");
 			}
 			for(size_t j = 0; j < n; j++) {
@@ -684,6 +697,8 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 		}
 		if(g_devices.empty()) g_devices.push_back(device());
 		g_publishAt = (size_t)envInt("BT2GPU_PUBLISH", 32, 1, 1 << 20);
+		g_batchMin = (size_t)envInt("BT2GPU_BATCH_MIN", 0, 0, 1 << 20);
+		g_batchWaitUs = (size_t)envInt("BT2GPU_BATCH_WAIT_US", 50, 1, 100000);
 		// per device: BT2GPU_FM_LANES x { exactSweep + oneMmSearch + ungapped | seeds + extend | locate } and
 		// BT2GPU_LANES x { DP windows }
 		const int fmLanes = envInt("BT2GPU_FM_LANES", 1, 1, 8);

@@ -530,7 +530,7 @@ static int dp_one(
 			out->edit_off = (uint32_t)*nedit_tot;
 			int ok = dp_backtrace(&m, job, cd[cural].score, row, col,
 			                      edits + *nedit_tot, edit_cap - *nedit_tot, &ned, out, &overflow);
-			if(overflow) { rc = 1; goto out; }
+			if(overflow) { rc = 2; goto out; }   /* 1 = candidate pool, 2 = edit pool */
 			if(m.local) { done_rc[2 * ndone] = (uint32_t)row; done_rc[2 * ndone + 1] = (uint32_t)col; ndone++; }
 			if(ok) { *nedit_tot += ned; got = 1; break; }
 			cural++;

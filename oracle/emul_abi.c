@@ -113,8 +113,10 @@ int bt2gpu_dp_align_batch(bt2gpu_ctx *c, const uint8_t *seq_pool, const uint8_t 
 	size_t nc = 0, ne = 0;
 	c->calls++;
 	if(!c->have_sc) return fail("bt2gpu_scoring_set must be called first");
-	return bt2oracle_dp_align_batch(&c->sc, seq_pool, qual_pool, pool_len, win_pool, win_len, jobs, njobs, max_aln, results, cands,
-	                                cand_cap, alns, edits, edit_cap, &nc, &ne) ? fail("edit pool overflow (raise edit_cap)") : 0;
+	const int rc = bt2oracle_dp_align_batch(&c->sc, seq_pool, qual_pool, pool_len, win_pool, win_len, jobs, njobs, max_aln, results, cands,
+	                                        cand_cap, alns, edits, edit_cap, &nc, &ne);
+	if(rc == 1) return fail("candidate pool overflow (raise cand_cap)");      /* the library's messages: the shim reads them */
+	return rc ? fail("edit pool overflow (raise edit_cap)") : 0;
 }
 int bt2gpu_ungapped_batch(bt2gpu_ctx *c, const uint8_t *seq_pool, const uint8_t *qual_pool, size_t pool_len, const uint8_t *win_pool,
                           size_t win_len, const bt2gpu_ungap_job *jobs, size_t njobs, bt2gpu_ungap_result *results, bt2gpu_edit *edits,
