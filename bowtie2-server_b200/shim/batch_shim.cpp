@@ -160,6 +160,7 @@ int g_nthreads = 0, g_nlanes = 1;
 std::vector<int> g_devices;        // BT2GPU_DEVICES=0,1,...: host thread i drives device g_devices[i % n] (one process, several GPUs)
 size_t g_stackBytes = 1u << 20;
 size_t g_batchMin = 0, g_batchWaitUs = 50;
+size_t g_localCands = 8192;        // BT2GPU_LOCAL_CANDS: candidate slots first asked for per local-mode window
 size_t g_publishAt = 32;           // BT2GPU_PUBLISH: a host thread hands its queued problems over at the latest after this many
 
 // glibc's allocator, as the reference uses it, gives memory back to the kernel whenever the top of a thread's arena
@@ -593,9 +594,9 @@ void Lane::execute(Batch& b) {
 				win.insert(win.end(), c.win, c.win + c.job.ncol + 1);
 				djobs.push_back(c.job);
 				// candidates: end-to-end, at most one per column; local, any cell can be one (rd_len x ncol) but a window has
-				// a few thousand -- ask for 8192 per window and come back with more if the pool overflows
+				// a few thousand -- ask for BT2GPU_LOCAL_CANDS (8192) per window and come back with more if the pool overflows
 				const size_t cells = (size_t)c.job.rd_len * c.job.ncol;
-				ccap += k.sc->monotone ? (size_t)c.job.ncol + 64 : (cells < 8192 ? cells : 8192) + 64;
+				ccap += k.sc->monotone ? (size_t)c.job.ncol + 64 : (cells < g_localCands ? cells : g_localCands) + 64;
 				cfull += k.sc->monotone ? (size_t)c.job.ncol + 64 : cells + 64;
 				ecap += (size_t)(c.job.rd_len + 64) * (k.max_aln < 4 ? k.max_aln : 4);
 			}
@@ -697,6 +698,7 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 		}
 		if(g_devices.empty()) g_devices.push_back(device());
 		g_publishAt = (size_t)envInt("BT2GPU_PUBLISH", 32, 1, 1 << 20);
+		g_localCands = (size_t)envInt("BT2GPU_LOCAL_CANDS", 8192, 1, 1 << 30);
 		g_batchMin = (size_t)envInt("BT2GPU_BATCH_MIN", 0, 0, 1 << 20);
 		g_batchWaitUs = (size_t)envInt("BT2GPU_BATCH_WAIT_US", 50, 1, 100000);
 		// per device: BT2GPU_FM_LANES x { exactSweep + oneMmSearch + ungapped | seeds + extend | locate } and

@@ -25,12 +25,12 @@ def work(tmp_path_factory):
     return w
 
 
-def _both(work, tag, server_args, client_args, index="lambda", workers=48, host_threads=2, lanes=2):
+def _both(work, tag, server_args, client_args, index="lambda", workers=48, host_threads=2, lanes=2, env=None):
     base = os.path.join(work, index)
     cpu, _ = D.run(D.CPU_SERVER, base, server_args, client_args, os.path.join(work, tag + "_cpu.sam"), threads=2)
     stats = os.path.join(work, tag + "_stats.txt")
     em, err = D.run(D.EMUL_SERVER, base, server_args, client_args, os.path.join(work, tag + "_emul.sam"), threads=workers,
-                    env={"BT2GPU_SHIM_STATS": stats, "BT2GPU_THREADS": str(host_threads), "BT2GPU_LANES": str(lanes)})
+                    env=dict({"BT2GPU_SHIM_STATS": stats, "BT2GPU_THREADS": str(host_threads), "BT2GPU_LANES": str(lanes)}, **(env or {})))
     st = dict((k, int(v)) for k, v in re.findall(r"(\w+)\s+(\d+)", open(stats).read()))
     assert len(cpu) == len(em)
     bad = [(a, b) for a, b in zip(cpu, em) if a != b]
@@ -66,6 +66,9 @@ def test_unpaired_ragged_and_local(work):
     f = os.path.join(work, "loc.fq")
     D.write_fastq(f, r, q, "loc")
     _both(work, "loc", ["--local"], ["-U", f])
+    # a candidate pool asked for too small (16 slots per window): the binding comes back with more until it fits, and a
+    # lane that waits for fuller batches gives the same records
+    _both(work, "loc16", ["--local"], ["-U", f], env={"BT2GPU_LOCAL_CANDS": "16", "BT2GPU_BATCH_MIN": "8", "BT2GPU_BATCH_WAIT_US": "200"})
 
 
 def test_near_exact_one_mismatch_and_ungapped(work):
