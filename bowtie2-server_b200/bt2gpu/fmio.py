@@ -83,7 +83,7 @@ def parse_seed_dump(path, limit=None):
             if k == "R":
                 if limit is not None and len(out) >= limit:
                     break
-                cur = dict(seq=t[3], qual=t[4] if len(t) > 4 else "", H=[], S=[], X=[], L=[], SD=None)
+                cur = dict(seq=t[3], qual=t[4] if len(t) > 4 else "", H=[], S=[], X=[], L=[], K=[], SD=None)
                 # a quality string may contain no spaces in FASTQ; keep exact slice of the line
                 cur["qual"] = line.rstrip("\n").split(" ", 4)[4]
                 out.append(cur)
@@ -98,6 +98,9 @@ def parse_seed_dump(path, limit=None):
             elif k == "S":
                 v = [int(x) for x in t[1:]]
                 cur["S"].append((v[0], v[1], v[2], [tuple(v[4 + 4 * j:8 + 4 * j]) for j in range(v[3])]))
+            elif k == "K":     # --seedmms: the reference strings of the ranges of the S line before it (key, length) ...
+                v = [int(x) for x in t[1:]]
+                cur["K"].append((v[0], v[1], [(v[3 + 2 * j], v[4 + 2 * j]) for j in range(v[2])]))
             elif k == "X":
                 cur["X"].append(tuple(int(x) for x in t[1:]))
             elif k == "L":

@@ -24,7 +24,7 @@ SYMBOLS = [
     "bt2gpu_ref_create", "bt2gpu_ref_destroy", "bt2gpu_ref_bytes", "bt2gpu_probe_random_gather", "bt2gpu_probe_dpx", "bt2gpu_dp_walked_cells",
     "bt2gpu_frame_seed_ext_batch", "bt2gpu_frame_mate_batch", "bt2gpu_pe_classify_batch", "bt2gpu_max_gaps_batch",
     "bt2gpu_joined_to_text_off_batch", "bt2gpu_hotpath_pairs_batch", "bt2gpu_ungapped_batch", "bt2gpu_frame_mate_rect_batch",
-    "bt2gpu_device_blocking_sync", "bt2gpu_device_sync_mode", "bt2gpu_ctx_set_wait", "bt2gpu_ctx_set_timing", "bt2gpu_noalloc_scratch_bytes", "bt2gpu_ungapped_batch_noalloc", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
+    "bt2gpu_device_blocking_sync", "bt2gpu_device_sync_mode", "bt2gpu_ctx_set_wait", "bt2gpu_seed_mm_batch", "bt2gpu_ctx_set_timing", "bt2gpu_noalloc_scratch_bytes", "bt2gpu_ungapped_batch_noalloc", "bt2gpu_ref_create_records", "bt2gpu_ref_create_bitpairs", "bt2gpu_hotpath_job_tidx",
 ]
 
 _lib = None
@@ -228,6 +228,18 @@ class Context:
         _check(self.lib.bt2gpu_seed_exact_batch(self._h, self._ix.fw, self._ix.bw, _ptr(jobs),
                                                 C.c_size_t(len(jobs)), _ptr(out)))
         return out
+
+    def seed_mm(self, jobs, mms, hit_cap=None):
+        """bt2gpu_seed_mm_batch: multi-zone seeds (-N mms) -> (results[njobs], hits in job order; results[j].hit_off /
+        nhits slice them)."""
+        n = len(jobs)
+        hit_cap = hit_cap or 256 * n + 1024
+        out = np.zeros(n, dtype=structs.mmseed_result)
+        hits = np.zeros(hit_cap, dtype=structs.mmseed_hit)
+        nh = C.c_size_t(0)
+        _check(self.lib.bt2gpu_seed_mm_batch(self._h, self._ix.fw, self._ix.bw, _ptr(jobs), C.c_size_t(n), C.c_int(mms),
+                                             _ptr(out), _ptr(hits), C.c_size_t(hit_cap), C.byref(nh)))
+        return out, hits[: nh.value]
 
     def seed_exact_stage(self, jobs):
         self._n_seed = len(jobs)

@@ -35,6 +35,8 @@ INT64_MIN = -(1 << 63)
 read = np.dtype([("rd_off", "<u4"), ("rd_len", "<u4")], align=True)
 seed_job = np.dtype([("read", "<u4"), ("off", "<u2"), ("len", "u1"), ("fw", "u1")], align=True)
 seed_hit = np.dtype([("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"), ("bwops", "<u4"), ("sides", "<u4")], align=True)
+mmseed_hit = np.dtype([("topf", "<u4"), ("botf", "<u4"), ("topb", "<u4"), ("botb", "<u4"), ("key", "<u8")], align=True)
+mmseed_result = np.dtype([("hit_off", "<u4"), ("nhits", "<u4"), ("bwops", "<u4"), ("bwedits", "<u4"), ("ntypes", "<u4"), ("pad", "<u4")], align=True)
 sweep_result = np.dtype([("top", "<u4", (2,)), ("bot", "<u4", (2,)), ("nedit", "<u2", (2,)),
                          ("done", "u1", (2,)), ("bwops", "<u4")], align=True)
 onemm_job = np.dtype([("minsc", "<i4"), ("nceil", "<i4"), ("nofw", "u1"), ("norc", "u1"), ("pad", "u1", (2,))], align=True)

@@ -1136,6 +1136,408 @@ extern "C" int bt2gpu_locate_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, cons
 }
 
 
+// ---- multi-zone seeds: -N 1 / -N 2 ----------------------------------------------------------------------------
+// Seed::mmSeeds (aligner_seed.cpp:365-448), Seed::instantiate (:213-358), startSearchSeedBi (:1633-1714), nextLocsBi
+// (:1364-1432), searchSeedBi with its mismatch branches (:1854-2033) and reportHit (:1575-1630), one THREAD per seed
+// offset of a read strand: the seed types of an offset (2 for -N 1, 3 for -N 2) advance in lock step, a mismatch
+// branch is followed to its end before anything else moves -- the order in which the reference's hits reach the
+// offset's SeedSearchCache, which the driver's RNG-driven choices see.  First version: scalar rank (one thread reads
+// the whole 64-byte side), correctness before speed; the branching is compile-time bounded (at most two edits).
+namespace bt2 {
+
+#define MM_MAXI 0x7fffffff
+#define MM_MAXLEN 32
+struct MmCons { int edits, mms, ins, dels, penalty, editsCeil, mmsCeil, insCeil, delsCeil, penaltyCeil; };
+__device__ __forceinline__ MmCons mmc_init() { MmCons c = { MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI, MM_MAXI }; return c; }
+__device__ __forceinline__ MmCons mmc_exact() { MmCons c = mmc_init(); c.edits = c.mms = c.ins = c.dels = c.penalty = 0; return c; }
+__device__ __forceinline__ MmCons mmc_mm(int n) { MmCons c = mmc_init(); c.mms = n; c.edits = c.dels = c.ins = 0; return c; }
+__device__ __forceinline__ bool mmc_must_match(const MmCons &c) { return (c.mms == 0 && c.edits == 0) || c.penalty == 0 || (c.mms == 0 && c.dels == 0 && c.ins == 0); }
+__device__ __forceinline__ bool mmc_can(const MmCons &c, int pen) { return (c.mms > 0 || c.edits > 0) && c.penalty >= pen; }
+__device__ __forceinline__ void mmc_charge(MmCons &c, int pen) { if(c.mms == 0) c.edits--; else c.mms--; c.penalty -= pen; }
+__device__ __forceinline__ bool mmc_ok(const MmCons &c) {
+	return c.edits <= c.editsCeil && c.mms <= c.mmsCeil && c.ins <= c.insCeil && c.dels <= c.delsCeil && c.penalty <= c.penaltyCeil;
+}
+__device__ __forceinline__ bool mmc_can_gap(const MmCons &c) { return ((c.ins > 0 || c.dels > 0) || c.edits > 0) && c.penalty > 0; }
+
+// countBt2SideEx + rowL by one thread (the quad version above, without the shuffles)
+__device__ __forceinline__ void thread_lf(const IndexDev &ix, uint32_t row, uint32_t val[4], int &rowc) {
+	const uint32_t side = row / 192u;
+	const int co = (int)(row - side * 192u);
+	const uint4 *sp = ix.sides + (size_t)side * 4;
+	const uint4 v0 = __ldg(sp), v1 = __ldg(sp + 1), v2 = __ldg(sp + 2), v3 = __ldg(sp + 3);
+	const uint32_t w[12] = { v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w };
+	uint32_t nC = 0, nG = 0, nT = 0;
+#pragma unroll
+	for(int k = 0; k < 12; k++) {
+		int mw = co - 16 * k;
+		mw = mw < 0 ? 0 : mw;
+		const uint32_t pm = pos_mask16(mw);
+		const uint32_t lo = w[k] & pm, hi = (w[k] >> 1) & pm;
+		nT += __popc(lo & hi);
+		nG += __popc(hi & ~lo);
+		nC += __popc(lo & ~hi);
+	}
+	const uint32_t nA = (uint32_t)co - (nC + nG + nT);
+	uint32_t wc = 0;
+#pragma unroll
+	for(int k = 0; k < 12; k++) if(k == (co >> 4)) wc = w[k];
+	rowc = (int)((wc >> (2 * (co & 15))) & 3u);
+	const uint32_t fix = (side == ix.zside && (uint32_t)co > ix.zco) ? 1u : 0u;
+	val[0] = ix.fchr[0] + v3.x + nA - fix;
+	val[1] = ix.fchr[1] + v3.y + nC;
+	val[2] = ix.fchr[2] + v3.z + nG;
+	val[3] = ix.fchr[3] + v3.w + nT;
+}
+
+struct MmSeed {                       // InstantiatedSeed: steps, zones, constraints after the Ns were charged, maxjump
+	int n; int8_t steps[MM_MAXLEN], z1[MM_MAXLEN], z2[MM_MAXLEN];
+	MmCons cons[3], overall;
+	int maxjump;
+};
+struct MmParam {                      // SeedAlignerSearchParams; the loci are functions of their rows
+	int seed;                         // which MmSeed
+	int step;
+	uint32_t topf, botf, topb, botb;
+	uint32_t trow, brow; bool bvalid; // SideLocus tloc / bloc
+	MmCons cv[3], overall;
+	int nedits; uint8_t epos[2], echr[2];
+	bool hasi0; uint32_t fwi0, bwi0;
+};
+struct MmCtx {
+	const IndexDev *fw, *bw;
+	const MmSeed *seeds;
+	const uint8_t *seq, *qual;        // the seed string and its qualities
+	bt2gpu_mmseed_hit *hits; uint32_t cap, n;
+	uint32_t bwops, bwedits;
+	int err;                          // 1 = hit slice full, 2 = a gap would be legal (the reference throws), 3 = deeper branching than two edits
+};
+
+// Seed::instantiate: false when the Ns of the window disqualify the seed
+__device__ bool mm_instantiate(int type, const MmCons zones[3], int seedlen, const uint8_t *seq, const uint8_t *qual, MmSeed &is) {
+	is.n = seedlen;
+	if(type == BT2GPU_SEED_EXACT) {
+		for(int k = 0; k < seedlen; k++) { is.steps[k] = (int8_t)-(seedlen - k); is.z1[k] = is.z2[k] = 0; }
+	} else if(type == BT2GPU_SEED_LEFT_TO_RIGHT) {
+		for(int k = 0; k < seedlen; k++) { is.steps[k] = (int8_t)(k + 1); is.z1[k] = is.z2[k] = (k < (seedlen + 1) / 2) ? 0 : 1; }
+		is.z1[seedlen - 1] = is.z2[seedlen - 1] = -1;
+	} else if(type == BT2GPU_SEED_RIGHT_TO_LEFT) {
+		for(int k = 0; k < seedlen; k++) {
+			is.steps[k] = (int8_t)-(seedlen - k);
+			is.z1[k] = (k < seedlen / 2) ? 0 : 1;
+			is.z2[k] = (k < (seedlen + 1) / 2 + 1) ? 0 : 1;
+		}
+		is.z1[seedlen - 1] = is.z2[seedlen - 1] = -1;
+	} else {
+		int step = 0;
+		for(int k = (seedlen + 3) / 4; k < seedlen - (seedlen / 4); k++) { is.z1[step] = is.z2[step] = 0; is.steps[step++] = (int8_t)(k + 1); }
+		for(int k = seedlen - (seedlen / 4); k < seedlen; k++) { is.z1[step] = is.z2[step] = 1; is.steps[step++] = (int8_t)(k + 1); }
+		is.z1[step - 1] = is.z2[step - 1] = -1;
+		for(int k = ((seedlen + 3) / 4) - 1; k >= 0; k--) { is.z1[step] = is.z2[step] = 2; is.steps[step++] = (int8_t)-(k + 1); }
+		is.z1[step - 1] = is.z2[step - 1] = -2;
+	}
+	for(int i = 0; i < 3; i++) is.cons[i] = zones[i];
+	is.overall = mmc_init();
+	bool streak = true;
+	const bool ltr = is.steps[0] > 0;
+	is.maxjump = 0;
+	for(int i = 0; i < is.n; i++) {
+		const int off = abs((int)is.steps[i]) - 1;
+		MmCons &cons = is.cons[abs((int)is.z1[i])];
+		const int c = seq[off], q = qual[off];
+		if(ltr != (is.steps[i] > 0) || is.z1[i] != 0 || is.z2[i] != 0) streak = false;
+		if(c == 4) {
+			if(mmc_can(cons, c_fm_npens[q])) mmc_charge(cons, c_fm_npens[q]);
+			else return false;
+		}
+		if(streak) is.maxjump++;
+	}
+	return true;
+}
+
+__device__ void mm_report(MmCtx &x, const MmParam &p) {
+	const MmSeed &s = x.seeds[p.seed];
+	unsigned long long key = 0;
+	for(int i = 0; i < s.n; i++) {
+		int c = x.seq[i];
+		for(int e = 0; e < p.nedits; e++) if(p.epos[e] == i) c = p.echr[e];
+		key = (key << 2) | (unsigned long long)(c & 3);
+	}
+	if(x.n >= x.cap) { x.err = 1; x.n++; return; }
+	bt2gpu_mmseed_hit h;
+	h.topf = p.topf; h.botf = p.botf; h.topb = p.topb; h.botb = p.botb; h.key = key;
+	x.hits[x.n++] = h;
+}
+
+__device__ __forceinline__ void mm_next_locs(const MmSeed &s, MmParam &p, int step) {      // nextLocsBi
+	if(step == s.n) return;
+	const bool ltr = s.steps[step] > 0;
+	const uint32_t top = ltr ? p.topb : p.topf, bot = ltr ? p.botb : p.botf;
+	p.trow = top;
+	p.bvalid = (bot - top != 1);
+	p.brow = bot;
+}
+
+__device__ __forceinline__ uint32_t mm_ftab_key(const IndexDev &ix, const uint8_t *seq, int off) {     // ftabSeqToInt(seq, off, false)
+	const int fc = ix.ftab_chars;
+	uint32_t v = 0;
+	for(int i = 0; i < fc; i++) {
+		const int c = ix.is_fw ? seq[off + i] : seq[off + fc - i - 1];
+		if(c > 3) return OFFMASK;
+		v = (v << 2) | (uint32_t)c;
+	}
+	return v;
+}
+
+__device__ void mm_param_init(MmCtx &x, MmParam &p, int seed) {
+	const MmSeed &s = x.seeds[seed];
+	p.seed = seed; p.step = 0;
+	p.topf = p.botf = p.topb = p.botb = 0; p.trow = p.brow = 0; p.bvalid = false;
+	for(int i = 0; i < 3; i++) p.cv[i] = s.cons[i];
+	p.overall = s.overall;
+	p.nedits = 0;
+	int off = abs((int)s.steps[0]) - 1;
+	const bool ltr = s.steps[0] > 0;
+	const int ftab_len = x.fw->ftab_chars;
+	p.hasi0 = (ftab_len > 1 && ftab_len <= s.maxjump);
+	p.fwi0 = p.bwi0 = 0;
+	if(p.hasi0) {
+		if(!ltr) off = off - ftab_len + 1;
+		p.fwi0 = mm_ftab_key(*x.fw, x.seq, off);
+		p.bwi0 = mm_ftab_key(*x.bw, x.seq, off);
+	}
+}
+
+__device__ bool mm_start(MmCtx &x, MmParam &p) {               // startSearchSeedBi: true = already done
+	const MmSeed &s = x.seeds[p.seed];
+	if(p.step == s.n) { mm_report(x, p); return true; }
+	if(p.step == 0) {
+		const int off = abs((int)s.steps[0]) - 1;
+		if(p.hasi0) {
+			p.topf = ftab_hi(*x.fw, p.fwi0); p.botf = ftab_lo(*x.fw, p.fwi0 + 1);
+			if(p.botf - p.topf == 0) return true;
+			p.topb = ftab_hi(*x.bw, p.bwi0); p.botb = p.topb + (p.botf - p.topf);
+			p.step += x.fw->ftab_chars;
+		} else if(s.maxjump > 0) {
+			const int c = x.seq[off];
+			p.topf = p.topb = x.fw->fchr[c];
+			p.botf = p.botb = x.fw->fchr[c + 1];
+			if(p.botf - p.topf == 0) return true;
+			p.step++;
+		} else {
+			p.topf = p.topb = 0;
+			p.botf = p.botb = x.fw->fchr[4];
+		}
+		if(p.step == s.n) { mm_report(x, p); return true; }
+		mm_next_locs(s, p, p.step);
+	}
+	return false;
+}
+
+template<int D> __device__ void mm_run(MmCtx &x, MmParam &p);
+template<> __device__ void mm_run<3>(MmCtx &x, MmParam &p);     // never reached: two edits at most
+
+// one step of one search (the body of searchSeedBi's inner loop); true = this search is done
+template<int D> __device__ bool mm_step(MmCtx &x, MmParam &p) {
+	const MmSeed &s = x.seeds[p.seed];
+	if(p.step >= s.n) return true;
+	const int i = p.step++;
+	uint32_t t[4] = {0, 0, 0, 0}, b[4] = {0, 0, 0, 0}, tp[4], bp[4];
+	const bool ltr = s.steps[i] > 0;
+	const int off = abs((int)s.steps[i]) - 1;
+	const IndexDev &ebwt = ltr ? *x.bw : *x.fw;
+	uint32_t ntop = ltr ? p.topb : p.topf;
+#pragma unroll
+	for(int k = 0; k < 4; k++) { tp[k] = ltr ? p.topf : p.topb; bp[k] = ltr ? p.botf : p.botb; }
+	// tf/bf = forward-index ranges, tb/bb = mirror ranges: (t, b) belong to the index of this step, (tp, bp) to the other
+	int tlc = 0;                                                  // rowL(tloc)
+	bool have_tl = false;
+	uint32_t tlv[4];
+	if(p.bvalid) {
+		x.bwops++;
+		int dummy;
+		thread_lf(ebwt, p.trow, t, tlc);
+		thread_lf(ebwt, p.brow, b, dummy);
+		bp[0] = tp[0] + (b[0] - t[0]); tp[1] = bp[0];
+		bp[1] = tp[1] + (b[1] - t[1]); tp[2] = bp[1];
+		bp[2] = tp[2] + (b[2] - t[2]); tp[3] = bp[2];
+		bp[3] = tp[3] + (b[3] - t[3]);
+	}
+	const int c = x.seq[off];
+	const bool leave_zone = s.z1[i] < 0;
+	MmCons &cons = p.cv[abs((int)s.z1[i])];
+	if(!(mmc_must_match(cons) && !mmc_must_match(p.overall)) || c == 4) {
+		bool bail = false;
+		if(!p.bvalid) {
+			x.bwops++;
+			thread_lf(ebwt, p.trow, tlv, tlc); have_tl = true;
+			if(ntop == ebwt.zoff) bail = true;                    // mapLF1(row&, l): -1 at '$'
+			else { ntop = pick4(tlv, tlc); t[tlc] = ntop; b[tlc] = ntop + 1; }
+		}
+		if(!bail) {
+			const int q = x.qual[off], pen = c_fm_mmpens[q];          // the raw quality character indexes the table (:1934)
+			if((mmc_can(cons, pen) && mmc_can(p.overall, pen)) || c == 4) {
+				const MmCons save_c = cons, save_o = p.overall;
+				if(c != 4) { mmc_charge(cons, pen); mmc_charge(p.overall, pen); }
+				if(!leave_zone || (mmc_ok(cons) && mmc_ok(p.overall))) {
+					for(int j = 0; j < 4; j++) {
+						if(j == c || b[j] == t[j]) continue;
+						if(D >= 2 || p.nedits >= 2) { x.err = 3; continue; }
+						MmParam p2 = p;
+						p2.topf = ltr ? tp[j] : t[j]; p2.botf = ltr ? bp[j] : b[j];
+						p2.topb = ltr ? t[j] : tp[j]; p2.botb = ltr ? b[j] : bp[j];
+						p2.epos[p2.nedits] = (uint8_t)off; p2.echr[p2.nedits] = (uint8_t)j; p2.nedits++;
+						mm_next_locs(s, p2, i + 1);
+						x.bwedits++;
+						p2.step = i + 1;
+						mm_run<D + 1>(x, p2);
+					}
+				}
+				cons = save_c; p.overall = save_o;
+			}
+			if(mmc_can_gap(cons) && mmc_can_gap(p.overall)) { x.err = 2; return true; }
+		}
+	}
+	if(c == 4) return true;
+	if(leave_zone && (!mmc_ok(cons) || !mmc_ok(p.overall))) return true;
+	if(!p.bvalid) {
+		x.bwops++;
+		if(!have_tl) { thread_lf(ebwt, p.trow, tlv, tlc); }
+		// mapLF1(row, l, c): the row tested against '$' is the one the mismatch branch above may have advanced
+		if(tlc != c || ntop == ebwt.zoff) return true;
+		t[c] = pick4(tlv, c);
+		b[c] = t[c] + 1;
+	}
+	if(pick4(b, c) == pick4(t, c)) return true;
+	p.topf = ltr ? pick4(tp, c) : pick4(t, c); p.botf = ltr ? pick4(bp, c) : pick4(b, c);
+	p.topb = ltr ? pick4(t, c) : pick4(tp, c); p.botb = ltr ? pick4(b, c) : pick4(bp, c);
+	if(i + 1 == s.n) { mm_report(x, p); return true; }
+	mm_next_locs(s, p, i + 1);
+	return false;
+}
+
+template<int D> __device__ void mm_run(MmCtx &x, MmParam &p) {   // searchSeedBi(1, &p) of a mismatch branch
+	if(mm_start(x, p)) return;
+	while(!mm_step<D>(x, p)) { }
+}
+template<> __device__ void mm_run<3>(MmCtx &x, MmParam &p) { x.err = 3; }
+
+__global__ void __launch_bounds__(64)
+k_seed_mm(const IndexDev fw, const IndexDev bw, const uint8_t *__restrict__ seqs, const uint8_t *__restrict__ quals,
+          const bt2gpu_read *__restrict__ reads, const bt2gpu_seed_job *__restrict__ jobs, uint32_t njobs, int mms,
+          uint32_t cap_per_job, bt2gpu_mmseed_result *__restrict__ out, bt2gpu_mmseed_hit *__restrict__ hits, int *__restrict__ errflag)
+{
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= njobs) return;
+	const bt2gpu_seed_job jb = jobs[j];
+	const bt2gpu_read rd = reads[jb.read];
+	const int len = jb.len;
+	uint8_t seq[MM_MAXLEN], qual[MM_MAXLEN];
+	for(int i = 0; i < len; i++) {                               // instantiateSeq: the window as it aligns to the Watson strand
+		const uint32_t o = rd.rd_off + jb.off + (jb.fw ? i : len - 1 - i);
+		const int c = seqs[o];
+		seq[i] = (uint8_t)(jb.fw ? c : comp_dna(c));
+		qual[i] = quals[o];
+	}
+	// Seed::mmSeeds
+	int types[3]; MmCons zones[3][3]; int npol = 0;
+	if(mms == 0) {
+		types[0] = BT2GPU_SEED_EXACT; zones[0][0] = zones[0][1] = zones[0][2] = mmc_exact(); npol = 1;
+	} else if(mms == 1) {
+		types[0] = BT2GPU_SEED_LEFT_TO_RIGHT; zones[0][0] = mmc_exact(); zones[0][1] = mmc_mm(1); zones[0][2] = mmc_exact();
+		types[1] = BT2GPU_SEED_RIGHT_TO_LEFT; zones[1][0] = mmc_exact(); zones[1][1] = mmc_mm(1); zones[1][1].mmsCeil = 0; zones[1][2] = mmc_exact();
+		npol = 2;
+	} else {
+		types[0] = BT2GPU_SEED_LEFT_TO_RIGHT; zones[0][0] = mmc_exact(); zones[0][1] = mmc_mm(2); zones[0][2] = mmc_exact();
+		types[1] = BT2GPU_SEED_RIGHT_TO_LEFT; zones[1][0] = mmc_exact(); zones[1][1] = mmc_mm(2); zones[1][1].mmsCeil = 1; zones[1][2] = mmc_exact();
+		types[2] = BT2GPU_SEED_INSIDE_OUT; zones[2][0] = mmc_exact(); zones[2][1] = mmc_mm(1); zones[2][1].mmsCeil = 0;
+		zones[2][2] = mmc_mm(1); zones[2][2].mmsCeil = 0;
+		npol = 3;
+	}
+	MmSeed seeds[3]; MmParam pv[3]; bool done[3];
+	MmCtx x;
+	x.fw = &fw; x.bw = &bw; x.seeds = seeds; x.seq = seq; x.qual = qual;
+	x.hits = hits + (size_t)j * cap_per_job; x.cap = cap_per_job; x.n = 0; x.bwops = x.bwedits = 0; x.err = 0;
+	int np = 0;
+	for(int k = 0; k < npol; k++)
+		if(mm_instantiate(types[k], zones[k], len, seq, qual, seeds[np])) { mm_param_init(x, pv[np], np); np++; }
+	int nleft = np;
+	for(int n = 0; n < np; n++) { done[n] = mm_start(x, pv[n]); if(done[n]) nleft--; }
+	while(nleft > 0) {
+		for(int n = 0; n < np; n++) {
+			if(done[n]) continue;
+			if(mm_step<0>(x, pv[n])) { done[n] = true; nleft--; }
+		}
+	}
+	bt2gpu_mmseed_result r;
+	r.hit_off = 0; r.nhits = x.n; r.bwops = x.bwops; r.bwedits = x.bwedits; r.ntypes = (uint32_t)np; r.pad = 0;
+	out[j] = r;
+	if(x.err) atomicMax(errflag, x.err);
+}
+
+} // namespace bt2
+
+extern "C" int bt2gpu_seed_mm_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+                                    const bt2gpu_seed_job *jobs, size_t njobs, int mms, bt2gpu_mmseed_result *out,
+                                    bt2gpu_mmseed_hit *hits, size_t hit_cap, size_t *nhits)
+{
+	if(!ctx || !ctx->fm) BT2_FAIL("bt2gpu_reads_stage must be called first");
+	if(!ctx->have_sc) BT2_FAIL("bt2gpu_scoring_set must be called first");
+	if(!out || !hits || !nhits) BT2_FAIL("null argument");
+	if(mms < 0 || mms > 2) BT2_FAIL("seed mismatches must be 0, 1 or 2 (-N)");
+	if(check_idx(ctx, fw, false) || check_idx(ctx, bw, false)) return 1;
+	if(fw->dev.ftab_chars != bw->dev.ftab_chars) BT2_FAIL("forward and mirror index disagree on ftabChars");
+	BT2_CUDA(cudaSetDevice(ctx->device));
+	FmState *f = ctx->fm;
+	*nhits = 0;
+	if(njobs == 0) return 0;
+	if(njobs > 0x0fffffffu) BT2_FAIL("too many seed jobs");
+	for(size_t i = 0; i < njobs; i++) {
+		const bt2gpu_seed_job &j = jobs[i];
+		if(j.read >= f->nreads) BT2_FAIL("seed job names a read that is not staged");
+		if(j.len < 1 || j.len > MM_MAXLEN) BT2_FAIL("seed length must be 1..32");
+		if((uint32_t)j.off + j.len > f->rdlen[j.read]) BT2_FAIL("seed window outside the read");
+	}
+	size_t per = hit_cap / njobs;
+	if(per < 1) BT2_FAIL("seed hit pool overflow (raise hit_cap)");
+	if(per > 4096) per = 4096;
+	if(f->jobs.reserve(njobs * sizeof(bt2gpu_seed_job)) || f->out.reserve(njobs * sizeof(bt2gpu_mmseed_result)) ||
+	   f->aux.reserve(njobs * per * sizeof(bt2gpu_mmseed_hit)) || f->scal.reserve(64) || f->h_scal.reserve(64)) return 1;
+	cudaStream_t s = ctx->stream;
+	BT2_CUDA(cudaMemcpyAsync(f->jobs.p, jobs, njobs * sizeof(bt2gpu_seed_job), cudaMemcpyHostToDevice, s));
+	BT2_CUDA(cudaMemsetAsync(f->scal.p, 0, 64, s));
+	if(ctx->kstart()) return 1;
+	k_seed_mm<<<(uint32_t)((njobs + 63) / 64), 64, 0, s>>>(fw->dev, bw->dev, f->seq.as<uint8_t>(), f->qual.as<uint8_t>(),
+		f->reads.as<bt2gpu_read>(), f->jobs.as<bt2gpu_seed_job>(), (uint32_t)njobs, mms, (uint32_t)per,
+		f->out.as<bt2gpu_mmseed_result>(), f->aux.as<bt2gpu_mmseed_hit>(), f->scal.as<int>());
+	ctx->launches++;
+	BT2_CUDA(cudaGetLastError());
+	if(ctx->kend()) return 1;
+	BT2_CUDA(bt2::settle(ctx, s));
+	BT2_CUDA(cudaMemcpyAsync(out, f->out.p, njobs * sizeof(bt2gpu_mmseed_result), cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(cudaMemcpyAsync(f->h_scal.p, f->scal.p, 64, cudaMemcpyDeviceToHost, s));
+	BT2_CUDA(bt2::wait_stream(ctx, s));
+	const int err = *f->h_scal.as<int>();
+	if(err == 1) BT2_FAIL("seed hit pool overflow (raise hit_cap)");
+	if(err == 2) BT2_FAIL("a seed zone would allow a gap: not implemented by the reference either (aligner_seed.cpp:1967)");
+	if(err) BT2_FAIL("seed search branched deeper than two edits");
+	// compact the per-job slices into the caller's pool, job order = hit order
+	std::vector<bt2gpu_mmseed_hit> tmp(njobs * per);
+	size_t tot = 0;
+	for(size_t i = 0; i < njobs; i++) tot += out[i].nhits;
+	if(tot > hit_cap) BT2_FAIL("seed hit pool overflow (raise hit_cap)");
+	if(tot) {
+		BT2_CUDA(cudaMemcpyAsync(tmp.data(), f->aux.p, njobs * per * sizeof(bt2gpu_mmseed_hit), cudaMemcpyDeviceToHost, s));
+		BT2_CUDA(bt2::wait_stream(ctx, s));
+	}
+	size_t o = 0;
+	for(size_t i = 0; i < njobs; i++) {
+		out[i].hit_off = (uint32_t)o;
+		for(uint32_t k = 0; k < out[i].nhits; k++) hits[o++] = tmp[i * per + k];
+	}
+	*nhits = tot;
+	return 0;
+}
+
 // ---- roofline probe ---------------------------------------------------------------------
 // Independent (not dependent-chain) random 64-byte side gathers over the index itself at full
 // occupancy: the HBM random-access ceiling the seed kernels are measured against

@@ -75,7 +75,7 @@ struct Fiber {
 	bool queued = false;             // on its host thread's run queue
 };
 
-enum Kind { K_DP = 0, K_UNGAP, K_SWEEP, K_ONEMM, K_SEEDS, K_EXTEND, K_LOCATE, K_NKINDS };
+enum Kind { K_DP = 0, K_UNGAP, K_SWEEP, K_ONEMM, K_SEEDS, K_SEEDMM, K_EXTEND, K_LOCATE, K_NKINDS };
 
 // Problems waiting to travel, by kind, and the workers that wait for them.
 struct Batch {
@@ -84,11 +84,12 @@ struct Batch {
 	std::vector<SweepCall*> sweeps;
 	std::vector<OneMmCall*> onemms;
 	std::vector<SeedsCall*> seeds;
+	std::vector<SeedsMmCall*> seedmms;
 	std::vector<ExtendCall*> extends;
 	std::vector<LocateCall*> locates;
 	std::vector<Fiber*> waiters;
 	bool empty() const { return waiters.empty(); }
-	void clear() { dps.clear(); ungaps.clear(); sweeps.clear(); onemms.clear(); seeds.clear(); extends.clear(); locates.clear(); waiters.clear(); }
+	void clear() { dps.clear(); ungaps.clear(); sweeps.clear(); onemms.clear(); seeds.clear(); seedmms.clear(); extends.clear(); locates.clear(); waiters.clear(); }
 	template<typename T> static void cat(std::vector<T>& d, std::vector<T>& s) { d.insert(d.end(), s.begin(), s.end()); s.clear(); }
 };
 
@@ -116,6 +117,7 @@ struct Lane {
 	std::vector<bt2gpu_sweep_result> swres;
 	std::vector<bt2gpu_onemm_job> ojobs; std::vector<bt2gpu_onemm_result> ores; std::vector<bt2gpu_ee_hit> ohits;
 	std::vector<bt2gpu_seed_job> sjobs; std::vector<bt2gpu_seed_hit> shits;
+	std::vector<bt2gpu_mmseed_result> mres; std::vector<bt2gpu_mmseed_hit> mhits;
 	std::vector<bt2gpu_extend_job> xjobs; std::vector<bt2gpu_extend_result> xres;
 	std::vector<uint32_t> rows, offs, steps;
 	void run();
@@ -273,7 +275,7 @@ void Worker::publish() {
 		}
 		if(wasEmpty) l->cv.notify_one();
 	};
-	to(K_SWEEP, &Batch::sweeps); to(K_ONEMM, &Batch::onemms); to(K_SEEDS, &Batch::seeds); to(K_EXTEND, &Batch::extends);
+	to(K_SWEEP, &Batch::sweeps); to(K_ONEMM, &Batch::onemms); to(K_SEEDS, &Batch::seeds); to(K_SEEDMM, &Batch::seedmms); to(K_EXTEND, &Batch::extends);
 	to(K_LOCATE, &Batch::locates); to(K_UNGAP, &Batch::ungaps); to(K_DP, &Batch::dps);
 	npending = 0;
 }
@@ -537,6 +539,52 @@ void Lane::execute(Batch& b) {
 			noteBatch(C_EXTEND, xjobs.size(), xjobs.size() * sizeof(bt2gpu_extend_job), xjobs.size() * sizeof(bt2gpu_extend_result));
 		}
 	}
+	// ---- multi-zone seeds (-N 1 / -N 2): by mismatch count; reads staged with their qualities (N penalties) ----
+	{
+		std::vector<char> taken(b.seedmms.size(), 0);
+		for(size_t i0 = 0; i0 < b.seedmms.size(); i0++) {
+			if(taken[i0]) continue;
+			const SeedsMmCall& k = *b.seedmms[i0];
+			std::vector<size_t> grp;
+			for(size_t i = i0; i < b.seedmms.size(); i++) {
+				const SeedsMmCall& c = *b.seedmms[i];
+				if(!taken[i] && c.fw == k.fw && c.bw == k.bw && c.mms == k.mms) { taken[i] = 1; grp.push_back(i); }
+			}
+			bind(*this, k.sc);
+			seq.clear(); qual.clear(); reads.clear(); sjobs.clear();
+			for(size_t i : grp) {
+				SeedsMmCall& c = *b.seedmms[i];
+				const uint32_t ri = (uint32_t)reads.size();
+				appendRead(*this, *c.rd);
+				for(bt2gpu_seed_job j : c.jobs) { j.read = ri; sjobs.push_back(j); }
+			}
+			stage(*this, true);
+			mres.resize(sjobs.size());
+			size_t cap = 64 * sjobs.size() + 256, n = 0;
+			const uint64_t t_mm = nowUs();
+			for(int attempt = 0; ; attempt++) {
+				mhits.resize(cap);
+				if(bt2gpu_seed_mm_batch(ctx, index(*k.fw, dev), index(*k.bw, dev), sjobs.data(), sjobs.size(), k.mms, mres.data(), mhits.data(), cap, &n) == 0) break;
+				if(attempt < 6 && strstr(bt2gpu_last_error(), "seed hit pool overflow")) { cap *= 4; continue; }
+				fail("bt2gpu_seed_mm_batch");
+			}
+			note(C_US_ABI_SEEDS, nowUs() - t_mm);
+			size_t o = 0;
+			for(size_t i : grp) {
+				SeedsMmCall& c = *b.seedmms[i];
+				c.res.assign(mres.begin() + o, mres.begin() + o + c.jobs.size());
+				c.hits.clear();
+				for(bt2gpu_mmseed_result& r : c.res) {
+					const uint32_t ho = (uint32_t)c.hits.size();
+					c.hits.insert(c.hits.end(), mhits.begin() + r.hit_off, mhits.begin() + r.hit_off + r.nhits);
+					r.hit_off = ho;
+				}
+				o += c.jobs.size();
+			}
+			noteBatch(C_SEEDS, sjobs.size(), 2 * seq.size() + reads.size() * sizeof(bt2gpu_read) + sjobs.size() * sizeof(bt2gpu_seed_job),
+			          sjobs.size() * sizeof(bt2gpu_mmseed_result) + n * sizeof(bt2gpu_mmseed_hit));
+		}
+	}
 	// ---- BW rows to text offsets ----
 	if(!b.locates.empty()) {
 		const size_t n = b.locates.size();
@@ -655,6 +703,7 @@ void ungapped(UngapCall& c) { travel(K_UNGAP, &Batch::ungaps, c); }
 void sweep(SweepCall& c)  { travel(K_SWEEP, &Batch::sweeps, c); }
 void oneMm(OneMmCall& c)  { travel(K_ONEMM, &Batch::onemms, c); }
 void seeds(SeedsCall& c)  { c.out.clear(); if(c.jobs.empty()) return; travel(K_SEEDS, &Batch::seeds, c); }
+void seedsMm(SeedsMmCall& c) { c.res.clear(); c.hits.clear(); if(c.jobs.empty()) return; travel(K_SEEDMM, &Batch::seedmms, c); }
 void extend(ExtendCall& c) { travel(K_EXTEND, &Batch::extends, c); }
 void locate(LocateCall& c) { travel(K_LOCATE, &Batch::locates, c); }
 
@@ -714,7 +763,7 @@ void spawnWorker(void (*fn)(void*), void *arg) {
 				h->lanes.push_back(l);
 				for(Kind k : kinds) h->of[k].push_back(l);
 			};
-			for(int i = 0; i < fmLanes; i++) { add({K_SWEEP, K_ONEMM, K_UNGAP}); add({K_SEEDS, K_EXTEND}); add({K_LOCATE}); }
+			for(int i = 0; i < fmLanes; i++) { add({K_SWEEP, K_ONEMM, K_UNGAP}); add({K_SEEDS, K_SEEDMM, K_EXTEND}); add({K_LOCATE}); }
 			for(int i = 0; i < g_nlanes; i++) add({K_DP});
 			for(Lane *l : h->lanes) { l->th = std::thread([l] { l->run(); }); l->th.detach(); }
 			g_hubs.push_back(h);

@@ -115,6 +115,24 @@ void seeds(SeedsCall& c) {
 	noted(C_SEEDS, c.jobs.size());
 }
 
+void seedsMm(SeedsMmCall& c) {
+	c.res.assign(c.jobs.size(), bt2gpu_mmseed_result());
+	c.hits.clear();
+	if(c.jobs.empty()) return;
+	bindScoring(*c.sc);
+	stageRead(*c.rd);
+	for(size_t i = 0; i < c.jobs.size(); i++) c.jobs[i].read = 0;
+	size_t cap = 64 * c.jobs.size() + 256, n = 0;
+	for(int attempt = 0; ; attempt++) {
+		c.hits.resize(cap);
+		if(bt2gpu_seed_mm_batch(ctx(), index(*c.fw), index(*c.bw), c.jobs.data(), c.jobs.size(), c.mms, c.res.data(), c.hits.data(), cap, &n) == 0) break;
+		if(attempt < 6 && strstr(bt2gpu_last_error(), "seed hit pool overflow")) { cap *= 4; continue; }
+		fail("bt2gpu_seed_mm_batch");
+	}
+	c.hits.resize(n);
+	noted(C_SEEDS, c.jobs.size());
+}
+
 void extend(ExtendCall& c) {
 	stageRead(*c.rd);
 	c.job.read = 0;

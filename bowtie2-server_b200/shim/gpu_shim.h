@@ -74,6 +74,15 @@ struct SeedsCall {
 };
 void seeds(SeedsCall& c);
 
+// SeedAligner::searchAllSeeds with multi-zone seeds (-N 1 / -N 2): all seed offsets of one read (bt2gpu_seed_mm_batch)
+struct SeedsMmCall {
+	const Ebwt *fw, *bw; const Scoring *sc; const Read *rd; int mms;
+	std::vector<bt2gpu_seed_job> jobs;          // one per (strand, offset); jobs[i].read is the binding's business
+	std::vector<bt2gpu_mmseed_result> res;      // out; one per job, hit_off relative to `hits`
+	std::vector<bt2gpu_mmseed_hit> hits;        // out; in the order of the reference's reportHit calls
+};
+void seedsMm(SeedsMmCall& c);
+
 // SwDriver::extend of one seed hit (bt2gpu_extend_batch)
 struct ExtendCall { const Ebwt *fw, *bw; const Read *rd; bt2gpu_extend_job job; bt2gpu_extend_result res; };
 void extend(ExtendCall& c);

@@ -126,7 +126,7 @@ pair<int, int> SeedAligner::instantiateSeeds(
 }
 
 /**
- * SeedAligner::searchAllSeeds (aligner_seed.cpp:597-718) for exact seeds (-N 0): every instantiated seed of the read
+ * SeedAligner::searchAllSeeds (aligner_seed.cpp:597-718).  Exact seeds (-N 0): every instantiated seed of the read
  * goes to the GPU in one bt2gpu_seed_exact_batch call (ftab jump + mapBiLFEx / mapLF1 steps, startSearchSeedBi :1633,
  * searchSeedBi :1854); the hits then go through the reference's own cache protocol (reportHit :1575 -> addOnTheFly,
  * beginAlign / addAllCached / finishAlign, SeedResults::add) in the reference's order: forward seeds by offset,
@@ -141,6 +141,14 @@ void SeedAligner::searchAllSeeds(
 	bwops_ = bwedits_ = 0;
 	uint64_t possearches = 0, seedsearches = 0, ooms = 0;
 	if(ebwtBw == NULL) { fprintf(stderr, "bt2gpu shim: searchAllSeeds needs the mirror index\n"); throw 1; }
+	// which policy (Seed::mmSeeds, aligner_seed.cpp:365-448): one exact seed, or the 2 / 3 multi-zone seeds of -N 1 / -N 2
+	int mms = -1;
+	if(seeds.size() == 1 && seeds[0].type == SEED_TYPE_EXACT) mms = 0;
+	else if(seeds.size() == 2 && seeds[0].type == SEED_TYPE_LEFT_TO_RIGHT && seeds[1].type == SEED_TYPE_RIGHT_TO_LEFT) mms = 1;
+	else if(seeds.size() == 3 && seeds[0].type == SEED_TYPE_LEFT_TO_RIGHT && seeds[1].type == SEED_TYPE_RIGHT_TO_LEFT &&
+	        seeds[2].type == SEED_TYPE_INSIDE_OUT) mms = 2;
+	else { fprintf(stderr, "bt2gpu shim: seed policy outside Seed::mmSeeds(0..2) is not on the CUDA path\n"); throw 1; }
+	if(mms == 0) {
 	bt2shim::SeedsCall sd;
 	sd.fw = ebwtFw; sd.bw = ebwtBw; sd.sc = &pens; sd.rd = &read;
 	for(int fwi = 0; fwi < 2; fwi++) {
@@ -149,12 +157,6 @@ void SeedAligner::searchAllSeeds(
 			EList<InstantiatedSeed>& iss = sr.instantiatedSeeds(fw, i);
 			if(iss.empty()) continue;              // seed window with an N, or a cross-read cache hit
 			possearches++;
-			// one seed type per offset, and it is the exact one (iss[j] was instantiated from seeds[j],
-			// aligner_seed.cpp:560-583; InstantiatedSeed::seedtypeidx is never assigned by the reference)
-			if(iss.size() != 1 || seeds.size() != 1 || seeds[0].type != SEED_TYPE_EXACT) {
-				fprintf(stderr, "bt2gpu shim: only exact seeds (-N 0) are on the CUDA path\n");
-				throw 1;
-			}
 			seedsearches++;
 			bt2gpu_seed_job j;
 			j.read = 0; j.off = (uint16_t)iss[0].seedoff; j.len = (uint8_t)sr.seqs(fw)[i].length(); j.fw = fw ? 1 : 0;
@@ -177,6 +179,50 @@ void SeedAligner::searchAllSeeds(
 			srcache.finishAlign();
 			if(srcache.qvValid()) sr.add(srcache.getQv(), cache.current(), (uint32_t)i, fw);
 		}
+	}
+	} else {
+	// -N 1 / -N 2: one job per seed offset; the device instantiates the offset's seed types as Seed::instantiate does
+	// and returns their hits in the order of the reference's reportHit calls (the types of an offset in lock step,
+	// mismatch branches depth first), each with the reference string it stands for
+	bt2shim::SeedsMmCall sd;
+	sd.fw = ebwtFw; sd.bw = ebwtBw; sd.sc = &pens; sd.rd = &read; sd.mms = mms;
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		for(size_t i = 0; i < sr.numOffs(); i++) {
+			EList<InstantiatedSeed>& iss = sr.instantiatedSeeds(fw, i);
+			if(iss.empty()) continue;
+			possearches++;
+			seedsearches += iss.size();
+			if(sr.seqs(fw)[i].length() > 32) { fprintf(stderr, "bt2gpu shim: seeds longer than 32 are not cacheable by the reference either\n"); throw 1; }
+			bt2gpu_seed_job j;
+			j.read = 0; j.off = (uint16_t)iss[0].seedoff; j.len = (uint8_t)sr.seqs(fw)[i].length(); j.fw = fw ? 1 : 0;
+			sd.jobs.push_back(j);
+		}
+	}
+	bt2shim::seedsMm(sd);
+	size_t k = 0;
+	BTDnaString rf;
+	for(int fwi = 0; fwi < 2; fwi++) {
+		const bool fw = (fwi == 0);
+		for(size_t i = 0; i < sr.numOffs(); i++) {
+			if(sr.instantiatedSeeds(fw, i).empty()) continue;
+			const bt2gpu_mmseed_result& r = sd.res[k++];
+			bwops_ += r.bwops; bwedits_ += r.bwedits;
+			const BTDnaString& seq = sr.seqs(fw)[i];
+			const size_t len = seq.length();
+			SeedSearchCache srcache(seq, sr.quals(fw)[i]);
+			for(uint32_t h = 0; h < r.nhits; h++) {
+				const bt2gpu_mmseed_hit& hit = sd.hits[r.hit_off + h];
+				rf.resize(len);
+				for(size_t p = 0; p < len; p++) rf.set((int)((hit.key >> (2 * (len - 1 - p))) & 3), p);
+				srcache.addOnTheFly(rf, hit.topf, hit.botf, hit.topb, hit.botb);       // reportHit: rf = seed with its edits applied
+			}
+			if(srcache.beginAlign(cache) == -1) { ooms++; continue; }
+			if(!srcache.addAllCached()) { ooms++; continue; }
+			srcache.finishAlign();
+			if(srcache.qvValid()) sr.add(srcache.getQv(), cache.current(), (uint32_t)i, fw);
+		}
+	}
 	}
 	prm.nSeedRanges = sr.numRanges();
 	prm.nSeedElts = sr.numElts();

@@ -296,6 +296,33 @@ typedef struct { uint32_t read; uint16_t off; uint8_t len; uint8_t fw; } bt2gpu_
 int bt2gpu_seed_exact_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
                             const bt2gpu_seed_job *jobs, size_t njobs, bt2gpu_seed_hit *out);
 
+/* ---- seeds with mismatches: -N 1 / -N 2 -----------------------------------------------------------------------
+ * Seed::oneMmSeeds / twoMmSeeds (aligner_seed.cpp:380-448) searched by searchSeedBi with its mismatch branches
+ * (:1854-2033).  One job = one seed offset of one read strand, as for bt2gpu_seed_exact_batch; the device instantiates
+ * the offset's seed types itself (Seed::instantiate :213-358, Ns charged to their zones) and searches them in the
+ * reference's order, so that the hits of an offset come back in the order of the reference's reportHit calls (:1575),
+ * i.e. the order its SeedSearchCache and the RNG-driven choices downstream see.  mms = 0 runs the exact seed through the
+ * same code (one hit at most).  Needs the reads staged WITH qualities and the scoring scheme set. */
+#define BT2GPU_SEED_EXACT         1   /* SEED_TYPE_EXACT (aligner_seed.h:305-308) */
+#define BT2GPU_SEED_LEFT_TO_RIGHT 2
+#define BT2GPU_SEED_RIGHT_TO_LEFT 3
+#define BT2GPU_SEED_INSIDE_OUT    4
+typedef struct {
+	uint32_t topf, botf, topb, botb;  /* BW range in the forward and in the mirror index                            */
+	uint64_t key;                     /* the reference string the range stands for (the seed with its mismatches    */
+	                                  /* applied), 2 bits per base, first base most significant: QKey / SAKey       */
+} bt2gpu_mmseed_hit;
+typedef struct {
+	uint32_t hit_off, nhits;          /* slice of the hit pool                                                      */
+	uint32_t bwops, bwedits;          /* SeedAligner::bwops_ / bwedits_ contributions                               */
+	uint32_t ntypes;                  /* seed types that instantiated (0: the Ns of the window disqualify them all) */
+	uint32_t pad;
+} bt2gpu_mmseed_result;
+/* Fails with "seed hit pool overflow (raise hit_cap)" when an offset has more hits than hit_cap / njobs. */
+int bt2gpu_seed_mm_batch(bt2gpu_ctx *ctx, const bt2gpu_index *fw, const bt2gpu_index *bw,
+                         const bt2gpu_seed_job *jobs, size_t njobs, int mms, bt2gpu_mmseed_result *out,
+                         bt2gpu_mmseed_hit *hits, size_t hit_cap, size_t *nhits);
+
 /* SeedAligner::exactSweep (aligner_seed.cpp:854-968), both strands of every staged read.
  * nedit = the reference's nedit[fwi] when the strand stopped; done = stopped because
  * nedit reached mine_max (then mineFw/mineRc = nedit); otherwise the sweep ran to the end

@@ -79,6 +79,34 @@ int bt2gpu_reads_stage(bt2gpu_ctx *c, const uint8_t *seq_pool, const uint8_t *qu
 	c->nreads = nreads;
 	return 0;
 }
+int bt2oracle_seed_mm_batch(const bt2gpu_index_desc *fw, const bt2gpu_index_desc *bw, const bt2gpu_scoring *scs, const uint8_t *seq_pool,
+                            const uint8_t *qual_pool, const bt2gpu_read *reads, const bt2gpu_seed_job *jobs, size_t njobs, int mms,
+                            uint32_t *hit_job, uint32_t *hit_ranges, uint64_t *hit_keys, size_t cap, size_t *nhits, uint32_t *out_n,
+                            uint64_t *bwops);
+int bt2gpu_seed_mm_batch(bt2gpu_ctx *c, const bt2gpu_index *fw, const bt2gpu_index *bw, const bt2gpu_seed_job *jobs, size_t njobs, int mms,
+                         bt2gpu_mmseed_result *out, bt2gpu_mmseed_hit *hits, size_t hit_cap, size_t *nhits) {
+	c->calls++;
+	if(!c->have_sc) return fail("bt2gpu_scoring_set must be called first");
+	*nhits = 0;
+	if(njobs == 0) return 0;
+	uint32_t *hj = (uint32_t*)malloc((hit_cap + 1) * 4), *hr = (uint32_t*)malloc((hit_cap + 1) * 16), *on = (uint32_t*)malloc(njobs * 4);
+	uint64_t *hk = (uint64_t*)malloc((hit_cap + 1) * 8), ops = 0;
+	size_t nh = 0;
+	/* job by job: the double reports bwops per job as the library does */
+	int rc = 0; size_t o = 0;
+	for(size_t j = 0; j < njobs && !rc; j++) {
+		size_t n1 = 0; uint64_t ops1 = 0;
+		rc = bt2oracle_seed_mm_batch(&fw->d, &bw->d, &c->sc, c->seq, c->qual, c->reads, jobs + j, 1, mms, hj, hr + 4 * o, hk + o, hit_cap - o, &n1, on + j, &ops1);
+		out[j].hit_off = (uint32_t)o; out[j].nhits = (uint32_t)n1; out[j].bwops = (uint32_t)ops1; out[j].bwedits = 0; out[j].ntypes = 0; out[j].pad = 0;
+		o += n1; ops += ops1;
+	}
+	nh = o;
+	for(size_t i = 0; i < nh && !rc; i++) { hits[i].topf = hr[4 * i]; hits[i].botf = hr[4 * i + 1]; hits[i].topb = hr[4 * i + 2]; hits[i].botb = hr[4 * i + 3]; hits[i].key = hk[i]; }
+	free(hj); free(hr); free(on); free(hk);
+	if(rc) return fail("seed hit pool overflow (raise hit_cap)");
+	*nhits = nh;
+	return 0;
+}
 int bt2gpu_exact_sweep_batch(bt2gpu_ctx *c, const bt2gpu_index *fw, int nofw, int norc, uint32_t mine_max, bt2gpu_sweep_result *out) {
 	c->calls++;
 	return bt2oracle_exact_sweep_batch(&fw->d, c->seq, c->reads, c->nreads, nofw, norc, mine_max, out) ? fail("sweep") : 0;

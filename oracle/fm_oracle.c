@@ -588,3 +588,285 @@ int bt2oracle_locate_batch(const Idx *ix, const uint32_t *rows, size_t n, uint32
 	}
 	return 0;
 }
+
+/* ----------------------------------------------------------------------------------------
+ * Multi-zone seeds, -N 1 / -N 2: Seed::mmSeeds (aligner_seed.cpp:365-448),
+ * Seed::instantiate (:213-358), startSearchSeedBi (:1633-1714), nextLocsBi (:1364-1432),
+ * searchSeedBi with its mismatch recursion (:1854-2033), reportHit (:1575-1630), and the order
+ * in which searchAllSeeds (:597-718) runs the seed types of one offset (lock step, recursions
+ * depth first).  -N 0 goes through the same code (one exact seed): it must agree with
+ * seed_exact_one above.  Pinned by tests/test_oracle_fm.py against ref_seed_dump --seedmms.
+ * The CUDA kernel for these seeds does not exist yet; this is the checker it will be held to.
+ * -------------------------------------------------------------------------------------- */
+#define MAX_I 0x7fffffff
+#define MM_MAXLEN 32
+enum { SEED_EXACT = 1, SEED_L2R = 2, SEED_R2L = 3, SEED_INSIDE_OUT = 4 };   /* aligner_seed.h SEED_TYPE_* */
+
+typedef struct { int edits, mms, ins, dels, penalty, editsCeil, mmsCeil, insCeil, delsCeil, penaltyCeil; } Cons;
+static Cons cons_init(void) { Cons c = { MAX_I, MAX_I, MAX_I, MAX_I, MAX_I, MAX_I, MAX_I, MAX_I, MAX_I, MAX_I }; return c; }
+static Cons cons_exact(void) { Cons c = cons_init(); c.edits = c.mms = c.ins = c.dels = c.penalty = 0; return c; }
+static Cons cons_mm(int n) { Cons c = cons_init(); c.mms = n; c.edits = c.dels = c.ins = 0; return c; }
+static int cons_must_match(const Cons *c) {                    /* aligner_seed.h:69-74 */
+	return (c->mms == 0 && c->edits == 0) || c->penalty == 0 || (c->mms == 0 && c->dels == 0 && c->ins == 0);
+}
+static int cons_can(const Cons *c, int pen) { return (c->mms > 0 || c->edits > 0) && c->penalty >= pen; }   /* canMismatch / canN */
+static void cons_charge(Cons *c, int pen) { if(c->mms == 0) c->edits--; else c->mms--; c->penalty -= pen; }
+static int cons_acceptable(const Cons *c) {
+	return c->edits <= c->editsCeil && c->mms <= c->mmsCeil && c->ins <= c->insCeil && c->dels <= c->delsCeil && c->penalty <= c->penaltyCeil;
+}
+static int cons_can_gap(const Cons *c) { return ((c->ins > 0 || c->dels > 0) || c->edits > 0) && c->penalty > 0; }
+
+typedef struct { int type; Cons zones[3]; } SeedPol;
+static int mm_seed_pols(int mms, SeedPol *p) {                 /* Seed::mmSeeds */
+	int n = 0;
+	if(mms == 0) {
+		p[n].type = SEED_EXACT; p[n].zones[0] = p[n].zones[1] = p[n].zones[2] = cons_exact(); n++;
+	} else if(mms == 1) {
+		p[n].type = SEED_L2R; p[n].zones[0] = cons_exact(); p[n].zones[1] = cons_mm(1); p[n].zones[2] = cons_exact(); n++;
+		p[n].type = SEED_R2L; p[n].zones[0] = cons_exact(); p[n].zones[1] = cons_mm(1); p[n].zones[1].mmsCeil = 0; p[n].zones[2] = cons_exact(); n++;
+	} else {
+		p[n].type = SEED_L2R; p[n].zones[0] = cons_exact(); p[n].zones[1] = cons_mm(2); p[n].zones[2] = cons_exact(); n++;
+		p[n].type = SEED_R2L; p[n].zones[0] = cons_exact(); p[n].zones[1] = cons_mm(2); p[n].zones[1].mmsCeil = 1; p[n].zones[2] = cons_exact(); n++;
+		p[n].type = SEED_INSIDE_OUT; p[n].zones[0] = cons_exact(); p[n].zones[1] = cons_mm(1); p[n].zones[1].mmsCeil = 0;
+		p[n].zones[2] = cons_mm(1); p[n].zones[2].mmsCeil = 0; n++;
+	}
+	return n;
+}
+
+typedef struct {
+	int n, steps[MM_MAXLEN], z1[MM_MAXLEN], z2[MM_MAXLEN];     /* InstantiatedSeed::steps / zones (first, second) */
+	Cons cons[3], overall;
+	int maxjump;
+} InstSeed;
+
+/* Seed::instantiate; returns 0 when the Ns of the seed window disqualify it */
+static int seed_instantiate(const SeedPol *pol, int seedlen, const uint8_t *seq, const uint8_t *qual, const Sc *sc, InstSeed *is) {
+	is->n = seedlen;
+	switch(pol->type) {
+	case SEED_EXACT:
+		for(int k = 0; k < seedlen; k++) { is->steps[k] = -(seedlen - k); is->z1[k] = is->z2[k] = 0; }
+		break;
+	case SEED_L2R:
+		for(int k = 0; k < seedlen; k++) { is->steps[k] = k + 1; is->z1[k] = is->z2[k] = (k < (seedlen + 1) / 2) ? 0 : 1; }
+		is->z1[seedlen - 1] = is->z2[seedlen - 1] = -1;
+		break;
+	case SEED_R2L:
+		for(int k = 0; k < seedlen; k++) {
+			is->steps[k] = -(seedlen - k);
+			is->z1[k] = (k < seedlen / 2) ? 0 : 1;
+			is->z2[k] = (k < (seedlen + 1) / 2 + 1) ? 0 : 1;
+		}
+		is->z1[seedlen - 1] = is->z2[seedlen - 1] = -1;
+		break;
+	default: {
+		int step = 0;
+		for(int k = (seedlen + 3) / 4; k < seedlen - (seedlen / 4); k++) { is->z1[step] = is->z2[step] = 0; is->steps[step++] = k + 1; }
+		for(int k = seedlen - (seedlen / 4); k < seedlen; k++) { is->z1[step] = is->z2[step] = 1; is->steps[step++] = k + 1; }
+		is->z1[step - 1] = is->z2[step - 1] = -1;
+		for(int k = ((seedlen + 3) / 4) - 1; k >= 0; k--) { is->z1[step] = is->z2[step] = 2; is->steps[step++] = -(k + 1); }
+		is->z1[step - 1] = is->z2[step - 1] = -2;
+		break;
+	}
+	}
+	for(int i = 0; i < 3; i++) is->cons[i] = pol->zones[i];
+	is->overall = cons_init();                                 /* mmSeeds: oall.init() */
+	int streak = 1, ltr = is->steps[0] > 0;
+	is->maxjump = 0;
+	for(int i = 0; i < is->n; i++) {
+		const int off = abs(is->steps[i]) - 1;
+		Cons *cons = &is->cons[abs(is->z1[i])];
+		const int c = seq[off], q = qual[off];
+		if(ltr != (is->steps[i] > 0) || is->z1[i] != 0 || is->z2[i] != 0) streak = 0;
+		if(c == 4) {
+			if(cons_can(cons, sc->npens[q])) cons_charge(cons, sc->npens[q]);
+			else return 0;
+		}
+		if(streak) is->maxjump++;
+	}
+	return 1;
+}
+
+typedef struct { uint32_t topf, botf, topb, botb; uint64_t key; uint32_t job; } MmHit;
+typedef struct { MmHit *hits; size_t cap, n; int overflow; uint64_t bwops, bwedits; const Idx *fw, *bw; const Sc *sc; uint32_t job; } MmCtx;
+
+typedef struct {
+	const InstSeed *s; const uint8_t *seq, *qual;
+	int step, depth;
+	uint32_t topf, botf, topb, botb;
+	Locus tloc, bloc;
+	Cons cv[3], overall;
+	int nedits, epos[4], echr[4];
+	int hasi0; uint32_t fwi0, bwi0;
+} MmParam;
+
+static void mm_report(MmCtx *x, const MmParam *p) {            /* reportHit: the reference string = seed with its edits applied */
+	uint8_t rf[MM_MAXLEN];
+	memcpy(rf, p->seq, (size_t)p->s->n);
+	for(int e = 0; e < p->nedits; e++) rf[p->epos[e]] = (uint8_t)p->echr[e];
+	uint64_t key = 0;
+	for(int i = 0; i < p->s->n; i++) key = (key << 2) | rf[i];
+	if(x->n >= x->cap) { x->overflow = 1; return; }
+	MmHit *h = &x->hits[x->n++];
+	h->topf = p->topf; h->botf = p->botf; h->topb = p->topb; h->botb = p->botb; h->key = key; h->job = x->job;
+}
+
+static void mm_next_locs(const InstSeed *s, Locus *tl, Locus *bl, uint32_t topf, uint32_t botf, uint32_t topb, uint32_t botb, int step) {
+	if(step == s->n) return;
+	if(s->steps[step] > 0) {                                   /* left to right: BWT' */
+		if(botb - topb == 1) { loc_from_row(tl, topb); bl->valid = 0; }
+		else init_locs(topb, botb, tl, bl);
+	} else {
+		if(botf - topf == 1) { loc_from_row(tl, topf); bl->valid = 0; }
+		else init_locs(topf, botf, tl, bl);
+	}
+}
+
+static int mm_start(MmCtx *x, MmParam *p) {                    /* startSearchSeedBi; 1 = already done */
+	const InstSeed *s = p->s;
+	if(p->step == s->n) { mm_report(x, p); return 1; }
+	if(p->step == 0) {
+		const int off = abs(s->steps[0]) - 1;
+		const int ftab_len = x->fw->ftab_chars;
+		if(p->hasi0) {
+			p->topf = ftab_hi(x->fw, p->fwi0); p->botf = ftab_lo(x->fw, p->fwi0 + 1);
+			if(p->botf - p->topf == 0) return 1;
+			p->topb = ftab_hi(x->bw, p->bwi0); p->botb = p->topb + (p->botf - p->topf);
+			p->step += ftab_len;
+		} else if(s->maxjump > 0) {
+			const int c = p->seq[off];
+			p->topf = p->topb = x->fw->fchr[c];
+			p->botf = p->botb = x->fw->fchr[c + 1];
+			if(p->botf - p->topf == 0) return 1;
+			p->step++;
+		} else {
+			p->topf = p->topb = 0;
+			p->botf = p->botb = x->fw->fchr[4];
+		}
+		if(p->step == s->n) { mm_report(x, p); return 1; }
+		mm_next_locs(s, &p->tloc, &p->bloc, p->topf, p->botf, p->topb, p->botb, p->step);
+	}
+	return 0;
+}
+
+static void mm_param_init(MmCtx *x, MmParam *p, const InstSeed *s, const uint8_t *seq, const uint8_t *qual) {
+	memset(p, 0, sizeof(*p));
+	p->s = s; p->seq = seq; p->qual = qual;
+	for(int i = 0; i < 3; i++) p->cv[i] = s->cons[i];
+	p->overall = s->overall;
+	/* CacheAndSeed (aligner_seed.cpp:84-112) */
+	int off = abs(s->steps[0]) - 1;
+	const int ltr = s->steps[0] > 0, ftab_len = x->fw->ftab_chars;
+	p->hasi0 = (ftab_len > 1 && ftab_len <= s->maxjump);
+	if(p->hasi0) {
+		if(!ltr) off = off - ftab_len + 1;
+		p->fwi0 = ftab_seq_to_int(x->fw, seq, (size_t)off, 0);
+		p->bwi0 = ftab_seq_to_int(x->bw, seq, (size_t)off, 0);
+	}
+}
+
+static void mm_search(MmCtx *x, MmParam *pv, size_t nparams) { /* searchSeedBi */
+	int done[8];
+	size_t nleft = nparams;
+	for(size_t n = 0; n < nparams; n++) { done[n] = mm_start(x, &pv[n]); if(done[n]) nleft--; }
+	while(nleft > 0) {
+		for(size_t n = 0; n < nparams; n++) {
+			if(done[n]) continue;
+			MmParam *p = &pv[n];
+			const InstSeed *s = p->s;
+			if(p->step >= s->n) { done[n] = 1; nleft--; continue; }
+			const int i = p->step++;
+			/* SeedAlignerSearchState::setOff (:1744-1770) */
+			uint32_t t[4] = {0, 0, 0, 0}, b[4] = {0, 0, 0, 0}, tp[4], bp[4], *tf, *tb, *bf, *bb, ntop;
+			const int ltr = s->steps[i] > 0, off = abs(s->steps[i]) - 1;
+			const Idx *ebwt;
+			if(ltr) { ebwt = x->bw; for(int k = 0; k < 4; k++) { tp[k] = p->topf; bp[k] = p->botf; } tf = tp; tb = t; bf = bp; bb = b; ntop = p->topb; }
+			else    { ebwt = x->fw; for(int k = 0; k < 4; k++) { tp[k] = p->topb; bp[k] = p->botb; } tf = t; tb = tp; bf = b; bb = bp; ntop = p->topf; }
+			if(p->bloc.valid) { x->bwops++; map_bi_lf_ex(ebwt, &p->tloc, &p->bloc, t, b, tp, bp); }
+			const int c = p->seq[off];
+			const int leave_zone = s->z1[i] < 0;
+			Cons *cons = &p->cv[abs(s->z1[i])];
+			if(!(cons_must_match(cons) && !cons_must_match(&p->overall)) || c == 4) {
+				int bail = 0;
+				if(!p->bloc.valid) {
+					x->bwops++;
+					const int cc = map_lf1(ebwt, &ntop, &p->tloc);       /* advances ntop, as the reference's call does */
+					if(cc < 0) bail = 1;
+					else { t[cc] = ntop; b[cc] = ntop + 1; }
+				}
+				if(!bail) {
+					const int q = p->qual[off], pen = x->sc->mmpens[q];     /* the raw quality character indexes the table (:1934) */
+					if((cons_can(cons, pen) && cons_can(&p->overall, pen)) || c == 4) {
+						const Cons save_c = *cons, save_o = p->overall;
+						if(c != 4) { cons_charge(cons, pen); cons_charge(&p->overall, pen); }
+						if(!leave_zone || (cons_acceptable(cons) && cons_acceptable(&p->overall))) {
+							for(int j = 0; j < 4; j++) {
+								if(j == c || b[j] == t[j]) continue;
+								MmParam p2 = *p;
+								p2.topf = tf[j]; p2.botf = bf[j]; p2.topb = tb[j]; p2.botb = bb[j];
+								p2.epos[p2.nedits] = off; p2.echr[p2.nedits] = j; p2.nedits++;
+								mm_next_locs(s, &p2.tloc, &p2.bloc, p2.topf, p2.botf, p2.topb, p2.botb, i + 1);
+								x->bwedits++;
+								p2.step = i + 1; p2.depth = p->depth + 1;
+								mm_search(x, &p2, 1);
+							}
+						}
+						*cons = save_c; p->overall = save_o;
+					}
+					if(cons_can_gap(cons) && cons_can_gap(&p->overall)) { x->overflow = 2; return; }   /* `throw 1; // TODO` in the reference */
+				}
+			}
+			if(c == 4) { done[n] = 1; nleft--; continue; }
+			if(leave_zone && (!cons_acceptable(cons) || !cons_acceptable(&p->overall))) { done[n] = 1; nleft--; continue; }
+			if(!p->bloc.valid) {
+				x->bwops++;
+				t[c] = map_lf1_c(ebwt, ntop, &p->tloc, c);
+				if(t[c] == OFF_MASK) { done[n] = 1; nleft--; continue; }
+				b[c] = t[c] + 1;
+			}
+			if(b[c] == t[c]) { done[n] = 1; nleft--; continue; }
+			p->topf = tf[c]; p->botf = bf[c]; p->topb = tb[c]; p->botb = bb[c];
+			if(i + 1 == s->n) { mm_report(x, p); done[n] = 1; nleft--; continue; }
+			mm_next_locs(s, &p->tloc, &p->bloc, p->topf, p->botf, p->topb, p->botb, i + 1);
+		}
+	}
+}
+
+/* One job = one seed offset of one read strand (what instantiateSeeds lays out); its hits come back in the order of the
+ * reportHit calls.  jobs[].len <= 32.  out_n[j] = hits of job j (they are contiguous in `hits`).  Returns 0, or 1 when
+ * `cap` is too small. */
+int bt2oracle_seed_mm_batch(const Idx *fw, const Idx *bw, const bt2gpu_scoring *scs, const uint8_t *seq_pool, const uint8_t *qual_pool,
+                            const bt2gpu_read *reads, const bt2gpu_seed_job *jobs, size_t njobs, int mms,
+                            uint32_t *hit_job, uint32_t *hit_ranges /* 4 per hit */, uint64_t *hit_keys, size_t cap, size_t *nhits,
+                            uint32_t *out_n, uint64_t *bwops)
+{
+	Sc sc; sc.mmpens = scs->mmpens; sc.npens = scs->npens; sc.match = scs->match_bonus;
+	MmCtx x; memset(&x, 0, sizeof(x));
+	x.hits = (MmHit*)malloc((cap + 1) * sizeof(MmHit)); x.cap = cap; x.fw = fw; x.bw = bw; x.sc = &sc;
+	SeedPol pols[3];
+	const int npol = mm_seed_pols(mms, pols);
+	for(size_t j = 0; j < njobs; j++) {
+		const bt2gpu_seed_job *jb = &jobs[j];
+		const bt2gpu_read *rd = &reads[jb->read];
+		uint8_t seq[MM_MAXLEN], qual[MM_MAXLEN];
+		const int len = jb->len;
+		/* instantiateSeq (aligner_seed.cpp:471-491): the window as it aligns to the Watson strand, qualities alongside */
+		seed_window(seq_pool + rd->rd_off, jb->off, len, jb->fw, seq);
+		for(int i = 0; i < len; i++) qual[i] = jb->fw ? qual_pool[rd->rd_off + jb->off + i] : qual_pool[rd->rd_off + jb->off + len - 1 - i];
+		InstSeed is[3]; MmParam pv[3]; size_t np = 0;
+		for(int k = 0; k < npol; k++)
+			if(seed_instantiate(&pols[k], len, seq, qual, &sc, &is[np])) { mm_param_init(&x, &pv[np], &is[np], seq, qual); np++; }
+		x.job = (uint32_t)j;
+		const size_t n0 = x.n;
+		if(np > 0) mm_search(&x, pv, np);
+		out_n[j] = (uint32_t)(x.n - n0);
+		if(x.overflow) break;
+	}
+	for(size_t i = 0; i < x.n; i++) {
+		hit_job[i] = x.hits[i].job; hit_keys[i] = x.hits[i].key;
+		hit_ranges[4 * i] = x.hits[i].topf; hit_ranges[4 * i + 1] = x.hits[i].botf; hit_ranges[4 * i + 2] = x.hits[i].topb; hit_ranges[4 * i + 3] = x.hits[i].botb;
+	}
+	*nhits = x.n; *bwops = x.bwops;
+	const int rc = x.overflow;
+	free(x.hits);
+	return rc;
+}

@@ -115,6 +115,12 @@ def main():
     dump(rep, fq, os.path.join(GOLD, "fm_rep.txt"), ["--maxloc", "24"])
     dump(rep, fq, os.path.join(GOLD, "fm_rep_local.txt"), ["--limit", "120", "--local", "-L", "20", "--interval", "1", "0.75",
                                                           "--maxloc", "4"])
+    # multi-zone seeds (-N 1, -N 2): ranges and their reference strings in the order of the reportHit calls
+    dump(lam, os.path.join(ex, "reads_1.fq"), os.path.join(GOLD, "fm_mm1_lambda_r1.txt"), ["--limit", "80", "--seedmms", "1", "--maxloc", "1"])
+    dump(rep, fq, os.path.join(GOLD, "fm_mm1_rep.txt"), ["--limit", "100", "--seedmms", "1", "--maxloc", "1"])
+    dump(rep, fq, os.path.join(GOLD, "fm_mm2_rep.txt"), ["--limit", "60", "--seedmms", "2", "--maxloc", "1"])
+    dump(lam, os.path.join(ex, "reads_2.fq"), os.path.join(GOLD, "fm_mm2_lambda_r2_L20.txt"),
+         ["--limit", "40", "--seedmms", "2", "-L", "20", "--interval", "1", "0.75", "--maxloc", "1"])
 
 
 if __name__ == "__main__":

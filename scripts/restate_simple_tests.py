@@ -103,12 +103,12 @@ def scalar(block, key):
 
 def runs_on_stock_reference(c):
     """Keep the cases the stock server/client pair (oracle/_ref) accepts with these options and that do not ask for
-    seeds with mismatches (-N 1/2, SEED=1/2, --multiseed=1..: not on the CUDA path) or side files."""
+    side files.  (Seeds with mismatches -- -N 1, SEED=1/2, --multiseed=1 -- are on the CUDA path since round 2.)"""
     import tempfile
     sys.path.insert(0, os.path.join(os.path.dirname(OUT), ".."))
     import dropin as D
     a = " ".join(c["args"])
-    if re.search(r"--un|--al|SEED=[12]|--multiseed=[12]|-N [12]|-N[12]|-p ", a):
+    if re.search(r"--un|--al|-p ", a):
         return False
     work = tempfile.mkdtemp(prefix="simple_")
     try:

@@ -209,6 +209,27 @@ class FmOracle:
         assert rc == 0, "oracle hit pool overflow"
         return out, hits[: nh.value]
 
+    def seed_mm(self, jobs, mms, cap=None):
+        """Multi-zone seeds (-N mms): per job (= seed offset of a read strand) the hits in the order of the reference's
+        reportHit calls -> (list of [(topf, botf, topb, botb, key), ...] per job, total bwops)."""
+        n = len(jobs)
+        cap = cap or 256 * n + 1024
+        hit_job = np.zeros(cap, dtype=np.uint32); rng_ = np.zeros(4 * cap, dtype=np.uint32); keys = np.zeros(cap, dtype=np.uint64)
+        out_n = np.zeros(n, dtype=np.uint32)
+        nh, ops = C.c_size_t(0), C.c_uint64(0)
+        rc = self.lib.bt2oracle_seed_mm_batch(
+            C.byref(self.dfw), C.byref(self.dbw), _ptr(self.sc), _ptr(self.pool.seq), _ptr(self.pool.qual), _ptr(self.pool.reads),
+            _ptr(jobs), C.c_size_t(n), C.c_int(mms), _ptr(hit_job), _ptr(rng_), _ptr(keys), C.c_size_t(cap), C.byref(nh),
+            _ptr(out_n), C.byref(ops))
+        assert rc == 0, "oracle multi-zone seed search failed (%d)" % rc
+        out, k = [], 0
+        for j in range(n):
+            out.append([(int(rng_[4 * i]), int(rng_[4 * i + 1]), int(rng_[4 * i + 2]), int(rng_[4 * i + 3]), int(keys[i]))
+                        for i in range(k, k + int(out_n[j]))])
+            k += int(out_n[j])
+        assert k == nh.value
+        return out, int(ops.value)
+
     def extend(self, jobs):
         out = np.zeros(len(jobs), dtype=structs.extend_result)
         rc = self.lib.bt2oracle_extend_batch(C.byref(self.dfw), C.byref(self.dbw), _ptr(self.pool.seq),

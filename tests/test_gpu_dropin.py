@@ -281,8 +281,7 @@ def test_reference_regression_cases(work, case):
 
 
 # The reference's regression table, restated (scripts/restate_simple_tests.py -> tests/golden/simple_cases.json: every
-# case of scripts/test/simple_tests.pl that gives its reads inline and that the stock server accepts; seeds with
-# mismatches excluded).  EVERY case runs through the batched binding (the path bench.py times); the per-call binding takes
+# case of scripts/test/simple_tests.pl that the stock server accepts, seed-mismatch cases (-N 1, SEED=1) included).  EVERY case runs through the batched binding (the path bench.py times); the per-call binding takes
 # every fourth case (BT2GPU_ALL_SIMPLE_CASES=1: all of them).
 import json
 
