@@ -1,12 +1,14 @@
 // batch_shim.cpp — the batched binding of gpu_shim.h and the worker scheduler of fiber.h.
 //
-// A call (dpAlign, sweep, seeds, ...) made on a worker's stack appends the problem to the pending batch of the worker's
-// host thread and suspends the worker.  The host thread's scheduler runs every runnable worker once, then hands the
-// pending batch to a free lane; the lane's helper thread executes it -- one bt2gpu_*_batch call per kind of problem,
-// host buffers in, host buffers out -- and marks the batch done; the scheduler then makes the batch's workers runnable
-// again.  Results are written into the callers' own call structs, so a worker finds its answer where the per-call
-// binding would have left it: the shim bodies (sw_aligner_gpu.cpp, seed_aligner_gpu.cpp, ...) are the same code in
-// both builds, and so is everything the reference's driver sees.
+// A call (dpAlign, sweep, seeds, seedsMm, extend, locate, ...) made on a worker's stack appends the problem to what the
+// worker's host thread has queued and suspends the worker.  The host thread runs its runnable workers round robin and
+// hands the queued problems -- at the latest every 16 workers -- to the LANE of their kind: one lane per kind of problem
+// and device (exactSweep + oneMmSearch + ungapped | seeds + extend | locate | DP windows), shared by all host threads.
+// A lane's thread takes whatever is queued for it, makes ONE bt2gpu_*_batch call per kind -- host buffers in, host
+// buffers out -- writes every answer into its caller's own call struct and gives the workers back to their host
+// threads, which make them runnable again.  A worker therefore finds its answer where the per-call binding would have
+// left it: the shim bodies (sw_aligner_gpu.cpp, seed_aligner_gpu.cpp, ...) are the same code in both builds, and so is
+// everything the reference's driver sees.  Batches grow with the load; the kinds run side by side on their own streams.
 //
 // No CPU path: a lane that cannot create its bt2gpu_ctx, or an ABI call that fails, ends the process with the error.
 #include <cstdio>
