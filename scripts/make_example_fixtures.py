@@ -35,6 +35,15 @@ def main():
             kept += 1
             if kept >= 500:
                 break
+    # the whole of C2 (10000 pairs) and the whole of C1 except its 7 reads of >= 2000 rows: run through the batched server
+    for name in ("reads_1", "reads_2"):
+        with gzip.open(os.path.join(OUT, "example_%s_all.fq.gz" % name), "wt") as out:
+            for rec in records(os.path.join(REF, "example", "reads", name + ".fq")):
+                out.writelines(rec)
+    with gzip.open(os.path.join(OUT, "example_longreads_all.fq.gz"), "wt") as out:
+        for rec in records(os.path.join(REF, "example", "reads", "longreads.fq")):
+            if len(rec[1].strip()) < 2000:
+                out.writelines(rec)
     print("wrote fixtures to", OUT)
 
 

@@ -204,6 +204,21 @@ def test_config_c2_example_pairs(work):
     _check(cpu, gpu)
 
 
+def test_configs_c1_c2_whole_files_through_the_batched_server(work):
+    """BASELINE.json configs[0] and [1] in full through the product path (the batched binding): all 10000 pairs of
+    example/reads/reads_{1,2}.fq end-to-end and --local, and every read of longreads.fq except its 7 reads of >= 2000 rows
+    (the checkpointed DP is not on the CUDA path; the server refuses those loudly), --sensitive."""
+    base = os.path.join(work, "lambda")
+    f1, f2 = _gunzip(work, "example_reads_1_all.fq.gz"), _gunzip(work, "example_reads_2_all.fq.gz")
+    fl = _gunzip(work, "example_longreads_all.fq.gz")
+    for tag, sargs, cargs, nrec in (("c2all", [], ["-1", f1, "-2", f2], 20000), ("c2lall", ["--local"], ["-1", f1, "-2", f2], 20000),
+                                    ("c1all", ["--sensitive"], ["-U", fl], 5993)):
+        cpu, _ = D.run(D.CPU_SERVER, base, sargs, cargs, os.path.join(work, tag + "_cpu.sam"), threads=8)
+        assert len(cpu) == nrec
+        st = _batched(work, tag, cpu, base, sargs, cargs, workers=512, host_threads=8)
+        assert st["align_calls_on_gpu"] > 3000 and st["abi_batch_jobs"] > 2 * st["abi_batches"], st
+
+
 def test_config_c3_c4_c5_shapes_on_random_genome(work):
     """BASELINE.json configs[2..4] at test scale: a 3 Mbp i.i.d. random reference in 10 sequences, 150 bp
     reads --very-sensitive (C3), 250 bp reads --local (C4), 2x150 pairs -I 0 -X 500 (C5); 4 worker threads, i.e. 4
