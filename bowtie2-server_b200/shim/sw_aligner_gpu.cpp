@@ -88,6 +88,35 @@ bool SwAligner::align(TAlScore& best) {
 	st.next = 0; st.minsc = minsc_;
 	sse8succ_ = r.width == 8; sse16succ_ = r.width == 16;
 	best = r.best;                           // INT64_MIN == MIN_I64
+	// SSEMetrics (aligner_swsse.h:32-78) as the reference's fill and gather routines keep them (ee_u8.cpp:791,1109-1144,
+	// 1197 and twins; NWORDS_PER_REG of the default SSE2 build: 16 / 8).  Which variants ran follows from align()'s own
+	// selection (aligner_sw.cpp:516-621): end-to-end runs u8 OR i16; local runs u8 and, when that saturated (the answer
+	// then came from the 16-bit fill), i16 as well.  Not kept: `fixup` (the lazy-F loop is an artefact of the striped
+	// layout), the columns of an 8-bit fill that saturated, and of the backtrace counters btcell, corerej and nrej (the
+	// kernel reports attempts and successes, not the reason of a failure: every failed attempt is booked as btfail); see
+	// nextAlignment below.  Checked against the reference's own counters by tests/test_shim_dp_replay.py.
+	{
+		const bool try8 = sc_->monotone ? (enable8_ && !readSse16_ && minsc_ >= -254) : (enable8_ && !readSse16_);
+		const bool ran16 = !try8 || (!sc_->monotone && r.width == 16);
+		SSEMetrics& m8 = extend_ ? sseU8ExtendMet_ : sseU8MateMet_;
+		SSEMetrics& m16 = extend_ ? sseI16ExtendMet_ : sseI16MateMet_;
+		if(try8) {
+			const size_t ninner = ncol * ((rdlen + 15) / 16);
+			m8.dp++;
+			// a saturated 8-bit fill stops at the column where it saturates: how far it got is not known here, and its
+			// columns are left out rather than overstated
+			if(!ran16) { m8.col += ncol; m8.cell += ninner * 16; m8.inner += ninner; }
+			if(ran16) m8.dpsat++;
+			else if(r.width == 8) m8.dpsucc++;
+			else m8.dpfail++;
+		}
+		if(ran16) {
+			const size_t ninner = ncol * ((rdlen + 7) / 8);
+			m16.dp++; m16.col += ncol; m16.cell += ninner * 8; m16.inner += ninner;
+			if(r.width == 16) m16.dpsucc++; else m16.dpfail++;
+		}
+		if(r.aligned || r.ncand > 0) (r.width == 16 ? m16 : m8).gathsol += r.ncand;
+	}
 	if(best == MIN_I64 || best < minsc_) {   // aligner_sw.cpp:681-686
 		if(dpLog_ != NULL) (*dpLog_) << ",0,0";
 		return false;
@@ -138,6 +167,12 @@ bool SwAligner::nextAlignment(SwResult& res, TAlScore minsc, RandomSource& rnd) 
 	for(uint32_t k = 0; k < tries; k++) {    // u8: init(reseed) ... init(reseed+1); i16: ... init(reseed)
 		uint32_t reseed = rnd.nextU32() + 1;
 		rnd.init(sse8succ_ ? reseed + 1 : reseed);
+	}
+	{	// one backtrace per draw (met.bt++, ee_u8.cpp:1296), one success when an alignment is handed out (:1875)
+		SSEMetrics& m = sse8succ_ ? (extend_ ? sseU8ExtendMet_ : sseU8MateMet_) : (extend_ ? sseI16ExtendMet_ : sseI16MateMet_);
+		m.bt += tries;
+		if(a != NULL) m.btsucc++;
+		m.btfail += tries - (a != NULL ? 1 : 0);
 	}
 	res.reset();
 	if(a == NULL) { cural_ = btncand_.size(); return false; }

@@ -89,6 +89,7 @@ int main(int argc, char** argv) {
 	double nceilC = 0.0, nceilL = 0.15;
 	size_t maxaln = 8, cminlen = 2000, cpow2 = 4, upto = (size_t)-1;
 	bool bench = false; int nthreads = 1;
+	bool printMet = false;
 	for(int i = 1; i < argc; i++) {
 		string a = argv[i];
 		if(a == "--log") logfn = argv[++i];
@@ -107,6 +108,7 @@ int main(int argc, char** argv) {
 		else if(a == "--maxaln") maxaln = (size_t)atol(argv[++i]);
 		else if(a == "--cp-min") cminlen = (size_t)atol(argv[++i]);
 		else if(a == "--upto") upto = (size_t)atol(argv[++i]);
+		else if(a == "--met") printMet = true;                  // SSEMetrics of the replay, one MET line per counter set, at the end
 		else if(a == "--bench") bench = true;
 		else if(a == "--threads") nthreads = atoi(argv[++i]);
 		else { cerr << "unknown arg " << a << endl; return 2; }
@@ -327,7 +329,19 @@ int main(int argc, char** argv) {
 			RandomSource probe = rnd;
 			cout << "E\t" << naln << '\t' << sw.cural_ << '\t' << probe.nextU32() << '\n';
 			pid++;
-			if(pid >= upto) return 0;
+			if(pid >= upto) break;
+		}
+		if(pid >= upto) break;
+	}
+	if(printMet) {
+		const SSEMetrics *ms[4] = { &sw.sseU8ExtendMet_, &sw.sseU8MateMet_, &sw.sseI16ExtendMet_, &sw.sseI16MateMet_ };
+		const char *nm[4] = { "u8ext", "u8mate", "i16ext", "i16mate" };
+		for(int k = 0; k < 4; k++) {
+			const SSEMetrics& m = *ms[k];
+			cout << "MET\t" << nm[k] << "\tdp=" << m.dp << "\tdpsat=" << m.dpsat << "\tdpfail=" << m.dpfail << "\tdpsucc=" << m.dpsucc
+			     << "\tcol=" << m.col << "\tcell=" << m.cell << "\tinner=" << m.inner << "\tfixup=" << m.fixup << "\tgathsol=" << m.gathsol
+			     << "\tbt=" << m.bt << "\tbtfail=" << m.btfail << "\tbtsucc=" << m.btsucc << "\tbtcell=" << m.btcell
+			     << "\tcorerej=" << m.corerej << "\tnrej=" << m.nrej << '\n';
 		}
 	}
 	return 0;
