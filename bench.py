@@ -439,6 +439,8 @@ def run_ours(args, rank, world, local_rank):
         shards = write_shards(td, "r%d" % rank, reads, quals, nclients)
         progress("FASTQ shards for %d clients written" % nclients)
         env = {"BT2GPU_DEVICE": str(local_rank), "BT2GPU_THREADS": str(threads), "BT2GPU_LANES": str(args.lanes)}
+        if ncores // world < 8:      # several servers on few cores (N ranks on one box): their lanes poll less often
+            env["BT2GPU_POLL_US"] = "50"
         barrier(False)
         try:
             e2e_s, srv_start, rss, sams, shim = server_steps(SB.GPUB_SERVER, base, workers, env, shards, td, "gpub%d" % rank,
